@@ -1,0 +1,59 @@
+"""Import the *real* reference modules from /root/reference (TEST INFRASTRUCTURE, build container only).
+
+``/root/reference`` does not exist on the GPU box, so nothing here may be used by ``-m gpu`` tests, ``smoke()``
+or ``bench.py``.  It is used by ``oracle/make_golden.py`` to dump golden vectors and by the CPU-side tests that
+pin the restatements in this directory against the reference itself (skipped when the tree is absent).
+
+Shims: ``skimage`` is not installed -> register empty modules before importing
+``third_party/tsdf_fusion_python/fusion.py`` (its line 7 is the only obstacle); ``hive.geometric`` needs a
+``matplotlib.pyplot`` stub and the numpy-1 aliases ``np.alltrue`` / ``np.product``.
+"""
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("HIVE_REFERENCE_ROOT", "/root/reference")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "third_party", "tsdf_fusion_python", "fusion.py"))
+
+
+def reference_fusion():
+    """The reference's ``fusion`` module (CPU mode only: PyCUDA is absent, fusion.py:9-18)."""
+    if "skimage" not in sys.modules:
+        sk = types.ModuleType("skimage")
+        sk.measure = types.ModuleType("skimage.measure")
+        sys.modules["skimage"] = sk
+        sys.modules["skimage.measure"] = sk.measure
+    path = os.path.join(REFERENCE_ROOT, "third_party", "tsdf_fusion_python")
+    if path not in sys.path:
+        sys.path.insert(0, path)
+    import logging
+    lvl = logging.getLogger().level
+    logging.getLogger().setLevel(logging.ERROR)
+    try:
+        import fusion  # noqa: the reference module
+    finally:
+        logging.getLogger().setLevel(lvl)
+    return fusion
+
+
+def reference_geometric():
+    """The reference's ``hive.geometric`` module."""
+    import numpy as np
+    if not hasattr(np, "alltrue"):
+        np.alltrue = np.all
+    if not hasattr(np, "product"):
+        np.product = np.prod
+    if "matplotlib" not in sys.modules:
+        mpl = types.ModuleType("matplotlib")
+        plt = types.ModuleType("matplotlib.pyplot")
+        plt.Axes = object
+        mpl.pyplot = plt
+        sys.modules["matplotlib"] = mpl
+        sys.modules["matplotlib.pyplot"] = plt
+    if REFERENCE_ROOT not in sys.path:
+        sys.path.insert(0, REFERENCE_ROOT)
+    import hive.geometric as geometric
+    return geometric
