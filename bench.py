@@ -1,0 +1,412 @@
+#!/usr/bin/env python
+"""Benchmark of the TSDF hot path: BASELINE.json's metric on BASELINE.json's config.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scene dense|room]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...   (N > 1)
+
+Workload (``config.workload``): BASELINE config C2 -- a 512^3 TSDF at 1 cm voxels integrating synthetic 640x480
+RGB-D frames; one *step* integrates a batch of ``--batch`` (default 30) frames, so the default K=10 steps are the
+300 frames of the config.  The headline scene is ``dense`` (camera outside the volume, U/N ~ 0.9: the HBM-roofline
+configuration); the realistic ``room`` scene is measured too and reported under ``"room"``.
+
+For N > 1 GPUs the volume is z-slab sharded (one 512^3 slab per GPU: weak scaling, the global volume is
+512 x 512 x 512N), every frame batch is NCCL-broadcast from rank 0 and each rank integrates it into its slab.
+
+``value``  : voxel-updates/s (voxels visited per frame x frames / time, as the reference README's FPS x volume),
+             frames already resident in HBM as packed texels, CUDA-event timed, max over ranks.
+``e2e``    : the same metric through the reference-facing call ``TSDFVolume.integrate(color_im, depth_im, K, pose)``
+             with host numpy buffers: H2D of every frame and a D2H read of the update counter inside the timed region.
+``roofline``: integrate kernel, algorithmic bytes (24 B per voxel the oracle updates + 8 B per pixel)
+             over its CUDA-event launch duration, against MEASURED_PEAKS.json's HBM copy bandwidth.
+``cpu_baseline``: the oracle's C/OpenMP port of the reference's CPU path (oracle/tsdf_oracle.c) on the host cores.
+
+``--impl reference`` times that same CPU port (the reference is Python/numba and cannot be compiled into
+``oracle/_ref``; the port is several times faster than the reference's numpy path, so the ratio is conservative).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "tsdf_voxel_updates_per_s"
+UNIT = "voxel-updates/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=30, help="frames per step")
+    ap.add_argument("--config", default="C2")
+    ap.add_argument("--scene", default="dense", choices=["dense", "room"])
+    ap.add_argument("--distinct-frames", type=int, default=60, help="distinct synthetic frames generated (cycled)")
+    ap.add_argument("--no-room", action="store_true", help="skip the secondary room-scene measurement")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-mesh", action="store_true")
+    ap.add_argument("--cpu-sample-frames", type=int, default=6)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def _gen_frame(job):
+    from hive_b200.synthetic import Scene
+    config, variant, i, dim = job
+    sc = _scene(config, variant, dim)
+    fr = sc.frame(i)
+    return fr.rgb, fr.depth, fr.pose
+
+
+def _scene(config, variant, dim=None):
+    from hive_b200 import synthetic
+    if dim is not None:
+        key = f"{config}x{dim[2]}"
+        if key not in synthetic.CONFIGS:
+            cfg = dict(synthetic.CONFIGS[config])
+            cfg["dim"] = tuple(dim)
+            synthetic.CONFIGS[key] = cfg
+        config = key
+    return synthetic.Scene(config, variant)
+
+
+def make_frames(config, variant, n, dim=None):
+    """Generate n synthetic frames on the host cores (process pool; called before CUDA is initialised)."""
+    import multiprocessing as mp
+    jobs = [(config, variant, i, dim) for i in range(n)]
+    procs = min(len(jobs), os.cpu_count() or 1)
+    if procs <= 1:
+        return [_gen_frame(j) for j in jobs]
+    with mp.get_context("fork").Pool(procs) as pool:
+        return pool.map(_gen_frame, jobs)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu_index, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], None, set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax = float(f[2])
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "power_w_max": max(power) if power else None, "samples": len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def load_traffic():
+    """Per-launch DRAM bytes of the integrate kernel from the committed ncu capture, if any."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "integrate_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def cpu_baseline(config, variant, frames, n_sample, dim=None):
+    """Oracle C port of fusion.py:260-303 on all host cores, bounded sample of the same workload."""
+    from oracle import c_oracle
+    c_oracle.build()
+    sc = _scene(config, variant, dim)
+    vol = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    n_vox = int(np.prod(vol._vol_dim))
+    rgb, depth, pose = frames[0]
+    vol.integrate(rgb, depth, sc.K, pose)  # warm-up (page faults of the 3 planes)
+    t0 = time.perf_counter()
+    for i in range(n_sample):
+        rgb, depth, pose = frames[(i + 1) % len(frames)]
+        vol.integrate(rgb, depth, sc.K, pose)
+    dt = time.perf_counter() - t0
+    return {"value": n_vox * n_sample / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
+            "sample": f"{n_sample} frames of {config}/{variant} ({'x'.join(map(str, vol._vol_dim))} voxels, "
+                      f"{depth.shape[1]}x{depth.shape[0]}) through oracle/tsdf_oracle.c (OpenMP), {dt:.1f} s",
+            "s_per_frame": dt / n_sample}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import c_oracle
+    c_oracle.build()
+    n_distinct = min(args.distinct_frames, 8)
+    frames = make_frames(args.config, args.scene, n_distinct)
+    sc = _scene(args.config, args.scene)
+    vol = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    n_vox = int(np.prod(vol._vol_dim))
+    for i in range(args.warmup):  # one frame per step: a bounded sample of the 30-frame step of the GPU arm
+        rgb, depth, pose = frames[i % len(frames)]
+        vol.integrate(rgb, depth, sc.K, pose)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        rgb, depth, pose = frames[(args.warmup + i) % len(frames)]
+        vol.integrate(rgb, depth, sc.K, pose)
+    dt = time.perf_counter() - t0
+    value = n_vox * args.steps / dt
+    cores = c_oracle.num_threads()
+    sample = (f"each step = 1 frame (of the GPU arm's {args.batch}-frame step) of {args.config}/{args.scene} through "
+              f"oracle/tsdf_oracle.c, the C/OpenMP port of fusion.py:260-303, {cores} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64/f32", "data": "synthetic",
+        "config": {"workload": f"{args.config} {'x'.join(map(str, vol._vol_dim))} TSDF, 640x480 frames, scene={args.scene}"},
+        "frames_per_s": args.steps / dt,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    n_gpus = max(world, 1)
+    base_cfg = args.config
+
+    from hive_b200 import synthetic
+    base_dim = synthetic.CONFIGS[base_cfg]["dim"]
+    dim = (base_dim[0], base_dim[1], base_dim[2] * n_gpus)  # weak scaling: one base volume per GPU along z
+    n_distinct = max(2, min(args.distinct_frames, args.batch * (args.steps + args.warmup)))
+
+    # Host-side synthetic data first (fork pool), CUDA afterwards.  Only rank 0 owns frames; others receive broadcasts.
+    scenes = [args.scene] + ([] if args.no_room or args.scene == "room" else ["room"])
+    frames = {v: make_frames(base_cfg, v, n_distinct, dim if n_gpus > 1 else None) if rank == 0 else None for v in scenes}
+
+    import torch
+    torch.cuda.set_device(local_rank)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from hive_b200 import build as hv_build
+    if rank == 0:
+        hv_build.build()
+    if world > 1:
+        dist.barrier()
+    from hive_b200.sharded import SlabShardedTSDFVolume
+
+    peak, peak_src = measured_peak()
+    out = None
+    results = {}
+    for variant in scenes:
+        sc = _scene(base_cfg, variant, dim if n_gpus > 1 else None)
+        res = _measure(args, sc, frames[variant], variant, world, rank, local_rank, torch, dist,
+                       SlabShardedTSDFVolume, peak)
+        results[variant] = res
+        torch.cuda.empty_cache()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    main = results[args.scene]
+    H, W = main["H"], main["W"]
+    out = {
+        "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64 projection / f32 state", "data": "synthetic",
+        "config": {
+            "workload": f"{base_cfg}: {'x'.join(map(str, dim))} TSDF @ {sc.voxel_size * 100:g} cm, {W}x{H} synthetic frames, "
+                        f"scene={args.scene}, {args.batch} frames/step",
+            "voxels": int(np.prod(dim)), "frames_per_step": args.batch, "scene": args.scene,
+            "parallelism": "single GPU" if n_gpus == 1 else f"z-slab x{n_gpus}, NCCL frame broadcast",
+            "l2": "volume planes (12 B/voxel, >= 1.6 GB per GPU) are far larger than the 126 MB L2; no flush needed",
+            "distinct_frames": n_distinct,
+        },
+        "frames_per_s": main["frames_per_s"],
+        "updated_fraction": main["updated_fraction"],
+        "e2e": main["e2e"],
+        "gpu_launches": main["gpu_launches"],
+        "clocks": main["clocks"],
+        "roofline": {
+            "bound": "hbm", "achieved": main["achieved_gbs"], "peak": peak, "unit": "GB/s",
+            "frac": main["achieved_gbs"] / peak, "traffic": None, "peak_source": peak_src,
+            "kernel": "hv::integrate_kernel",
+            "algorithmic_bytes_per_launch": main["bytes_per_launch"],
+            "avg_launch_ms": main["avg_launch_ms"],
+            "frac_of_8000_spec": main["achieved_gbs"] / 8000.0,
+        },
+    }
+    tr = load_traffic()
+    if tr is not None:
+        out["roofline"]["traffic"] = tr.get("dram_bytes_per_launch")
+        out["roofline"]["traffic_source"] = tr.get("source")
+    if "room" in results and args.scene != "room":
+        r = results["room"]
+        out["room"] = {k: r[k] for k in ("value", "frames_per_s", "updated_fraction", "achieved_gbs", "avg_launch_ms")}
+        out["room"]["roofline_frac"] = r["achieved_gbs"] / peak
+        out["room"]["e2e_value"] = r["e2e"]["value"]
+    if main.get("mesh") is not None:
+        out["mesh"] = main["mesh"]
+    if not args.no_cpu_baseline and n_gpus == 1:
+        out["cpu_baseline"] = cpu_baseline(base_cfg, args.scene, frames[args.scene], args.cpu_sample_frames)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vol, peak):
+    B, K, Wm = args.batch, args.steps, args.warmup
+    vol = Vol(sc.vol_bnds.copy(), sc.voxel_size, world_size=world, rank=rank)
+    n_vox_global = int(np.prod(vol.global_dim))
+    H, W = sc.H, sc.W
+
+    # ---- device-resident path -----------------------------------------------------------------------------------
+    dev_frames = vol.upload_frames(frames, sc.K)  # rank 0 uploads; other ranks get an empty receiver of the same shape
+    n_f = dev_frames.num_frames
+
+    def step_device(s):
+        idx = [(s * B + j) % n_f for j in range(B)]
+        vol.integrate_batch_device(dev_frames, idx)
+
+    vol.count_updates(False)
+    for s in range(Wm):
+        step_device(s)
+    vol.count_updates(True)
+    vol.reset_update_counter()
+    _barrier(world, dist, torch)
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(K):
+        step_device(Wm + s)
+    e1.record()
+    torch.cuda.synchronize()
+    _barrier(world, dist, torch)
+    clocks = sampler.stop() if sampler is not None else None
+    ms = _max_over_ranks(e0.elapsed_time(e1), world, dist, torch)
+    local_updates = vol.num_updated_local()
+    total_updates = _sum_over_ranks(local_updates, world, dist, torch)
+    n_frames = K * B
+    value = n_vox_global * n_frames / (ms / 1000.0)
+
+    # roofline of the dominant kernel on this rank: algorithmic bytes / event-timed launch duration
+    launches = n_frames
+    bytes_per_launch = (24.0 * local_updates + 8.0 * H * W * n_frames) / launches
+    avg_launch_ms = ms / launches
+    achieved_gbs = bytes_per_launch / (avg_launch_ms / 1000.0) / 1e9
+
+    # ---- end-to-end path: host numpy frames through TSDFVolume.integrate -------------------------------------------
+    vol.count_updates(True)
+    for s in range(min(Wm, 3)):
+        vol.integrate_batch_host(frames, [(s * B + j) % n_f for j in range(B)], sc.K)
+    vol.read_update_counter()
+    _barrier(world, dist, torch)
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e2.record()
+    for s in range(K):
+        vol.integrate_batch_host(frames, [((Wm + s) * B + j) % n_f for j in range(B)], sc.K)
+        vol.read_update_counter()  # D2H read of the step's result
+    e3.record()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t0) * 1000.0
+    _barrier(world, dist, torch)
+    ms_e2e = _max_over_ranks(max(e2.elapsed_time(e3), wall_ms), world, dist, torch)
+    e2e_value = n_vox_global * n_frames / (ms_e2e / 1000.0)
+
+    mesh = None
+    if not args.no_mesh and hasattr(vol, "get_mesh_timed") and variant == args.scene:
+        mesh = vol.get_mesh_timed()
+
+    return {
+        "value": value, "ms_per_step": ms / K, "frames_per_s": n_frames / (ms / 1000.0),
+        "updated_fraction": total_updates / float(n_vox_global * n_frames),
+        "achieved_gbs": achieved_gbs, "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_launch_ms,
+        "gpu_launches": launches, "clocks": clocks, "H": H, "W": W, "mesh": mesh,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * (H * W * 7 + 12 * 8 + 16),
+                "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e / K,
+                "api": "TSDFVolume.integrate(color_im, depth_im, cam_intr, cam_pose) with host numpy buffers"},
+    }
+
+
+def _barrier(world, dist, torch):
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+
+
+def _max_over_ranks(x, world, dist, torch):
+    if world == 1:
+        return float(x)
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _sum_over_ranks(x, world, dist, torch):
+    if world == 1:
+        return int(x)
+    t = torch.tensor([x], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return int(t.item())
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -90,10 +90,11 @@ class TSDFVolume:
             self._tsdf_vol_gpu = torch.ones((X, Y, self._pitch), dtype=torch.float32, device=dev)
             self._weight_vol_gpu = torch.zeros((X, Y, self._pitch), dtype=torch.float32, device=dev)
             self._color_vol_gpu = torch.zeros((X, Y, self._pitch), dtype=torch.float32, device=dev)
-            wz = np.zeros(self._pitch, dtype=np.float32)
+            # float32-rounded coordinates, stored widened to float64 (the kernel projects in float64)
+            wz = np.zeros(self._pitch, dtype=np.float64)
             wz[:Z] = _world_table(self._vol_origin[2], self._voxel_size, Z, self._z0)
-            self._wx = torch.from_numpy(_world_table(self._vol_origin[0], self._voxel_size, X)).to(dev)
-            self._wy = torch.from_numpy(_world_table(self._vol_origin[1], self._voxel_size, Y)).to(dev)
+            self._wx = torch.from_numpy(_world_table(self._vol_origin[0], self._voxel_size, X).astype(np.float64)).to(dev)
+            self._wy = torch.from_numpy(_world_table(self._vol_origin[1], self._voxel_size, Y).astype(np.float64)).to(dev)
             self._wz = torch.from_numpy(wz).to(dev)
             self._updated = torch.zeros(1, dtype=torch.int64, device=dev)
             self._copy_stream = torch.cuda.Stream(device=dev)
@@ -221,6 +222,24 @@ class TSDFVolume:
                                                    ctypes.c_void_p(stream.cuda_stream)))
             stream.synchronize()
         return DeviceFrames(texels, w2cs, intr, H, W)
+
+    def upload_into(self, color_im, depth_im, texels_out):
+        """H2D + pack one host frame into ``texels_out`` (an (H*W,) int64 device tensor) on the current stream."""
+        torch = self._torch
+        depth_im = np.asarray(depth_im)
+        im_h, im_w = depth_im.shape
+        st = self._ensure_stage(im_h, im_w)
+        slot = self._frame_no & 1
+        self._frame_no += 1
+        st["uploaded"][slot].synchronize()
+        st["h_depth"][slot].numpy()[...] = depth_im
+        st["h_rgb"][slot].numpy()[...] = self._as_rgb_u8(color_im)
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream()
+            _lib.check(self._lib.hv_upload_frame(
+                _ptr(st["h_depth"][slot]), _ptr(st["h_rgb"][slot]), im_h, im_w, _ptr(st["d_depth"][slot]),
+                _ptr(st["d_rgb"][slot]), _ptr(texels_out), ctypes.c_void_p(stream.cuda_stream)))
+            st["uploaded"][slot].record(stream)
 
     def integrate_device(self, frames: DeviceFrames, index: int, obs_weight=1.):
         """Integrate frame ``index`` of a ``DeviceFrames`` batch (inputs already resident in HBM)."""

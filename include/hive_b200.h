@@ -56,8 +56,9 @@ int hv_upload_frame(const float* h_depth, const uint8_t* h_rgb, int H, int W, fl
  *
  * tsdf / weight / color : float32 planes laid out [X][Y][pitch] (z fastest, fusion.py:54-57), `pitch` >= Z floats per
  *                         column, a multiple of 4, base pointers 16-byte aligned.  Only z in [0, Z) is touched.
- * wx, wy, wz            : float32 world coordinate of voxel index i on each axis, computed by the reference formula
- *                         float32(float64(origin) + voxel_size * i) (fusion.py:183-188); wz holds `pitch` entries.
+ * wx, wy, wz            : world coordinate of voxel index i on each axis, computed by the reference formula
+ *                         float32(float64(origin) + voxel_size * i) (fusion.py:183-188) and then widened to float64
+ *                         (the kernel projects in float64); wz holds `pitch` entries, 16-byte aligned.
  *                         For a z-slab shard the caller passes the slab's slice of the global table.
  * h_world2cam           : HOST, 12 doubles, rows 0..2 of inv(cam_pose) (fusion.py:263).
  * h_intr                : HOST, 4 floats fx, fy, cx, cy (float32 like fusion.py:196-198).
@@ -67,7 +68,7 @@ int hv_upload_frame(const float* h_depth, const uint8_t* h_rgb, int H, int W, fl
  *                         (valid_pts.sum(), fusion.py:279).  NULL to skip.
  * ---------------------------------------------------------------------------------------------------------- */
 int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims, int64_t pitch,
-                 const float* wx, const float* wy, const float* wz, const double* h_world2cam, const float* h_intr,
+                 const double* wx, const double* wy, const double* wz, const double* h_world2cam, const float* h_intr,
                  const void* texels, int H, int W, double trunc, double obs_weight, unsigned long long* updated,
                  void* stream);
 
