@@ -31,7 +31,7 @@ SIGNATURES = {
     "hv_pack_frame": [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
     "hv_upload_frame": [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_integrate": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                     c_void_p, c_int, c_int, c_double, c_double, c_void_p, c_void_p],
+                     c_void_p, c_int, c_int, c_double, c_double, c_int, c_void_p, c_void_p],
 }
 
 

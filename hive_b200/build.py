@@ -17,6 +17,9 @@ LIB_PATH = os.path.join(HERE, "libhive_b200.so")
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+    # no implicit FMA contraction: every fused multiply-add in the kernels is written explicitly, because parity with
+    # the oracle depends on where roundings happen (nvcc contracts even __fadd2_rn(__fmul2_rn(..)) otherwise)
+    "-fmad=false",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "-shared", "-Xptxas", "-warn-spills",
 ]
 

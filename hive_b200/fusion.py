@@ -102,6 +102,7 @@ class TSDFVolume:
         self._stage = None  # lazily sized to the first frame
         self._frame_no = 0
         self.count_updates = False
+        self._integer_weights, self._weight_sum = True, 0.0  # see _weights_flag
 
     # ------------------------------------------------------------------ reference-compatible attributes
     @property
@@ -195,12 +196,22 @@ class TSDFVolume:
             ev.record(compute)
             st["consumed"][slot] = ev
 
+    def _weights_flag(self, obs_weight) -> int:
+        """HV_INTEGRATE_INTEGER_WEIGHTS while every weight ever integrated was a small positive integer."""
+        ow = float(obs_weight)
+        if self._integer_weights and ow >= 1.0 and ow == int(ow) and self._weight_sum + ow < 2 ** 20:
+            self._weight_sum += ow
+            return 1
+        self._integer_weights = False
+        return 0
+
     def _launch(self, texels, H, W, intr, w2c, obs_weight, stream):
         _lib.check(self._lib.hv_integrate(
             _ptr(self._tsdf_vol_gpu), _ptr(self._weight_vol_gpu), _ptr(self._color_vol_gpu),
             ctypes.cast(self._dims_c, ctypes.c_void_p), self._pitch, _ptr(self._wx), _ptr(self._wy), _ptr(self._wz),
             w2c.ctypes.data_as(ctypes.c_void_p), intr.ctypes.data_as(ctypes.c_void_p), _ptr(texels), H, W,
-            self._trunc_margin, float(obs_weight), _ptr(self._updated) if self.count_updates else None,
+            self._trunc_margin, float(obs_weight), self._weights_flag(obs_weight),
+            _ptr(self._updated) if self.count_updates else None,
             ctypes.c_void_p(stream.cuda_stream)))
 
     # ------------------------------------------------------------------ device-resident frames (bench / sharded driver)

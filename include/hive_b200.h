@@ -64,13 +64,18 @@ int hv_upload_frame(const float* h_depth, const uint8_t* h_rgb, int H, int W, fl
  * h_intr                : HOST, 4 floats fx, fy, cx, cy (float32 like fusion.py:196-198).
  * texels                : frame from hv_pack_frame.
  * trunc                 : truncation margin, 5 * voxel_size (fusion.py:39).   obs_weight: fusion.py:217.
+ * flags                 : HV_INTEGRATE_INTEGER_WEIGHTS = the caller guarantees that obs_weight and every weight already
+ *                         stored in the volume are non-negative integers below 2^20 (true for a volume only ever fed
+ *                         integer obs_weights, e.g. the reference's constant 1.0).  It selects a shorter, still
+ *                         bit-exact, division sequence; 0 is always safe.
  * updated               : optional device uint64 accumulator; the kernel adds the number of voxels it updated
  *                         (valid_pts.sum(), fusion.py:279).  NULL to skip.
  * ---------------------------------------------------------------------------------------------------------- */
+#define HV_INTEGRATE_INTEGER_WEIGHTS 1
 int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims, int64_t pitch,
                  const double* wx, const double* wy, const double* wz, const double* h_world2cam, const float* h_intr,
-                 const void* texels, int H, int W, double trunc, double obs_weight, unsigned long long* updated,
-                 void* stream);
+                 const void* texels, int H, int W, double trunc, double obs_weight, int flags,
+                 unsigned long long* updated, void* stream);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,8 @@ def main():
         print()
     if "--source" in sys.argv:
         src = page(rep, "source")
+        while src and (len(src[0]) < 4 or src[0][0].strip() == "Kernel Name"):
+            src = src[1:]
         if len(src) > 2:
             h = src[0]
             def col(name):
@@ -75,6 +77,23 @@ def main():
                         return 0.0
                 tot = sum(num(r[c_samp]) for r in body) or 1.0
                 body.sort(key=lambda r: -num(r[c_samp]))
+                c_thr = col("Thread Instructions Executed")
+                ops, tot_i = {}, 0.0
+                for r in body:
+                    txt = r[c_src].strip().split()
+                    if not txt:
+                        continue
+                    op = (txt[1] if txt[0].startswith("@") and len(txt) > 1 else txt[0]).split(".")[0]
+                    n = num(r[c_inst]) if c_inst is not None else 0.0
+                    o = ops.setdefault(op, [0.0, 0.0])
+                    o[0] += n
+                    o[1] += num(r[c_samp])
+                    tot_i += n
+                print(f"## SASS opcode mix: {len(body)} static instructions, {tot_i:.0f} warp-instructions executed\n")
+                print("| opcode | % of executed warp-instructions | % of stall samples |\n|---|---:|---:|")
+                for op, (n, sm) in sorted(ops.items(), key=lambda kv: -kv[1][0])[:25]:
+                    print(f"| {op} | {100 * n / (tot_i or 1):.1f} | {100 * sm / tot:.1f} |")
+                print()
                 print("## hottest lines / instructions by warp-state samples (first launch)\n")
                 print("| samples % | instr executed | source |\n|---:|---:|---|")
                 for r in body[:40]:
