@@ -21,7 +21,8 @@ HV_E_CAPACITY = -5
 _lib = None
 _lock = threading.Lock()
 
-c_void_p, c_int, c_int64, c_double = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double
+c_void_p, c_int, c_int64, c_double, c_float = (ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double,
+                                                ctypes.c_float)
 
 # name -> argtypes; every function returns int.  Kept in step with include/hive_b200.h (tests/test_abi.py checks it).
 SIGNATURES = {
@@ -32,6 +33,11 @@ SIGNATURES = {
     "hv_upload_frame": [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_integrate": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                      c_void_p, c_int, c_int, c_double, c_double, c_int, c_void_p, c_void_p],
+    "hv_mc_scratch_bytes": [c_void_p, c_int, c_int, c_void_p],
+    "hv_mc_count": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_mc_emit": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
+                   c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                   c_void_p, c_void_p, c_void_p, c_void_p],
 }
 
 

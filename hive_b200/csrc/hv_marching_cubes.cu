@@ -1,0 +1,642 @@
+// Marching-cubes mesh extraction for sm_100a (B200).
+//
+// Replaces the `measure.marching_cubes(tsdf_vol, level=0)` call of TSDFVolume.get_mesh / get_point_cloud
+// (third_party/tsdf_fusion_python/fusion.py:317,338) and the in-tree post-processing after it (fusion.py:339-348:
+// nearest-voxel colour gather, b/g/r unpack, voxel -> world transform).  The arithmetic contract is the one restated in
+// oracle/mc_oracle.c (scikit-image itself is not available anywhere on the box: parity unpinned).
+//
+// Pipeline (all HBM-bound streaming / compaction, no tensor cores):
+//   1. mc_sign_kernel    one pass over the TSDF plane (4 B/voxel): one bit per voxel (v > level) and min/max.  The bit
+//                        volume is N/8 bytes (16 MB for 512^3) and stays L2-resident for everything that follows.
+//   2. mc_count_kernel   one thread per group of 32 z-consecutive voxels: bit-parallel edge masks (which voxels own a
+//                        vertex on their +axis0/+axis1/+axis2 edge or a cube-centre vertex) and the triangle count of
+//                        the group's active cubes.  TSDF values are only touched for cubes with an ambiguous face.
+//   3. scan kernels      exclusive prefix sums of the per-group (vertex, triangle) counts.
+//   4. mc_emit_kernel    re-walks the active cubes and writes triangles; a vertex index is recovered from the owner
+//                        group's prefix + popcounts of its masks, so no per-voxel index volume exists.  Vertices come out
+//                        sorted by (owner voxel in scan order, axis) and triangles in cube scan order: deterministic.
+//   5. mc_vertex_kernel  one thread per vertex: position, accumulated normal, colour, world transform.
+//
+// z-slab shards pass one halo plane below / above the slab (`halo_lo` / `halo_hi`); keys carry global voxel indices so
+// per-slab meshes can be stitched exactly (hive_b200/sharded.py).
+#include "hv_common.cuh"
+
+#include <float.h>
+
+#define HV_MC_TABLE static __device__ const
+#include "hv_mc_tables.h"
+
+namespace hv {
+
+struct McGrid {
+    const float* tsdf;
+    const float* halo_lo;  // [X][Y] plane just below local z = 0, or null
+    const float* halo_hi;  // [X][Y] plane just above local z = Z - 1, or null
+    const float* color;
+    const float* chalo_lo;
+    const float* chalo_hi;
+    int X, Y, Z, pitch;
+    int hl;              // 1 if halo_lo is present: "zb" coordinates are local z + hl
+    int Zb;              // Z + hl + hh: planes visible to this shard
+    int G;               // groups of 32 zb per column
+    int own_lo, own_hi;  // zb range of the voxels / cubes this shard owns
+    long long zoff;      // global z of zb = 0
+    long long Zg;        // global Z
+    double level;
+    // scratch
+    unsigned int* bits;   // [X*Y*G]
+    uint4* gmask;         // [X*Y*G] owner masks: axis0, axis1, axis2, centre
+    uint2* gcount;        // [X*Y*G] (vertices, triangles)
+    uint2* goff;          // [X*Y*G] exclusive prefix of gcount
+    uint2* bsum;          // per scan block
+    unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float)
+    long long n_groups;
+};
+
+__device__ __forceinline__ float mc_fetch(const McGrid& g, const float* vol, const float* lo, const float* hi, int x,
+                                          int y, int zb) {
+    const int z = zb - g.hl;
+    const size_t col = (size_t)x * g.Y + y;
+    if (z < 0) return __ldg(lo + col);
+    if (z >= g.Z) return __ldg(hi + col);
+    return __ldg(vol + col * (size_t)g.pitch + z);
+}
+
+__device__ __forceinline__ int float_order_key(float f) {
+    const int i = __float_as_int(f);
+    return i >= 0 ? i : i ^ 0x7fffffff;
+}
+
+// ---- 1. sign bits + min/max ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) mc_sign_kernel(const McGrid g) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+    int kmin = 0x7fffffff, kmax = (int)0x80000000;
+    for (long long gi = warp0; gi < g.n_groups; gi += n_warps) {
+        const long long col = gi / g.G;
+        const int gq = (int)(gi - col * g.G);
+        const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+        const int zb = gq * 32 + lane;
+        bool pos = false;
+        if (zb < g.Zb) {
+            const float v = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb);
+            pos = (double)v > g.level;
+            if (v == v) {
+                const int k = float_order_key(v);
+                kmin = min(kmin, k);
+                kmax = max(kmax, k);
+            }
+        }
+        const unsigned int word = __ballot_sync(0xffffffffu, pos);
+        if (lane == 0) g.bits[gi] = word;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+        kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+    }
+    if (lane == 0) {
+        atomicMin(reinterpret_cast<int*>(g.totals + 2), kmin);
+        atomicMax(reinterpret_cast<int*>(g.totals + 3), kmax);
+    }
+}
+
+// ---- cube helpers -----------------------------------------------------------------------------------------------------
+struct CubeWords {
+    unsigned int w[8];    // per corner: the word whose bit k is that corner of cube (x, y, 32*gq + k)
+    unsigned int active;  // cubes of this group that exist, are owned and are crossed by the surface
+    unsigned int own;     // owned voxels of this group
+    unsigned int b00, b01, b10, u00;
+};
+
+__device__ __forceinline__ unsigned int range_mask(int lo, int hi, int base) {
+    // bits k with lo <= base + k < hi
+    const int a = max(lo - base, 0), b = min(hi - base, 32);
+    if (a >= b) return 0u;
+    const unsigned int upto_b = (b >= 32) ? 0xffffffffu : ((1u << b) - 1u);
+    return upto_b & ~((1u << a) - 1u);
+}
+
+__device__ __forceinline__ void load_pair(const McGrid& g, int x, int y, int gq, bool in, unsigned int& b, unsigned int& u) {
+    b = 0u;
+    u = 0u;
+    if (!in) return;
+    const size_t gi = ((size_t)x * g.Y + y) * g.G + gq;
+    b = g.bits[gi];
+    const unsigned int nxt = (gq + 1 < g.G) ? g.bits[gi + 1] : 0u;
+    u = (b >> 1) | (nxt << 31);
+}
+
+__device__ __forceinline__ CubeWords load_cube_words(const McGrid& g, int x, int y, int gq) {
+    CubeWords c;
+    const bool x1 = x + 1 < g.X, y1 = y + 1 < g.Y;
+    unsigned int b00, b01, b10, b11, u00, u01, u10, u11;
+    load_pair(g, x, y, gq, true, b00, u00);
+    load_pair(g, x, y + 1, gq, y1, b01, u01);
+    load_pair(g, x + 1, y, gq, x1, b10, u10);
+    load_pair(g, x + 1, y + 1, gq, x1 && y1, b11, u11);
+    // corner i offsets (axis0, axis1, axis2): see kMcCornerOff
+    c.w[0] = b00; c.w[1] = u00; c.w[2] = u01; c.w[3] = b01;
+    c.w[4] = b10; c.w[5] = u10; c.w[6] = u11; c.w[7] = b11;
+    c.b00 = b00; c.b01 = b01; c.b10 = b10; c.u00 = u00;
+    const int base = gq * 32;
+    c.own = range_mask(g.own_lo, g.own_hi, base);
+    const unsigned int all8 = b00 & b01 & b10 & b11 & u00 & u01 & u10 & u11;
+    const unsigned int any8 = b00 | b01 | b10 | b11 | u00 | u01 | u10 | u11;
+    c.active = (x1 && y1) ? (any8 & ~all8 & c.own & range_mask(0, g.Zb - 1, base)) : 0u;
+    return c;
+}
+
+__device__ __forceinline__ int cube_index(const CubeWords& c, int k) {
+    int idx = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) idx |= (int)((c.w[i] >> k) & 1u) << i;
+    return idx;
+}
+
+__device__ __forceinline__ void load_cube_values(const McGrid& g, int x, int y, int zb, double v[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float f = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x + kMcCornerOff[3 * i], y + kMcCornerOff[3 * i + 1],
+                                 zb + kMcCornerOff[3 * i + 2]);
+        v[i] = (double)f - g.level;
+    }
+}
+
+// Resolves the ambiguous faces with the asymptotic decider (same statement as oracle/mc_oracle.c:mc_variant).
+__device__ __forceinline__ int cube_variant(int idx, const double v[8]) {
+    int variant = kMcVariantBase[idx];
+    const int namb = kMcAmbCount[idx];
+    const unsigned int faces = kMcAmbFaces[idx];
+    for (int k = 0; k < namb; ++k) {
+        const int f = (faces >> (3 * k)) & 7;
+        int a = kMcFaceCorner[4 * f], b = kMcFaceCorner[4 * f + 1], c = kMcFaceCorner[4 * f + 2], d = kMcFaceCorner[4 * f + 3];
+        if (!((idx >> a) & 1)) {
+            const int t = a; a = b; b = c; c = d; d = t;
+        }
+        const double pos = __dmul_rn(v[a], v[c]), neg = __dmul_rn(v[b], v[d]);
+        if (pos > neg) variant += 1 << k;
+    }
+    return variant;
+}
+
+__device__ __forceinline__ int cube_variant_at(const McGrid& g, int idx, int x, int y, int zb) {
+    if (kMcAmbCount[idx] == 0) return kMcVariantBase[idx];
+    double v[8];
+    load_cube_values(g, x, y, zb, v);
+    return cube_variant(idx, v);
+}
+
+// ---- 2. per-group owner masks and counts ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) mc_count_kernel(const McGrid g) {
+    const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gi >= g.n_groups) return;
+    const long long col = gi / g.G;
+    const int gq = (int)(gi - col * g.G);
+    const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+    const CubeWords c = load_cube_words(g, x, y, gq);
+    const int base = gq * 32;
+    uint4 m;
+    m.x = (x + 1 < g.X) ? ((c.b00 ^ c.b10) & c.own) : 0u;
+    m.y = (y + 1 < g.Y) ? ((c.b00 ^ c.b01) & c.own) : 0u;
+    m.z = (c.b00 ^ c.u00) & c.own & range_mask(0, g.Zb - 1, base);
+    m.w = 0u;
+    unsigned int ntri = 0;
+    for (unsigned int rest = c.active; rest; rest &= rest - 1) {
+        const int k = __ffs(rest) - 1;
+        const int idx = cube_index(c, k);
+        const int variant = cube_variant_at(g, idx, x, y, base + k);
+        ntri += kMcVarNtri[variant];
+        if ((kMcVarMult[variant] >> 48) & 15ull) m.w |= 1u << k;
+    }
+    g.gmask[gi] = m;
+    g.gcount[gi] = make_uint2(__popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w), ntri);
+}
+
+// ---- 3. exclusive scan of uint2 counts (reduce, scan the block sums, apply) ----------------------------------------------
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ uint2 add2(uint2 a, uint2 b) { return make_uint2(a.x + b.x, a.y + b.y); }
+
+__device__ uint2 block_exclusive_scan(uint2 v, uint2& total) {
+    __shared__ uint2 warp_sums[kScanThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint2 inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int ux = __shfl_up_sync(0xffffffffu, inc.x, o), uy = __shfl_up_sync(0xffffffffu, inc.y, o);
+        if (lane >= o) inc = add2(inc, make_uint2(ux, uy));
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    uint2 carry = make_uint2(0, 0), tot = make_uint2(0, 0);
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+        if (w < warp) carry = add2(carry, warp_sums[w]);
+        tot = add2(tot, warp_sums[w]);
+    }
+    __syncthreads();
+    total = tot;
+    return make_uint2(carry.x + inc.x - v.x, carry.y + inc.y - v.y);
+}
+
+__global__ void __launch_bounds__(kScanThreads) mc_scan_reduce_kernel(const McGrid g) {
+    const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * kScanItems;
+    uint2 s = make_uint2(0, 0);
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i)
+        if (base + i < g.n_groups) s = add2(s, g.gcount[base + i]);
+    uint2 total;
+    block_exclusive_scan(s, total);
+    if (threadIdx.x == 0) g.bsum[blockIdx.x] = total;
+}
+
+// one block: exclusive scan of the block sums in place, 64-bit totals
+__global__ void __launch_bounds__(kScanThreads) mc_scan_top_kernel(const McGrid g, int n_blocks) {
+    __shared__ unsigned long long carry_v, carry_t;
+    if (threadIdx.x == 0) carry_v = carry_t = 0ull;
+    __syncthreads();
+    for (int start = 0; start < n_blocks; start += kScanThreads) {
+        const int i = start + threadIdx.x;
+        const uint2 v = (i < n_blocks) ? g.bsum[i] : make_uint2(0, 0);
+        uint2 total;
+        const uint2 ex = block_exclusive_scan(v, total);
+        const unsigned long long cv = carry_v, ct = carry_t;
+        if (i < n_blocks) g.bsum[i] = make_uint2((unsigned int)(cv + ex.x), (unsigned int)(ct + ex.y));
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            carry_v = cv + total.x;
+            carry_t = ct + total.y;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        g.totals[0] = carry_v;
+        g.totals[1] = carry_t;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads) mc_scan_apply_kernel(const McGrid g) {
+    const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * kScanItems;
+    uint2 item[kScanItems];
+    uint2 s = make_uint2(0, 0);
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        item[i] = (base + i < g.n_groups) ? g.gcount[base + i] : make_uint2(0, 0);
+        s = add2(s, item[i]);
+    }
+    uint2 total;
+    uint2 run = add2(block_exclusive_scan(s, total), g.bsum[blockIdx.x]);
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        if (base + i < g.n_groups) g.goff[base + i] = run;
+        run = add2(run, item[i]);
+    }
+}
+
+// ---- 4. emit triangles and vertex keys ------------------------------------------------------------------------------
+struct McEmit {
+    int32_t* faces;                  // [T][3] local vertex indices, or null
+    unsigned long long* face_keys;   // [T][3] global vertex keys, or null
+    unsigned long long* vert_keys;   // [V]
+};
+
+__device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x, int y, int zb, int axis) {
+    const unsigned long long lin = ((unsigned long long)x * g.Y + y) * (unsigned long long)g.Zg + (unsigned long long)(zb + g.zoff);
+    return lin * 4ull + (unsigned long long)axis;
+}
+
+__device__ __forceinline__ int vertex_index(const McGrid& g, int x, int y, int zb, int axis) {
+    const size_t og = ((size_t)x * g.Y + y) * g.G + (zb >> 5);
+    const int bit = zb & 31;
+    const uint4 m = g.gmask[og];
+    const unsigned int low = (1u << bit) - 1u;
+    int r = (int)g.goff[og].x + __popc(m.x & low) + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
+    if (axis > 0) r += (m.x >> bit) & 1u;
+    if (axis > 1) r += (m.y >> bit) & 1u;
+    if (axis > 2) r += (m.z >> bit) & 1u;
+    return r;
+}
+
+__global__ void __launch_bounds__(256) mc_emit_kernel(const McGrid g, const McEmit out) {
+    const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gi >= g.n_groups) return;
+    const uint2 cnt = g.gcount[gi];
+    if (cnt.x == 0 && cnt.y == 0) return;
+    const long long col = gi / g.G;
+    const int gq = (int)(gi - col * g.G);
+    const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+    const int base = gq * 32;
+    const uint2 off = g.goff[gi];
+
+    if (cnt.x) {  // keys of the vertices this group owns, ordered by (voxel, axis)
+        const uint4 m = g.gmask[gi];
+        unsigned int vi = off.x;
+        for (unsigned int rest = m.x | m.y | m.z | m.w; rest; rest &= rest - 1) {
+            const int k = __ffs(rest) - 1;
+            if ((m.x >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 0);
+            if ((m.y >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 1);
+            if ((m.z >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 2);
+            if ((m.w >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 3);
+        }
+    }
+    if (cnt.y) {
+        const CubeWords c = load_cube_words(g, x, y, gq);
+        size_t ti = off.y;
+        for (unsigned int rest = c.active; rest; rest &= rest - 1) {
+            const int k = __ffs(rest) - 1;
+            const int zb = base + k;
+            const int idx = cube_index(c, k);
+            const int variant = cube_variant_at(g, idx, x, y, zb);
+            const int ntri = kMcVarNtri[variant];
+            const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
+            for (int t = 0; t < 3 * ntri; ++t) {
+                const int e = tri[t];
+                int ox = 0, oy = 0, oz = 0, axis = 3;
+                if (e < 12) {
+                    ox = kMcEdgeOwner[4 * e], oy = kMcEdgeOwner[4 * e + 1], oz = kMcEdgeOwner[4 * e + 2];
+                    axis = kMcEdgeOwner[4 * e + 3];
+                }
+                if (out.face_keys) {
+                    out.face_keys[3 * ti + t] = vertex_key(g, x + ox, y + oy, zb + oz, axis);
+                } else {
+                    out.faces[3 * ti + t] = vertex_index(g, x + ox, y + oy, zb + oz, axis);
+                }
+            }
+            ti += ntri;
+        }
+    }
+}
+
+// ---- 5. vertices: position, normal, colour ----------------------------------------------------------------------------
+struct McVerts {
+    const unsigned long long* vert_keys;
+    long long n_verts;
+    float* verts_world;  // [V][3]
+    float* verts_voxel;  // [V][3] or null
+    float* normals;      // [V][3]
+    uint8_t* colors;     // [V][3] r, g, b
+    float voxel_size;
+    float origin[3];
+};
+
+// Adds `mult` times this cube's interpolated down-hill gradient at edge `e` (12 = centre) to the float32 accumulator.
+__device__ __forceinline__ void add_cube_gradient(const double v[8], int e, int mult, float acc[3]) {
+    if (mult == 0) return;
+    double w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int bitk = 4 >> k;  // offset bit of axis k in the d0*4 + d1*2 + d2 code
+        double gk;
+        if (e < 12) {
+            const int lo = kMcEdgeCorner[2 * e], hi = kMcEdgeCorner[2 * e + 1];
+            const int clo = kMcCornerOff[3 * lo] * 4 + kMcCornerOff[3 * lo + 1] * 2 + kMcCornerOff[3 * lo + 2];
+            const int chi = kMcCornerOff[3 * hi] * 4 + kMcCornerOff[3 * hi + 1] * 2 + kMcCornerOff[3 * hi + 2];
+            const double g_lo = v[kMcCornerAt[clo & ~bitk]] - v[kMcCornerAt[clo | bitk]];
+            const double g_hi = v[kMcCornerAt[chi & ~bitk]] - v[kMcCornerAt[chi | bitk]];
+            gk = __dadd_rn(__dmul_rn(g_lo, w[lo]), __dmul_rn(g_hi, w[hi]));
+        } else {
+            gk = 0.0;
+            for (int i = 0; i < 8; ++i) {
+                const int ci = kMcCornerOff[3 * i] * 4 + kMcCornerOff[3 * i + 1] * 2 + kMcCornerOff[3 * i + 2];
+                const double gi = v[kMcCornerAt[ci & ~bitk]] - v[kMcCornerAt[ci | bitk]];
+                gk = __dadd_rn(gk, __dmul_rn(w[i], gi));
+            }
+        }
+        const float gf = (float)gk;
+        for (int j = 0; j < mult; ++j) acc[k] = __fadd_rn(acc[k], gf);
+    }
+}
+
+__global__ void __launch_bounds__(128) mc_vertex_kernel(const McGrid g, const McVerts out) {
+    const long long vi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (vi >= out.n_verts) return;
+    const unsigned long long key = out.vert_keys[vi];
+    const int axis = (int)(key & 3ull);
+    const unsigned long long lin = key >> 2;
+    const long long zg = (long long)(lin % (unsigned long long)g.Zg);
+    const unsigned long long col = lin / (unsigned long long)g.Zg;
+    const int y = (int)(col % (unsigned long long)g.Y), x = (int)(col / (unsigned long long)g.Y);
+    const int zb = (int)(zg - g.zoff);
+    const int p[3] = {x, y, zb};
+    const int dim[3] = {g.X, g.Y, g.Zb};
+
+    double pos[3] = {(double)x, (double)y, (double)zg};
+    float acc[3] = {0.0f, 0.0f, 0.0f};
+    double v[8];
+    if (axis == 3) {
+        load_cube_values(g, x, y, zb, v);
+        int idx = 0;
+        for (int i = 0; i < 8; ++i) idx |= (v[i] > 0.0 ? 1 : 0) << i;
+        const int variant = cube_variant(idx, v);
+        double f[3] = {0.0, 0.0, 0.0}, ff = 0.0;
+        for (int i = 0; i < 8; ++i) {
+            const double w = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
+            for (int k = 0; k < 3; ++k) f[k] = __dadd_rn(f[k], __dmul_rn((double)kMcCornerOff[3 * i + k], w));
+            ff = __dadd_rn(ff, w);
+        }
+        for (int k = 0; k < 3; ++k) pos[k] = __dadd_rn(pos[k], f[k] / ff);
+        add_cube_gradient(v, 12, (int)((kMcVarMult[variant] >> 48) & 15ull), acc);
+    } else {
+        int q[3] = {x, y, zb};
+        q[axis] += 1;
+        const double v_lo = (double)mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb) - g.level;
+        const double v_hi = (double)mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, q[0], q[1], q[2]) - g.level;
+        const double w_lo = 1.0 / ((double)FLT_EPSILON + fabs(v_lo)), w_hi = 1.0 / ((double)FLT_EPSILON + fabs(v_hi));
+        pos[axis] = __dadd_rn(pos[axis], w_hi / __dadd_rn(w_lo, w_hi));
+        // the (up to four) cubes around the edge, in scan order (axis0 outermost): larger offsets first
+        const int b = (axis == 0) ? 1 : 0, c = (axis == 2) ? 1 : 2;
+        for (int db = 1; db >= 0; --db) {
+            for (int dc = 1; dc >= 0; --dc) {
+                int base[3] = {p[0], p[1], p[2]};
+                base[b] -= db;
+                base[c] -= dc;
+                if (base[b] < 0 || base[c] < 0 || base[b] + 1 >= dim[b] || base[c] + 1 >= dim[c]) continue;
+                int d[3] = {0, 0, 0};
+                d[b] = db;
+                d[c] = dc;
+                const int e = kMcEdgeAt[axis * 8 + d[0] * 4 + d[1] * 2 + d[2]];
+                load_cube_values(g, base[0], base[1], base[2], v);
+                int idx = 0;
+                for (int i = 0; i < 8; ++i) idx |= (v[i] > 0.0 ? 1 : 0) << i;
+                const int variant = cube_variant(idx, v);
+                add_cube_gradient(v, e, (int)((kMcVarMult[variant] >> (4 * e)) & 15ull), acc);
+            }
+        }
+    }
+    const float pv[3] = {(float)pos[0], (float)pos[1], (float)pos[2]};
+    const double len = sqrt(__dadd_rn(__dadd_rn(__dmul_rn((double)acc[0], (double)acc[0]), __dmul_rn((double)acc[1], (double)acc[1])),
+                                      __dmul_rn((double)acc[2], (double)acc[2])));
+    if (len > 0.0)
+        for (int k = 0; k < 3; ++k) acc[k] = (float)((double)acc[k] / len);
+    // colour of the nearest voxel (fusion.py:339,343-348), half-to-even like np.round
+    const int i0 = (int)rintf(pv[0]), i1 = (int)rintf(pv[1]);
+    const int i2 = (int)((long long)rintf(pv[2]) - g.zoff);
+    const unsigned int packed = (unsigned int)mc_fetch(g, g.color, g.chalo_lo, g.chalo_hi, i0, i1, i2);
+    for (int k = 0; k < 3; ++k) {
+        out.verts_world[3 * vi + k] = __fadd_rn(__fmul_rn(pv[k], out.voxel_size), out.origin[k]);  // fusion.py:340
+        if (out.verts_voxel) out.verts_voxel[3 * vi + k] = pv[k];
+        out.normals[3 * vi + k] = acc[k];
+    }
+    out.colors[3 * vi + 0] = (uint8_t)(packed & 255u);
+    out.colors[3 * vi + 1] = (uint8_t)((packed >> 8) & 255u);
+    out.colors[3 * vi + 2] = (uint8_t)((packed >> 16) & 255u);
+}
+
+}  // namespace hv
+
+// ---- C ABI ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct McLayout {
+    long long n_groups;
+    int G, Zb, n_scan_blocks;
+    size_t off_bits, off_gmask, off_gcount, off_goff, off_bsum, total;
+};
+
+size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+
+int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
+    HV_REQUIRE(h_dims, "marching cubes: null dims");
+    const int64_t X = h_dims[0], Y = h_dims[1], Z = h_dims[2];
+    HV_REQUIRE(X >= 1 && Y >= 1 && Z >= 1 && X < (1ll << 30) && Y < (1ll << 30) && Z < (1ll << 30),
+               "marching cubes: bad dims %lld x %lld x %lld", (long long)X, (long long)Y, (long long)Z);
+    L->Zb = (int)Z + (lo ? 1 : 0) + (hi ? 1 : 0);
+    L->G = (L->Zb + 31) / 32;
+    L->n_groups = (long long)X * Y * L->G;
+    HV_REQUIRE(L->n_groups < (1ll << 40), "marching cubes: volume too large");
+    L->n_scan_blocks = (int)((L->n_groups + hv::kScanTile - 1) / hv::kScanTile);
+    size_t o = 0;
+    L->off_gmask = o;  // 16-byte elements first
+    o = align_up(o + (size_t)L->n_groups * sizeof(uint4));
+    L->off_gcount = o;
+    o = align_up(o + (size_t)L->n_groups * sizeof(uint2));
+    L->off_goff = o;
+    o = align_up(o + (size_t)L->n_groups * sizeof(uint2));
+    L->off_bits = o;
+    o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
+    L->off_bsum = o;
+    o = align_up(o + (size_t)L->n_scan_blocks * sizeof(uint2));
+    L->total = o;
+    return HV_OK;
+}
+
+int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims,
+            int64_t pitch, double level, void* scratch, int64_t scratch_bytes, McLayout* L) {
+    int rc = mc_layout(h_dims, halo_lo != nullptr, halo_hi != nullptr, L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(tsdf && scratch, "marching cubes: null pointer");
+    HV_REQUIRE(pitch >= h_dims[2], "marching cubes: pitch %lld < Z", (long long)pitch);
+    HV_REQUIRE(((uintptr_t)scratch & 255) == 0, "marching cubes: scratch must be 256-byte aligned");
+    if ((size_t)scratch_bytes < L->total) {
+        hv::set_error("marching cubes: scratch of %lld bytes, need %lld", (long long)scratch_bytes, (long long)L->total);
+        return HV_E_CAPACITY;
+    }
+    char* s = static_cast<char*>(scratch);
+    g->tsdf = tsdf;
+    g->halo_lo = halo_lo;
+    g->halo_hi = halo_hi;
+    g->color = g->chalo_lo = g->chalo_hi = nullptr;
+    g->X = (int)h_dims[0];
+    g->Y = (int)h_dims[1];
+    g->Z = (int)h_dims[2];
+    g->pitch = (int)pitch;
+    g->hl = halo_lo ? 1 : 0;
+    g->Zb = L->Zb;
+    g->G = L->G;
+    g->own_lo = g->hl;
+    g->own_hi = g->hl + g->Z;
+    g->zoff = -(long long)g->hl;
+    g->Zg = g->Z;
+    g->level = level;
+    g->bits = reinterpret_cast<unsigned int*>(s + L->off_bits);
+    g->gmask = reinterpret_cast<uint4*>(s + L->off_gmask);
+    g->gcount = reinterpret_cast<uint2*>(s + L->off_gcount);
+    g->goff = reinterpret_cast<uint2*>(s + L->off_goff);
+    g->bsum = reinterpret_cast<uint2*>(s + L->off_bsum);
+    g->totals = nullptr;
+    g->n_groups = L->n_groups;
+    return HV_OK;
+}
+
+}  // namespace
+
+extern "C" int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, int64_t* h_bytes) {
+    McLayout L;
+    int rc = mc_layout(h_dims, has_halo_lo != 0, has_halo_hi != 0, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(h_bytes, "hv_mc_scratch_bytes: null output");
+    *h_bytes = (int64_t)L.total;
+    return HV_OK;
+}
+
+extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims,
+                           int64_t pitch, double level, void* scratch, int64_t scratch_bytes,
+                           unsigned long long* totals, void* stream) {
+    hv::McGrid g;
+    McLayout L;
+    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(totals, "hv_mc_count: null totals");
+    g.totals = totals;
+    cudaStream_t st = hv::as_stream(stream);
+    const unsigned long long init[4] = {0ull, 0ull, 0x7fffffffull, 0x80000000ull};
+    HV_CUDA(cudaMemcpyAsync(totals, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    const int sms = hv::device_info().sm_count;
+    const long long want = (g.n_groups + 7) / 8;  // 8 warps per block, one group per warp per iteration
+    const int sign_blocks = (int)(want < (long long)sms * 8 ? (want > 0 ? want : 1) : (long long)sms * 8);
+    hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g);
+    const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
+    hv::mc_count_kernel<<<group_blocks, 256, 0, st>>>(g);
+    hv::mc_scan_reduce_kernel<<<L.n_scan_blocks, hv::kScanThreads, 0, st>>>(g);
+    hv::mc_scan_top_kernel<<<1, hv::kScanThreads, 0, st>>>(g, L.n_scan_blocks);
+    hv::mc_scan_apply_kernel<<<L.n_scan_blocks, hv::kScanThreads, 0, st>>>(g);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                          const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                          double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
+                          float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
+                          float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces,
+                          unsigned long long* face_keys, unsigned long long* vert_keys, void* stream) {
+    hv::McGrid g;
+    McLayout L;
+    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(color && h_origin && vert_keys && verts_world && normals && colors, "hv_mc_emit: null pointer");
+    HV_REQUIRE((faces != nullptr) != (face_keys != nullptr), "hv_mc_emit: pass exactly one of faces / face_keys");
+    HV_REQUIRE((halo_lo != nullptr) == (color_halo_lo != nullptr) && (halo_hi != nullptr) == (color_halo_hi != nullptr),
+               "hv_mc_emit: tsdf and colour halos must come in pairs");
+    HV_REQUIRE(faces == nullptr || (!halo_lo && !halo_hi), "hv_mc_emit: a shard with halos must emit face_keys");
+    HV_REQUIRE(n_verts >= 0 && n_tris >= 0 && n_verts < (1ll << 31) && n_tris < (1ll << 31), "hv_mc_emit: bad counts");
+    HV_REQUIRE(z_global_dim >= z_global_offset + g.Z, "hv_mc_emit: slab exceeds the global z extent");
+    g.color = color;
+    g.chalo_lo = color_halo_lo;
+    g.chalo_hi = color_halo_hi;
+    g.zoff = z_global_offset - g.hl;
+    g.Zg = z_global_dim;
+    cudaStream_t st = hv::as_stream(stream);
+    hv::McEmit em{faces, face_keys, vert_keys};
+    const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
+    hv::mc_emit_kernel<<<group_blocks, 256, 0, st>>>(g, em);
+    if (n_verts > 0) {
+        hv::McVerts mv;
+        mv.vert_keys = vert_keys;
+        mv.n_verts = n_verts;
+        mv.verts_world = verts_world;
+        mv.verts_voxel = verts_voxel;
+        mv.normals = normals;
+        mv.colors = colors;
+        mv.voxel_size = voxel_size;
+        for (int k = 0; k < 3; ++k) mv.origin[k] = h_origin[k];
+        hv::mc_vertex_kernel<<<(unsigned int)((n_verts + 127) / 128), 128, 0, st>>>(g, mv);
+    }
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}

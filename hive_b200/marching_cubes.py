@@ -1,0 +1,170 @@
+"""Marching-cubes mesh extraction on the GPU: host side of ``hv_mc_count`` / ``hv_mc_emit``.
+
+Replaces ``skimage.measure.marching_cubes(tsdf_vol, level=0)`` plus the post-processing of
+``TSDFVolume.get_mesh`` (third_party/tsdf_fusion_python/fusion.py:332-350).  ``marching_cubes`` mirrors the skimage
+signature HIVE relies on (volume, level -> verts, faces, normals, values; ``ValueError`` when the level is outside the
+data range -- ``scripts/experiments.py:167`` catches exactly that -- and ``RuntimeError`` when no surface is found).
+There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _key_to_float(key: int) -> float:
+    """Inverse of the order-preserving int32 key the kernels use for the min/max reduction."""
+    key = int(key) & 0xFFFFFFFF
+    if key >= 0x80000000:
+        key -= 1 << 32
+    bits = key if key >= 0 else key ^ 0x7FFFFFFF
+    return float(np.array([bits & 0xFFFFFFFF], dtype=np.uint32).view(np.float32)[0])
+
+
+@dataclass
+class DeviceMesh:
+    """A mesh resident in HBM (torch tensors)."""
+    verts: object  # (V, 3) float32 world coordinates
+    verts_voxel: object  # (V, 3) float32 voxel units (what skimage returns), or None
+    normals: object  # (V, 3) float32
+    colors: object  # (V, 3) uint8 r, g, b
+    faces: object  # (T, 3) int32 indices, or None when face_keys is used
+    face_keys: object  # (T, 3) int64 global vertex keys, or None
+    vert_keys: object  # (V,) int64 global vertex keys, ascending
+    vmin: float
+    vmax: float
+
+    def to_host(self):
+        return (self.verts.cpu().numpy(), self.faces.cpu().numpy(), self.normals.cpu().numpy(),
+                self.colors.cpu().numpy())
+
+
+class McPlan:
+    """Scratch + launch state of one extraction over planes ``[X][Y][pitch]`` (optionally a z-slab with halo planes)."""
+
+    def __init__(self, tsdf, color, dims, pitch, halo=None, z_global_offset=0, z_global_dim=None, level=0.0):
+        torch = _lib.require_cuda()
+        self._torch = torch
+        self._lib = _lib.load()
+        self.tsdf, self.color = tsdf, color
+        self.dims = (ctypes.c_int64 * 3)(*[int(d) for d in dims])
+        self.pitch = int(pitch)
+        self.level = float(level)
+        self.halo = halo or {}  # keys: tsdf_lo, tsdf_hi, color_lo, color_hi -> (X, Y) float32 device tensors
+        self.z_global_offset = int(z_global_offset)
+        self.z_global_dim = int(dims[2]) if z_global_dim is None else int(z_global_dim)
+        nbytes = ctypes.c_int64(0)
+        _lib.check(self._lib.hv_mc_scratch_bytes(ctypes.cast(self.dims, ctypes.c_void_p),
+                                                 int(self.halo.get("tsdf_lo") is not None),
+                                                 int(self.halo.get("tsdf_hi") is not None), ctypes.byref(nbytes)))
+        self.scratch_bytes = int(nbytes.value)
+        self.device = tsdf.device
+        with torch.cuda.device(self.device):
+            self.scratch = torch.empty(self.scratch_bytes + 256, dtype=torch.uint8, device=self.device)
+            pad = (-self.scratch.data_ptr()) % 256
+            self.scratch_ptr = ctypes.c_void_p(self.scratch.data_ptr() + pad)
+            self.totals = torch.zeros(4, dtype=torch.int64, device=self.device)
+
+    def count(self):
+        """Launch the classification; returns the device tensor of totals (no sync)."""
+        torch = self._torch
+        with torch.cuda.device(self.device):
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_count(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                _ptr(self.totals), stream))
+        return self.totals
+
+    def read_totals(self):
+        n_verts, n_tris, kmin, kmax = (int(v) for v in self.totals.cpu().tolist())
+        return n_verts, n_tris, _key_to_float(kmin), _key_to_float(kmax)
+
+    def emit(self, n_verts, n_tris, voxel_size, origin, want_voxel=False, keys=False) -> DeviceMesh:
+        torch = self._torch
+        dev = self.device
+        origin = np.ascontiguousarray(origin, dtype=np.float32)
+        with torch.cuda.device(dev):
+            verts = torch.empty((n_verts, 3), dtype=torch.float32, device=dev)
+            verts_voxel = torch.empty((n_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
+            normals = torch.empty((n_verts, 3), dtype=torch.float32, device=dev)
+            colors = torch.empty((n_verts, 3), dtype=torch.uint8, device=dev)
+            vert_keys = torch.empty((max(n_verts, 1),), dtype=torch.int64, device=dev)
+            faces = None if keys else torch.empty((n_tris, 3), dtype=torch.int32, device=dev)
+            face_keys = torch.empty((n_tris, 3), dtype=torch.int64, device=dev) if keys else None
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_emit(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
+                _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
+                origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
+                _ptr(colors), _ptr(faces), _ptr(face_keys), _ptr(vert_keys), stream))
+        return DeviceMesh(verts, verts_voxel, normals, colors, faces, face_keys, vert_keys[:n_verts], 0.0, 0.0)
+
+
+def check_surface(level, vmin, vmax, n_verts):
+    """The two errors of skimage.measure.marching_cubes that HIVE can observe."""
+    if level < vmin or level > vmax:
+        raise ValueError("Surface level must be within volume data range.")
+    if n_verts == 0:
+        raise RuntimeError("No surface found at the given iso value.")
+
+
+def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
+    """Mesh of a (single-GPU, whole) ``TSDFVolume`` as device tensors."""
+    X, Y, Z = (int(d) for d in vol._local_dim)
+    assert min(X, Y, Z) >= 2, "Input array must be at least 2x2x2."
+    plan = McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, (X, Y, Z), vol._pitch, level=level)
+    plan.count()
+    n_verts, n_tris, vmin, vmax = plan.read_totals()
+    check_surface(level, vmin, vmax, n_verts)
+    mesh = plan.emit(n_verts, n_tris, vol._voxel_size, vol._vol_origin, want_voxel=want_voxel)
+    mesh.vmin, mesh.vmax = vmin, vmax
+    return mesh
+
+
+def extract_mesh(vol):
+    """``TSDFVolume.get_mesh`` (fusion.py:332-350): verts (V,3) f32 world, faces (F,3) i32, norms (V,3) f32,
+    colors (V,3) u8."""
+    return extract_device_mesh(vol).to_host()
+
+
+def marching_cubes(volume, level=None, *, spacing=(1., 1., 1.), gradient_direction='descent', step_size=1,
+                   allow_degenerate=True, method='lewiner', mask=None):
+    """GPU drop-in for the ``skimage.measure.marching_cubes`` call of fusion.py:338 on a host array.
+
+    Only the argument values the reference uses are supported (defaults, ``level`` given); returns
+    ``(verts, faces, normals, values)`` with verts in voxel units, axis order (axis0, axis1, axis2).
+    """
+    torch = _lib.require_cuda()
+    if (tuple(spacing) != (1., 1., 1.) or gradient_direction != 'descent' or step_size != 1 or not allow_degenerate
+            or mask is not None or method not in ('lewiner', '_lorensen', 'lorensen')):
+        raise NotImplementedError("hive_b200.marching_cubes supports the reference's call only (fusion.py:338)")
+    volume = np.asarray(volume)
+    if volume.ndim != 3:
+        raise ValueError("Input volume should be a 3D numpy array.")
+    if min(volume.shape) < 2:
+        raise ValueError("Input array must be at least 2x2x2.")
+    vol32 = np.ascontiguousarray(volume, dtype=np.float32)
+    if level is None:
+        level = 0.5 * (float(vol32.min()) + float(vol32.max()))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    tsdf = torch.from_numpy(vol32).to(dev)
+    color = torch.zeros_like(tsdf)
+    X, Y, Z = vol32.shape
+    plan = McPlan(tsdf, color, (X, Y, Z), Z, level=float(level))
+    plan.count()
+    n_verts, n_tris, vmin, vmax = plan.read_totals()
+    check_surface(float(level), vmin, vmax, n_verts)
+    mesh = plan.emit(n_verts, n_tris, 1.0, np.zeros(3, np.float32), want_voxel=True)
+    values = np.full(n_verts, np.float32(level))
+    return mesh.verts_voxel.cpu().numpy(), mesh.faces.cpu().numpy(), mesh.normals.cpu().numpy(), values

@@ -77,6 +77,40 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
                  const void* texels, int H, int W, double trunc, double obs_weight, int flags,
                  unsigned long long* updated, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Marching cubes.  Replaces `measure.marching_cubes(tsdf_vol, level=0)` inside TSDFVolume.get_mesh /
+ * get_point_cloud (fusion.py:317,338 -- scikit-image's Lewiner implementation, a third-party dependency) and the
+ * in-tree post-processing fusion.py:339-348 (nearest-voxel colour gather, b/g/r unpack, voxel -> world transform).
+ *
+ * Two calls with a host read of two counters in between (the output size is data dependent):
+ *   hv_mc_count  classifies the volume into `scratch` and writes totals[0] = #vertices, totals[1] = #triangles,
+ *                totals[2] / totals[3] = min / max of the volume as order-preserving int32 keys of the floats
+ *                (key = bits >= 0 ? bits : bits ^ 0x7fffffff) for skimage's "level within data range" check
+ *                (ValueError, relied on by scripts/experiments.py:167).
+ *   hv_mc_emit   writes the mesh.  Vertices are sorted by (owner voxel in C scan order, edge axis); triangles by cube
+ *                scan order; right-hand normals of the faces point towards increasing values (what skimage returns
+ *                for its default gradient_direction='descent').
+ *
+ * tsdf / color : float32 planes [X][Y][pitch] (z fastest), h_dims = {X, Y, Z}.
+ * halo_lo / halo_hi (and the colour pair): optional [X][Y] planes just below z = 0 / above z = Z-1 of a z-slab
+ *                shard (NULL for a whole volume).  A shard owns the cubes whose base voxel lies in its slab.
+ * scratch      : device buffer of hv_mc_scratch_bytes() bytes, 256-byte aligned; must be kept between the two calls.
+ * z_global_offset / z_global_dim : position of the slab in the global volume (0 / Z for a whole volume); vertex keys
+ *                are ((x*Y + y)*z_global_dim + z_global)*4 + axis, axis 3 = the extra vertex inside a cube.
+ * faces / face_keys : exactly one is non-NULL: int32 [T][3] indices into this call's vertices (whole volume only), or
+ *                uint64 [T][3] global vertex keys (shards: seam vertices belong to the neighbouring shard).
+ * verts_voxel  : optional [V][3] positions in voxel units (what skimage itself returns); NULL to skip.
+ * ---------------------------------------------------------------------------------------------------------- */
+int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, int64_t* h_bytes);
+int hv_mc_count(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims, int64_t pitch,
+                double level, void* scratch, int64_t scratch_bytes, unsigned long long* totals, void* stream);
+int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+               const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+               double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
+               float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
+               float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
+               unsigned long long* vert_keys, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,3 +76,45 @@ class COracleTSDFVolume:
 
     def get_volume(self):
         return self._tsdf_vol_cpu, self._color_vol_cpu
+
+
+def marching_cubes(volume, level=0.0, with_keys=False):
+    """``skimage.measure.marching_cubes(volume, level)`` as restated by mc_oracle.c (fusion.py:338; PARITY UNPINNED,
+    see the header of that file).  Returns (verts f32 (V,3) in voxel units, faces i32 (F,3), normals f32 (V,3),
+    values f32 (V,)) like skimage; ``with_keys`` appends the canonical edge key of every vertex."""
+    vol = np.ascontiguousarray(volume, dtype=np.float32)
+    if vol.ndim != 3:
+        raise ValueError("Input volume should be a 3D numpy array.")
+    if min(vol.shape) < 2:
+        raise ValueError("Input array must be at least 2x2x2.")
+    L = lib()
+    L.hvo_marching_cubes.restype = ctypes.c_int
+    L.hvo_mesh_nv.restype = ctypes.c_int64
+    L.hvo_mesh_nf.restype = ctypes.c_int64
+    handle = ctypes.c_void_p()
+    rc = L.hvo_marching_cubes(_p(vol), ctypes.c_int64(vol.shape[0]), ctypes.c_int64(vol.shape[1]),
+                              ctypes.c_int64(vol.shape[2]), ctypes.c_double(float(level)), ctypes.byref(handle))
+    if rc == -1:
+        raise ValueError("Surface level must be within volume data range.")
+    if rc != 0:
+        raise MemoryError(f"hvo_marching_cubes failed ({rc})")
+    try:
+        nv, nf = int(L.hvo_mesh_nv(handle)), int(L.hvo_mesh_nf(handle))
+        if nv == 0:
+            raise RuntimeError("No surface found at the given iso value.")
+        verts = np.empty((nv, 3), np.float32)
+        normals = np.empty((nv, 3), np.float32)
+        keys = np.empty(nv, np.int64)
+        faces = np.empty((nf, 3), np.int32)
+        L.hvo_mesh_copy(handle, _p(verts), _p(normals), _p(keys), _p(faces))
+    finally:
+        L.hvo_mc_free(handle)
+    values = np.full(nv, np.float32(level))
+    return (verts, faces, normals, values, keys) if with_keys else (verts, faces, normals, values)
+
+
+def get_mesh(tsdf_vol, color_vol, voxel_size, vol_origin):
+    """TSDFVolume.get_mesh (fusion.py:332-350): marching cubes at level 0, then the in-tree post-processing."""
+    verts, faces, norms, _ = marching_cubes(tsdf_vol, 0.0)
+    verts_w, colors = fo.mesh_postprocess(verts, color_vol, voxel_size, vol_origin)
+    return verts_w, faces, norms, colors

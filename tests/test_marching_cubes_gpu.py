@@ -1,0 +1,119 @@
+"""GPU parity of marching cubes / get_mesh against the oracle (oracle/mc_oracle.c, restating fusion.py:338-348).
+
+Gates (BASELINE.json north_star): triangle topology and counts bit-exact, vertex positions within 1e-4 voxel units
+(they are in fact bit-equal), colours bit-exact.  The product numbers vertices by (owner voxel, axis) while the serial
+oracle numbers them in first-touch order, so meshes are compared after renumbering both through the canonical edge key.
+"""
+import numpy as np
+import pytest
+
+from hive_b200.synthetic import Scene
+
+pytestmark = pytest.mark.gpu
+
+
+def _canon(verts, faces, normals, keys):
+    order = np.argsort(keys, kind="stable")
+    rank = np.empty_like(order)
+    rank[order] = np.arange(len(order))
+    return verts[order], rank[faces].astype(np.int32), normals[order], keys[order]
+
+
+def _compare(volume, level, c_oracle):
+    from hive_b200 import marching_cubes as mc
+    ov, of, on, _, ok = c_oracle.marching_cubes(volume, level, with_keys=True)
+    ov, of, on, ok = _canon(ov, of, on, ok)
+    gv, gf, gn, gvals = mc.marching_cubes(volume, level)
+    assert gv.dtype == np.float32 and gf.dtype == np.int32 and gn.dtype == np.float32
+    assert gv.shape == ov.shape, "vertex count differs"
+    assert gf.shape == of.shape, "triangle count differs"
+    assert np.array_equal(gf, of), "triangle topology differs"
+    assert np.abs(gv - ov).max() <= 1e-4
+    assert np.array_equal(gv, ov)  # same float64 interpolation, same float32 rounding
+    assert np.abs(gn - on).max() <= 1e-6
+    assert (gvals == np.float32(level)).all()
+    return gv, gf
+
+
+def _sphere(n, centre, radius):
+    g = np.mgrid[0:n[0], 0:n[1], 0:n[2]].astype(np.float32)
+    c = np.asarray(centre, np.float32)[:, None, None, None]
+    return (np.sqrt(((g - c) ** 2).sum(0)) - np.float32(radius)).astype(np.float32)
+
+
+def test_sphere_matches_oracle_and_is_closed(c_oracle):
+    vol = _sphere((48, 40, 70), (23.3, 19.6, 34.2), 15.1)
+    v, f = _compare(vol, 0.0, c_oracle)
+    e = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]]).astype(np.int64)
+    fwd, rev = e[:, 0] * len(v) + e[:, 1], e[:, 1] * len(v) + e[:, 0]
+    assert len(np.unique(fwd)) == len(fwd) and np.array_equal(np.sort(fwd), np.sort(rev))  # closed 2-manifold
+    assert len(v) - len(e) // 2 + len(f) == 2  # Euler characteristic of a sphere
+    p = v[f]
+    outward = np.einsum("ij,ij->i", np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]), p.mean(1) - [23.3, 19.6, 34.2])
+    assert (outward > 0).all()  # right-hand normals towards increasing values
+
+
+@pytest.mark.parametrize("shape", [(24, 20, 28), (9, 33, 65), (5, 4, 2), (2, 2, 2), (3, 3, 97)])
+def test_noise_volume_exercises_every_ambiguous_case(shape, c_oracle):
+    rng = np.random.default_rng(sum(shape))
+    _compare(rng.standard_normal(shape).astype(np.float32), 0.0, c_oracle)
+
+
+def test_nonzero_level_and_exact_zeros(c_oracle):
+    rng = np.random.default_rng(3)
+    vol = rng.integers(-3, 4, size=(17, 19, 40)).astype(np.float32)  # many voxels exactly on the level
+    _compare(vol, 0.0, c_oracle)
+    _compare(vol, 0.5, c_oracle)
+    _compare(rng.random((20, 20, 20)).astype(np.float32), 0.37, c_oracle)
+
+
+def test_errors_match_skimage_contract(c_oracle):
+    from hive_b200 import marching_cubes as mc
+    ones = np.ones((8, 8, 8), np.float32)
+    with pytest.raises(ValueError):  # level below the data range: what an untouched TSDF volume gives (experiments.py:167)
+        mc.marching_cubes(ones, 0.0)
+    with pytest.raises(ValueError):
+        c_oracle.marching_cubes(ones, 0.0)
+    with pytest.raises(RuntimeError):  # level inside the range but no voxel strictly above it
+        mc.marching_cubes(np.zeros((8, 8, 8), np.float32), 0.0)
+    with pytest.raises(RuntimeError):
+        c_oracle.marching_cubes(np.zeros((8, 8, 8), np.float32), 0.0)
+    with pytest.raises(ValueError):
+        mc.marching_cubes(np.zeros((8, 8), np.float32), 0.0)
+
+
+@pytest.mark.parametrize("config,variant,frames", [("tiny", "room", 6), ("small", "room", 8), ("small", "dense", 3)])
+def test_get_mesh_matches_oracle(config, variant, frames, c_oracle):
+    from hive_b200.fusion import TSDFVolume
+    scene = Scene(config, variant)
+    gpu = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    orc = c_oracle.COracleTSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    for i in range(frames):
+        fr = scene.frame(i)
+        gpu.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+        orc.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+    tsdf, color = gpu.get_volume()
+    assert np.array_equal(color, orc._color_vol_cpu)
+    # oracle mesh of the GPU's own planes (isolates marching cubes from the 1e-5 TSDF tolerance)
+    ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
+    ov, of, on, ok = _canon(ov, of, on, ok)
+    from oracle import fusion_oracle as fo
+    ow, oc = fo.mesh_postprocess(ov, color, gpu._voxel_size, gpu._vol_origin)
+    verts, faces, norms, colors = gpu.get_mesh()
+    assert verts.dtype == np.float32 and faces.dtype == np.int32 and norms.dtype == np.float32 and colors.dtype == np.uint8
+    assert verts.shape == ow.shape and len(verts) > 100
+    assert np.array_equal(faces, of)
+    assert np.array_equal(verts, ow)
+    assert np.array_equal(colors, oc)
+    assert np.abs(norms - on).max() <= 1e-6
+    # the object stays usable after get_mesh (the reference pops its CUDA context, fusion.py:349)
+    pc = gpu.get_point_cloud()
+    assert pc.shape == (len(verts), 6) and np.array_equal(pc[:, :3], verts)
+
+
+def test_get_mesh_on_untouched_volume_raises_value_error():
+    from hive_b200.fusion import TSDFVolume
+    scene = Scene("tiny", "room")
+    vol = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    with pytest.raises(ValueError):
+        vol.get_mesh()
