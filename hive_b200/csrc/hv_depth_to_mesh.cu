@@ -1,0 +1,497 @@
+// Per-frame depth-to-mesh for sm_100a (B200): back-projection + lattice triangulation + face filter, batched over frames.
+//
+// Replaces, for HIVE's dynamic foreground meshes (hive/pipeline.py:386-409):
+//   point_cloud_from_depth / image2world        hive/geometric.py:107-126,183-206
+//   Pipeline._triangulate_faces                 hive/pipeline.py:651-667   (scipy.spatial.Delaunay on pixel coordinates)
+//   Pipeline._filter_faces                      hive/pipeline.py:670-694   (edge <= max_pixel_distance px, |d depth| <= max)
+//
+// The Delaunay triangulation of a subset of the integer lattice, after the 2-pixel edge filter, has a closed form
+// (validated there against scipy): only two triangle shapes survive --
+//   * unit right triangles: a 2x2 quad with 4 valid corners gives two (split along one diagonal), with exactly 3 valid
+//     corners gives one;
+//   * "bridge" triangles (sqrt2, sqrt2, 2) around an ABSENT pixel whose 4-neighbours N, E, S, W are present: 3 present
+//     give one, 4 present give two.
+// Co-circular points make Qhull's choice of diagonal arbitrary; here it is a rule (the diagonal with the smaller depth
+// difference, ties -> main / horizontal) or, for parity tests, a caller-provided per-pixel bitmap.
+//
+// One thread per pixel; vertex ids are row-major ranks of the valid pixels (np.nonzero order, geometric.py:121),
+// obtained from per-32-pixel valid-bit words + a prefix over the words, so no per-pixel id map is materialised.
+// Faces are compacted with warp scans in pixel order: the output is deterministic.
+#include "hv_common.cuh"
+
+namespace hv {
+
+struct D2mGrid {
+    const float* depth;    // [B][H][W]
+    const uint8_t* mask;   // [B][H][W] or null (all true)
+    const uint8_t* diag;   // [B][H][W] or null; bit 0: quad owned by the pixel uses the anti-diagonal, bit 1: hole at the
+                           // pixel is split N-S
+    int B, H, W;
+    int words_per_frame;   // ceil(H*W / 32)
+    long long n_words;
+    float max_depth_distance;
+    int bridges;
+    int verts_only;        // skip triangulation (point_cloud_from_depth)
+    unsigned int* wbits;   // [n_words] valid bits
+    uint2* wcount;         // [n_words] (vertices, faces)
+    uint2* woff;           // [n_words] exclusive prefix
+    uint2* bsum;
+};
+
+struct PixelFaces {
+    int n;
+    int2 p[4][3];  // pixel coordinates (u, v) of the corners, winding with negative signed area in (u, v)
+};
+
+__device__ __forceinline__ bool d2m_valid(const D2mGrid& g, int b, int u, int v, float& d) {
+    d = 0.0f;
+    if (u < 0 || v < 0 || u >= g.W || v >= g.H) return false;
+    const size_t i = ((size_t)b * g.H + v) * g.W + u;
+    if (g.mask && !g.mask[i]) return false;
+    d = __ldg(g.depth + i);
+    return d > 0.0f;
+}
+
+__device__ __forceinline__ bool depth_ok(const D2mGrid& g, float a, float b, float c) {
+    // pipeline.py:686-690: all three edges, float32 differences against the float32 threshold
+    return fabsf(__fsub_rn(a, b)) <= g.max_depth_distance && fabsf(__fsub_rn(c, b)) <= g.max_depth_distance &&
+           fabsf(__fsub_rn(a, c)) <= g.max_depth_distance;
+}
+
+__device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, bool keep_coords, int2 a, float da, int2 b,
+                                          float db, int2 c, float dc) {
+    if (!depth_ok(g, da, db, dc)) return;
+    if (keep_coords) {
+        f.p[f.n][0] = a;
+        f.p[f.n][1] = b;
+        f.p[f.n][2] = c;
+    }
+    ++f.n;
+}
+
+// Faces owned by pixel (u, v): the quad whose top-left corner it is, and -- if the pixel itself is absent -- the hole
+// around it.
+__device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int v, bool self_valid, float d_self,
+                                            bool keep_coords, PixelFaces& f) {
+    f.n = 0;
+    const unsigned int ov = g.diag ? g.diag[((size_t)b * g.H + v) * g.W + u] : 0u;
+    float db, dc, dd;
+    const bool vb = d2m_valid(g, b, u + 1, v, db), vc = d2m_valid(g, b, u, v + 1, dc), vd = d2m_valid(g, b, u + 1, v + 1, dd);
+    const int2 A = make_int2(u, v), Bp = make_int2(u + 1, v), C = make_int2(u, v + 1), D = make_int2(u + 1, v + 1);
+    const int nq = (int)self_valid + (int)vb + (int)vc + (int)vd;
+    if (nq == 4) {
+        const bool anti = g.diag ? (ov & 1u) : !(fabsf(__fsub_rn(d_self, dd)) <= fabsf(__fsub_rn(db, dc)));
+        if (!anti) {
+            push_face(g, f, keep_coords, A, d_self, D, dd, Bp, db);
+            push_face(g, f, keep_coords, A, d_self, C, dc, D, dd);
+        } else {
+            push_face(g, f, keep_coords, A, d_self, C, dc, Bp, db);
+            push_face(g, f, keep_coords, Bp, db, C, dc, D, dd);
+        }
+    } else if (nq == 3) {
+        if (!vd) push_face(g, f, keep_coords, A, d_self, C, dc, Bp, db);
+        else if (!self_valid) push_face(g, f, keep_coords, Bp, db, C, dc, D, dd);
+        else if (!vb) push_face(g, f, keep_coords, A, d_self, C, dc, D, dd);
+        else push_face(g, f, keep_coords, A, d_self, D, dd, Bp, db);
+    }
+    if (!self_valid && g.bridges) {
+        float dn, de, ds, dw;
+        const bool vn = d2m_valid(g, b, u, v - 1, dn), ve = d2m_valid(g, b, u + 1, v, de), vs = d2m_valid(g, b, u, v + 1, ds),
+                   vw = d2m_valid(g, b, u - 1, v, dw);
+        const int2 N = make_int2(u, v - 1), E = make_int2(u + 1, v), S = make_int2(u, v + 1), Wp = make_int2(u - 1, v);
+        const int nh = (int)vn + (int)ve + (int)vs + (int)vw;
+        if (nh == 4) {
+            const bool vertical = g.diag ? ((ov >> 1) & 1u) : !(fabsf(__fsub_rn(dw, de)) <= fabsf(__fsub_rn(dn, ds)));
+            if (!vertical) {
+                push_face(g, f, keep_coords, Wp, dw, E, de, N, dn);
+                push_face(g, f, keep_coords, Wp, dw, S, ds, E, de);
+            } else {
+                push_face(g, f, keep_coords, N, dn, S, ds, E, de);
+                push_face(g, f, keep_coords, N, dn, Wp, dw, S, ds);
+            }
+        } else if (nh == 3) {
+            if (!vn) push_face(g, f, keep_coords, Wp, dw, S, ds, E, de);
+            else if (!vs) push_face(g, f, keep_coords, Wp, dw, E, de, N, dn);
+            else if (!ve) push_face(g, f, keep_coords, N, dn, Wp, dw, S, ds);
+            else push_face(g, f, keep_coords, N, dn, S, ds, E, de);
+        }
+    }
+}
+
+// one warp per 32-pixel word
+__global__ void __launch_bounds__(256) d2m_count_kernel(const D2mGrid g) {
+    const int lane = threadIdx.x & 31;
+    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= g.n_words) return;
+    const int b = (int)(w / g.words_per_frame);
+    const int i = (int)(w - (long long)b * g.words_per_frame) * 32 + lane;
+    bool valid = false;
+    unsigned int nf = 0;
+    if (i < g.H * g.W) {
+        const int v = i / g.W, u = i - v * g.W;
+        float d;
+        valid = d2m_valid(g, b, u, v, d);
+        if (!g.verts_only) {
+            PixelFaces f;
+            pixel_faces(g, b, u, v, valid, d, false, f);
+            nf = (unsigned int)f.n;
+        }
+    }
+    const unsigned int bits = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nf += __shfl_xor_sync(0xffffffffu, nf, o);
+    if (lane == 0) {
+        g.wbits[w] = bits;
+        g.wcount[w] = make_uint2(__popc(bits), nf);
+    }
+}
+
+struct D2mOut {
+    const double* cams;  // [B][12]: R row-major (9), t (3) -- world-to-camera, as hive/geometric.py passes them
+    double Kinv[9];
+    double* verts;        // [V][3]
+    int32_t* faces;       // [F][3] frame-local vertex ids
+    int32_t* points2d;    // [V][2] (u, v) or null
+    float* vdepth;        // [V] or null
+    long long* frame_off; // [B+1][2] (vertex, face) start of every frame in the concatenated outputs
+    unsigned long long n_verts, n_faces;
+};
+
+__device__ __forceinline__ int d2m_rank(const D2mGrid& g, int b, int2 p, unsigned int vbase) {
+    const int i = p.y * g.W + p.x;
+    const size_t w = (size_t)b * g.words_per_frame + (i >> 5);
+    return (int)(g.woff[w].x + __popc(g.wbits[w] & ((1u << (i & 31)) - 1u)) - vbase);
+}
+
+__global__ void __launch_bounds__(256) d2m_emit_kernel(const D2mGrid g, const D2mOut out) {
+    const int lane = threadIdx.x & 31;
+    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= g.n_words) return;
+    const int b = (int)(w / g.words_per_frame);
+    const int wf = (int)(w - (long long)b * g.words_per_frame);
+    const uint2 cnt = g.wcount[w];
+    const uint2 off = g.woff[w];
+    const unsigned int vbase = g.woff[(size_t)b * g.words_per_frame].x;
+    if (wf == 0 && lane == 0) {
+        out.frame_off[2 * b] = off.x;
+        out.frame_off[2 * b + 1] = off.y;
+        if (b == g.B - 1) {
+            out.frame_off[2 * g.B] = (long long)out.n_verts;
+            out.frame_off[2 * g.B + 1] = (long long)out.n_faces;
+        }
+    }
+    if (cnt.x == 0 && cnt.y == 0) return;
+    const int i = wf * 32 + lane;
+    const bool in = i < g.H * g.W;
+    const int v = in ? i / g.W : 0, u = in ? i - v * g.W : 0;
+    float d = 0.0f;
+    const bool valid = in && d2m_valid(g, b, u, v, d);
+    PixelFaces f;
+    f.n = 0;
+    if (in && cnt.y) pixel_faces(g, b, u, v, valid, d, true, f);
+
+    if (valid) {  // image2world, hive/geometric.py:200-204 (float64)
+        const size_t vi = off.x + __popc(g.wbits[w] & ((1u << lane) - 1u));
+        const double* R = out.cams + 12 * (size_t)b;
+        const double* t = R + 9;
+        const double du = (double)u, dv = (double)v, dd = (double)d;
+        double X[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double pc = fma(out.Kinv[3 * k + 2], 1.0, fma(out.Kinv[3 * k + 1], dv, __dmul_rn(out.Kinv[3 * k], du)));
+            X[k] = __dsub_rn(__dmul_rn(dd, pc), t[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k)  // R^T @ X
+            out.verts[3 * vi + k] = fma(R[6 + k], X[2], fma(R[3 + k], X[1], __dmul_rn(R[k], X[0])));
+        if (out.points2d) {
+            out.points2d[2 * vi] = u;
+            out.points2d[2 * vi + 1] = v;
+        }
+        if (out.vdepth) out.vdepth[vi] = d;
+    }
+    if (cnt.y) {
+        unsigned int inc = (unsigned int)f.n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+        }
+        size_t fi = (size_t)off.y + inc - (unsigned int)f.n;
+        for (int k = 0; k < f.n; ++k, ++fi)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) out.faces[3 * fi + c] = d2m_rank(g, b, f.p[k][c], vbase);
+    }
+}
+
+// ---- elementwise projection helpers (hive/geometric.py:155-206) and the generic face filter (pipeline.py:670-694) --------
+__global__ void __launch_bounds__(256) image2world_kernel(const double* __restrict__ pts, const double* __restrict__ depth,
+                                                          long long n, const double* __restrict__ cam /* Kinv 9, R 9, t 3 */,
+                                                          double scale, double* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double u = __dmul_rn(pts[2 * i], scale), v = __dmul_rn(pts[2 * i + 1], scale), d = depth[i];
+    const double *Kinv = cam, *R = cam + 9, *t = cam + 18;
+    double X[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double pc = fma(Kinv[3 * k + 2], 1.0, fma(Kinv[3 * k + 1], v, __dmul_rn(Kinv[3 * k], u)));
+        X[k] = __dsub_rn(__dmul_rn(d, pc), t[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) out[3 * i + k] = fma(R[6 + k], X[2], fma(R[3 + k], X[1], __dmul_rn(R[k], X[0])));
+}
+
+__global__ void __launch_bounds__(256) world2image_kernel(const double* __restrict__ pts, long long n,
+                                                          const double* __restrict__ cam /* K 9, R 9, t 3 */, double scale,
+                                                          int round_half_even, double* __restrict__ uv,
+                                                          double* __restrict__ depth) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double *K = cam, *R = cam + 9, *t = cam + 18;
+    const double p0 = pts[3 * i], p1 = pts[3 * i + 1], p2 = pts[3 * i + 2];
+    double c[3], q[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        c[k] = __dadd_rn(fma(R[3 * k + 2], p2, fma(R[3 * k + 1], p1, __dmul_rn(R[3 * k], p0))), t[k]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) q[k] = fma(K[3 * k + 2], c[2], fma(K[3 * k + 1], c[1], __dmul_rn(K[3 * k], c[0])));
+    double a = (q[0] / q[2]) / scale, b = (q[1] / q[2]) / scale;
+    if (round_half_even) {
+        a = rint(a);
+        b = rint(b);
+    }
+    uv[2 * i] = a;
+    uv[2 * i + 1] = b;
+    depth[i] = q[2];
+}
+
+struct FilterArgs {
+    const int32_t* pts;   // [N][2]
+    const void* depth;    // [N] float32 or float64
+    const int32_t* faces; // [F][3]
+    long long n_faces;
+    double max_pixel_distance, max_depth_distance;
+    unsigned int* wbits;
+    uint2* wcount;
+    uint2* woff;
+    int32_t* out;
+};
+
+template <typename T>
+__device__ __forceinline__ bool face_ok(const FilterArgs& a, long long f) {
+    const int i0 = a.faces[3 * f], i1 = a.faces[3 * f + 1], i2 = a.faces[3 * f + 2];
+    const int ea[3] = {i0, i2, i0}, eb[3] = {i1, i1, i2};  // pipeline.py:686: edges (0,1), (2,1), (0,2)
+    const T* depth = static_cast<const T*>(a.depth);
+    const T max_dd = (T)a.max_depth_distance;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const long long dx = (long long)a.pts[2 * ea[k]] - a.pts[2 * eb[k]], dy = (long long)a.pts[2 * ea[k] + 1] - a.pts[2 * eb[k] + 1];
+        ok = ok && (sqrt((double)(dx * dx + dy * dy)) <= a.max_pixel_distance);
+        const T dd = depth[ea[k]] - depth[eb[k]];
+        ok = ok && ((dd < (T)0 ? -dd : dd) <= max_dd);
+    }
+    return ok;
+}
+
+template <typename T, bool kEmit>
+__global__ void __launch_bounds__(256) filter_faces_kernel(const FilterArgs a) {
+    const int lane = threadIdx.x & 31;
+    const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long w = f >> 5;
+    if (w * 32 >= a.n_faces) return;
+    const bool keep = f < a.n_faces && face_ok<T>(a, f);
+    const unsigned int bits = __ballot_sync(0xffffffffu, keep);
+    if (!kEmit) {
+        if (lane == 0) a.wcount[w] = make_uint2(__popc(bits), 0u);
+    } else if (keep) {
+        const size_t o = a.woff[w].x + __popc(bits & ((1u << lane) - 1u));
+        a.out[3 * o] = a.faces[3 * f];
+        a.out[3 * o + 1] = a.faces[3 * f + 1];
+        a.out[3 * o + 2] = a.faces[3 * f + 2];
+    }
+}
+
+}  // namespace hv
+
+// ---- C ABI ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct D2mLayout {
+    int words_per_frame;
+    long long n_words;
+    size_t off_bits, off_count, off_off, off_bsum, total;
+};
+
+size_t d2m_align(size_t v) { return (v + 255) & ~(size_t)255; }
+
+int d2m_layout(int B, int H, int W, D2mLayout* L) {
+    HV_REQUIRE(B >= 1 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30) && B < (1 << 24),
+               "depth-to-mesh: bad batch %d x %d x %d", B, H, W);
+    L->words_per_frame = (int)(((long long)H * W + 31) / 32);
+    L->n_words = (long long)B * L->words_per_frame;
+    size_t o = 0;
+    L->off_count = o;
+    o = d2m_align(o + (size_t)L->n_words * sizeof(uint2));
+    L->off_off = o;
+    o = d2m_align(o + (size_t)L->n_words * sizeof(uint2));
+    L->off_bits = o;
+    o = d2m_align(o + (size_t)L->n_words * sizeof(unsigned int));
+    L->off_bsum = o;
+    o = d2m_align(o + (size_t)hv::scan_tiles(L->n_words) * sizeof(uint2));
+    L->total = o;
+    return HV_OK;
+}
+
+int d2m_grid(hv::D2mGrid* g, const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+             float max_depth_distance, int flags, void* scratch, int64_t scratch_bytes, D2mLayout* L) {
+    int rc = d2m_layout(B, H, W, L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(depth && scratch, "depth-to-mesh: null pointer");
+    HV_REQUIRE(((uintptr_t)scratch & 255) == 0, "depth-to-mesh: scratch must be 256-byte aligned");
+    HV_REQUIRE(max_depth_distance >= 0.0f, "depth-to-mesh: max_depth_distance must be >= 0");
+    if ((size_t)scratch_bytes < L->total) {
+        hv::set_error("depth-to-mesh: scratch of %lld bytes, need %lld", (long long)scratch_bytes, (long long)L->total);
+        return HV_E_CAPACITY;
+    }
+    char* s = static_cast<char*>(scratch);
+    g->depth = depth;
+    g->mask = mask;
+    g->diag = diag;
+    g->B = B;
+    g->H = H;
+    g->W = W;
+    g->words_per_frame = L->words_per_frame;
+    g->n_words = L->n_words;
+    g->max_depth_distance = max_depth_distance;
+    g->bridges = (flags & HV_D2M_BRIDGES) ? 1 : 0;
+    g->verts_only = (flags & HV_D2M_VERTS_ONLY) ? 1 : 0;
+    g->wbits = reinterpret_cast<unsigned int*>(s + L->off_bits);
+    g->wcount = reinterpret_cast<uint2*>(s + L->off_count);
+    g->woff = reinterpret_cast<uint2*>(s + L->off_off);
+    g->bsum = reinterpret_cast<uint2*>(s + L->off_bsum);
+    return HV_OK;
+}
+
+}  // namespace
+
+extern "C" int hv_d2m_scratch_bytes(int B, int H, int W, int64_t* h_bytes) {
+    D2mLayout L;
+    int rc = d2m_layout(B, H, W, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(h_bytes, "hv_d2m_scratch_bytes: null output");
+    *h_bytes = (int64_t)L.total;
+    return HV_OK;
+}
+
+extern "C" int hv_d2m_count(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                            float max_depth_distance, int flags, void* scratch, int64_t scratch_bytes,
+                            unsigned long long* totals, void* stream) {
+    hv::D2mGrid g;
+    D2mLayout L;
+    int rc = d2m_grid(&g, depth, mask, diag, B, H, W, max_depth_distance, flags, scratch, scratch_bytes, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(totals, "hv_d2m_count: null totals");
+    cudaStream_t st = hv::as_stream(stream);
+    const unsigned int blocks = (unsigned int)((g.n_words + 7) / 8);
+    hv::d2m_count_kernel<<<blocks, 256, 0, st>>>(g);
+    hv::exclusive_scan_u2(g.wcount, g.woff, g.bsum, g.n_words, totals, st);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                           float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
+                           int64_t scratch_bytes, int64_t n_verts, int64_t n_faces, double* verts, int32_t* faces,
+                           int32_t* points2d, float* vdepth, long long* frame_offsets, void* stream) {
+    hv::D2mGrid g;
+    D2mLayout L;
+    int rc = d2m_grid(&g, depth, mask, diag, B, H, W, max_depth_distance, flags, scratch, scratch_bytes, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(h_kinv && cams && verts && frame_offsets && (faces || n_faces == 0), "hv_d2m_emit: null pointer");
+    HV_REQUIRE(n_verts >= 0 && n_faces >= 0, "hv_d2m_emit: bad counts");
+    hv::D2mOut out;
+    out.cams = cams;
+    for (int k = 0; k < 9; ++k) out.Kinv[k] = h_kinv[k];
+    out.verts = verts;
+    out.faces = faces;
+    out.points2d = points2d;
+    out.vdepth = vdepth;
+    out.frame_off = frame_offsets;
+    out.n_verts = (unsigned long long)n_verts;
+    out.n_faces = (unsigned long long)n_faces;
+    const unsigned int blocks = (unsigned int)((g.n_words + 7) / 8);
+    hv::d2m_emit_kernel<<<blocks, 256, 0, hv::as_stream(stream)>>>(g, out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_image2world(const double* points2d, const double* depth, int64_t n, const double* cam, double scale,
+                              double* out, void* stream) {
+    if (n == 0) return HV_OK;
+    HV_REQUIRE(points2d && depth && cam && out && n > 0, "hv_image2world: bad arguments");
+    hv::image2world_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, hv::as_stream(stream)>>>(points2d, depth, n, cam, scale, out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_world2image(const double* points, int64_t n, const double* cam, double scale, int round_half_even,
+                              double* uv, double* depth, void* stream) {
+    if (n == 0) return HV_OK;
+    HV_REQUIRE(points && cam && uv && depth && n > 0, "hv_world2image: bad arguments");
+    HV_REQUIRE(scale != 0.0, "hv_world2image: scale_factor must be non-zero");
+    hv::world2image_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, hv::as_stream(stream)>>>(points, n, cam, scale,
+                                                                                              round_half_even, uv, depth);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_filter_faces_scratch_bytes(int64_t n_faces, int64_t* h_bytes) {
+    HV_REQUIRE(n_faces >= 0 && h_bytes, "hv_filter_faces_scratch_bytes: bad arguments");
+    const long long words = (n_faces + 31) / 32;
+    *h_bytes = (int64_t)(d2m_align((size_t)words * 8) * 2 + d2m_align((size_t)hv::scan_tiles(words) * 8 + 8));
+    return HV_OK;
+}
+
+/* phase 0: count (totals[0] = kept faces); phase 1: write the kept faces, order preserved, to `out`. */
+extern "C" int hv_filter_faces(const int32_t* points2d, const void* depth, int depth_is_f64, const int32_t* faces,
+                               int64_t n_faces, double max_pixel_distance, double max_depth_distance, void* scratch,
+                               int64_t scratch_bytes, int phase, unsigned long long* totals, int32_t* out, void* stream) {
+    if (n_faces == 0) return HV_OK;
+    HV_REQUIRE(points2d && depth && faces && scratch && n_faces > 0, "hv_filter_faces: bad arguments");
+    int64_t need = 0;
+    hv_filter_faces_scratch_bytes(n_faces, &need);
+    if (scratch_bytes < need) {
+        hv::set_error("hv_filter_faces: scratch of %lld bytes, need %lld", (long long)scratch_bytes, (long long)need);
+        return HV_E_CAPACITY;
+    }
+    const long long words = (n_faces + 31) / 32;
+    char* s = static_cast<char*>(scratch);
+    hv::FilterArgs a;
+    a.pts = points2d;
+    a.depth = depth;
+    a.faces = faces;
+    a.n_faces = n_faces;
+    a.max_pixel_distance = max_pixel_distance;
+    a.max_depth_distance = max_depth_distance;
+    a.wbits = nullptr;
+    a.wcount = reinterpret_cast<uint2*>(s);
+    a.woff = reinterpret_cast<uint2*>(s + d2m_align((size_t)words * 8));
+    uint2* bsum = reinterpret_cast<uint2*>(s + 2 * d2m_align((size_t)words * 8));
+    a.out = out;
+    cudaStream_t st = hv::as_stream(stream);
+    const unsigned int blocks = (unsigned int)((words * 32 + 255) / 256);
+    if (phase == 0) {
+        HV_REQUIRE(totals, "hv_filter_faces: null totals");
+        if (depth_is_f64) hv::filter_faces_kernel<double, false><<<blocks, 256, 0, st>>>(a);
+        else hv::filter_faces_kernel<float, false><<<blocks, 256, 0, st>>>(a);
+        hv::exclusive_scan_u2(a.wcount, a.woff, bsum, words, totals, st);
+    } else {
+        HV_REQUIRE(out, "hv_filter_faces: null output");
+        if (depth_is_f64) hv::filter_faces_kernel<double, true><<<blocks, 256, 0, st>>>(a);
+        else hv::filter_faces_kernel<float, true><<<blocks, 256, 0, st>>>(a);
+    }
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}

@@ -48,7 +48,7 @@ struct McGrid {
     uint4* gmask;         // [X*Y*G] owner masks: axis0, axis1, axis2, centre
     uint2* gcount;        // [X*Y*G] (vertices, triangles)
     uint2* goff;          // [X*Y*G] exclusive prefix of gcount
-    uint2* bsum;          // per scan block
+    uint2* bsum;          // scratch of the scan
     unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float)
     long long n_groups;
 };
@@ -212,88 +212,6 @@ __global__ void __launch_bounds__(256) mc_count_kernel(const McGrid g) {
     }
     g.gmask[gi] = m;
     g.gcount[gi] = make_uint2(__popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w), ntri);
-}
-
-// ---- 3. exclusive scan of uint2 counts (reduce, scan the block sums, apply) ----------------------------------------------
-constexpr int kScanThreads = 256;
-constexpr int kScanItems = 8;
-constexpr int kScanTile = kScanThreads * kScanItems;
-
-__device__ __forceinline__ uint2 add2(uint2 a, uint2 b) { return make_uint2(a.x + b.x, a.y + b.y); }
-
-__device__ uint2 block_exclusive_scan(uint2 v, uint2& total) {
-    __shared__ uint2 warp_sums[kScanThreads / 32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint2 inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned int ux = __shfl_up_sync(0xffffffffu, inc.x, o), uy = __shfl_up_sync(0xffffffffu, inc.y, o);
-        if (lane >= o) inc = add2(inc, make_uint2(ux, uy));
-    }
-    if (lane == 31) warp_sums[warp] = inc;
-    __syncthreads();
-    uint2 carry = make_uint2(0, 0), tot = make_uint2(0, 0);
-    for (int w = 0; w < kScanThreads / 32; ++w) {
-        if (w < warp) carry = add2(carry, warp_sums[w]);
-        tot = add2(tot, warp_sums[w]);
-    }
-    __syncthreads();
-    total = tot;
-    return make_uint2(carry.x + inc.x - v.x, carry.y + inc.y - v.y);
-}
-
-__global__ void __launch_bounds__(kScanThreads) mc_scan_reduce_kernel(const McGrid g) {
-    const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * kScanItems;
-    uint2 s = make_uint2(0, 0);
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i)
-        if (base + i < g.n_groups) s = add2(s, g.gcount[base + i]);
-    uint2 total;
-    block_exclusive_scan(s, total);
-    if (threadIdx.x == 0) g.bsum[blockIdx.x] = total;
-}
-
-// one block: exclusive scan of the block sums in place, 64-bit totals
-__global__ void __launch_bounds__(kScanThreads) mc_scan_top_kernel(const McGrid g, int n_blocks) {
-    __shared__ unsigned long long carry_v, carry_t;
-    if (threadIdx.x == 0) carry_v = carry_t = 0ull;
-    __syncthreads();
-    for (int start = 0; start < n_blocks; start += kScanThreads) {
-        const int i = start + threadIdx.x;
-        const uint2 v = (i < n_blocks) ? g.bsum[i] : make_uint2(0, 0);
-        uint2 total;
-        const uint2 ex = block_exclusive_scan(v, total);
-        const unsigned long long cv = carry_v, ct = carry_t;
-        if (i < n_blocks) g.bsum[i] = make_uint2((unsigned int)(cv + ex.x), (unsigned int)(ct + ex.y));
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            carry_v = cv + total.x;
-            carry_t = ct + total.y;
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        g.totals[0] = carry_v;
-        g.totals[1] = carry_t;
-    }
-}
-
-__global__ void __launch_bounds__(kScanThreads) mc_scan_apply_kernel(const McGrid g) {
-    const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * kScanItems;
-    uint2 item[kScanItems];
-    uint2 s = make_uint2(0, 0);
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        item[i] = (base + i < g.n_groups) ? g.gcount[base + i] : make_uint2(0, 0);
-        s = add2(s, item[i]);
-    }
-    uint2 total;
-    uint2 run = add2(block_exclusive_scan(s, total), g.bsum[blockIdx.x]);
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        if (base + i < g.n_groups) g.goff[base + i] = run;
-        run = add2(run, item[i]);
-    }
 }
 
 // ---- 4. emit triangles and vertex keys ------------------------------------------------------------------------------
@@ -592,9 +510,7 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g);
     const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
     hv::mc_count_kernel<<<group_blocks, 256, 0, st>>>(g);
-    hv::mc_scan_reduce_kernel<<<L.n_scan_blocks, hv::kScanThreads, 0, st>>>(g);
-    hv::mc_scan_top_kernel<<<1, hv::kScanThreads, 0, st>>>(g, L.n_scan_blocks);
-    hv::mc_scan_apply_kernel<<<L.n_scan_blocks, hv::kScanThreads, 0, st>>>(g);
+    hv::exclusive_scan_u2(g.gcount, g.goff, g.bsum, g.n_groups, totals, st);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

@@ -1,0 +1,191 @@
+"""GPU drop-ins for the back-projection functions of ``hive/geometric.py`` (lines 66-78, 107-206).
+
+Same names, arguments, return shapes/dtypes and assertion behaviour as the reference; host numpy in, host numpy out,
+the arithmetic (float64, like the reference) runs in hand-written sm_100a kernels behind the C ABI.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _lib
+
+__all__ = ["get_pose_components", "point_cloud_from_depth", "point_cloud_from_rgbd", "world2image", "image2world",
+           "depth_to_mesh_batch", "DepthMeshBatch"]
+
+_EYE = np.eye(3)
+_ZERO_T = np.zeros((3, 1))
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def validate_shape(x, x_name, expected_shape):
+    """hive/utils.py:38-63 (None = any size)."""
+    assert len(x.shape) == len(expected_shape), \
+        f"{x_name} was expected to have {len(expected_shape)} dimensions but got {len(x.shape)}."
+    for dim, expected in zip(x.shape, expected_shape):
+        assert expected is None or dim == expected, \
+            f"{x_name} was expected to have the shape {expected_shape}, but got {x.shape}."
+
+
+def validate_camera_parameter_shapes(K, R, t):
+    validate_shape(K, 'K', (3, 3))
+    validate_shape(R, 'R', (3, 3))
+    validate_shape(t, 't', (3, 1))
+
+
+def get_pose_components(pose):
+    """hive/geometric.py:66-78: R (3,3) and t (3,1) views of a 4x4 pose."""
+    validate_shape(pose, 'pose', (4, 4))
+    return pose[:3, :3], pose[:3, 3:]
+
+
+def _kinv64(K):
+    """inv(K) computed in K's own dtype (float32 from HIVE, hive/io.py:1100), then widened: geometric.py:202."""
+    return np.ascontiguousarray(np.linalg.inv(np.asarray(K)), dtype=np.float64)
+
+
+def _cam21(M, R, t):
+    return np.concatenate([np.asarray(M, dtype=np.float64).reshape(9), np.asarray(R, dtype=np.float64).reshape(9),
+                           np.asarray(t, dtype=np.float64).reshape(3)])
+
+
+class DepthMeshBatch:
+    """Concatenated meshes of a batch of frames (device tensors) with per-frame offsets."""
+
+    def __init__(self, verts, faces, points2d, vdepth, frame_offsets):
+        self.verts, self.faces, self.points2d, self.vdepth = verts, faces, points2d, vdepth
+        self.frame_offsets = frame_offsets  # host (B+1, 2) int64
+
+    def __len__(self):
+        return self.frame_offsets.shape[0] - 1
+
+    def frame(self, i):
+        """(vertices (N,3) f64, faces (F,3) i32, points2d (N,2) i32, depth (N,) f32) of frame i as host numpy."""
+        v0, f0 = self.frame_offsets[i]
+        v1, f1 = self.frame_offsets[i + 1]
+        return (self.verts[v0:v1].cpu().numpy(), self.faces[f0:f1].cpu().numpy(),
+                self.points2d[v0:v1].cpu().numpy() if self.points2d is not None else None,
+                self.vdepth[v0:v1].cpu().numpy() if self.vdepth is not None else None)
+
+
+def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, diag=None, want_points=True):
+    """Core batched call on device tensors.  depth (B,H,W) f32, mask (B,H,W) u8 or None, cams (B,12) f64."""
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    B, H, W = (int(s) for s in depth.shape)
+    dev = depth.device
+    with torch.cuda.device(dev):
+        nbytes = ctypes.c_int64(0)
+        _lib.check(lib.hv_d2m_scratch_bytes(B, H, W, ctypes.byref(nbytes)))
+        scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+        sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
+        totals = torch.zeros(2, dtype=torch.int64, device=dev)
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        mdd = ctypes.c_float(np.float32(max_depth_distance))
+        _lib.check(lib.hv_d2m_count(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags, sptr, int(nbytes.value),
+                                    _ptr(totals), stream))
+        n_verts, n_faces = (int(v) for v in totals.cpu().tolist())
+        verts = torch.empty((n_verts, 3), dtype=torch.float64, device=dev)
+        faces = torch.empty((n_faces, 3), dtype=torch.int32, device=dev)
+        points2d = torch.empty((n_verts, 2), dtype=torch.int32, device=dev) if want_points else None
+        vdepth = torch.empty((n_verts,), dtype=torch.float32, device=dev) if want_points else None
+        frame_off = torch.zeros((B + 1, 2), dtype=torch.int64, device=dev)
+        kinv = np.ascontiguousarray(kinv, dtype=np.float64)
+        _lib.check(lib.hv_d2m_emit(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags,
+                                   kinv.ctypes.data_as(ctypes.c_void_p), _ptr(cams), sptr, int(nbytes.value), n_verts,
+                                   n_faces, _ptr(verts), _ptr(faces), _ptr(points2d), _ptr(vdepth), _ptr(frame_off), stream))
+        return DepthMeshBatch(verts, faces, points2d, vdepth, frame_off.cpu().numpy())
+
+
+def d2m_flags(max_pixel_distance) -> int:
+    """The lattice rule is exact for max_pixel_distance in [sqrt2, sqrt5); HIVE's default is 2."""
+    mpd = float(max_pixel_distance)
+    if np.sqrt(2.0) <= mpd < 2.0:
+        return 0
+    if 2.0 <= mpd < np.sqrt(5.0):
+        return 1  # HV_D2M_BRIDGES
+    raise NotImplementedError(
+        f"max_pixel_distance={mpd}: the closed-form lattice triangulation covers [sqrt(2), sqrt(5)) only")
+
+
+def depth_to_mesh_batch(depths, masks, K, poses, max_pixel_distance=2, max_depth_distance=0.1, diag=None):
+    """Per-frame foreground meshes for a batch of frames (hive/pipeline.py:386-409 fused).
+
+    depths (B,H,W) float32, masks (B,H,W) bool/uint8 or None, K (3,3), poses (B,4,4) world-to-camera
+    (hive/pipeline.py:357).  Returns a ``DepthMeshBatch``.
+    """
+    torch = _lib.require_cuda()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    depths = np.ascontiguousarray(depths, dtype=np.float32)
+    poses = np.asarray(poses, dtype=np.float64)
+    B = depths.shape[0]
+    cams = np.concatenate([poses[:, :3, :3].reshape(B, 9), poses[:, :3, 3].reshape(B, 3)], axis=1)
+    d = torch.from_numpy(depths).to(dev)
+    m = None if masks is None else torch.from_numpy(np.ascontiguousarray(masks).astype(np.uint8)).to(dev)
+    g = None if diag is None else torch.from_numpy(np.ascontiguousarray(diag, dtype=np.uint8)).to(dev)
+    c = torch.from_numpy(np.ascontiguousarray(cams)).to(dev)
+    return depth_to_mesh_device(d, m, _kinv64(K), c, max_depth_distance, d2m_flags(max_pixel_distance), g)
+
+
+def point_cloud_from_depth(depth, mask, K, R=_EYE, t=_ZERO_T):
+    """hive/geometric.py:107-126: (N, 3) float64 world points of ``mask & (depth > 0)``, row-major order."""
+    torch = _lib.require_cuda()
+    validate_camera_parameter_shapes(K, R, t)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    depth = np.asarray(depth)
+    assert np.asarray(mask).shape == depth.shape
+    d = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float32)[None]).to(dev)
+    m = torch.from_numpy(np.ascontiguousarray(mask).astype(np.uint8)[None]).to(dev)
+    cams = torch.from_numpy(_cam21(np.eye(3), R, t)[9:][None].copy()).to(dev)
+    out = depth_to_mesh_device(d, m, _kinv64(K), cams, 0.0, 2, want_points=False)  # HV_D2M_VERTS_ONLY
+    return out.verts.cpu().numpy()
+
+
+def point_cloud_from_rgbd(rgb, depth, mask, K, R=_EYE, t=_ZERO_T):
+    """hive/geometric.py:129-152: points plus (N, 4) RGBA (alpha 255) in the dtype of ``rgb``."""
+    points = point_cloud_from_depth(depth, mask, K, R, t)
+    valid = np.asarray(mask) & (np.asarray(depth) > 0.0)
+    colour = np.zeros(shape=(len(points), 4), dtype=rgb.dtype)
+    colour[:, :3] = rgb[valid]
+    colour[:, 3] = 255
+    return points, colour
+
+
+def image2world(points, depth, K, R=_EYE, t=_ZERO_T, scale_factor=1.0):
+    """hive/geometric.py:183-206."""
+    torch = _lib.require_cuda()
+    points, depth = np.asarray(points), np.asarray(depth)
+    validate_shape(points, 'points', (None, 2))
+    validate_shape(depth, 'depth', (points.shape[0],))
+    validate_camera_parameter_shapes(K, R, t)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = points.shape[0]
+    p = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float64)).to(dev)
+    d = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float64)).to(dev)
+    cam = torch.from_numpy(_cam21(_kinv64(K), R, t)).to(dev)
+    out = torch.empty((n, 3), dtype=torch.float64, device=dev)
+    _lib.check(_lib.load().hv_image2world(_ptr(p), _ptr(d), n, _ptr(cam), float(scale_factor), _ptr(out),
+                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out.cpu().numpy()
+
+
+def world2image(points, K, R=_EYE, t=_ZERO_T, scale_factor=1.0, dtype=np.int32):
+    """hive/geometric.py:155-180: ((N, 2) pixel coordinates in ``dtype``, (N,) float64 depth)."""
+    torch = _lib.require_cuda()
+    points = np.asarray(points)
+    validate_shape(points, 'points', (None, 3))
+    validate_camera_parameter_shapes(K, R, t)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = points.shape[0]
+    p = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float64)).to(dev)
+    cam = torch.from_numpy(_cam21(np.asarray(K, dtype=np.float64), R, t)).to(dev)
+    uv = torch.empty((n, 2), dtype=torch.float64, device=dev)
+    depth = torch.empty((n,), dtype=torch.float64, device=dev)
+    _lib.check(_lib.load().hv_world2image(_ptr(p), n, _ptr(cam), float(scale_factor),
+                                          int(issubclass(dtype, np.integer)), _ptr(uv), _ptr(depth),
+                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return np.array(uv.cpu().numpy(), dtype=dtype), depth.cpu().numpy()

@@ -1,0 +1,114 @@
+"""GPU drop-ins for the triangulation hot spots of ``hive/pipeline.py`` (lines 651-694) and the fused per-frame
+foreground mesh step built from them (``process_frame``, pipeline.py:386-409).
+
+``Pipeline._triangulate_faces`` / ``Pipeline._filter_faces`` keep the reference's names and signatures.  One documented
+difference: the reference's ``_triangulate_faces`` returns the *full* Delaunay triangulation (including the long
+triangles that fill the convex hull) and relies on ``_filter_faces`` to drop every face with an edge longer than
+``max_pixel_distance``; here ``_triangulate_faces`` already returns only the faces that can survive that pixel filter
+(on the pixel lattice they have a closed form), so ``_filter_faces(_triangulate_faces(p), ...)`` -- the
+only way HIVE uses them (pipeline.py:404-409, 580-582) -- is unchanged, modulo the diagonal of co-circular quads, which
+Qhull picks arbitrarily.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib
+from . import geometric
+
+__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh"]
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+@dataclass
+class MeshFilteringOptions:
+    """hive/options.py:274 defaults."""
+    max_pixel_distance: int = 2
+    max_depth_distance: float = 0.1
+    min_num_components: int = 5
+
+
+def depth_to_mesh(depth, mask, K, R=geometric._EYE, t=geometric._ZERO_T, options: MeshFilteringOptions = None,
+                  diag=None):
+    """One frame of pipeline.py:386-409 fused: returns (vertices (N,3) f64, faces (F,3) i32, points2d (N,2) i32,
+    masked_depth (N,) f32)."""
+    options = options or MeshFilteringOptions()
+    pose = np.eye(4)
+    pose[:3, :3] = R
+    pose[:3, 3:] = np.asarray(t).reshape(3, 1)
+    batch = geometric.depth_to_mesh_batch(np.asarray(depth)[None], None if mask is None else np.asarray(mask)[None], K,
+                                          pose[None], options.max_pixel_distance, options.max_depth_distance,
+                                          None if diag is None else np.asarray(diag)[None])
+    return batch.frame(0)
+
+
+class Pipeline:
+    """Only the static hot-path helpers of ``hive.pipeline.Pipeline``."""
+
+    @staticmethod
+    def _triangulate_faces(points: np.ndarray, max_pixel_distance=2, diag=None) -> np.ndarray:
+        """pipeline.py:651-667 for points on the integer pixel lattice (what HIVE passes, pipeline.py:393-397)."""
+        points = np.asarray(points)
+        geometric.validate_shape(points, 'points', (None, 2))
+        assert np.issubdtype(points.dtype, np.integer) or np.array_equal(points, np.round(points)), \
+            "hive_b200 triangulates pixel-lattice points only"
+        torch = _lib.require_cuda()
+        pts = points.astype(np.int64)
+        u0, v0 = pts[:, 0].min(), pts[:, 1].min()
+        W, H = int(pts[:, 0].max() - u0 + 1), int(pts[:, 1].max() - v0 + 1)
+        lin = (pts[:, 1] - v0) * W + (pts[:, 0] - u0)
+        assert len(np.unique(lin)) == len(lin), "duplicate points"
+        grid = np.zeros(H * W, dtype=np.float32)
+        grid[lin] = 1.0
+        dev = torch.device("cuda", torch.cuda.current_device())
+        d = torch.from_numpy(grid.reshape(1, H, W)).to(dev)
+        g = None
+        if diag is not None:
+            g = torch.from_numpy(np.ascontiguousarray(diag, dtype=np.uint8).reshape(1, H, W)).to(dev)
+        cams = torch.zeros((1, 12), dtype=torch.float64, device=dev)
+        out = geometric.depth_to_mesh_device(d, None, np.eye(3), cams, np.float32(np.inf),
+                                             geometric.d2m_flags(max_pixel_distance), g, want_points=False)
+        faces = out.faces.cpu().numpy()
+        order = np.argsort(lin, kind="stable")  # rank in row-major order -> index in the caller's array
+        if not np.array_equal(order, np.arange(len(lin))):
+            faces = order[faces].astype(np.int32)
+        return faces
+
+    @staticmethod
+    def _filter_faces(points2d, depth, faces, options: MeshFilteringOptions):
+        """pipeline.py:670-694 for arbitrary faces (order preserving)."""
+        points2d, depth, faces = np.asarray(points2d), np.asarray(depth), np.asarray(faces)
+        geometric.validate_shape(points2d, 'points2d', (None, 2))
+        geometric.validate_shape(depth, 'depth', (points2d.shape[0],))
+        geometric.validate_shape(faces, 'faces', (None, 3))
+        n_faces = faces.shape[0]
+        if n_faces == 0:
+            return faces
+        torch = _lib.require_cuda()
+        lib = _lib.load()
+        dev = torch.device("cuda", torch.cuda.current_device())
+        is64 = depth.dtype == np.float64
+        p = torch.from_numpy(np.ascontiguousarray(points2d, dtype=np.int32)).to(dev)
+        d = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float64 if is64 else np.float32)).to(dev)
+        f = torch.from_numpy(np.ascontiguousarray(faces, dtype=np.int32)).to(dev)
+        nbytes = ctypes.c_int64(0)
+        _lib.check(lib.hv_filter_faces_scratch_bytes(n_faces, ctypes.byref(nbytes)))
+        scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+        sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
+        totals = torch.zeros(2, dtype=torch.int64, device=dev)
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        mdd = float(np.float32(options.max_depth_distance)) if not is64 else float(options.max_depth_distance)
+        args = (_ptr(p), _ptr(d), int(is64), _ptr(f), n_faces, float(options.max_pixel_distance), mdd, sptr,
+                int(nbytes.value))
+        _lib.check(lib.hv_filter_faces(*args, 0, _ptr(totals), None, stream))
+        kept = int(totals[0].item())
+        out = torch.empty((kept, 3), dtype=torch.int32, device=dev)
+        if kept:
+            _lib.check(lib.hv_filter_faces(*args, 1, _ptr(totals), _ptr(out), stream))
+        return out.cpu().numpy().astype(faces.dtype, copy=False)

@@ -111,6 +111,60 @@ int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, co
                float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
                unsigned long long* vert_keys, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Depth-to-mesh, batched over frames.  Replaces, for the per-frame foreground meshes of hive/pipeline.py:386-409,
+ *   point_cloud_from_depth / image2world   hive/geometric.py:107-126, 183-206
+ *   Pipeline._triangulate_faces            hive/pipeline.py:651-667 (scipy.spatial.Delaunay on the pixel lattice)
+ *   Pipeline._filter_faces                 hive/pipeline.py:670-694
+ * using the closed form of "lattice Delaunay + 2-pixel edge filter" (SURVEY.md App. D).
+ *
+ * depth : [B][H][W] float32 (0 = invalid).   mask : [B][H][W] uint8 (non-zero = keep) or NULL.
+ * diag  : NULL, or [B][H][W] uint8 overriding the otherwise arbitrary diagonal of co-circular points: bit 0 = the 2x2
+ *         quad whose top-left pixel this is splits along the anti-diagonal, bit 1 = the hole at this pixel splits N-S.
+ * flags : HV_D2M_BRIDGES = also emit the (sqrt2, sqrt2, 2) triangles over 1-pixel holes, i.e. max_pixel_distance in
+ *         [2, sqrt5) (HIVE's default 2, hive/options.py:274); without it, max_pixel_distance in [sqrt2, 2).
+ * max_depth_distance : pipeline.py:689, compared in float32 like the reference.
+ * Two calls (output sizes are data dependent): hv_d2m_count writes totals[0] = #vertices, totals[1] = #faces of the
+ * whole batch; hv_d2m_emit writes the concatenated outputs.  Vertex ids in `faces` are frame-local ranks of the valid
+ * pixels in row-major order (np.nonzero order); winding has negative signed area in (u, v), like the reference's
+ * reversed Delaunay simplices.  frame_offsets: [B+1][2] int64 (vertex, face) start of each frame.
+ * h_kinv : HOST, 9 doubles, inv(K) computed in K's own dtype (geometric.py:202).  cams: DEVICE, [B][12] doubles, the
+ * world-to-camera R (row-major) and t that geometric.py takes.  points2d ([V][2] int32 u,v) and vdepth ([V] float32)
+ * are optional.
+ * ---------------------------------------------------------------------------------------------------------- */
+#define HV_D2M_BRIDGES 1
+#define HV_D2M_VERTS_ONLY 2 /* point_cloud_from_depth: back-projection only, no faces */
+int hv_d2m_scratch_bytes(int B, int H, int W, int64_t* h_bytes);
+int hv_d2m_count(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                 float max_depth_distance, int flags, void* scratch, int64_t scratch_bytes, unsigned long long* totals,
+                 void* stream);
+int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
+                int64_t scratch_bytes, int64_t n_verts, int64_t n_faces, double* verts, int32_t* faces, int32_t* points2d,
+                float* vdepth, long long* frame_offsets, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Elementwise projections, float64 like the reference.  `cam` is a DEVICE array of 21 doubles: a 3x3 matrix
+ * (row-major), then the world-to-camera R (row-major) and t.
+ *   hv_image2world  hive/geometric.py:183-206: the matrix is inv(K); out[i] = R^T (depth[i] * Kinv [u*s, v*s, 1] - t)
+ *   hv_world2image  hive/geometric.py:155-180: the matrix is K; c = K (R p + t); depth = c_z; uv = c_xy / c_z / s,
+ *                   rounded half-to-even when the reference would (integer dtype).
+ * ---------------------------------------------------------------------------------------------------------- */
+int hv_image2world(const double* points2d, const double* depth, int64_t n, const double* cam, double scale, double* out,
+                   void* stream);
+int hv_world2image(const double* points, int64_t n, const double* cam, double scale, int round_half_even, double* uv,
+                   double* depth, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Generic face filter, Pipeline._filter_faces (hive/pipeline.py:670-694) for arbitrary faces: keeps a face iff its
+ * three edges (0,1), (2,1), (0,2) are <= max_pixel_distance long in the image and differ by <= max_depth_distance
+ * in depth.  Order preserving.  Two phases around a host read of totals[0] (phase 0 counts, phase 1 writes).
+ * ---------------------------------------------------------------------------------------------------------- */
+int hv_filter_faces_scratch_bytes(int64_t n_faces, int64_t* h_bytes);
+int hv_filter_faces(const int32_t* points2d, const void* depth, int depth_is_f64, const int32_t* faces, int64_t n_faces,
+                    double max_pixel_distance, double max_depth_distance, void* scratch, int64_t scratch_bytes, int phase,
+                    unsigned long long* totals, int32_t* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,7 @@ _LIB = None
 def build(force: bool = False) -> str:
     """Compile the C restatements (gcc, a second or two)."""
     so = os.path.join(_HERE, "libhive_oracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("tsdf_oracle.c", "mc_oracle.c", "mc_tables.h", "d2m_oracle.c")]
+    srcs = [os.path.join(_HERE, f) for f in ("tsdf_oracle.c", "mc_oracle.c", "mc_tables.h")]
     stale = force or not os.path.exists(so) or any(
         os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if stale:

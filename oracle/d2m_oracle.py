@@ -1,0 +1,104 @@
+"""ORACLE -- test infrastructure, not product code.
+
+CPU restatement of HIVE's per-frame depth-to-mesh step:
+
+* ``point_cloud_from_depth`` / ``image2world`` / ``world2image``  -- hive/geometric.py:107-126, 183-206, 155-180
+  (verbatim numpy; pinned against the real module through tests/golden/backproject.npz, oracle/make_golden.py);
+* ``triangulate_faces`` / ``filter_faces``  -- Pipeline._triangulate_faces / _filter_faces, hive/pipeline.py:651-694
+  (``hive.pipeline`` itself cannot be imported: trimesh, openmesh, detectron2 are absent; both are 10-line static
+  methods around ``scipy.spatial.Delaunay``).  PARITY UNPINNED for the triangulation: Qhull lives in scipy
+  (pinned 1.7.3 in requirements.txt:2, 1.18 here), the reference has no test for it, and on the pixel lattice every
+  2x2 quad is co-circular, so the diagonal Qhull picks is arbitrary.  ``diagonals`` recovers the
+  diagonals a given Delaunay run chose so that the CUDA kernel can be compared face-for-face.
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this module.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def image2world(points, depth, K, R=np.eye(3), t=np.zeros((3, 1)), scale_factor=1.0):
+    """hive/geometric.py:183-206."""
+    num_points = points.shape[0]
+    points2d = np.vstack((points.T * scale_factor, np.ones(num_points)))
+    points_camera_space = np.linalg.inv(K) @ points2d
+    points_world_space = R.T @ (depth * points_camera_space - t)
+    return points_world_space.T
+
+
+def world2image(points, K, R=np.eye(3), t=np.zeros((3, 1)), scale_factor=1.0, dtype=np.int32):
+    """hive/geometric.py:155-180."""
+    camera_space_coords = K @ (R @ points.T + t)
+    depth = camera_space_coords[2, :]
+    pixel_coords = camera_space_coords[0:2, :] / depth / scale_factor
+    if issubclass(dtype, np.integer):
+        pixel_coords = np.round(pixel_coords)
+    pixel_coords = np.array(pixel_coords.T, dtype=dtype)
+    return pixel_coords, depth
+
+
+def point_cloud_from_depth(depth, mask, K, R=np.eye(3), t=np.zeros((3, 1))):
+    """hive/geometric.py:107-126."""
+    valid_pixels = mask & (depth > 0.0)
+    V, U = valid_pixels.nonzero()
+    points2d = np.array([U, V]).T
+    return image2world(points2d, depth[valid_pixels], K, R, t)
+
+
+def triangulate_faces(points, return_raw=False):
+    """Pipeline._triangulate_faces, hive/pipeline.py:651-667."""
+    from scipy.spatial import Delaunay
+    tri = Delaunay(points)
+    faces = np.asarray(tri.simplices)
+    faces = faces[:, ::-1]  # "reverse winding order to ensure culling works as expected"
+    return faces
+
+
+def filter_faces(points2d, depth, faces, max_pixel_distance=2, max_depth_distance=0.1):
+    """Pipeline._filter_faces, hive/pipeline.py:670-694 (options.py:274 defaults)."""
+    pixel_distances = np.linalg.norm(points2d[faces[:, [0, 2, 0]]] - points2d[faces[:, [1, 1, 2]]], axis=-1)
+    depth_proj = depth.reshape((*depth.shape, 1))
+    depth_distances = np.linalg.norm(depth_proj[faces[:, [0, 2, 0]]] - depth_proj[faces[:, [1, 1, 2]]], axis=-1)
+    valid_faces = np.all((pixel_distances <= max_pixel_distance) & (depth_distances <= max_depth_distance), axis=1)
+    return faces[valid_faces]
+
+
+def frame_mesh(depth, mask, K, R, t, max_pixel_distance=2, max_depth_distance=0.1):
+    """process_frame's geometric core, hive/pipeline.py:386-409: vertices, filtered faces, and the raw Delaunay faces."""
+    vertices = point_cloud_from_depth(depth, mask, K, R, t)
+    valid = mask & (depth > 0)
+    v, u = valid.nonzero()
+    points2d = np.array([u, v]).T
+    masked_depth = depth[valid]
+    raw = triangulate_faces(points2d)
+    faces = filter_faces(points2d, masked_depth, raw, max_pixel_distance, max_depth_distance)
+    return vertices, faces, points2d, masked_depth, raw
+
+
+def diagonals(points2d, raw_faces, H, W):
+    """Per-pixel override bitmap for the CUDA kernel from the diagonals this Delaunay run chose: bit 0 = the quad
+    whose top-left pixel this is was split along its anti-diagonal, bit 1 = the hole at this pixel was split N-S."""
+    diag = np.zeros((H, W), dtype=np.uint8)
+    p = points2d[raw_faces]  # (F, 3, 2)
+    for a, b in ((0, 1), (1, 2), (2, 0)):
+        d = p[:, b] - p[:, a]
+        lo = np.minimum(p[:, a], p[:, b])
+        third = p[:, 3 - a - b]
+        unit = np.abs(p - p.mean(axis=1, keepdims=True)).max(axis=(1, 2)) < 1.0  # fits in a 2x2 quad
+        anti = unit & (np.abs(d[:, 0]) == 1) & (np.abs(d[:, 1]) == 1) & (d[:, 0] * d[:, 1] == -1)
+        diag[lo[anti, 1], lo[anti, 0]] |= 1
+        # bridge triangles: the long edge (length 2) is the chosen diagonal of the diamond around an absent pixel;
+        # only diamonds with all four neighbours present have a choice, a vertical long edge marks N-S
+        vert = (d[:, 0] == 0) & (np.abs(d[:, 1]) == 2) & (np.abs(third[:, 0] - p[:, a, 0]) == 1) & \
+               (third[:, 1] == lo[:, 1] + 1)
+        diag[lo[vert, 1] + 1, lo[vert, 0]] |= 2
+    return diag
+
+
+def canonical_faces(faces):
+    """Faces as a sorted array of cyclically-normalised triples (orientation preserved): set comparison."""
+    f = np.asarray(faces, dtype=np.int64)
+    k = np.argmin(f, axis=1)
+    rolled = np.stack([f[np.arange(len(f)), (k + i) % 3] for i in range(3)], axis=1)
+    return rolled[np.lexsort((rolled[:, 2], rolled[:, 1], rolled[:, 0]))]

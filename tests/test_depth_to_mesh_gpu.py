@@ -1,0 +1,140 @@
+"""GPU parity of the per-frame depth-to-mesh path against the oracle (oracle/d2m_oracle.py, restating
+hive/geometric.py:107-206 and hive/pipeline.py:651-694) and the golden vectors produced by the real hive.geometric.
+
+Vertices: float64, compared to 1e-9 relative (the reference multiplies through BLAS dgemm, whose summation order is
+not specified).  Faces: Qhull's diagonal on co-circular lattice quads is arbitrary, so face sets are
+compared exactly after feeding the kernel the diagonals that the oracle's Delaunay run happened to choose, and through
+diagonal-independent properties otherwise.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from hive_b200.synthetic import Scene
+from oracle import d2m_oracle as d2m
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _frame(config="small", index=2):
+    scene = Scene(config, "room")
+    fr = scene.frame(index)
+    w2c = np.linalg.inv(fr.pose)
+    return scene, fr, w2c[:3, :3], w2c[:3, 3:]
+
+
+def _close(a, b, rel=1e-9):
+    return np.abs(a - b).max() <= rel * max(1.0, np.abs(b).max())
+
+
+def test_point_cloud_matches_reference_golden():
+    from hive_b200 import geometric
+    g = np.load(os.path.join(GOLDEN, "backproject.npz"))
+    scene, fr, R, t = _frame("small", int(g["frame_index"]))
+    pts = geometric.point_cloud_from_depth(fr.depth, fr.mask > 0, scene.K, R, t)
+    assert pts.dtype == np.float64 and pts.shape == g["points"].shape
+    assert _close(pts, g["points"])
+    full = geometric.point_cloud_from_depth(fr.depth, np.ones_like(fr.mask, dtype=bool), scene.K, R, t)
+    assert len(full) == int(g["n_nomask"]) and _close(full[:64], g["points_nomask_head"])
+    uv, depth = geometric.world2image(g["points"], scene.K, R, t)
+    assert uv.dtype == np.int32 and np.array_equal(uv, g["uv"]) and _close(depth, g["depth"])
+    # image2world on explicit points, and the float (non-rounded) branch of world2image
+    v, u = (fr.mask > 0).nonzero()
+    sel = fr.depth[v, u] > 0
+    p2 = np.array([u[sel], v[sel]]).T
+    assert _close(geometric.image2world(p2, fr.depth[v[sel], u[sel]], scene.K, R, t), g["points"])
+    uvf, _ = geometric.world2image(g["points"], scene.K, R, t, dtype=np.float64)
+    assert np.abs(uvf - p2).max() < 1e-4  # inv(K) is taken in float32 (geometric.py:202)
+
+
+@pytest.mark.parametrize("config,index", [("small", 2), ("small", 5), ("tiny", 1)])
+def test_frame_mesh_matches_oracle_with_its_diagonals(config, index):
+    from hive_b200 import pipeline
+    scene, fr, R, t = _frame(config, index)
+    mask = fr.mask > 0
+    ov, of, op2, omd, raw = d2m.frame_mesh(fr.depth, mask, scene.K, R, t)
+    diag = d2m.diagonals(op2, raw, scene.H, scene.W)
+    verts, faces, p2, md = pipeline.depth_to_mesh(fr.depth, mask, scene.K, R, t, diag=diag)
+    assert verts.dtype == np.float64 and faces.dtype == np.int32
+    assert np.array_equal(p2, op2) and np.array_equal(md, omd)
+    assert _close(verts, ov)
+    assert np.array_equal(d2m.canonical_faces(faces), d2m.canonical_faces(of))
+
+
+def _random_case(rng, H, W, hole_p, depth_jumps):
+    mask = rng.random((H, W)) > hole_p
+    depth = np.full((H, W), 1.5, np.float32)
+    if depth_jumps:
+        depth += (rng.random((H, W)) * 0.3).astype(np.float32)  # neighbouring depths straddle the 0.1 m threshold
+    depth[rng.random((H, W)) < 0.05] = 0.0
+    return depth, mask
+
+
+@pytest.mark.parametrize("H,W,hole_p,jumps", [(24, 31, 0.1, False), (33, 40, 0.3, True), (17, 64, 0.02, True),
+                                              (40, 37, 0.5, False), (12, 12, 0.0, True)])
+def test_random_masks_face_sets(H, W, hole_p, jumps):
+    from hive_b200 import pipeline
+    rng = np.random.default_rng(H * 1000 + W)
+    depth, mask = _random_case(rng, H, W, hole_p, jumps)
+    K = np.array([[50.0, 0, W / 2], [0, 50.0, H / 2], [0, 0, 1]], dtype=np.float32)
+    ov, of, op2, omd, raw = d2m.frame_mesh(depth, mask, K, np.eye(3), np.zeros((3, 1)))
+    diag = d2m.diagonals(op2, raw, H, W)
+    verts, faces, p2, md = pipeline.depth_to_mesh(depth, mask, K, diag=diag)
+    assert _close(verts, ov) and np.array_equal(p2, op2)
+    assert np.array_equal(d2m.canonical_faces(faces), d2m.canonical_faces(of))
+    # the production rule (no injected diagonals): every face is legal, oriented, unique
+    verts2, faces2, _, _ = pipeline.depth_to_mesh(depth, mask, K)
+    assert np.array_equal(verts2, verts)
+    assert len(d2m.filter_faces(op2, omd, faces2)) == len(faces2)
+    p = op2[faces2].astype(np.int64)
+    e1, e2 = p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]
+    assert (e1[:, 0] * e2[:, 1] - e1[:, 1] * e2[:, 0] < 0).all()
+    assert len(np.unique(np.sort(faces2, axis=1), axis=0)) == len(faces2)
+    if not jumps:  # without depth discontinuities the face COUNT does not depend on the diagonal
+        assert len(faces2) == len(of)
+
+
+def test_triangulate_then_filter_composition_matches_oracle():
+    from hive_b200.pipeline import MeshFilteringOptions, Pipeline
+    rng = np.random.default_rng(11)
+    depth, mask = _random_case(rng, 30, 45, 0.2, True)
+    valid = mask & (depth > 0)
+    v, u = valid.nonzero()
+    p2 = np.array([u, v]).T
+    md = depth[valid]
+    raw = d2m.triangulate_faces(p2)
+    want = d2m.filter_faces(p2, md, raw)
+    diag = d2m.diagonals(p2, raw, 30, 45)
+    u0, v0 = p2[:, 0].min(), p2[:, 1].min()
+    sub = diag[v0:p2[:, 1].max() + 1, u0:p2[:, 0].max() + 1]
+    tri = Pipeline._triangulate_faces(p2, diag=sub)
+    got = Pipeline._filter_faces(p2, md, tri, MeshFilteringOptions())
+    assert np.array_equal(d2m.canonical_faces(got), d2m.canonical_faces(want))
+    # _filter_faces on the oracle's own (unfiltered) Delaunay faces: same faces, same order
+    assert np.array_equal(Pipeline._filter_faces(p2, md, raw, MeshFilteringOptions()), want)
+    # shuffled input order is mapped back to the caller's indices
+    perm = rng.permutation(len(p2))
+    tri_s = Pipeline._triangulate_faces(p2[perm], diag=sub)
+    assert np.array_equal(d2m.canonical_faces(perm[tri_s]), d2m.canonical_faces(tri))
+
+
+def test_batch_equals_single_frames_and_handles_empty_frames():
+    from hive_b200 import geometric, pipeline
+    scene = Scene("small", "room")
+    frames = [scene.frame(i) for i in range(4)]
+    depths = np.stack([f.depth for f in frames])
+    masks = np.stack([f.mask > 0 for f in frames])
+    masks[2] = False  # a frame without any foreground
+    poses = np.stack([np.linalg.inv(f.pose) for f in frames])
+    batch = geometric.depth_to_mesh_batch(depths, masks, scene.K, poses)
+    assert len(batch) == 4
+    assert batch.frame_offsets[2, 0] == batch.frame_offsets[3, 0] and batch.frame_offsets[2, 1] == batch.frame_offsets[3, 1]
+    for i in (0, 1, 3):
+        v, f, p2, md = batch.frame(i)
+        sv, sf, sp2, smd = pipeline.depth_to_mesh(depths[i], masks[i], scene.K, poses[i][:3, :3], poses[i][:3, 3:])
+        assert np.array_equal(v, sv) and np.array_equal(f, sf) and np.array_equal(p2, sp2)
+        assert len(v) > 0 and f.max() < len(v)
+    v, f, _, _ = batch.frame(2)
+    assert v.shape == (0, 3) and f.shape == (0, 3)
