@@ -56,7 +56,9 @@ def parse_args():
     ap.add_argument("--no-room", action="store_true", help="skip the secondary room-scene measurement")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mesh", action="store_true")
-    ap.add_argument("--cpu-sample-frames", type=int, default=6)
+    ap.add_argument("--cpu-sample-frames", type=int, default=40)
+    ap.add_argument("--d2m-frames", type=int, default=120, help="frames per depth-to-mesh batch")
+    ap.add_argument("--no-d2m", action="store_true")
     return ap.parse_args()
 
 
@@ -217,6 +219,76 @@ def run_reference(args):
     }))
 
 
+
+# ----------------------------------------------------------------------------------------------------------------------
+def measure_mesh(vol, torch, peak, repeats=5):
+    """get_mesh device time (count + scan + host read of the two totals + emit + vertices), median of `repeats`."""
+    from hive_b200 import marching_cubes as mc
+    times, mesh = [], None
+    for r in range(repeats + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        mesh = mc.extract_device_mesh(vol)
+        e1.record()
+        torch.cuda.synchronize()
+        if r > 0:
+            times.append(e0.elapsed_time(e1))
+    ms = float(np.median(times))
+    V, F = int(mesh.verts.shape[0]), int(mesh.faces.shape[0])
+    n = int(np.prod(vol._local_dim))
+    algo = 4.0 * n + 4.0 * V + 28.0 * V + 12.0 * F  # SURVEY.md §8(d)
+    t0 = time.perf_counter()
+    verts, faces, norms, colors = vol.get_mesh()
+    e2e_ms = (time.perf_counter() - t0) * 1000.0
+    return {"mc_ms": ms, "vertices": V, "triangles": F, "voxels": n, "algorithmic_bytes": algo,
+            "achieved_gbs": algo / (ms / 1e3) / 1e9, "roofline_frac": algo / (ms / 1e3) / 1e9 / peak,
+            "get_mesh_e2e_ms": e2e_ms, "d2h_bytes": int(verts.nbytes + faces.nbytes + norms.nbytes + colors.nbytes),
+            "scene": "room", "launches_per_extraction": 8}
+
+
+def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
+    """Per-frame foreground depth-to-mesh (BASELINE config C4 shape: 640x480, frame-partitioned across ranks)."""
+    from hive_b200 import geometric
+    B = args.d2m_frames
+    sc = _scene(base_cfg, "room")
+    n_distinct = min(12, B)
+    fr = [sc.frame(i + 1000 * rank) for i in range(n_distinct)]  # every rank owns its own frame range: no collective
+    depths = np.stack([fr[i % n_distinct].depth for i in range(B)])
+    masks = np.stack([(fr[i % n_distinct].mask > 0) for i in range(B)]).astype(np.uint8)
+    poses = np.stack([np.linalg.inv(fr[i % n_distinct].pose) for i in range(B)])
+    dev = torch.device("cuda", torch.cuda.current_device())
+    d = torch.from_numpy(depths).to(dev)
+    m = torch.from_numpy(masks).to(dev)
+    cams = torch.from_numpy(np.concatenate([poses[:, :3, :3].reshape(B, 9), poses[:, :3, 3].reshape(B, 3)], axis=1)).to(dev)
+    kinv = geometric._kinv64(sc.K)
+    times, out = [], None
+    for r in range(repeats + 1):
+        _barrier(world, dist, torch)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = geometric.depth_to_mesh_device(d, m, kinv, cams, 0.1, 1)
+        e1.record()
+        torch.cuda.synchronize()
+        if r > 0:
+            times.append(_max_over_ranks(e0.elapsed_time(e1), world, dist, torch))
+    ms = float(np.median(times))
+    V, F = int(out.verts.shape[0]), int(out.faces.shape[0])
+    H, W = sc.H, sc.W
+    algo = 5.0 * H * W * B + 36.0 * V + 12.0 * F  # depth f32 + mask u8 in; f64 xyz + (u, v, depth) + faces out
+    # end to end: host numpy in, host numpy out (H2D of depth+mask, D2H of vertices and faces)
+    t0 = time.perf_counter()
+    batch = geometric.depth_to_mesh_batch(depths, masks, sc.K, poses)
+    hv, hf = batch.verts.cpu().numpy(), batch.faces.cpu().numpy()
+    e2e_s = time.perf_counter() - t0
+    e2e_fps = _sum_over_ranks(int(B / e2e_s), world, dist, torch)
+    return {"frames_per_s": world * B / (ms / 1e3), "ms_per_batch": ms, "frames_per_batch_per_gpu": B,
+            "vertices": V, "faces": F, "achieved_gbs": algo / (ms / 1e3) / 1e9,
+            "roofline_frac": algo / (ms / 1e3) / 1e9 / peak, "e2e_frames_per_s": float(e2e_fps),
+            "h2d_bytes": int(depths.nbytes + masks.nbytes), "d2h_bytes": int(hv.nbytes + hf.nbytes),
+            "workload": f"{B} frames/GPU of {W}x{H}, instance masks of the room scene, frame-partitioned"}
+
+
 # ----------------------------------------------------------------------------------------------------------------------
 def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -255,6 +327,10 @@ def run_ours(args):
                        SlabShardedTSDFVolume, peak)
         results[variant] = res
         torch.cuda.empty_cache()
+
+    d2m_res = None
+    if not args.no_d2m:
+        d2m_res = measure_d2m(args, base_cfg, world, rank, torch, dist, peak)
 
     if rank != 0:
         if world > 1:
@@ -297,8 +373,11 @@ def run_ours(args):
         out["room"] = {k: r[k] for k in ("value", "frames_per_s", "updated_fraction", "achieved_gbs", "avg_launch_ms")}
         out["room"]["roofline_frac"] = r["achieved_gbs"] / peak
         out["room"]["e2e_value"] = r["e2e"]["value"]
-    if main.get("mesh") is not None:
-        out["mesh"] = main["mesh"]
+    for r in results.values():
+        if r.get("mesh") is not None:
+            out["mesh"] = r["mesh"]
+    if d2m_res is not None:
+        out["depth_to_mesh"] = d2m_res
     if not args.no_cpu_baseline and n_gpus == 1:
         out["cpu_baseline"] = cpu_baseline(base_cfg, args.scene, frames[args.scene], args.cpu_sample_frames)
     print(json.dumps(out))
@@ -367,8 +446,8 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     e2e_value = n_vox_global * n_frames / (ms_e2e / 1000.0)
 
     mesh = None
-    if not args.no_mesh and hasattr(vol, "get_mesh_timed") and variant == args.scene:
-        mesh = vol.get_mesh_timed()
+    if not args.no_mesh and variant == "room" and world == 1:
+        mesh = measure_mesh(vol.local, torch, peak)
 
     return {
         "value": value, "ms_per_step": ms / K, "frames_per_s": n_frames / (ms / 1000.0),
