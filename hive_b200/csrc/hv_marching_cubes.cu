@@ -68,37 +68,60 @@ __device__ __forceinline__ int float_order_key(float f) {
 }
 
 // ---- 1. sign bits + min/max ----------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) mc_sign_kernel(const McGrid g) {
+// A warp covers 128 consecutive zb of one column (each lane a float4 -> 4 sign bits, 8 lanes -> one 32-bit word) and
+// strides over (column, segment) tiles; whole-volume shards (no low halo, 16-byte aligned columns) take the LDG.128 path.
+struct McSignGeom {
+    int segs;        // 128-zb segments per column
+    int n_tiles;     // columns * segs
+    int vec;         // 1: z == zb and columns are float4-aligned
+};
+
+__global__ void __launch_bounds__(256) mc_sign_kernel(const McGrid g, const McSignGeom sg) {
     const int lane = threadIdx.x & 31;
-    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
-    int kmin = 0x7fffffff, kmax = (int)0x80000000;
-    for (long long gi = warp0; gi < g.n_groups; gi += n_warps) {
-        const long long col = gi / g.G;
-        const int gq = (int)(gi - col * g.G);
-        const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
-        const int zb = gq * 32 + lane;
-        bool pos = false;
-        if (zb < g.Zb) {
-            const float v = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb);
-            pos = (double)v > g.level;
-            if (v == v) {
-                const int k = float_order_key(v);
-                kmin = min(kmin, k);
-                kmax = max(kmax, k);
-            }
+    const int warp0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int n_warps = (int)((gridDim.x * blockDim.x) >> 5);
+    float vmin = INFINITY, vmax = -INFINITY;
+    const float level_f = (float)g.level;  // exact compare needs double only when the level is not a float
+    const bool level_exact = (double)level_f == g.level;
+    for (int tile = warp0; tile < sg.n_tiles; tile += n_warps) {
+        const int col = tile / sg.segs;
+        const int seg = tile - col * sg.segs;
+        const int zb0 = seg * 128 + lane * 4;
+        float v[4];
+        if (sg.vec && zb0 + 3 < g.Z) {
+            const float4 q = __ldcs(reinterpret_cast<const float4*>(g.tsdf + (size_t)col * g.pitch + zb0));
+            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+        } else {
+            const int x = col / g.Y, y = col - x * g.Y;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                v[k] = (zb0 + k < g.Zb) ? mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb0 + k) : NAN;
         }
-        const unsigned int word = __ballot_sync(0xffffffffu, pos);
-        if (lane == 0) g.bits[gi] = word;
+        unsigned int nib = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const bool pos = level_exact ? (v[k] > level_f) : ((double)v[k] > g.level);  // NaN (padding) -> 0
+            nib |= pos ? (1u << k) : 0u;
+            vmin = fminf(vmin, v[k]);  // fminf / fmaxf ignore NaN
+            vmax = fmaxf(vmax, v[k]);
+        }
+        unsigned int word = nib << (4 * (lane & 7));
+        word |= __shfl_xor_sync(0xffffffffu, word, 1);
+        word |= __shfl_xor_sync(0xffffffffu, word, 2);
+        word |= __shfl_xor_sync(0xffffffffu, word, 4);
+        const int gq = seg * 4 + (lane >> 3);
+        if ((lane & 7) == 0 && gq < g.G) g.bits[(size_t)col * g.G + gq] = word;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
-        kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
     }
     if (lane == 0) {
-        atomicMin(reinterpret_cast<int*>(g.totals + 2), kmin);
-        atomicMax(reinterpret_cast<int*>(g.totals + 3), kmax);
+        if (vmin <= vmax) {  // at least one real value seen
+            atomicMin(reinterpret_cast<int*>(g.totals + 2), float_order_key(vmin));
+            atomicMax(reinterpret_cast<int*>(g.totals + 3), float_order_key(vmax));
+        }
     }
 }
 
@@ -219,6 +242,7 @@ struct McEmit {
     int32_t* faces;                  // [T][3] local vertex indices, or null
     unsigned long long* face_keys;   // [T][3] global vertex keys, or null
     unsigned long long* vert_keys;   // [V]
+    unsigned long long* face_cubes;  // [T] global linear index of the cube that produced the face, or null
 };
 
 __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x, int y, int zb, int axis) {
@@ -279,6 +303,7 @@ __global__ void __launch_bounds__(256) mc_emit_kernel(const McGrid g, const McEm
                 }
                 if (out.face_keys) {
                     out.face_keys[3 * ti + t] = vertex_key(g, x + ox, y + oy, zb + oz, axis);
+                    if (out.face_cubes && t % 3 == 0) out.face_cubes[ti + t / 3] = vertex_key(g, x, y, zb, 0) >> 2;
                 } else {
                     out.faces[3 * ti + t] = vertex_index(g, x + ox, y + oy, zb + oz, axis);
                 }
@@ -505,9 +530,16 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     const unsigned long long init[4] = {0ull, 0ull, 0x7fffffffull, 0x80000000ull};
     HV_CUDA(cudaMemcpyAsync(totals, init, sizeof(init), cudaMemcpyHostToDevice, st));
     const int sms = hv::device_info().sm_count;
-    const long long want = (g.n_groups + 7) / 8;  // 8 warps per block, one group per warp per iteration
-    const int sign_blocks = (int)(want < (long long)sms * 8 ? (want > 0 ? want : 1) : (long long)sms * 8);
-    hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g);
+    hv::McSignGeom sg;
+    sg.segs = (g.Zb + 127) / 128;
+    const long long n_tiles = (long long)g.X * g.Y * sg.segs;
+    HV_REQUIRE(n_tiles < (1ll << 31), "hv_mc_count: too many columns");
+    sg.n_tiles = (int)n_tiles;
+    sg.vec = (!halo_lo && (pitch & 3) == 0 && ((uintptr_t)tsdf & 15) == 0) ? 1 : 0;
+    const long long want = (n_tiles + 7) / 8;  // 8 warps per block
+    const long long cap = (long long)sms * 8;
+    const int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
+    hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g, sg);
     const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
     hv::mc_count_kernel<<<group_blocks, 256, 0, st>>>(g);
     hv::exclusive_scan_u2(g.gcount, g.goff, g.bsum, g.n_groups, totals, st);
@@ -520,17 +552,19 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
                           double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
                           float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
                           float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces,
-                          unsigned long long* face_keys, unsigned long long* vert_keys, void* stream) {
+                          unsigned long long* face_keys, unsigned long long* face_cubes, unsigned long long* vert_keys,
+                          void* stream) {
     hv::McGrid g;
     McLayout L;
     int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, &L);
     if (rc != HV_OK) return rc;
+    HV_REQUIRE(n_verts >= 0 && n_tris >= 0 && n_verts < (1ll << 31) && n_tris < (1ll << 31), "hv_mc_emit: bad counts");
+    if (n_verts == 0 && n_tris == 0) return HV_OK;  // a shard the surface does not cross
     HV_REQUIRE(color && h_origin && vert_keys && verts_world && normals && colors, "hv_mc_emit: null pointer");
     HV_REQUIRE((faces != nullptr) != (face_keys != nullptr), "hv_mc_emit: pass exactly one of faces / face_keys");
     HV_REQUIRE((halo_lo != nullptr) == (color_halo_lo != nullptr) && (halo_hi != nullptr) == (color_halo_hi != nullptr),
                "hv_mc_emit: tsdf and colour halos must come in pairs");
     HV_REQUIRE(faces == nullptr || (!halo_lo && !halo_hi), "hv_mc_emit: a shard with halos must emit face_keys");
-    HV_REQUIRE(n_verts >= 0 && n_tris >= 0 && n_verts < (1ll << 31) && n_tris < (1ll << 31), "hv_mc_emit: bad counts");
     HV_REQUIRE(z_global_dim >= z_global_offset + g.Z, "hv_mc_emit: slab exceeds the global z extent");
     g.color = color;
     g.chalo_lo = color_halo_lo;
@@ -538,7 +572,7 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     g.zoff = z_global_offset - g.hl;
     g.Zg = z_global_dim;
     cudaStream_t st = hv::as_stream(stream);
-    hv::McEmit em{faces, face_keys, vert_keys};
+    hv::McEmit em{faces, face_keys, vert_keys, face_keys ? face_cubes : nullptr};
     const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
     hv::mc_emit_kernel<<<group_blocks, 256, 0, st>>>(g, em);
     if (n_verts > 0) {

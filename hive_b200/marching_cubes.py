@@ -38,6 +38,7 @@ class DeviceMesh:
     colors: object  # (V, 3) uint8 r, g, b
     faces: object  # (T, 3) int32 indices, or None when face_keys is used
     face_keys: object  # (T, 3) int64 global vertex keys, or None
+    face_cubes: object  # (T,) int64 global cube index of each face (with face_keys), or None
     vert_keys: object  # (V,) int64 global vertex keys, ascending
     vmin: float
     vmax: float
@@ -100,6 +101,7 @@ class McPlan:
             vert_keys = torch.empty((max(n_verts, 1),), dtype=torch.int64, device=dev)
             faces = None if keys else torch.empty((n_tris, 3), dtype=torch.int32, device=dev)
             face_keys = torch.empty((n_tris, 3), dtype=torch.int64, device=dev) if keys else None
+            face_cubes = torch.empty((n_tris,), dtype=torch.int64, device=dev) if keys else None
             stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
             _lib.check(self._lib.hv_mc_emit(
                 _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
@@ -107,8 +109,8 @@ class McPlan:
                 ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
                 self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
                 origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
-                _ptr(colors), _ptr(faces), _ptr(face_keys), _ptr(vert_keys), stream))
-        return DeviceMesh(verts, verts_voxel, normals, colors, faces, face_keys, vert_keys[:n_verts], 0.0, 0.0)
+                _ptr(colors), _ptr(faces), _ptr(face_keys), _ptr(face_cubes), _ptr(vert_keys), stream))
+        return DeviceMesh(verts, verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys[:n_verts], 0.0, 0.0)
 
 
 def check_surface(level, vmin, vmax, n_verts):

@@ -4,8 +4,10 @@ The reference is single-GPU (device 0 hard-coded, fusion.py:65); this layer is n
 independent given the frame, so integration needs no reduction: the global ``[X][Y][Z]`` volume is cut along z into
 ``world_size`` contiguous slabs, one dense C-order array per GPU.  Each rank integrates every frame into its slab; the
 slab's slice of the global z world-coordinate table makes the result identical to the unsharded volume.  The only
-data-path collective is the NCCL broadcast of each frame batch (packed texels) from rank 0, double-buffered so the
-broadcast of batch s+1 overlaps the integration of batch s; camera poses are tiny and broadcast once, up front.
+data-path collective of integration is the NCCL broadcast of each frame batch (packed texels) from rank 0,
+double-buffered so the broadcast of batch s+1 overlaps the integration of batch s; camera poses are tiny and broadcast
+once, up front.  Mesh extraction exchanges one boundary plane per seam and stitches the per-slab meshes on rank 0
+through global edge keys (``get_mesh``).
 
 One process per GPU (``torch.distributed``); ``world_size == 1`` degenerates to a plain ``TSDFVolume``.
 """
@@ -153,3 +155,118 @@ class SlabShardedTSDFVolume:
         parts = [None] * self.world_size if self.rank == 0 else None
         self._dist.gather_object(w, parts, dst=0)
         return np.concatenate(parts, axis=2) if self.rank == 0 else None
+
+    # ------------------------------------------------------------------ mesh extraction (seam-stitched marching cubes)
+    def _boundary_planes(self):
+        """(first, last) z-planes of this slab's tsdf and colour volumes as contiguous (X, Y) tensors."""
+        loc = self.local
+        Z = int(loc._local_dim[2])
+        t, c = loc._tsdf_vol_gpu, loc._color_vol_gpu
+        return (t[:, :, 0].contiguous(), t[:, :, Z - 1].contiguous(), c[:, :, 0].contiguous(),
+                c[:, :, Z - 1].contiguous())
+
+    def get_mesh(self):
+        """``TSDFVolume.get_mesh`` of the global volume on rank 0 (``None`` x4 elsewhere).
+
+        Each slab owns the cubes whose base voxel it holds; the planes either side of a seam are exchanged once
+        (one tsdf + one colour plane per direction), every rank emits its vertices with global edge keys and its faces
+        as key triples, and rank 0 resolves keys to indices.  The result is identical -- vertex and face order
+        included -- to the mesh of the unsharded volume.
+        """
+        from . import marching_cubes as mc
+        if self.world_size == 1:
+            return self.local.get_mesh()
+        dist, loc = self._dist, self.local
+        z0, z1 = self.ranges[self.rank]
+        Zg = self.global_dim[2]
+        first_t, last_t, first_c, last_c = self._boundary_planes()
+        halo = exchange_halo_planes(dist, self.rank, self.world_size,
+                                    {"tsdf": (first_t, last_t), "color": (first_c, last_c)})
+        X, Y, Z = (int(d) for d in loc._local_dim)
+        plan = mc.McPlan(loc._tsdf_vol_gpu, loc._color_vol_gpu, (X, Y, Z), loc._pitch, halo=halo, z_global_offset=z0,
+                         z_global_dim=Zg)
+        plan.count()
+        n_verts, n_tris, vmin, vmax = plan.read_totals()
+        stats = self._torch.tensor([float(n_verts), -vmin, vmax], dtype=self._torch.float64, device=loc.device)
+        counts = stats[:1].clone()
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        mc.check_surface(0.0, -float(stats[1].item()), float(stats[2].item()), int(counts[0].item()))
+        mesh = plan.emit(n_verts, n_tris, loc._voxel_size, loc._vol_origin, keys=True)
+        part = {"verts": mesh.verts, "normals": mesh.normals, "colors": mesh.colors, "vert_keys": mesh.vert_keys,
+                "face_keys": mesh.face_keys, "face_cubes": mesh.face_cubes}
+        parts = gather_mesh_parts(dist, self.rank, self.world_size, part, loc.device)
+        if self.rank != 0:
+            return None, None, None, None
+        verts, faces, normals, colors = stitch_mesh_parts(parts)
+        return verts.cpu().numpy(), faces.cpu().numpy(), normals.cpu().numpy(), colors.cpu().numpy()
+
+
+def exchange_halo_planes(dist, rank, world_size, planes):
+    """Seam exchange: every rank sends its first plane down and its last plane up.  ``planes`` maps a name to
+    (first, last); returns {name_lo, name_hi} tensors (absent at the ends of the stack)."""
+    import torch
+    ops, out = [], {}
+    for name, (first, last) in planes.items():
+        if rank > 0:
+            out[f"{name}_lo"] = torch.empty_like(first)
+            ops.append(dist.P2POp(dist.isend, first, rank - 1))
+            ops.append(dist.P2POp(dist.irecv, out[f"{name}_lo"], rank - 1))
+        if rank < world_size - 1:
+            out[f"{name}_hi"] = torch.empty_like(last)
+            ops.append(dist.P2POp(dist.isend, last, rank + 1))
+            ops.append(dist.P2POp(dist.irecv, out[f"{name}_hi"], rank + 1))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return out
+
+
+_PART_FIELDS = (("verts", 3, "float32"), ("normals", 3, "float32"), ("colors", 3, "uint8"), ("vert_keys", 0, "int64"),
+                ("face_keys", 3, "int64"), ("face_cubes", 0, "int64"))
+
+
+def gather_mesh_parts(dist, rank, world_size, part, device):
+    """Variable-length gather of the per-slab mesh parts to rank 0 (sizes by all_gather, payload by send/recv)."""
+    import torch
+    sizes = torch.tensor([part["vert_keys"].shape[0], part["face_cubes"].shape[0]], dtype=torch.int64, device=device)
+    all_sizes = [torch.zeros_like(sizes) for _ in range(world_size)]
+    dist.all_gather(all_sizes, sizes)
+    if rank != 0:
+        for name, _, _ in _PART_FIELDS:
+            if part[name].numel():
+                dist.send(part[name].contiguous(), dst=0)
+        return None
+    parts = [part]
+    for src in range(1, world_size):
+        nv, nf = (int(v) for v in all_sizes[src].tolist())
+        got = {}
+        for name, cols, dtype in _PART_FIELDS:
+            n = nf if name.startswith("face") else nv
+            shape = (n, cols) if cols else (n,)
+            got[name] = torch.empty(shape, dtype=getattr(torch, dtype), device=device)
+            if got[name].numel():
+                dist.recv(got[name], src=src)
+        parts.append(got)
+    return parts
+
+
+def stitch_mesh_parts(parts):
+    """Resolve the per-slab meshes into one: vertices sorted by global edge key (the whole-volume vertex order), faces
+    sorted by the cube that produced them (stable: the in-cube triangle order is kept), face keys -> vertex indices."""
+    import torch
+    keys = torch.cat([p["vert_keys"] for p in parts])
+    order = torch.argsort(keys, stable=True)
+    sorted_keys = keys[order]
+    assert bool((sorted_keys[1:] != sorted_keys[:-1]).all()), "a seam vertex was emitted by two slabs"
+    verts = torch.cat([p["verts"] for p in parts])[order]
+    normals = torch.cat([p["normals"] for p in parts])[order]
+    colors = torch.cat([p["colors"] for p in parts])[order]
+    face_keys = torch.cat([p["face_keys"] for p in parts])
+    face_cubes = torch.cat([p["face_cubes"] for p in parts])
+    forder = torch.argsort(face_cubes, stable=True)
+    face_keys = face_keys[forder]
+    idx = torch.searchsorted(sorted_keys, face_keys.reshape(-1))
+    assert bool((sorted_keys[idx.clamp(max=sorted_keys.numel() - 1)] == face_keys.reshape(-1)).all()), \
+        "a face references a vertex no slab emitted"
+    return verts, idx.reshape(-1, 3).to(torch.int32), normals, colors

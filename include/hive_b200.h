@@ -99,6 +99,8 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  *                are ((x*Y + y)*z_global_dim + z_global)*4 + axis, axis 3 = the extra vertex inside a cube.
  * faces / face_keys : exactly one is non-NULL: int32 [T][3] indices into this call's vertices (whole volume only), or
  *                uint64 [T][3] global vertex keys (shards: seam vertices belong to the neighbouring shard).
+ * face_cubes   : optional, with face_keys: uint64 [T] global linear index ((x*Y + y)*z_global_dim + z) of the cube each
+ *                face came from -- the merge key that restores the whole-volume face order when shards are stitched.
  * verts_voxel  : optional [V][3] positions in voxel units (what skimage itself returns); NULL to skip.
  * ---------------------------------------------------------------------------------------------------------- */
 int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, int64_t* h_bytes);
@@ -109,7 +111,7 @@ int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, co
                double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
                float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
                float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
-               unsigned long long* vert_keys, void* stream);
+               unsigned long long* face_cubes, unsigned long long* vert_keys, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Depth-to-mesh, batched over frames.  Replaces, for the per-frame foreground meshes of hive/pipeline.py:386-409,

@@ -78,7 +78,7 @@ class COracleTSDFVolume:
         return self._tsdf_vol_cpu, self._color_vol_cpu
 
 
-def marching_cubes(volume, level=0.0, with_keys=False):
+def marching_cubes(volume, level=0.0, with_keys=False, with_cubes=False):
     """``skimage.measure.marching_cubes(volume, level)`` as restated by mc_oracle.c (fusion.py:338; PARITY UNPINNED,
     see the header of that file).  Returns (verts f32 (V,3) in voxel units, faces i32 (F,3), normals f32 (V,3),
     values f32 (V,)) like skimage; ``with_keys`` appends the canonical edge key of every vertex."""
@@ -106,10 +106,13 @@ def marching_cubes(volume, level=0.0, with_keys=False):
         normals = np.empty((nv, 3), np.float32)
         keys = np.empty(nv, np.int64)
         faces = np.empty((nf, 3), np.int32)
-        L.hvo_mesh_copy(handle, _p(verts), _p(normals), _p(keys), _p(faces))
+        cubes = np.empty(nf, np.int64)
+        L.hvo_mesh_copy(handle, _p(verts), _p(normals), _p(keys), _p(faces), _p(cubes))
     finally:
         L.hvo_mc_free(handle)
     values = np.full(nv, np.float32(level))
+    if with_cubes:
+        return verts, faces, normals, values, keys, cubes
     return (verts, faces, normals, values, keys) if with_keys else (verts, faces, normals, values)
 
 
