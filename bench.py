@@ -309,6 +309,7 @@ def run_ours(args):
     import torch
     torch.cuda.set_device(local_rank)
     import torch.distributed as dist
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from hive_b200 import build as hv_build
