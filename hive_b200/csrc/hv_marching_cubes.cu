@@ -49,6 +49,8 @@ struct McGrid {
     uint2* gcount;        // [X*Y*G] (vertices, triangles)
     uint2* goff;          // [X*Y*G] exclusive prefix of gcount
     uint2* bsum;          // scratch of the scan
+    unsigned int* active; // [n_groups] compacted ids of the groups that own a vertex or a triangle (any order)
+    unsigned int* n_active;
     unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float)
     long long n_groups;
 };
@@ -234,7 +236,19 @@ __global__ void __launch_bounds__(256) mc_count_kernel(const McGrid g) {
         if ((kMcVarMult[variant] >> 48) & 15ull) m.w |= 1u << k;
     }
     g.gmask[gi] = m;
-    g.gcount[gi] = make_uint2(__popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w), ntri);
+    const unsigned int nv = __popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w);
+    g.gcount[gi] = make_uint2(nv, ntri);
+    // warp-aggregated append to the work list of mc_emit_kernel
+    const bool has_work = (nv | ntri) != 0u;
+    const unsigned int vote = __ballot_sync(__activemask(), has_work);
+    if (has_work) {
+        const int lane = threadIdx.x & 31;
+        const int leader = __ffs(vote) - 1;
+        unsigned int base0 = 0;
+        if (lane == leader) base0 = atomicAdd(g.n_active, (unsigned int)__popc(vote));
+        base0 = __shfl_sync(vote, base0, leader);
+        g.active[base0 + __popc(vote & ((1u << lane) - 1u))] = (unsigned int)gi;
+    }
 }
 
 // ---- 4. emit triangles and vertex keys ------------------------------------------------------------------------------
@@ -262,37 +276,43 @@ __device__ __forceinline__ int vertex_index(const McGrid& g, int x, int y, int z
     return r;
 }
 
+// One warp per active group, one lane per voxel / cube of the group.
 __global__ void __launch_bounds__(256) mc_emit_kernel(const McGrid g, const McEmit out) {
-    const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gi >= g.n_groups) return;
-    const uint2 cnt = g.gcount[gi];
-    if (cnt.x == 0 && cnt.y == 0) return;
-    const long long col = gi / g.G;
-    const int gq = (int)(gi - col * g.G);
-    const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
-    const int base = gq * 32;
-    const uint2 off = g.goff[gi];
+    const int lane = threadIdx.x & 31;
+    const unsigned int n_active = *g.n_active;
+    const unsigned int n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (unsigned int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_active; w += n_warps) {
+        const long long gi = g.active[w];
+        const uint2 cnt = g.gcount[gi];
+        const long long col = gi / g.G;
+        const int gq = (int)(gi - col * g.G);
+        const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+        const int zb = gq * 32 + lane;
+        const uint2 off = g.goff[gi];
+        const unsigned int low = (1u << lane) - 1u;
 
-    if (cnt.x) {  // keys of the vertices this group owns, ordered by (voxel, axis)
-        const uint4 m = g.gmask[gi];
-        unsigned int vi = off.x;
-        for (unsigned int rest = m.x | m.y | m.z | m.w; rest; rest &= rest - 1) {
-            const int k = __ffs(rest) - 1;
-            if ((m.x >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 0);
-            if ((m.y >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 1);
-            if ((m.z >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 2);
-            if ((m.w >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, base + k, 3);
+        if (cnt.x) {  // keys of the vertices this voxel owns; order inside the group: (voxel, axis)
+            const uint4 m = g.gmask[gi];
+            unsigned int vi = off.x + __popc(m.x & low) + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
+            if ((m.x >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 0);
+            if ((m.y >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 1);
+            if ((m.z >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 2);
+            if ((m.w >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 3);
         }
-    }
-    if (cnt.y) {
-        const CubeWords c = load_cube_words(g, x, y, gq);
-        size_t ti = off.y;
-        for (unsigned int rest = c.active; rest; rest &= rest - 1) {
-            const int k = __ffs(rest) - 1;
-            const int zb = base + k;
-            const int idx = cube_index(c, k);
-            const int variant = cube_variant_at(g, idx, x, y, zb);
-            const int ntri = kMcVarNtri[variant];
+        if (cnt.y) {
+            const CubeWords c = load_cube_words(g, x, y, gq);
+            int ntri = 0, variant = 0;
+            if ((c.active >> lane) & 1u) {
+                variant = cube_variant_at(g, cube_index(c, lane), x, y, zb);
+                ntri = kMcVarNtri[variant];
+            }
+            unsigned int inc = (unsigned int)ntri;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += up;
+            }
+            const size_t ti = (size_t)off.y + inc - (unsigned int)ntri;
             const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
             for (int t = 0; t < 3 * ntri; ++t) {
                 const int e = tri[t];
@@ -308,7 +328,6 @@ __global__ void __launch_bounds__(256) mc_emit_kernel(const McGrid g, const McEm
                     out.faces[3 * ti + t] = vertex_index(g, x + ox, y + oy, zb + oz, axis);
                 }
             }
-            ti += ntri;
         }
     }
 }
@@ -438,7 +457,7 @@ namespace {
 struct McLayout {
     long long n_groups;
     int G, Zb, n_scan_blocks;
-    size_t off_bits, off_gmask, off_gcount, off_goff, off_bsum, total;
+    size_t off_bits, off_gmask, off_gcount, off_goff, off_bsum, off_active, off_nactive, total;
 };
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -464,6 +483,10 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
     L->off_bsum = o;
     o = align_up(o + (size_t)L->n_scan_blocks * sizeof(uint2));
+    L->off_active = o;
+    o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
+    L->off_nactive = o;
+    o = align_up(o + sizeof(unsigned int));
     L->total = o;
     return HV_OK;
 }
@@ -501,6 +524,8 @@ int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float*
     g->gcount = reinterpret_cast<uint2*>(s + L->off_gcount);
     g->goff = reinterpret_cast<uint2*>(s + L->off_goff);
     g->bsum = reinterpret_cast<uint2*>(s + L->off_bsum);
+    g->active = reinterpret_cast<unsigned int*>(s + L->off_active);
+    g->n_active = reinterpret_cast<unsigned int*>(s + L->off_nactive);
     g->totals = nullptr;
     g->n_groups = L->n_groups;
     return HV_OK;
@@ -529,6 +554,7 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     cudaStream_t st = hv::as_stream(stream);
     const unsigned long long init[4] = {0ull, 0ull, 0x7fffffffull, 0x80000000ull};
     HV_CUDA(cudaMemcpyAsync(totals, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    HV_CUDA(cudaMemsetAsync(g.n_active, 0, sizeof(unsigned int), st));
     const int sms = hv::device_info().sm_count;
     hv::McSignGeom sg;
     sg.segs = (g.Zb + 127) / 128;
@@ -573,8 +599,14 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     g.Zg = z_global_dim;
     cudaStream_t st = hv::as_stream(stream);
     hv::McEmit em{faces, face_keys, vert_keys, face_keys ? face_cubes : nullptr};
-    const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
-    hv::mc_emit_kernel<<<group_blocks, 256, 0, st>>>(g, em);
+    // one warp per active group; the list length lives on the device, so size the grid by what the outputs imply
+    long long emit_warps = n_verts + n_tris;  // >= number of active groups
+    if (emit_warps > g.n_groups) emit_warps = g.n_groups;
+    const long long max_blocks = (long long)hv::device_info().sm_count * 16;
+    long long emit_blocks = (emit_warps + 7) / 8;
+    if (emit_blocks > max_blocks) emit_blocks = max_blocks;
+    if (emit_blocks < 1) emit_blocks = 1;
+    hv::mc_emit_kernel<<<(unsigned int)emit_blocks, 256, 0, st>>>(g, em);
     if (n_verts > 0) {
         hv::McVerts mv;
         mv.vert_keys = vert_keys;
