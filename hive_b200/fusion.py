@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes
 import logging
+import os
 
 import numpy as np
 
@@ -23,6 +24,10 @@ from . import _lib
 __all__ = ["TSDFVolume", "rigid_transform", "get_view_frustum", "meshwrite", "pcwrite", "FUSION_GPU_MODE"]
 
 FUSION_GPU_MODE = 1  # fusion.py:14 -- this implementation is GPU-only
+
+#: explicit integrate kernel (include/hive_b200.h: 0 default, 1 = v3 straight-line, 2 = pipelined without culling);
+#: profiling / A-B tests only, every kernel gives identical results
+INTEGRATE_KERNEL = int(os.environ.get("HV_INTEGRATE_KERNEL", "0"))
 
 
 def _ptr(t):
@@ -102,6 +107,7 @@ class TSDFVolume:
         self._stage = None  # lazily sized to the first frame
         self._frame_no = 0
         self.count_updates = False
+        self.integrate_kernel = INTEGRATE_KERNEL
         self._integer_weights, self._weight_sum = True, 0.0  # see _weights_flag
 
     # ------------------------------------------------------------------ reference-compatible attributes
@@ -210,7 +216,7 @@ class TSDFVolume:
             _ptr(self._tsdf_vol_gpu), _ptr(self._weight_vol_gpu), _ptr(self._color_vol_gpu),
             ctypes.cast(self._dims_c, ctypes.c_void_p), self._pitch, _ptr(self._wx), _ptr(self._wy), _ptr(self._wz),
             w2c.ctypes.data_as(ctypes.c_void_p), intr.ctypes.data_as(ctypes.c_void_p), _ptr(texels), H, W,
-            self._trunc_margin, float(obs_weight), self._weights_flag(obs_weight),
+            self._trunc_margin, float(obs_weight), self._weights_flag(obs_weight) | (self.integrate_kernel << 8),
             _ptr(self._updated) if self.count_updates else None,
             ctypes.c_void_p(stream.cuda_stream)))
 

@@ -12,10 +12,11 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-5
 
 
-def _run_pair(scene, n_frames, c_oracle, obs_weight=1.0, frames=None):
+def _run_pair(scene, n_frames, c_oracle, obs_weight=1.0, frames=None, kernel=0):
     from hive_b200.fusion import TSDFVolume
     gpu = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
     gpu.count_updates = True
+    gpu.integrate_kernel = kernel
     orc = c_oracle.COracleTSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
     total = 0
     for i in range(n_frames):
@@ -38,11 +39,12 @@ def _check(gpu, orc, total):
     return float(np.abs(tsdf - orc._tsdf_vol_cpu).max())
 
 
+@pytest.mark.parametrize("kernel", [0, 1, 2, 3, 4, 5])  # include/hive_b200.h HV_INTEGRATE_KERNEL_*
 @pytest.mark.parametrize("variant", ["room", "dense"])
 @pytest.mark.parametrize("config", ["tiny", "small"])
-def test_integrate_matches_oracle(config, variant, c_oracle):
+def test_integrate_matches_oracle(config, variant, kernel, c_oracle):
     scene = Scene(config, variant)
-    gpu, orc, total = _run_pair(scene, scene.num_frames, c_oracle)
+    gpu, orc, total = _run_pair(scene, scene.num_frames, c_oracle, kernel=kernel)
     assert total > 0
     _check(gpu, orc, total)
 
@@ -62,10 +64,11 @@ def test_integrate_many_frames_accumulation(c_oracle):
     _check(gpu, orc, total)
 
 
+@pytest.mark.parametrize("kernel", [1, 3, 5])
 @pytest.mark.parametrize("obs_weight", [2.0, 0.3])
-def test_integrate_obs_weight(obs_weight, c_oracle):
+def test_integrate_obs_weight(obs_weight, kernel, c_oracle):
     scene = Scene("tiny", "room")
-    gpu, orc, total = _run_pair(scene, 4, c_oracle, obs_weight=obs_weight)
+    gpu, orc, total = _run_pair(scene, 4, c_oracle, obs_weight=obs_weight, kernel=kernel)
     _check(gpu, orc, total)
 
 
@@ -112,3 +115,38 @@ def test_integrate_float64_inputs_like_demo(c_oracle):
     tsdf, color = gpu.get_volume()
     assert np.abs(tsdf - orc._tsdf_vol_cpu).max() <= TOL
     assert np.array_equal(color, orc._color_vol_cpu)
+
+
+@pytest.mark.parametrize("kernel", [3, 5])
+def test_integrate_culling_grazing_poses(kernel, c_oracle):
+    """Segment-level frustum culling must never drop a voxel the oracle updates: cameras whose image borders graze
+    the volume at shallow angles, cameras inside the volume (segments crossing the camera plane), large rotations."""
+    from hive_b200.synthetic import Frame
+    scene = Scene("small", "room")
+    rng = np.random.default_rng(7)
+    base = [scene.frame(i) for i in range(4)]
+    frames = []
+    for i in range(12):
+        fr = base[i % 4]
+        a = rng.uniform(-np.pi, np.pi, 3) * (0.15 if i < 4 else 1.0)
+        cx, sx, cy, sy, cz, sz = np.cos(a[0]), np.sin(a[0]), np.cos(a[1]), np.sin(a[1]), np.cos(a[2]), np.sin(a[2])
+        R = (np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]]) @ np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]]) @
+             np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]]))
+        pose = fr.pose.copy()
+        pose[:3, :3] = pose[:3, :3] @ R
+        pose[:3, 3] += rng.uniform(-1.5, 1.5, 3)
+        frames.append(Frame(fr.rgb, fr.depth, fr.mask, pose))
+    gpu, orc, total = _run_pair(scene, len(frames), c_oracle, frames=frames, kernel=kernel)
+    assert total > 0
+    _check(gpu, orc, total)
+
+
+@pytest.mark.parametrize("kernel", [1, 3, 5])
+def test_integrate_ragged_z(kernel, c_oracle):
+    """Z not a multiple of 4 or 128: the last float4 of a column is partial and the last segment is short."""
+    from hive_b200 import synthetic
+    synthetic.CONFIGS["ragged"] = dict(dim=(33, 29, 131), vs=0.04, frames=4, H=60, W=80)
+    scene = Scene("ragged", "room")
+    gpu, orc, total = _run_pair(scene, 4, c_oracle, kernel=kernel)
+    assert total > 0
+    _check(gpu, orc, total)
