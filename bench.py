@@ -359,7 +359,7 @@ def run_ours(args):
         "roofline": {
             "bound": "hbm", "achieved": main["achieved_gbs"], "peak": peak, "unit": "GB/s",
             "frac": main["achieved_gbs"] / peak, "traffic": None, "peak_source": peak_src,
-            "kernel": "hv::integrate_kernel",
+            "kernel": "hv::integrate_pipe_kernel",
             "algorithmic_bytes_per_launch": main["bytes_per_launch"],
             "avg_launch_ms": main["avg_launch_ms"],
             "frac_of_8000_spec": main["achieved_gbs"] / 8000.0,

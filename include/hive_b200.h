@@ -74,12 +74,11 @@ int hv_upload_frame(const float* h_depth, const uint8_t* h_rgb, int H, int W, fl
 #define HV_INTEGRATE_INTEGER_WEIGHTS 1
 /* Bits 8..15 of `flags` pick a kernel explicitly (profiling and A/B tests; every kernel gives identical results);
  * 0 = the library's default. */
-#define HV_INTEGRATE_KERNEL_V3 1         /* straight-line loop (profiles/r01_integrate_v3b.md) */
-#define HV_INTEGRATE_KERNEL_PIPE 2       /* projection of tile i+1 overlapped with the volume loads of tile i */
-#define HV_INTEGRATE_KERNEL_PIPE_CULL 3  /* + segment-level frustum culling */
-#define HV_INTEGRATE_KERNEL_ASYNC 4      /* volume loads in flight in shared memory (cp.async ring) */
-#define HV_INTEGRATE_KERNEL_ASYNC_CULL 5 /* + segment-level frustum culling */
-#define HV_INTEGRATE_KERNEL_DEFAULT HV_INTEGRATE_KERNEL_ASYNC_CULL
+#define HV_INTEGRATE_KERNEL_V3 1         /* straight-line loop over tiles (profiles/r01_integrate_v3b.md) */
+#define HV_INTEGRATE_KERNEL_PIPE 2       /* column walker: projection of tile i+1 overlapped with the loads of tile i */
+#define HV_INTEGRATE_KERNEL_PIPE_CULL 3  /* + segment-level frustum culling (switched off by the kernel itself when the
+                                            whole volume is inside the frustum) */
+#define HV_INTEGRATE_KERNEL_DEFAULT HV_INTEGRATE_KERNEL_PIPE_CULL
 #define HV_INTEGRATE_KERNEL(v) ((v) << 8)
 int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims, int64_t pitch,
                  const double* wx, const double* wy, const double* wz, const double* h_world2cam, const float* h_intr,

@@ -39,7 +39,7 @@ def _check(gpu, orc, total):
     return float(np.abs(tsdf - orc._tsdf_vol_cpu).max())
 
 
-@pytest.mark.parametrize("kernel", [0, 1, 2, 3, 4, 5])  # include/hive_b200.h HV_INTEGRATE_KERNEL_*
+@pytest.mark.parametrize("kernel", [0, 1, 2, 3])  # include/hive_b200.h HV_INTEGRATE_KERNEL_*
 @pytest.mark.parametrize("variant", ["room", "dense"])
 @pytest.mark.parametrize("config", ["tiny", "small"])
 def test_integrate_matches_oracle(config, variant, kernel, c_oracle):
@@ -64,7 +64,7 @@ def test_integrate_many_frames_accumulation(c_oracle):
     _check(gpu, orc, total)
 
 
-@pytest.mark.parametrize("kernel", [1, 3, 5])
+@pytest.mark.parametrize("kernel", [1, 2, 3])
 @pytest.mark.parametrize("obs_weight", [2.0, 0.3])
 def test_integrate_obs_weight(obs_weight, kernel, c_oracle):
     scene = Scene("tiny", "room")
@@ -117,7 +117,7 @@ def test_integrate_float64_inputs_like_demo(c_oracle):
     assert np.array_equal(color, orc._color_vol_cpu)
 
 
-@pytest.mark.parametrize("kernel", [3, 5])
+@pytest.mark.parametrize("kernel", [3])
 def test_integrate_culling_grazing_poses(kernel, c_oracle):
     """Segment-level frustum culling must never drop a voxel the oracle updates: cameras whose image borders graze
     the volume at shallow angles, cameras inside the volume (segments crossing the camera plane), large rotations."""
@@ -141,7 +141,7 @@ def test_integrate_culling_grazing_poses(kernel, c_oracle):
     _check(gpu, orc, total)
 
 
-@pytest.mark.parametrize("kernel", [1, 3, 5])
+@pytest.mark.parametrize("kernel", [1, 2, 3])
 def test_integrate_ragged_z(kernel, c_oracle):
     """Z not a multiple of 4 or 128: the last float4 of a column is partial and the last segment is short."""
     from hive_b200 import synthetic
