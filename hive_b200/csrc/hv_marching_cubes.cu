@@ -276,59 +276,85 @@ __device__ __forceinline__ int vertex_index(const McGrid& g, int x, int y, int z
     return r;
 }
 
-// One warp per active group, one lane per voxel / cube of the group.
-__global__ void __launch_bounds__(256) mc_emit_kernel(const McGrid g, const McEmit out) {
-    const int lane = threadIdx.x & 31;
-    const unsigned int n_active = *g.n_active;
-    const unsigned int n_warps = (gridDim.x * blockDim.x) >> 5;
-    for (unsigned int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_active; w += n_warps) {
-        const long long gi = g.active[w];
-        const uint2 cnt = g.gcount[gi];
-        const long long col = gi / g.G;
-        const int gq = (int)(gi - col * g.G);
-        const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
-        const int zb = gq * 32 + lane;
-        const uint2 off = g.goff[gi];
-        const unsigned int low = (1u << lane) - 1u;
+// Writes the triangles of one cube (x, y, zb) with tiling `variant` at triangle offset ti.
+__device__ __forceinline__ void emit_cube(const McGrid& g, const McEmit& out, int x, int y, int zb, int variant, size_t ti) {
+    const int n = 3 * (int)kMcVarNtri[variant];
+    const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
+    for (int t = 0; t < n; ++t) {
+        const int e = tri[t];
+        int ox = 0, oy = 0, oz = 0, axis = 3;
+        if (e < 12) {
+            ox = kMcEdgeOwner[4 * e], oy = kMcEdgeOwner[4 * e + 1], oz = kMcEdgeOwner[4 * e + 2];
+            axis = kMcEdgeOwner[4 * e + 3];
+        }
+        if (out.face_keys) {
+            out.face_keys[3 * ti + t] = vertex_key(g, x + ox, y + oy, zb + oz, axis);
+            if (out.face_cubes && t % 3 == 0) out.face_cubes[ti + t / 3] = vertex_key(g, x, y, zb, 0) >> 2;
+        } else {
+            out.faces[3 * ti + t] = vertex_index(g, x + ox, y + oy, zb + oz, axis);
+        }
+    }
+}
 
-        if (cnt.x) {  // keys of the vertices this voxel owns; order inside the group: (voxel, axis)
-            const uint4 m = g.gmask[gi];
-            unsigned int vi = off.x + __popc(m.x & low) + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
-            if ((m.x >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 0);
-            if ((m.y >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 1);
-            if ((m.z >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 2);
-            if ((m.w >> lane) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 3);
-        }
-        if (cnt.y) {
-            const CubeWords c = load_cube_words(g, x, y, gq);
-            int ntri = 0, variant = 0;
-            if ((c.active >> lane) & 1u) {
-                variant = cube_variant_at(g, cube_index(c, lane), x, y, zb);
-                ntri = kMcVarNtri[variant];
-            }
-            unsigned int inc = (unsigned int)ntri;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += up;
-            }
-            const size_t ti = (size_t)off.y + inc - (unsigned int)ntri;
-            const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
-            for (int t = 0; t < 3 * ntri; ++t) {
-                const int e = tri[t];
-                int ox = 0, oy = 0, oz = 0, axis = 3;
-                if (e < 12) {
-                    ox = kMcEdgeOwner[4 * e], oy = kMcEdgeOwner[4 * e + 1], oz = kMcEdgeOwner[4 * e + 2];
-                    axis = kMcEdgeOwner[4 * e + 3];
-                }
-                if (out.face_keys) {
-                    out.face_keys[3 * ti + t] = vertex_key(g, x + ox, y + oy, zb + oz, axis);
-                    if (out.face_cubes && t % 3 == 0) out.face_cubes[ti + t / 3] = vertex_key(g, x, y, zb, 0) >> 2;
-                } else {
-                    out.faces[3 * ti + t] = vertex_index(g, x + ox, y + oy, zb + oz, axis);
+// A block takes 256 entries of the active-group list.  Phase 1, one thread per group: the keys of the vertices the
+// group owns, and one record per surface cube (position, tiling, triangle offset) pushed into a shared-memory list.
+// Phase 2, one thread per record: the triangles.  (r01: with one warp per group and one lane per cube, 75-90 % of the
+// lanes idled in the triangle loop -- a group of 32 cubes is crossed by the surface in only a handful of them.)
+constexpr int kEmitThreads = 256;
+constexpr int kEmitCap = 2048;  // records per round; cubes beyond it are written by their phase-1 thread directly
+
+__global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, const McEmit out) {
+    __shared__ uint4 s_list[kEmitCap];
+    __shared__ unsigned int s_n;
+    const unsigned int n_active = *g.n_active;
+    for (unsigned int base = blockIdx.x * kEmitThreads; base < n_active; base += gridDim.x * kEmitThreads) {
+        if (threadIdx.x == 0) s_n = 0u;
+        __syncthreads();
+        const unsigned int a = base + threadIdx.x;
+        if (a < n_active) {
+            const long long gi = g.active[a];
+            const uint2 cnt = g.gcount[gi];
+            const uint2 off = g.goff[gi];
+            const long long col = gi / g.G;
+            const int gq = (int)(gi - col * g.G);
+            const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+            if (cnt.x) {  // vertex keys, order inside the group: (voxel, axis)
+                const uint4 m = g.gmask[gi];
+                size_t vi = off.x;
+                for (unsigned int rest = m.x | m.y | m.z | m.w; rest; rest &= rest - 1) {
+                    const int k = __ffs(rest) - 1;
+                    const int zb = gq * 32 + k;
+                    if ((m.x >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 0);
+                    if ((m.y >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 1);
+                    if ((m.z >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 2);
+                    if ((m.w >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 3);
                 }
             }
+            if (cnt.y) {
+                const CubeWords c = load_cube_words(g, x, y, gq);
+                unsigned int toff = off.y;
+                for (unsigned int rest = c.active; rest; rest &= rest - 1) {
+                    const int k = __ffs(rest) - 1;
+                    const int zb = gq * 32 + k;
+                    const int variant = cube_variant_at(g, cube_index(c, k), x, y, zb);
+                    const unsigned int ntri = kMcVarNtri[variant];
+                    if (ntri == 0u) continue;
+                    const unsigned int slot = atomicAdd(&s_n, 1u);
+                    if (slot < (unsigned int)kEmitCap)
+                        s_list[slot] = make_uint4((unsigned int)x, (unsigned int)y, (unsigned int)zb | ((unsigned int)variant << 22), toff);
+                    else
+                        emit_cube(g, out, x, y, zb, variant, toff);
+                    toff += ntri;
+                }
+            }
         }
+        __syncthreads();
+        const unsigned int n = min(s_n, (unsigned int)kEmitCap);
+        for (unsigned int i = threadIdx.x; i < n; i += kEmitThreads) {
+            const uint4 r = s_list[i];
+            emit_cube(g, out, (int)r.x, (int)r.y, (int)(r.z & 0x3fffffu), (int)(r.z >> 22), r.w);
+        }
+        __syncthreads();
     }
 }
 
@@ -347,20 +373,28 @@ struct McVerts {
 // Adds `mult` times this cube's interpolated down-hill gradient at edge `e` (12 = centre) to the float32 accumulator.
 __device__ __forceinline__ void add_cube_gradient(const double v[8], int e, int mult, float acc[3]) {
     if (mult == 0) return;
+    // weights 1 / (FLT_EPSILON + |v|): only the edge's two end corners are needed for e < 12 (all 8 for the centre);
+    // computing all eight per cube cost 32 double divisions per vertex (r01 ncu: mc_vertex_kernel 100 us)
     double w[8];
+    int lo = 0, hi = 0, clo = 0, chi = 0;
+    if (e < 12) {
+        lo = kMcEdgeCorner[2 * e], hi = kMcEdgeCorner[2 * e + 1];
+        clo = kMcCornerOff[3 * lo] * 4 + kMcCornerOff[3 * lo + 1] * 2 + kMcCornerOff[3 * lo + 2];
+        chi = kMcCornerOff[3 * hi] * 4 + kMcCornerOff[3 * hi + 1] * 2 + kMcCornerOff[3 * hi + 2];
+        w[0] = 1.0 / ((double)FLT_EPSILON + fabs(v[lo]));
+        w[1] = 1.0 / ((double)FLT_EPSILON + fabs(v[hi]));
+    } else {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) w[i] = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
+        for (int i = 0; i < 8; ++i) w[i] = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
+    }
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const int bitk = 4 >> k;  // offset bit of axis k in the d0*4 + d1*2 + d2 code
         double gk;
         if (e < 12) {
-            const int lo = kMcEdgeCorner[2 * e], hi = kMcEdgeCorner[2 * e + 1];
-            const int clo = kMcCornerOff[3 * lo] * 4 + kMcCornerOff[3 * lo + 1] * 2 + kMcCornerOff[3 * lo + 2];
-            const int chi = kMcCornerOff[3 * hi] * 4 + kMcCornerOff[3 * hi + 1] * 2 + kMcCornerOff[3 * hi + 2];
             const double g_lo = v[kMcCornerAt[clo & ~bitk]] - v[kMcCornerAt[clo | bitk]];
             const double g_hi = v[kMcCornerAt[chi & ~bitk]] - v[kMcCornerAt[chi | bitk]];
-            gk = __dadd_rn(__dmul_rn(g_lo, w[lo]), __dmul_rn(g_hi, w[hi]));
+            gk = __dadd_rn(__dmul_rn(g_lo, w[0]), __dmul_rn(g_hi, w[1]));
         } else {
             gk = 0.0;
             for (int i = 0; i < 8; ++i) {
@@ -470,7 +504,7 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     L->Zb = (int)Z + (lo ? 1 : 0) + (hi ? 1 : 0);
     L->G = (L->Zb + 31) / 32;
     L->n_groups = (long long)X * Y * L->G;
-    HV_REQUIRE(L->n_groups < (1ll << 40), "marching cubes: volume too large");
+    HV_REQUIRE(L->n_groups < (1ll << 40) && L->Zb < (1 << 22), "marching cubes: volume too large");
     L->n_scan_blocks = (int)((L->n_groups + hv::kScanTile - 1) / hv::kScanTile);
     size_t o = 0;
     L->off_gmask = o;  // 16-byte elements first
@@ -599,14 +633,14 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     g.Zg = z_global_dim;
     cudaStream_t st = hv::as_stream(stream);
     hv::McEmit em{faces, face_keys, vert_keys, face_keys ? face_cubes : nullptr};
-    // one warp per active group; the list length lives on the device, so size the grid by what the outputs imply
-    long long emit_warps = n_verts + n_tris;  // >= number of active groups
-    if (emit_warps > g.n_groups) emit_warps = g.n_groups;
-    const long long max_blocks = (long long)hv::device_info().sm_count * 16;
-    long long emit_blocks = (emit_warps + 7) / 8;
+    // one thread per active group; the list length lives on the device, so size the grid by what the outputs imply
+    long long emit_groups = n_verts + n_tris;  // >= number of active groups
+    if (emit_groups > g.n_groups) emit_groups = g.n_groups;
+    const long long max_blocks = (long long)hv::device_info().sm_count * 8;
+    long long emit_blocks = (emit_groups + hv::kEmitThreads - 1) / hv::kEmitThreads;
     if (emit_blocks > max_blocks) emit_blocks = max_blocks;
     if (emit_blocks < 1) emit_blocks = 1;
-    hv::mc_emit_kernel<<<(unsigned int)emit_blocks, 256, 0, st>>>(g, em);
+    hv::mc_emit_kernel<<<(unsigned int)emit_blocks, hv::kEmitThreads, 0, st>>>(g, em);
     if (n_verts > 0) {
         hv::McVerts mv;
         mv.vert_keys = vert_keys;

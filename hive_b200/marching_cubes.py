@@ -9,6 +9,7 @@ There is no CPU fallback.
 from __future__ import annotations
 
 import ctypes
+import threading
 from dataclasses import dataclass
 
 import numpy as np
@@ -46,6 +47,17 @@ class DeviceMesh:
     def to_host(self):
         return (self.verts.cpu().numpy(), self.faces.cpu().numpy(), self.normals.cpu().numpy(),
                 self.colors.cpu().numpy())
+
+
+_PINNED = {}
+
+
+def _pinned_totals(torch, device):
+    key = (threading.get_ident(), str(device))
+    buf = _PINNED.get(key)
+    if buf is None:
+        buf = _PINNED[key] = torch.empty(4, dtype=torch.int64).pin_memory()
+    return buf
 
 
 class McPlan:
@@ -86,7 +98,14 @@ class McPlan:
         return self.totals
 
     def read_totals(self):
-        n_verts, n_tris, kmin, kmax = (int(v) for v in self.totals.cpu().tolist())
+        """The one host round trip of an extraction (output sizes are data dependent): async D2H of the four counters
+        into a cached pinned buffer, then a stream synchronise (a pageable ``.cpu()`` costs several times more)."""
+        torch = self._torch
+        host = _pinned_totals(torch, self.device)
+        with torch.cuda.device(self.device):
+            host.copy_(self.totals, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist())
         return n_verts, n_tris, _key_to_float(kmin), _key_to_float(kmax)
 
     def emit(self, n_verts, n_tris, voxel_size, origin, want_voxel=False, keys=False) -> DeviceMesh:
