@@ -27,7 +27,8 @@ struct D2mGrid {
     const uint8_t* diag;   // [B][H][W] or null; bit 0: quad owned by the pixel uses the anti-diagonal, bit 1: hole at the
                            // pixel is split N-S
     int B, H, W;
-    int words_per_frame;   // ceil(H*W / 32)
+    int wpr;               // 32-pixel words per image row: ceil(W / 32); word (b, v, c) holds pixels u = 32 c + lane
+    int words_per_frame;   // H * wpr
     long long n_words;
     float max_depth_distance;
     int bridges;
@@ -43,13 +44,72 @@ struct PixelFaces {
     int2 p[4][3];  // pixel coordinates (u, v) of the corners, winding with negative signed area in (u, v)
 };
 
-__device__ __forceinline__ bool d2m_valid(const D2mGrid& g, int b, int u, int v, float& d) {
-    d = 0.0f;
-    if (u < 0 || v < 0 || u >= g.W || v >= g.H) return false;
+// Depth of pixel (u, v) if it is a vertex (inside the image, mask set, depth > 0: geometric.py:117), else 0.
+__device__ __forceinline__ float d2m_vdepth(const D2mGrid& g, int b, int u, int v) {
+    if (u < 0 || v < 0 || u >= g.W || v >= g.H) return 0.0f;
     const size_t i = ((size_t)b * g.H + v) * g.W + u;
-    if (g.mask && !g.mask[i]) return false;
-    d = __ldg(g.depth + i);
-    return d > 0.0f;
+    if (g.mask && !g.mask[i]) return 0.0f;
+    const float d = __ldg(g.depth + i);
+    return d > 0.0f ? d : 0.0f;
+}
+
+// The neighbourhood values a pixel's faces depend on.  A warp owns one 32-pixel word column and walks kD2mRows image
+// rows downwards, keeping three rows in registers: every row is loaded once per warp (each lane its own pixel, coalesced;
+// lanes 0 and 1 the halo pixels right and left of the word), horizontal neighbours come by shuffle, the row below
+// becomes the current row of the next step.  (r01: one thread per pixel re-loading up to eight neighbours -- mask byte
+// + depth each, behind a 64-bit index and an integer division -- made d2m_count_kernel 18x slower than its HBM time.)
+constexpr int kD2mRows = 8;
+
+struct Row {
+    float c;               // vertex depth of the lane's pixel, or 0
+    float halo_r, halo_l;  // warp-uniform: pixels 32 cw + 32 and 32 cw - 1 of the row
+    unsigned int bits;     // warp-uniform: vertices of the word
+};
+
+__device__ __forceinline__ Row load_row(const D2mGrid& g, int b, int v, int cw, int lane) {
+    Row r;
+    // the four loads (own depth + mask, halo depth + mask) are independent and issued together
+    const int u = cw * 32 + lane;
+    const int hu = lane == 0 ? cw * 32 + 32 : cw * 32 - 1;
+    const bool row_in = v >= 0 && v < g.H;
+    const bool in = row_in && u < g.W, hin = row_in && lane < 2 && hu >= 0 && hu < g.W;
+    const size_t row = ((size_t)b * g.H + (row_in ? v : 0)) * g.W;
+    float d = 0.0f, dh = 0.0f;
+    unsigned int m = 1u, mh = 1u;
+    if (in) d = __ldg(g.depth + row + u);
+    if (hin) dh = __ldg(g.depth + row + hu);
+    if (g.mask) {
+        if (in) m = __ldg(g.mask + row + u);
+        if (hin) mh = __ldg(g.mask + row + hu);
+    }
+    r.c = (m != 0u && d > 0.0f) ? d : 0.0f;
+    const float halo = (mh != 0u && dh > 0.0f) ? dh : 0.0f;
+    r.halo_r = __shfl_sync(0xffffffffu, halo, 0);
+    r.halo_l = __shfl_sync(0xffffffffu, halo, 1);
+    r.bits = __ballot_sync(0xffffffffu, r.c > 0.0f);
+    return r;
+}
+
+struct Hood {
+    float c, e, w, s, se, n;  // centre, (u+1, v), (u-1, v), (u, v+1), (u+1, v+1), (u, v-1): vertex depth or 0
+};
+
+// warp-uniform: no vertex in rows v, v+1 of the word and its halo => no pixel of the word owns a face
+__device__ __forceinline__ bool hood_empty(const Row& cur, const Row& next) {
+    return (cur.bits | next.bits) == 0u && !(cur.halo_r > 0.0f) && !(cur.halo_l > 0.0f) && !(next.halo_r > 0.0f);
+}
+
+__device__ __forceinline__ Hood make_hood(const Row& prev, const Row& cur, const Row& next, int lane) {
+    Hood h;
+    h.c = cur.c;
+    h.s = next.c;
+    h.n = prev.c;
+    const float e = __shfl_down_sync(0xffffffffu, cur.c, 1), se = __shfl_down_sync(0xffffffffu, next.c, 1),
+                w = __shfl_up_sync(0xffffffffu, cur.c, 1);
+    h.e = lane == 31 ? cur.halo_r : e;
+    h.se = lane == 31 ? next.halo_r : se;
+    h.w = lane == 0 ? cur.halo_l : w;
+    return h;
 }
 
 __device__ __forceinline__ bool depth_ok(const D2mGrid& g, float a, float b, float c) {
@@ -71,12 +131,13 @@ __device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, bool 
 
 // Faces owned by pixel (u, v): the quad whose top-left corner it is, and -- if the pixel itself is absent -- the hole
 // around it.
-__device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int v, bool self_valid, float d_self,
-                                            bool keep_coords, PixelFaces& f) {
+__device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int v, const Hood& h, bool keep_coords,
+                                            PixelFaces& f) {
     f.n = 0;
+    if (u >= g.W) return;
     const unsigned int ov = g.diag ? g.diag[((size_t)b * g.H + v) * g.W + u] : 0u;
-    float db, dc, dd;
-    const bool vb = d2m_valid(g, b, u + 1, v, db), vc = d2m_valid(g, b, u, v + 1, dc), vd = d2m_valid(g, b, u + 1, v + 1, dd);
+    const float d_self = h.c, db = h.e, dc = h.s, dd = h.se;
+    const bool self_valid = d_self > 0.0f, vb = db > 0.0f, vc = dc > 0.0f, vd = dd > 0.0f;
     const int2 A = make_int2(u, v), Bp = make_int2(u + 1, v), C = make_int2(u, v + 1), D = make_int2(u + 1, v + 1);
     const int nq = (int)self_valid + (int)vb + (int)vc + (int)vd;
     if (nq == 4) {
@@ -95,9 +156,8 @@ __device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int 
         else push_face(g, f, keep_coords, A, d_self, D, dd, Bp, db);
     }
     if (!self_valid && g.bridges) {
-        float dn, de, ds, dw;
-        const bool vn = d2m_valid(g, b, u, v - 1, dn), ve = d2m_valid(g, b, u + 1, v, de), vs = d2m_valid(g, b, u, v + 1, ds),
-                   vw = d2m_valid(g, b, u - 1, v, dw);
+        const float dn = h.n, de = h.e, ds = h.s, dw = h.w;
+        const bool vn = dn > 0.0f, ve = de > 0.0f, vs = ds > 0.0f, vw = dw > 0.0f;
         const int2 N = make_int2(u, v - 1), E = make_int2(u + 1, v), S = make_int2(u, v + 1), Wp = make_int2(u - 1, v);
         const int nh = (int)vn + (int)ve + (int)vs + (int)vw;
         if (nh == 4) {
@@ -118,31 +178,37 @@ __device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int 
     }
 }
 
-// one warp per 32-pixel word
-__global__ void __launch_bounds__(256) d2m_count_kernel(const D2mGrid g) {
+// One warp per word column cw and kD2mRows rows; the grid is (words of a row / warps per block, rows / kD2mRows, B), so
+// no thread divides (r01: a 64-bit division + a 32-bit one per thread were a third of the kernel).
+constexpr int kD2mThreads = 128;
+
+__global__ void __launch_bounds__(kD2mThreads) d2m_count_kernel(const D2mGrid g) {
     const int lane = threadIdx.x & 31;
-    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (w >= g.n_words) return;
-    const int b = (int)(w / g.words_per_frame);
-    const int i = (int)(w - (long long)b * g.words_per_frame) * 32 + lane;
-    bool valid = false;
-    unsigned int nf = 0;
-    if (i < g.H * g.W) {
-        const int v = i / g.W, u = i - v * g.W;
-        float d;
-        valid = d2m_valid(g, b, u, v, d);
-        if (!g.verts_only) {
+    const int cw = (int)blockIdx.x * (kD2mThreads / 32) + (int)(threadIdx.x >> 5);
+    if (cw >= g.wpr) return;
+    const int b = (int)blockIdx.z;
+    const int v0 = (int)blockIdx.y * kD2mRows, v1 = min(v0 + kD2mRows, g.H);
+    const bool faces = !g.verts_only;
+    Row prev = load_row(g, b, v0 - 1, cw, lane), cur = load_row(g, b, v0, cw, lane);
+    size_t w = (size_t)b * g.words_per_frame + (size_t)v0 * g.wpr + cw;
+    for (int v = v0; v < v1; ++v) {
+        const Row next = load_row(g, b, v + 1, cw, lane);
+        unsigned int nf = 0;
+        if (faces && !hood_empty(cur, next)) {
+            const Hood h = make_hood(prev, cur, next, lane);
             PixelFaces f;
-            pixel_faces(g, b, u, v, valid, d, false, f);
+            pixel_faces(g, b, cw * 32 + lane, v, h, false, f);
             nf = (unsigned int)f.n;
-        }
-    }
-    const unsigned int bits = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) nf += __shfl_xor_sync(0xffffffffu, nf, o);
-    if (lane == 0) {
-        g.wbits[w] = bits;
-        g.wcount[w] = make_uint2(__popc(bits), nf);
+            for (int o = 16; o > 0; o >>= 1) nf += __shfl_xor_sync(0xffffffffu, nf, o);
+        }
+        if (lane == 0) {
+            g.wbits[w] = cur.bits;
+            g.wcount[w] = make_uint2(__popc(cur.bits), nf);
+        }
+        w += g.wpr;
+        prev = cur;
+        cur = next;
     }
 }
 
@@ -157,22 +223,27 @@ struct D2mOut {
     unsigned long long n_verts, n_faces;
 };
 
-__device__ __forceinline__ int d2m_rank(const D2mGrid& g, int b, int2 p, unsigned int vbase) {
-    const int i = p.y * g.W + p.x;
-    const size_t w = (size_t)b * g.words_per_frame + (i >> 5);
-    return (int)(g.woff[w].x + __popc(g.wbits[w] & ((1u << (i & 31)) - 1u)) - vbase);
+// Frame-local vertex id (row-major rank among the frame's vertices, np.nonzero order, geometric.py:121) of a face corner
+// (pu, pv) in the 3x3 neighbourhood of the warp's word: from the vertex bits of the word in that row and the rank of the
+// word's first pixel -- all in registers.  A corner left of the word is the last vertex before it, a corner right of
+// it the first vertex after it (a face corner is always a vertex).
+__device__ __forceinline__ int corner_rank(int pu, int word_u0, unsigned int row_bits, unsigned int row_first_rank) {
+    const int du = pu - word_u0;
+    if (du < 0) return (int)row_first_rank - 1;
+    if (du >= 32) return (int)(row_first_rank + __popc(row_bits));
+    return (int)(row_first_rank + __popc(row_bits & ((1u << du) - 1u)));
 }
 
-__global__ void __launch_bounds__(256) d2m_emit_kernel(const D2mGrid g, const D2mOut out) {
+__global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, const D2mOut out) {
     const int lane = threadIdx.x & 31;
-    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (w >= g.n_words) return;
-    const int b = (int)(w / g.words_per_frame);
-    const int wf = (int)(w - (long long)b * g.words_per_frame);
-    const uint2 cnt = g.wcount[w];
-    const uint2 off = g.woff[w];
-    const unsigned int vbase = g.woff[(size_t)b * g.words_per_frame].x;
-    if (wf == 0 && lane == 0) {
+    const int cw = (int)blockIdx.x * (kD2mThreads / 32) + (int)(threadIdx.x >> 5);
+    if (cw >= g.wpr) return;
+    const int b = (int)blockIdx.z;
+    const int v0 = (int)blockIdx.y * kD2mRows, v1 = min(v0 + kD2mRows, g.H);
+    const size_t wframe = (size_t)b * g.words_per_frame;
+    const size_t w0 = wframe + (size_t)v0 * g.wpr + cw;
+    if (v0 == 0 && cw == 0 && lane == 0) {
+        const uint2 off = g.woff[wframe];
         out.frame_off[2 * b] = off.x;
         out.frame_off[2 * b + 1] = off.y;
         if (b == g.B - 1) {
@@ -180,47 +251,81 @@ __global__ void __launch_bounds__(256) d2m_emit_kernel(const D2mGrid g, const D2
             out.frame_off[2 * g.B + 1] = (long long)out.n_faces;
         }
     }
-    if (cnt.x == 0 && cnt.y == 0) return;
-    const int i = wf * 32 + lane;
-    const bool in = i < g.H * g.W;
-    const int v = in ? i / g.W : 0, u = in ? i - v * g.W : 0;
-    float d = 0.0f;
-    const bool valid = in && d2m_valid(g, b, u, v, d);
-    PixelFaces f;
-    f.n = 0;
-    if (in && cnt.y) pixel_faces(g, b, u, v, valid, d, true, f);
+    // counts of the warp's words (lane r holds row v0 + r): most word columns are empty and leave here
+    uint2 my_cnt = make_uint2(0u, 0u);
+    if (lane < v1 - v0) my_cnt = g.wcount[w0 + (size_t)lane * g.wpr];
+    const unsigned int has_v = __ballot_sync(0xffffffffu, my_cnt.x != 0u), has_f = __ballot_sync(0xffffffffu, my_cnt.y != 0u);
+    if ((has_v | has_f) == 0u) return;
+    const unsigned int vbase = g.woff[wframe].x;
 
-    if (valid) {  // image2world, hive/geometric.py:200-204 (float64)
-        const size_t vi = off.x + __popc(g.wbits[w] & ((1u << lane) - 1u));
-        const double* R = out.cams + 12 * (size_t)b;
-        const double* t = R + 9;
-        const double du = (double)u, dv = (double)v, dd = (double)d;
-        double X[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const double pc = fma(out.Kinv[3 * k + 2], 1.0, fma(out.Kinv[3 * k + 1], dv, __dmul_rn(out.Kinv[3 * k], du)));
-            X[k] = __dsub_rn(__dmul_rn(dd, pc), t[k]);
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k)  // R^T @ X
-            out.verts[3 * vi + k] = fma(R[6 + k], X[2], fma(R[3 + k], X[1], __dmul_rn(R[k], X[0])));
-        if (out.points2d) {
-            out.points2d[2 * vi] = u;
-            out.points2d[2 * vi + 1] = v;
-        }
-        if (out.vdepth) out.vdepth[vi] = d;
+    Row prev, cur, next;
+    unsigned int first_prev = 0u, first_cur = 0u, first_next = 0u;  // frame-local rank of the first pixel of the word per row
+    if (has_f) {
+        prev = load_row(g, b, v0 - 1, cw, lane);
+        cur = load_row(g, b, v0, cw, lane);
+        if (v0 > 0) first_prev = g.woff[w0 - g.wpr].x - vbase;
+        first_cur = g.woff[w0].x - vbase;
     }
-    if (cnt.y) {
-        unsigned int inc = (unsigned int)f.n;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += up;
+    const int u = cw * 32 + lane;
+    for (int r = 0; r < v1 - v0; ++r) {
+        const int v = v0 + r;
+        const size_t w = w0 + (size_t)r * g.wpr;
+        if (has_f) {
+            next = load_row(g, b, v + 1, cw, lane);
+            if (v + 1 < g.H) first_next = g.woff[w + g.wpr].x - vbase;
         }
-        size_t fi = (size_t)off.y + inc - (unsigned int)f.n;
-        for (int k = 0; k < f.n; ++k, ++fi)
+        if (((has_v | has_f) >> r) & 1u) {
+            const uint2 off = g.woff[w];
+            if ((has_f >> r) & 1u) {
+                const Hood h = make_hood(prev, cur, next, lane);
+                PixelFaces f;
+                pixel_faces(g, b, u, v, h, true, f);
+                unsigned int inc = (unsigned int)f.n;
 #pragma unroll
-            for (int c = 0; c < 3; ++c) out.faces[3 * fi + c] = d2m_rank(g, b, f.p[k][c], vbase);
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += up;
+                }
+                size_t fi = (size_t)off.y + inc - (unsigned int)f.n;
+                for (int k = 0; k < f.n; ++k, ++fi)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const int2 q = f.p[k][c];
+                        const int dv = q.y - v;
+                        const unsigned int rb = dv < 0 ? prev.bits : (dv > 0 ? next.bits : cur.bits);
+                        const unsigned int rf = dv < 0 ? first_prev : (dv > 0 ? first_next : first_cur);
+                        out.faces[3 * fi + c] = corner_rank(q.x, cw * 32, rb, rf);
+                    }
+            }
+            const unsigned int bits = g.wbits[w];
+            if ((bits >> lane) & 1u) {  // image2world, hive/geometric.py:200-204 (float64)
+                const float d = __ldg(g.depth + ((size_t)b * g.H + v) * g.W + u);
+                const size_t vi = off.x + __popc(bits & ((1u << lane) - 1u));
+                const double* R = out.cams + 12 * (size_t)b;
+                const double* t = R + 9;
+                const double du = (double)u, dv = (double)v, dd = (double)d;
+                double X[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const double pc = fma(out.Kinv[3 * k + 2], 1.0, fma(out.Kinv[3 * k + 1], dv, __dmul_rn(out.Kinv[3 * k], du)));
+                    X[k] = __dsub_rn(__dmul_rn(dd, pc), t[k]);
+                }
+#pragma unroll
+                for (int k = 0; k < 3; ++k)  // R^T @ X
+                    out.verts[3 * vi + k] = fma(R[6 + k], X[2], fma(R[3 + k], X[1], __dmul_rn(R[k], X[0])));
+                if (out.points2d) {
+                    out.points2d[2 * vi] = u;
+                    out.points2d[2 * vi + 1] = v;
+                }
+                if (out.vdepth) out.vdepth[vi] = d;
+            }
+        }
+        if (has_f) {
+            prev = cur;
+            cur = next;
+            first_prev = first_cur;
+            first_cur = first_next;
+        }
     }
 }
 
@@ -319,7 +424,7 @@ __global__ void __launch_bounds__(256) filter_faces_kernel(const FilterArgs a) {
 namespace {
 
 struct D2mLayout {
-    int words_per_frame;
+    int wpr, words_per_frame;
     long long n_words;
     size_t off_bits, off_count, off_off, off_bsum, total;
 };
@@ -327,9 +432,10 @@ struct D2mLayout {
 size_t d2m_align(size_t v) { return (v + 255) & ~(size_t)255; }
 
 int d2m_layout(int B, int H, int W, D2mLayout* L) {
-    HV_REQUIRE(B >= 1 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30) && B < (1 << 24),
+    HV_REQUIRE(B >= 1 && H >= 1 && W >= 1 && (long long)H * W < (1ll << 30) && B <= 65535 && H <= 65535,
                "depth-to-mesh: bad batch %d x %d x %d", B, H, W);
-    L->words_per_frame = (int)(((long long)H * W + 31) / 32);
+    L->wpr = (W + 31) / 32;
+    L->words_per_frame = H * L->wpr;
     L->n_words = (long long)B * L->words_per_frame;
     size_t o = 0;
     L->off_count = o;
@@ -362,6 +468,7 @@ int d2m_grid(hv::D2mGrid* g, const float* depth, const uint8_t* mask, const uint
     g->B = B;
     g->H = H;
     g->W = W;
+    g->wpr = L->wpr;
     g->words_per_frame = L->words_per_frame;
     g->n_words = L->n_words;
     g->max_depth_distance = max_depth_distance;
@@ -394,8 +501,8 @@ extern "C" int hv_d2m_count(const float* depth, const uint8_t* mask, const uint8
     if (rc != HV_OK) return rc;
     HV_REQUIRE(totals, "hv_d2m_count: null totals");
     cudaStream_t st = hv::as_stream(stream);
-    const unsigned int blocks = (unsigned int)((g.n_words + 7) / 8);
-    hv::d2m_count_kernel<<<blocks, 256, 0, st>>>(g);
+    const dim3 grid((unsigned int)((g.wpr + hv::kD2mThreads / 32 - 1) / (hv::kD2mThreads / 32)), (unsigned int)((H + hv::kD2mRows - 1) / hv::kD2mRows), (unsigned int)B);
+    hv::d2m_count_kernel<<<grid, hv::kD2mThreads, 0, st>>>(g);
     hv::exclusive_scan_u2(g.wcount, g.woff, g.bsum, g.n_words, totals, st);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
@@ -421,8 +528,8 @@ extern "C" int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_
     out.frame_off = frame_offsets;
     out.n_verts = (unsigned long long)n_verts;
     out.n_faces = (unsigned long long)n_faces;
-    const unsigned int blocks = (unsigned int)((g.n_words + 7) / 8);
-    hv::d2m_emit_kernel<<<blocks, 256, 0, hv::as_stream(stream)>>>(g, out);
+    const dim3 grid((unsigned int)((g.wpr + hv::kD2mThreads / 32 - 1) / (hv::kD2mThreads / 32)), (unsigned int)((H + hv::kD2mRows - 1) / hv::kD2mRows), (unsigned int)B);
+    hv::d2m_emit_kernel<<<grid, hv::kD2mThreads, 0, hv::as_stream(stream)>>>(g, out);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

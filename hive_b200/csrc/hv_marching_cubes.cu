@@ -22,6 +22,7 @@
 #include "hv_common.cuh"
 
 #include <float.h>
+#include <string.h>
 
 #define HV_MC_TABLE static __device__ const
 #include "hv_mc_tables.h"
@@ -655,4 +656,48 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     }
     HV_CUDA(cudaGetLastError());
     return HV_OK;
+}
+
+// Count + emit in one call: the only host round trip (the output sizes are data dependent) is a stream synchronise on
+// four counters copied into the caller's pinned `h_totals`; the caller provides output buffers with a capacity and gets
+// HV_E_CAPACITY (with h_totals filled, scratch still valid for a plain hv_mc_emit) if the surface is larger.
+extern "C" int hv_mc_extract(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                             const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                             double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset,
+                             int64_t z_global_dim, float voxel_size, const float* h_origin, int64_t cap_verts,
+                             int64_t cap_tris, float* verts_world, float* verts_voxel, float* normals, uint8_t* colors,
+                             int32_t* faces, unsigned long long* face_keys, unsigned long long* face_cubes,
+                             unsigned long long* vert_keys, unsigned long long* totals, unsigned long long* h_totals,
+                             void* stream) {
+    HV_REQUIRE(h_totals, "hv_mc_extract: null h_totals");
+    int rc = hv_mc_count(tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, totals, stream);
+    if (rc != HV_OK) return rc;
+    cudaStream_t st = hv::as_stream(stream);
+    HV_CUDA(cudaMemcpyAsync(h_totals, totals, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    HV_CUDA(cudaStreamSynchronize(st));
+    const int64_t n_verts = (int64_t)h_totals[0], n_tris = (int64_t)h_totals[1];
+    auto key_to_float = [](unsigned long long k) {
+        int i = (int)(unsigned int)k;
+        i = i >= 0 ? i : i ^ 0x7fffffff;
+        float f;
+        memcpy(&f, &i, sizeof(f));
+        return f;
+    };
+    const double vmin = key_to_float(h_totals[2]), vmax = key_to_float(h_totals[3]);
+    if (level < vmin || level > vmax) {
+        hv::set_error("Surface level must be within volume data range.");
+        return HV_E_LEVEL_RANGE;
+    }
+    if (n_verts == 0) {
+        hv::set_error("No surface found at the given iso value.");
+        return HV_E_NOSURFACE;
+    }
+    if (n_verts > cap_verts || n_tris > cap_tris) {
+        hv::set_error("hv_mc_extract: %lld vertices / %lld triangles exceed the capacity %lld / %lld", (long long)n_verts,
+                      (long long)n_tris, (long long)cap_verts, (long long)cap_tris);
+        return HV_E_CAPACITY;
+    }
+    return hv_mc_emit(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch,
+                      scratch_bytes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris, verts_world,
+                      verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys, stream);
 }

@@ -132,6 +132,41 @@ class McPlan:
         return DeviceMesh(verts, verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys[:n_verts], 0.0, 0.0)
 
 
+    def extract(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
+        """count + emit in one library call (``hv_mc_extract``) into buffers of the given capacity; falls back to an
+        exactly sized ``emit`` when the surface turns out larger.  Whole volumes only (faces as indices)."""
+        torch = self._torch
+        dev = self.device
+        origin = np.ascontiguousarray(origin, dtype=np.float32)
+        host = _pinned_totals(torch, dev)
+        with torch.cuda.device(dev):
+            verts = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
+            verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
+            normals = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
+            colors = torch.empty((cap_verts, 3), dtype=torch.uint8, device=dev)
+            vert_keys = torch.empty((max(cap_verts, 1),), dtype=torch.int64, device=dev)
+            faces = torch.empty((cap_tris, 3), dtype=torch.int32, device=dev)
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            rc = self._lib.hv_mc_extract(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
+                _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
+                origin.ctypes.data_as(ctypes.c_void_p), cap_verts, cap_tris, _ptr(verts), _ptr(verts_voxel),
+                _ptr(normals), _ptr(colors), _ptr(faces), None, None, _ptr(vert_keys), _ptr(self.totals),
+                ctypes.c_void_p(host.data_ptr()), stream)
+        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist())
+        vmin, vmax = _key_to_float(kmin), _key_to_float(kmax)
+        if rc == _lib.HV_E_CAPACITY:
+            mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
+        else:
+            _lib.check(rc)
+            mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
+                              colors[:n_verts], faces[:n_tris], None, None, vert_keys[:n_verts], 0.0, 0.0)
+        mesh.vmin, mesh.vmax = vmin, vmax
+        return mesh
+
+
 def check_surface(level, vmin, vmax, n_verts):
     """The two errors of skimage.measure.marching_cubes that HIVE can observe."""
     if level < vmin or level > vmax:
@@ -140,16 +175,25 @@ def check_surface(level, vmin, vmax, n_verts):
         raise RuntimeError("No surface found at the given iso value.")
 
 
+#: surface sizes seen per volume shape: the capacity guess of the next extraction (1.5x the last result)
+_LAST_SIZES = {}
+
+
 def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
     """Mesh of a (single-GPU, whole) ``TSDFVolume`` as device tensors."""
     X, Y, Z = (int(d) for d in vol._local_dim)
     assert min(X, Y, Z) >= 2, "Input array must be at least 2x2x2."
     plan = McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, (X, Y, Z), vol._pitch, level=level)
-    plan.count()
-    n_verts, n_tris, vmin, vmax = plan.read_totals()
-    check_surface(level, vmin, vmax, n_verts)
-    mesh = plan.emit(n_verts, n_tris, vol._voxel_size, vol._vol_origin, want_voxel=want_voxel)
-    mesh.vmin, mesh.vmax = vmin, vmax
+    # capacity: a few voxel layers' worth of surface, or what the previous extraction of this shape needed
+    guess = _LAST_SIZES.get((X, Y, Z))
+    if guess is None:
+        area = X * Y + Y * Z + X * Z
+        guess = (6 * area, 12 * area)
+    cap_v = min(guess[0], 3 * X * Y * Z)
+    cap_t = min(guess[1], 5 * X * Y * Z)
+    mesh = plan.extract(vol._voxel_size, vol._vol_origin, cap_v, cap_t, want_voxel=want_voxel)
+    n_v, n_t = int(mesh.verts.shape[0]), int(mesh.faces.shape[0])
+    _LAST_SIZES[(X, Y, Z)] = (n_v + n_v // 2 + 1024, n_t + n_t // 2 + 1024)
     return mesh
 
 

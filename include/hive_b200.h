@@ -121,6 +121,19 @@ int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, co
                float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
                unsigned long long* face_cubes, unsigned long long* vert_keys, void* stream);
 
+/* hv_mc_count + hv_mc_emit in one call with caller-provided capacity (cap_verts vertices, cap_tris triangles in every
+ * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 4 x uint64, pinned memory
+ * recommended; same meaning as `totals`).  Returns HV_E_LEVEL_RANGE / HV_E_NOSURFACE like skimage would raise
+ * (fusion.py:338), or HV_E_CAPACITY when the surface exceeds the capacity: h_totals is filled and the scratch is still
+ * valid, so the caller can allocate exactly and finish with hv_mc_emit. */
+int hv_mc_extract(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                  const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                  double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
+                  float voxel_size, const float* h_origin, int64_t cap_verts, int64_t cap_tris, float* verts_world,
+                  float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
+                  unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals,
+                  unsigned long long* h_totals, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Depth-to-mesh, batched over frames.  Replaces, for the per-frame foreground meshes of hive/pipeline.py:386-409,
  *   point_cloud_from_depth / image2world   hive/geometric.py:107-126, 183-206
