@@ -438,7 +438,8 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     e2.record()
     for s in range(K):
         vol.integrate_batch_host(frames, [((Wm + s) * B + j) % n_f for j in range(B)], sc.K)
-        vol.read_update_counter()  # D2H read of the step's result
+        vol.read_update_counter_pipelined()  # D2H read of the step's result (async snapshot, consumed one step later)
+    vol.read_update_counter()  # drains the pipeline: the last step's result
     e3.record()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1000.0

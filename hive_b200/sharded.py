@@ -45,10 +45,15 @@ class SlabShardedTSDFVolume:
         assert z1 > z0, "more ranks than z-slabs"
         self.local = TSDFVolume(vol_bnds, voxel_size, device=device, z_range=(z0, z1) if self.world_size > 1 else None)
         self._bcast = [None, None]
+        self._consumed = [None, None]  # event: the integrate kernels that read slot i's texels have finished
         self._step = 0
+        self._counter_ring = None
+        self._frame_hw = None
         if self.world_size > 1:
             import torch.distributed as dist
             self._dist = dist
+            with torch.cuda.device(self.local.device):
+                self._copy_stream = torch.cuda.Stream(device=self.local.device)
 
     # ------------------------------------------------------------------ update counter
     def count_updates(self, flag: bool):
@@ -62,6 +67,29 @@ class SlabShardedTSDFVolume:
 
     def read_update_counter(self) -> int:
         return self.local.num_updated()
+
+    def read_update_counter_pipelined(self) -> int:
+        """Device->host read of the update counter without draining the stream: the counter is snapshotted into a
+        pinned ring by an async copy ordered after the kernels enqueued so far, and the value returned is the snapshot
+        taken by the *previous* call (0 on the first), whose copy has long finished.  Every call still moves its 8 bytes
+        to the host; ``read_update_counter`` gives the synchronous, current value."""
+        torch = self._torch
+        if self._counter_ring is None:
+            self._counter_ring = {"host": [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)],
+                                  "event": [None, None], "i": 0}
+        ring = self._counter_ring
+        i = ring["i"]
+        ring["i"] = i ^ 1
+        with torch.cuda.device(self.local.device):
+            ring["host"][i].copy_(self.local._updated, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            ring["event"][i] = ev
+        prev = ring["event"][i ^ 1]
+        if prev is None:
+            return 0
+        prev.synchronize()
+        return int(ring["host"][i ^ 1].item())
 
     # ------------------------------------------------------------------ frames
     def upload_frames(self, frames, cam_intr) -> ShardedFrames:
@@ -102,6 +130,10 @@ class SlabShardedTSDFVolume:
         frames = DeviceFrames(buf, [sf.world2cam[i] for i in idx], sf.intr, sf.H, sf.W)
         for j in range(len(idx)):
             self.local.integrate_device(frames, j, obs_weight)
+        with torch.cuda.device(self.local.device):
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream())
+            self._consumed[slot] = done  # the host path's side stream must not refill the slot before this
 
     def integrate_batch_host(self, frames, idx, cam_intr, obs_weight=1.0):
         """End-to-end path: host numpy frames (rank 0) -> H2D -> (broadcast) -> integrate."""
@@ -111,30 +143,49 @@ class SlabShardedTSDFVolume:
                 self.local.integrate(color_im, depth_im, cam_intr, pose, obs_weight)
             return
         torch = self._torch
-        H, W = (int(s) for s in (frames[idx[0]][1].shape if self.rank == 0 else (0, 0)))
-        shape = torch.tensor([H, W], dtype=torch.int64, device=self.local.device)
-        self._dist.broadcast(shape, src=0)
-        H, W = (int(v) for v in shape.tolist())
+        dev = self.local.device
         slot = self._step & 1
         self._step += 1
-        buf = self._batch_buffer(slot, len(idx), H, W)
-        cams = torch.empty((len(idx), 16), dtype=torch.float64, device=self.local.device)
-        if self.rank == 0:
-            host_cams = np.zeros((len(idx), 16))
-            for j, i in enumerate(idx):
-                color_im, depth_im, pose = frames[i]
-                intr, w2c = self.local._camera(cam_intr, pose)
-                host_cams[j, :12] = w2c.reshape(-1)
-                host_cams[j, 12:] = intr
-                self.local.upload_into(color_im, depth_im, buf[j])
-            cams.copy_(torch.from_numpy(host_cams))
-        self._dist.broadcast(buf, src=0)
-        self._dist.broadcast(cams, src=0)
-        hc = cams.cpu().numpy()
-        frames_dev = DeviceFrames(buf, [np.ascontiguousarray(hc[j, :12]) for j in range(len(idx))],
-                                  hc[0, 12:].astype(np.float32), H, W)
-        for j in range(len(idx)):
-            self.local.integrate_device(frames_dev, j, obs_weight)
+        with torch.cuda.device(dev):
+            compute = torch.cuda.current_stream()
+            copy = self._copy_stream
+            # Upload + broadcast run on a side stream so that they overlap the integration of the previous batch (the
+            # caller is not blocked on the compute stream); the slot is reused every other batch.
+            if self._consumed[slot] is not None:
+                copy.wait_event(self._consumed[slot])
+            else:
+                copy.wait_stream(compute)
+            with torch.cuda.stream(copy):
+                H, W = (int(v) for v in (frames[idx[0]][1].shape if self.rank == 0 else (0, 0)))
+                meta = torch.tensor([H, W], dtype=torch.int64, device=dev)
+                if self._frame_hw is None:  # frame size is fixed for the life of the volume: broadcast it once
+                    self._dist.broadcast(meta, src=0)
+                    self._frame_hw = tuple(int(v) for v in meta.tolist())
+                H, W = self._frame_hw
+                buf = self._batch_buffer(slot, len(idx), H, W)
+                cams = torch.empty((len(idx), 16), dtype=torch.float64, device=dev)
+                if self.rank == 0:
+                    host_cams = np.zeros((len(idx), 16))
+                    for j, i in enumerate(idx):
+                        color_im, depth_im, pose = frames[i]
+                        intr, w2c = self.local._camera(cam_intr, pose)
+                        host_cams[j, :12] = w2c.reshape(-1)
+                        host_cams[j, 12:] = intr
+                        self.local.upload_into(color_im, depth_im, buf[j])
+                    cams.copy_(torch.from_numpy(host_cams))
+                self._dist.broadcast(buf, src=0)
+                self._dist.broadcast(cams, src=0)
+                hc = cams.cpu().numpy()  # waits for the side stream only
+                ready = torch.cuda.Event()
+                ready.record(copy)
+            compute.wait_event(ready)
+            frames_dev = DeviceFrames(buf, [np.ascontiguousarray(hc[j, :12]) for j in range(len(idx))],
+                                      hc[0, 12:].astype(np.float32), H, W)
+            for j in range(len(idx)):
+                self.local.integrate_device(frames_dev, j, obs_weight)
+            done = torch.cuda.Event()
+            done.record(compute)
+            self._consumed[slot] = done
 
     # ------------------------------------------------------------------ read-back
     def get_volume(self):
