@@ -238,9 +238,14 @@ def measure_mesh(vol, torch, peak, repeats=5):
     V, F = int(mesh.verts.shape[0]), int(mesh.faces.shape[0])
     n = int(np.prod(vol._local_dim))
     algo = 4.0 * n + 4.0 * V + 28.0 * V + 12.0 * F
-    t0 = time.perf_counter()
-    verts, faces, norms, colors = vol.get_mesh()
-    e2e_ms = (time.perf_counter() - t0) * 1000.0
+    e2e = []
+    for r in range(4):  # first call sizes the pinned staging blocks; median of the next three
+        verts = faces = norms = colors = None  # a caller that drops the previous mesh: its pinned blocks are reused
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        verts, faces, norms, colors = vol.get_mesh()
+        e2e.append((time.perf_counter() - t0) * 1000.0)
+    e2e_ms = float(np.median(e2e[1:]))
     return {"mc_ms": ms, "vertices": V, "triangles": F, "voxels": n, "algorithmic_bytes": algo,
             "achieved_gbs": algo / (ms / 1e3) / 1e9, "roofline_frac": algo / (ms / 1e3) / 1e9 / peak,
             "get_mesh_e2e_ms": e2e_ms, "d2h_bytes": int(verts.nbytes + faces.nbytes + norms.nbytes + colors.nbytes),
@@ -277,15 +282,21 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
     H, W = sc.H, sc.W
     algo = 5.0 * H * W * B + 36.0 * V + 12.0 * F  # depth f32 + mask u8 in; f64 xyz + (u, v, depth) + faces out
     # end to end: host numpy in, host numpy out (H2D of depth+mask, D2H of vertices and faces)
-    t0 = time.perf_counter()
-    batch = geometric.depth_to_mesh_batch(depths, masks, sc.K, poses)
-    hv, hf = batch.verts.cpu().numpy(), batch.faces.cpu().numpy()
-    e2e_s = time.perf_counter() - t0
+    e2e = []
+    for r in range(4):  # first call sizes the pinned staging blocks; median of the next three
+        hv = hf = hp = hd = None
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        batch = geometric.depth_to_mesh_batch(depths, masks, sc.K, poses)
+        hv, hf, hp, hd = batch.to_host()
+        e2e.append(time.perf_counter() - t0)
+        del batch
+    e2e_s = float(np.median(e2e[1:]))
     e2e_fps = _sum_over_ranks(int(B / e2e_s), world, dist, torch)
     return {"frames_per_s": world * B / (ms / 1e3), "ms_per_batch": ms, "frames_per_batch_per_gpu": B,
             "vertices": V, "faces": F, "achieved_gbs": algo / (ms / 1e3) / 1e9,
             "roofline_frac": algo / (ms / 1e3) / 1e9 / peak, "e2e_frames_per_s": float(e2e_fps),
-            "h2d_bytes": int(depths.nbytes + masks.nbytes), "d2h_bytes": int(hv.nbytes + hf.nbytes),
+            "h2d_bytes": int(depths.nbytes + masks.nbytes), "d2h_bytes": int(hv.nbytes + hf.nbytes + hp.nbytes + hd.nbytes),
             "workload": f"{B} frames/GPU of {W}x{H}, instance masks of the room scene, frame-partitioned"}
 
 

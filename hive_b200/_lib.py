@@ -49,6 +49,12 @@ SIGNATURES = {
     "hv_image2world": [c_void_p, c_void_p, c_int64, c_void_p, c_double, c_void_p, c_void_p],
     "hv_world2image": [c_void_p, c_int64, c_void_p, c_double, c_int, c_void_p, c_void_p, c_void_p],
     "hv_filter_faces_scratch_bytes": [c_int64, c_void_p],
+    "hv_dilate_scratch_bytes": [c_int, c_int, c_int, c_void_p],
+    "hv_dilate_mask": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_pack_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_upload_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_depth_max": [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p],
     "hv_filter_faces": [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_double, c_double, c_void_p, c_int64, c_int,
                         c_void_p, c_void_p, c_void_p],
 }

@@ -1,0 +1,198 @@
+// Per-frame image preparation that sits either side of the TSDF / depth-to-mesh kernels:
+//
+//   * dilate_mask: hive/image_processing.py:32-48 -- cv2.dilate(mask, 3x3 rect, iterations=n) followed by astype(bool).
+//     n iterations of a 3x3 rectangle are one dilation with a (2n+1)^2 square (OpenCV itself folds the iterations into
+//     the kernel size for rectangular elements); the border is ignored (morphologyDefaultBorderValue).  So
+//         out[v][u] = any(mask[v-n..v+n][u-n..u+n] != 0),   n = 0 -> mask != 0.
+//     Done on bit-planes: one ballot per 32 pixels, a horizontal pass of 2n+1 funnel shifts per word, a vertical OR of
+//     2n+1 words.  A 640x480 mask is 9600 words: everything stays in L1/L2.
+//   * masked frame upload: hive/fusion.py:118-121 (`depth_im[dilate_mask(mask) > 0] = 0`) fused into the texel pack of
+//     hv_pack_frame, so the dilated mask never exists as an image and the depth frame is never rewritten.
+//   * depth_max: the np.max(depth_im) of get_view_frustum (fusion.py:364) for a batch of frames.
+#include "hv_common.cuh"
+
+namespace hv {
+
+// bits[(b*H + v)*Ww + w] bit l  <=>  mask[b][v][32*w + l] != 0 ; bits past W are zero.  One warp per word.
+__global__ void __launch_bounds__(256) mask_bits_kernel(const uint8_t* __restrict__ mask, long long rows, int W, int Ww,
+                                                        uint32_t* __restrict__ bits) {
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= rows * Ww) return;
+    const long long row = warp / Ww;
+    const int w = (int)(warp - row * Ww);
+    const int u = w * 32 + lane;
+    const bool on = u < W && mask[row * W + u] != 0;
+    const uint32_t word = __ballot_sync(0xffffffffu, on);
+    if (lane == 0) bits[warp] = word;
+}
+
+// 32 bits of a row starting at bit offset `off` (may be negative or run past the row: zeros there).
+__device__ __forceinline__ uint32_t row_window(const uint32_t* __restrict__ row, int Ww, int off) {
+    const int i = off >> 5;  // arithmetic shift: floor
+    const int sh = off & 31;
+    const uint32_t lo = (i >= 0 && i < Ww) ? row[i] : 0u;
+    const uint32_t hi = (i + 1 >= 0 && i + 1 < Ww) ? row[i + 1] : 0u;
+    return __funnelshift_r(lo, hi, sh);
+}
+
+// Horizontal dilation by n on each side: hb word = OR over s in [-n, n] of the row shifted by s.
+__global__ void __launch_bounds__(256) mask_hdilate_kernel(const uint32_t* __restrict__ bits, long long rows, int W,
+                                                           int Ww, int n, uint32_t* __restrict__ hbits) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * Ww) return;
+    const long long row = idx / Ww;
+    const int w = (int)(idx - row * Ww);
+    const uint32_t* r = bits + row * Ww;
+    uint32_t acc = 0;
+    for (int s = -n; s <= n; ++s) acc |= row_window(r, Ww, w * 32 + s);
+    const int tail = W - w * 32;  // keep bits past W clear
+    if (tail < 32) acc &= (tail <= 0) ? 0u : ((1u << tail) - 1u);
+    hbits[idx] = acc;
+}
+
+__device__ __forceinline__ uint32_t vdilate_word(const uint32_t* __restrict__ hbits, int H, int Ww, int v, int w, int n) {
+    const int v0 = max(0, v - n), v1 = min(H - 1, v + n);
+    uint32_t acc = 0;
+    for (int r = v0; r <= v1; ++r) acc |= hbits[(long long)r * Ww + w];
+    return acc;
+}
+
+// Vertical pass + expansion to a uint8 0/1 image.
+__global__ void __launch_bounds__(256) mask_vdilate_kernel(const uint32_t* __restrict__ hbits, int B, int H, int W, int Ww,
+                                                           int n, uint8_t* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long total = (long long)B * H * W;
+    if (i >= total) return;
+    const long long row = i / W;
+    const int u = (int)(i - row * W);
+    const int b = (int)(row / H);
+    const int v = (int)(row - (long long)b * H);
+    const uint32_t word = vdilate_word(hbits + (long long)b * H * Ww, H, Ww, v, u >> 5, n);
+    out[i] = (word >> (u & 31)) & 1u;
+}
+
+// hv_pack_frame with `depth = 0` wherever the dilated mask is set (hive/fusion.py:121).
+__global__ void __launch_bounds__(256) pack_frame_masked_kernel(const float* __restrict__ depth,
+                                                                const uint8_t* __restrict__ rgb,
+                                                                const uint32_t* __restrict__ hbits, int H, int W, int Ww,
+                                                                int n, uint2* __restrict__ texels) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= H * W) return;
+    const int v = i / W, u = i - v * W;
+    const uint32_t word = vdilate_word(hbits, H, Ww, v, u >> 5, n);
+    const bool masked = (word >> (u & 31)) & 1u;
+    const unsigned int r = rgb[3 * i + 0], g = rgb[3 * i + 1], b = rgb[3 * i + 2];
+    texels[i] = make_uint2(masked ? 0u : __float_as_uint(depth[i]), (b << 16) | (g << 8) | r);
+}
+
+// Per-frame maximum of a (B, n) float32 array, NaN-free input assumed (depth maps); result as ordered-int atomicMax.
+__global__ void __launch_bounds__(256) depth_max_kernel(const float* __restrict__ depth, long long n,
+                                                        int* __restrict__ out_keys) {
+    const int b = blockIdx.y;
+    const float* d = depth + (long long)b * n;
+    float m = -INFINITY;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        m = fmaxf(m, d[i]);
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) {
+        const int bitsv = __float_as_int(m);
+        atomicMax(out_keys + b, bitsv >= 0 ? bitsv : bitsv ^ 0x7fffffff);  // order-preserving float -> int key
+    }
+}
+
+__global__ void depth_max_finish_kernel(const int* __restrict__ keys, int B, float* __restrict__ out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const int k = keys[b];
+    out[b] = __int_as_float(k >= 0 ? k : k ^ 0x7fffffff);
+}
+
+static inline int words_per_row(int W) { return (W + 31) / 32; }
+
+static int launch_bits_and_hdilate(const uint8_t* mask, long long rows, int W, int n, uint32_t* raw, uint32_t* hb,
+                                   cudaStream_t st) {
+    const int Ww = words_per_row(W);
+    const long long words = rows * Ww;
+    mask_bits_kernel<<<(unsigned)((words * 32 + 255) / 256), 256, 0, st>>>(mask, rows, W, Ww, raw);
+    HV_CUDA(cudaGetLastError());
+    mask_hdilate_kernel<<<(unsigned)((words + 255) / 256), 256, 0, st>>>(raw, rows, W, Ww, n, hb);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+}  // namespace hv
+
+extern "C" int hv_dilate_scratch_bytes(int B, int H, int W, int64_t* bytes) {
+    HV_REQUIRE(bytes && B > 0 && H > 0 && W > 0, "hv_dilate_scratch_bytes: bad arguments");
+    *bytes = 2ll * B * H * hv::words_per_row(W) * (int64_t)sizeof(uint32_t);
+    return HV_OK;
+}
+
+extern "C" int hv_dilate_mask(const uint8_t* mask, int B, int H, int W, int iterations, void* scratch,
+                              int64_t scratch_bytes, uint8_t* out, void* stream) {
+    HV_REQUIRE(mask && out && scratch, "hv_dilate_mask: null pointer");
+    HV_REQUIRE(B > 0 && H > 0 && W > 0 && iterations >= 0, "hv_dilate_mask: bad arguments");
+    HV_REQUIRE((long long)B * H * W < (1ll << 40), "hv_dilate_mask: batch too large");
+    int64_t need = 0;
+    hv_dilate_scratch_bytes(B, H, W, &need);
+    HV_REQUIRE(scratch_bytes >= need && ((uintptr_t)scratch & 3) == 0, "hv_dilate_mask: scratch too small or unaligned");
+    const int Ww = hv::words_per_row(W);
+    uint32_t* raw = reinterpret_cast<uint32_t*>(scratch);
+    uint32_t* hb = raw + (long long)B * H * Ww;
+    cudaStream_t st = hv::as_stream(stream);
+    const int rc = hv::launch_bits_and_hdilate(mask, (long long)B * H, W, iterations, raw, hb, st);
+    if (rc != HV_OK) return rc;
+    const long long total = (long long)B * H * W;
+    hv::mask_vdilate_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(hb, B, H, W, Ww, iterations, out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_pack_frame_masked(const float* depth, const uint8_t* rgb, const uint8_t* mask, int H, int W,
+                                    int iterations, void* scratch, int64_t scratch_bytes, void* texels, void* stream) {
+    HV_REQUIRE(depth && rgb && mask && texels && scratch, "hv_pack_frame_masked: null pointer");
+    HV_REQUIRE(H > 0 && W > 0 && (long long)H * W < (1ll << 30) && iterations >= 0, "hv_pack_frame_masked: bad arguments");
+    HV_REQUIRE(((uintptr_t)texels & 7) == 0, "hv_pack_frame_masked: texels must be 8-byte aligned");
+    int64_t need = 0;
+    hv_dilate_scratch_bytes(1, H, W, &need);
+    HV_REQUIRE(scratch_bytes >= need && ((uintptr_t)scratch & 3) == 0,
+               "hv_pack_frame_masked: scratch too small or unaligned");
+    const int Ww = hv::words_per_row(W);
+    uint32_t* raw = reinterpret_cast<uint32_t*>(scratch);
+    uint32_t* hb = raw + (long long)H * Ww;
+    cudaStream_t st = hv::as_stream(stream);
+    const int rc = hv::launch_bits_and_hdilate(mask, H, W, iterations, raw, hb, st);
+    if (rc != HV_OK) return rc;
+    const int n = H * W;
+    hv::pack_frame_masked_kernel<<<(n + 255) / 256, 256, 0, st>>>(depth, rgb, hb, H, W, Ww, iterations,
+                                                                 reinterpret_cast<uint2*>(texels));
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_upload_frame_masked(const float* h_depth, const uint8_t* h_rgb, const uint8_t* h_mask, int H, int W,
+                                      int iterations, float* d_depth, uint8_t* d_rgb, uint8_t* d_mask, void* scratch,
+                                      int64_t scratch_bytes, void* texels, void* stream) {
+    HV_REQUIRE(h_depth && h_rgb && h_mask && d_depth && d_rgb && d_mask, "hv_upload_frame_masked: null pointer");
+    HV_REQUIRE(H > 0 && W > 0, "hv_upload_frame_masked: bad frame size %d x %d", H, W);
+    const size_t n = (size_t)H * W;
+    cudaStream_t st = hv::as_stream(stream);
+    HV_CUDA(cudaMemcpyAsync(d_depth, h_depth, n * sizeof(float), cudaMemcpyHostToDevice, st));
+    HV_CUDA(cudaMemcpyAsync(d_rgb, h_rgb, n * 3, cudaMemcpyHostToDevice, st));
+    HV_CUDA(cudaMemcpyAsync(d_mask, h_mask, n, cudaMemcpyHostToDevice, st));
+    return hv_pack_frame_masked(d_depth, d_rgb, d_mask, H, W, iterations, scratch, scratch_bytes, texels, stream);
+}
+
+extern "C" int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scratch, float* out, void* stream) {
+    HV_REQUIRE(depth && keys_scratch && out && B > 0 && n > 0, "hv_depth_max: bad arguments");
+    HV_REQUIRE(B <= 65535, "hv_depth_max: at most 65535 frames per call");
+    cudaStream_t st = hv::as_stream(stream);
+    HV_CUDA(cudaMemsetAsync(keys_scratch, 0x80, (size_t)B * sizeof(int), st));  // 0x80808080: below every finite key
+    const int bx = (int)((n + 256 * 8 - 1) / (256 * 8));
+    hv::depth_max_kernel<<<dim3(bx < 1 ? 1 : (bx > 64 ? 64 : bx), B), 256, 0, st>>>(depth, n, keys_scratch);
+    HV_CUDA(cudaGetLastError());
+    hv::depth_max_finish_kernel<<<(B + 127) / 128, 128, 0, st>>>(keys_scratch, B, out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}

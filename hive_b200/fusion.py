@@ -20,6 +20,7 @@ import os
 import numpy as np
 
 from . import _lib
+from . import _xfer
 
 __all__ = ["TSDFVolume", "rigid_transform", "get_view_frustum", "meshwrite", "pcwrite", "FUSION_GPU_MODE"]
 
@@ -126,6 +127,8 @@ class TSDFVolume:
     def _download(self, plane):
         Z = int(self._local_dim[2])
         t = plane if self._pitch == Z else plane[:, :, :Z].contiguous()
+        if t.numel() * 4 <= (1 << 30):  # page-locked staging up to 1 GiB per plane; pageable beyond that
+            return _xfer.to_host(t)
         return t.cpu().numpy()
 
     # ------------------------------------------------------------------ staging
@@ -142,6 +145,10 @@ class TSDFVolume:
                 "d_depth": [torch.empty((H, W), dtype=torch.float32, device=dev) for _ in range(2)],
                 "d_rgb": [torch.empty((H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)],
                 "texels": [torch.empty((H * W,), dtype=torch.int64, device=dev) for _ in range(2)],
+                # optional dynamic-object mask of the frame (hive/fusion.py:118-121), dilated on the device
+                "h_mask": [torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(2)],
+                "d_mask": [torch.empty((H, W), dtype=torch.uint8, device=dev) for _ in range(2)],
+                "mask_bits": [torch.empty((2 * H * ((W + 31) // 32),), dtype=torch.int32, device=dev) for _ in range(2)],
                 "uploaded": [torch.cuda.Event() for _ in range(2)],  # H2D + pack of the slot finished
                 "consumed": [None, None],  # integrate that read the slot's texels finished
             }
@@ -166,10 +173,15 @@ class TSDFVolume:
         return intr, w2c
 
     # ------------------------------------------------------------------ integrate
-    def integrate(self, color_im, depth_im, cam_intr, cam_pose, obs_weight=1.):
+    def integrate(self, color_im, depth_im, cam_intr, cam_pose, obs_weight=1., mask=None, mask_dilation_iterations=0):
         """Integrate an RGB-D frame into the TSDF volume (fusion.py:217-303).
 
         Host numpy inputs; the H2D copy of the frame runs on a side stream and overlaps the previous frame's kernel.
+
+        ``mask`` (extension, not in the reference signature): the frame's dynamic-object mask.  Depth is zeroed wherever
+        the mask, dilated ``mask_dilation_iterations`` times by a 3x3 rectangle, is non-zero -- the
+        ``depth_im[dilate_mask(mask) > 0] = 0.0`` that hive/fusion.py:118-121 does on the host before every call,
+        fused into the frame upload (``depth_im`` itself is left untouched).
         """
         torch = self._torch
         depth_im = np.asarray(depth_im)
@@ -185,6 +197,10 @@ class TSDFVolume:
         st["uploaded"][slot].synchronize()
         st["h_depth"][slot].numpy()[...] = depth_im  # converts to float32 (fusion.py:252)
         st["h_rgb"][slot].numpy()[...] = rgb
+        if mask is not None:
+            mask = np.asarray(mask)
+            assert mask.shape == (im_h, im_w), "mask must match depth_im"
+            np.not_equal(mask, 0, out=st["h_mask"][slot].numpy().view(np.bool_))
         with torch.cuda.device(self.device):
             compute = torch.cuda.current_stream()
             copy = self._copy_stream
@@ -192,9 +208,17 @@ class TSDFVolume:
                 copy.wait_event(st["consumed"][slot])
             else:
                 copy.wait_stream(compute)
-            _lib.check(self._lib.hv_upload_frame(
-                _ptr(st["h_depth"][slot]), _ptr(st["h_rgb"][slot]), im_h, im_w, _ptr(st["d_depth"][slot]),
-                _ptr(st["d_rgb"][slot]), _ptr(st["texels"][slot]), ctypes.c_void_p(copy.cuda_stream)))
+            if mask is None:
+                _lib.check(self._lib.hv_upload_frame(
+                    _ptr(st["h_depth"][slot]), _ptr(st["h_rgb"][slot]), im_h, im_w, _ptr(st["d_depth"][slot]),
+                    _ptr(st["d_rgb"][slot]), _ptr(st["texels"][slot]), ctypes.c_void_p(copy.cuda_stream)))
+            else:
+                bits = st["mask_bits"][slot]
+                _lib.check(self._lib.hv_upload_frame_masked(
+                    _ptr(st["h_depth"][slot]), _ptr(st["h_rgb"][slot]), _ptr(st["h_mask"][slot]), im_h, im_w,
+                    int(mask_dilation_iterations), _ptr(st["d_depth"][slot]), _ptr(st["d_rgb"][slot]),
+                    _ptr(st["d_mask"][slot]), _ptr(bits), bits.numel() * 4, _ptr(st["texels"][slot]),
+                    ctypes.c_void_p(copy.cuda_stream)))
             st["uploaded"][slot].record(copy)
             compute.wait_event(st["uploaded"][slot])
             self._launch(st["texels"][slot], im_h, im_w, intr, w2c, obs_weight, compute)

@@ -10,6 +10,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
+from . import _xfer
 
 __all__ = ["get_pose_components", "point_cloud_from_depth", "point_cloud_from_rgbd", "world2image", "image2world",
            "depth_to_mesh_batch", "DepthMeshBatch"]
@@ -67,9 +68,13 @@ class DepthMeshBatch:
         """(vertices (N,3) f64, faces (F,3) i32, points2d (N,2) i32, depth (N,) f32) of frame i as host numpy."""
         v0, f0 = self.frame_offsets[i]
         v1, f1 = self.frame_offsets[i + 1]
-        return (self.verts[v0:v1].cpu().numpy(), self.faces[f0:f1].cpu().numpy(),
-                self.points2d[v0:v1].cpu().numpy() if self.points2d is not None else None,
-                self.vdepth[v0:v1].cpu().numpy() if self.vdepth is not None else None)
+        return _xfer.to_host(self.verts[v0:v1], self.faces[f0:f1],
+                             self.points2d[v0:v1] if self.points2d is not None else None,
+                             self.vdepth[v0:v1] if self.vdepth is not None else None)
+
+    def to_host(self):
+        """(verts, faces, points2d, vdepth) of the whole batch as host numpy (faces index per-frame vertex ranges)."""
+        return _xfer.to_host(self.verts, self.faces, self.points2d, self.vdepth)
 
 
 def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, diag=None, want_points=True):
@@ -120,14 +125,14 @@ def depth_to_mesh_batch(depths, masks, K, poses, max_pixel_distance=2, max_depth
     """
     torch = _lib.require_cuda()
     dev = torch.device("cuda", torch.cuda.current_device())
-    depths = np.ascontiguousarray(depths, dtype=np.float32)
+    depths = np.asarray(depths)
     poses = np.asarray(poses, dtype=np.float64)
     B = depths.shape[0]
     cams = np.concatenate([poses[:, :3, :3].reshape(B, 9), poses[:, :3, 3].reshape(B, 3)], axis=1)
-    d = torch.from_numpy(depths).to(dev)
-    m = None if masks is None else torch.from_numpy(np.ascontiguousarray(masks).astype(np.uint8)).to(dev)
-    g = None if diag is None else torch.from_numpy(np.ascontiguousarray(diag, dtype=np.uint8)).to(dev)
-    c = torch.from_numpy(np.ascontiguousarray(cams)).to(dev)
+    d = _xfer.to_device(depths, dev, np.float32)
+    m = None if masks is None else _xfer.to_device(masks, dev, np.uint8)
+    g = None if diag is None else _xfer.to_device(diag, dev, np.uint8)
+    c = _xfer.to_device(cams, dev)
     return depth_to_mesh_device(d, m, _kinv64(K), c, max_depth_distance, d2m_flags(max_pixel_distance), g)
 
 
@@ -138,11 +143,11 @@ def point_cloud_from_depth(depth, mask, K, R=_EYE, t=_ZERO_T):
     dev = torch.device("cuda", torch.cuda.current_device())
     depth = np.asarray(depth)
     assert np.asarray(mask).shape == depth.shape
-    d = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float32)[None]).to(dev)
-    m = torch.from_numpy(np.ascontiguousarray(mask).astype(np.uint8)[None]).to(dev)
+    d = _xfer.to_device(depth[None], dev, np.float32)
+    m = _xfer.to_device(np.asarray(mask)[None], dev, np.uint8)
     cams = torch.from_numpy(_cam21(np.eye(3), R, t)[9:][None].copy()).to(dev)
     out = depth_to_mesh_device(d, m, _kinv64(K), cams, 0.0, 2, want_points=False)  # HV_D2M_VERTS_ONLY
-    return out.verts.cpu().numpy()
+    return _xfer.to_host(out.verts)
 
 
 def point_cloud_from_rgbd(rgb, depth, mask, K, R=_EYE, t=_ZERO_T):
@@ -164,13 +169,13 @@ def image2world(points, depth, K, R=_EYE, t=_ZERO_T, scale_factor=1.0):
     validate_camera_parameter_shapes(K, R, t)
     dev = torch.device("cuda", torch.cuda.current_device())
     n = points.shape[0]
-    p = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float64)).to(dev)
-    d = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float64)).to(dev)
+    p = _xfer.to_device(points, dev, np.float64)
+    d = _xfer.to_device(depth, dev, np.float64)
     cam = torch.from_numpy(_cam21(_kinv64(K), R, t)).to(dev)
     out = torch.empty((n, 3), dtype=torch.float64, device=dev)
     _lib.check(_lib.load().hv_image2world(_ptr(p), _ptr(d), n, _ptr(cam), float(scale_factor), _ptr(out),
                                           ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
-    return out.cpu().numpy()
+    return _xfer.to_host(out)
 
 
 def world2image(points, K, R=_EYE, t=_ZERO_T, scale_factor=1.0, dtype=np.int32):
@@ -181,11 +186,12 @@ def world2image(points, K, R=_EYE, t=_ZERO_T, scale_factor=1.0, dtype=np.int32):
     validate_camera_parameter_shapes(K, R, t)
     dev = torch.device("cuda", torch.cuda.current_device())
     n = points.shape[0]
-    p = torch.from_numpy(np.ascontiguousarray(points, dtype=np.float64)).to(dev)
+    p = _xfer.to_device(points, dev, np.float64)
     cam = torch.from_numpy(_cam21(np.asarray(K, dtype=np.float64), R, t)).to(dev)
     uv = torch.empty((n, 2), dtype=torch.float64, device=dev)
     depth = torch.empty((n,), dtype=torch.float64, device=dev)
     _lib.check(_lib.load().hv_world2image(_ptr(p), n, _ptr(cam), float(scale_factor),
                                           int(issubclass(dtype, np.integer)), _ptr(uv), _ptr(depth),
                                           ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
-    return np.array(uv.cpu().numpy(), dtype=dtype), depth.cpu().numpy()
+    uv_h, depth_h = _xfer.to_host(uv, depth)
+    return np.array(uv_h, dtype=dtype), depth_h

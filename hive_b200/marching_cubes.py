@@ -15,6 +15,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _lib
+from . import _xfer
 
 
 def _ptr(t):
@@ -45,8 +46,7 @@ class DeviceMesh:
     vmax: float
 
     def to_host(self):
-        return (self.verts.cpu().numpy(), self.faces.cpu().numpy(), self.normals.cpu().numpy(),
-                self.colors.cpu().numpy())
+        return _xfer.to_host(self.verts, self.faces, self.normals, self.colors)
 
 
 _PINNED = {}
@@ -223,7 +223,7 @@ def marching_cubes(volume, level=None, *, spacing=(1., 1., 1.), gradient_directi
     if level is None:
         level = 0.5 * (float(vol32.min()) + float(vol32.max()))
     dev = torch.device("cuda", torch.cuda.current_device())
-    tsdf = torch.from_numpy(vol32).to(dev)
+    tsdf = _xfer.to_device(vol32, dev)
     color = torch.zeros_like(tsdf)
     X, Y, Z = vol32.shape
     plan = McPlan(tsdf, color, (X, Y, Z), Z, level=float(level))
@@ -232,4 +232,5 @@ def marching_cubes(volume, level=None, *, spacing=(1., 1., 1.), gradient_directi
     check_surface(float(level), vmin, vmax, n_verts)
     mesh = plan.emit(n_verts, n_tris, 1.0, np.zeros(3, np.float32), want_voxel=True)
     values = np.full(n_verts, np.float32(level))
-    return mesh.verts_voxel.cpu().numpy(), mesh.faces.cpu().numpy(), mesh.normals.cpu().numpy(), values
+    verts, faces, normals = _xfer.to_host(mesh.verts_voxel, mesh.faces, mesh.normals)
+    return verts, faces, normals, values

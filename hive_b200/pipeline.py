@@ -17,6 +17,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _lib
+from . import _xfer
 from . import geometric
 
 __all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh"]
@@ -74,7 +75,7 @@ class Pipeline:
         cams = torch.zeros((1, 12), dtype=torch.float64, device=dev)
         out = geometric.depth_to_mesh_device(d, None, np.eye(3), cams, np.float32(np.inf),
                                              geometric.d2m_flags(max_pixel_distance), g, want_points=False)
-        faces = out.faces.cpu().numpy()
+        faces = _xfer.to_host(out.faces)
         order = np.argsort(lin, kind="stable")  # rank in row-major order -> index in the caller's array
         if not np.array_equal(order, np.arange(len(lin))):
             faces = order[faces].astype(np.int32)
@@ -94,9 +95,9 @@ class Pipeline:
         lib = _lib.load()
         dev = torch.device("cuda", torch.cuda.current_device())
         is64 = depth.dtype == np.float64
-        p = torch.from_numpy(np.ascontiguousarray(points2d, dtype=np.int32)).to(dev)
-        d = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float64 if is64 else np.float32)).to(dev)
-        f = torch.from_numpy(np.ascontiguousarray(faces, dtype=np.int32)).to(dev)
+        p = _xfer.to_device(points2d, dev, np.int32)
+        d = _xfer.to_device(depth, dev, np.float64 if is64 else np.float32)
+        f = _xfer.to_device(faces, dev, np.int32)
         nbytes = ctypes.c_int64(0)
         _lib.check(lib.hv_filter_faces_scratch_bytes(n_faces, ctypes.byref(nbytes)))
         scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
@@ -111,4 +112,4 @@ class Pipeline:
         out = torch.empty((kept, 3), dtype=torch.int32, device=dev)
         if kept:
             _lib.check(lib.hv_filter_faces(*args, 1, _ptr(totals), _ptr(out), stream))
-        return out.cpu().numpy().astype(faces.dtype, copy=False)
+        return _xfer.to_host(out).astype(faces.dtype, copy=False)

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import numpy as np
 
+from . import _xfer
 from .fusion import DeviceFrames, TSDFVolume
 
 
@@ -250,7 +251,7 @@ class SlabShardedTSDFVolume:
         if self.rank != 0:
             return None, None, None, None
         verts, faces, normals, colors = stitch_mesh_parts(parts)
-        return verts.cpu().numpy(), faces.cpu().numpy(), normals.cpu().numpy(), colors.cpu().numpy()
+        return _xfer.to_host(verts, faces, normals, colors)
 
 
 def exchange_halo_planes(dist, rank, world_size, planes):

@@ -216,3 +216,45 @@ class Scene:
     def frames(self, n: int | None = None):
         for i in range(self.num_frames if n is None else n):
             yield self.frame(i)
+
+
+class _Trajectory:
+    """The two calls the TSDF driver makes on ``HiveDataset.camera_trajectory`` (hive/fusion.py:51, 111)."""
+
+    def __init__(self, matrices):
+        self._m = np.asarray(matrices, dtype=np.float64)
+
+    def inverse(self):
+        return _Trajectory(np.linalg.inv(self._m))
+
+    def to_homogenous_transforms(self):
+        return self._m.copy()
+
+
+class _Indexed:
+    def __init__(self, fn):
+        self._fn = fn
+
+    def __getitem__(self, i):
+        return self._fn(i)  # a fresh array per access, like decoding a PNG (hive/io.py:550)
+
+
+class SyntheticDataset:
+    """Duck-typed stand-in for ``hive.io.HiveDataset`` as read by ``hive.fusion.tsdf_fusion`` (hive/fusion.py:79-134):
+    world-to-camera trajectory, RGB / depth / instance-mask frame accessors, float32 camera matrix."""
+
+    def __init__(self, scene: Scene, num_frames: int | None = None, has_inpainted_frame_data: bool = False):
+        self.scene = scene
+        self.num_frames = scene.num_frames if num_frames is None else int(num_frames)
+        self.camera_matrix = scene.K
+        self.has_inpainted_frame_data = has_inpainted_frame_data
+        self._cache = {}
+        self.camera_trajectory = _Trajectory([np.linalg.inv(scene.pose(i)) for i in range(self.num_frames)])
+        self.bg_rgb_dataset = _Indexed(lambda i: self._frame(i).rgb.copy())
+        self.bg_depth_dataset = _Indexed(lambda i: self._frame(i).depth.copy())
+        self.mask_dataset = _Indexed(lambda i: self._frame(i).mask.copy())
+
+    def _frame(self, i):
+        if i not in self._cache:
+            self._cache[i] = self.scene.frame(i)
+        return self._cache[i]

@@ -188,6 +188,29 @@ int hv_filter_faces(const int32_t* points2d, const void* depth, int depth_is_f64
                     double max_pixel_distance, double max_depth_distance, void* scratch, int64_t scratch_bytes, int phase,
                     unsigned long long* totals, int32_t* out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Frame preparation either side of the kernels above.
+ *
+ * hv_dilate_mask replaces hive.image_processing.dilate_mask (hive/image_processing.py:32-48): cv2.dilate with the
+ * default 3x3 rectangle (hive/options.py:248), `iterations` times, then astype(bool) -- i.e. out = 1 where any
+ * mask pixel within Chebyshev distance `iterations` is non-zero.  Batched over B frames.  mask/out: (B,H,W) uint8.
+ *
+ * hv_pack_frame_masked / hv_upload_frame_masked replace the per-frame masking of the TSDF driver,
+ * hive/fusion.py:118-121 (`mask = dilate_mask(mask); depth_im[mask > 0] = 0.0`), fused into the texel pack:
+ * texel.depth = 0 where the dilated mask is set.
+ *
+ * hv_depth_max: np.max(depth_im) of get_view_frustum (fusion.py:364) for B frames of n pixels; keys_scratch = B ints.
+ * ---------------------------------------------------------------------------------------------------------- */
+int hv_dilate_scratch_bytes(int B, int H, int W, int64_t* h_bytes);
+int hv_dilate_mask(const uint8_t* mask, int B, int H, int W, int iterations, void* scratch, int64_t scratch_bytes,
+                   uint8_t* out, void* stream);
+int hv_pack_frame_masked(const float* depth, const uint8_t* rgb, const uint8_t* mask, int H, int W, int iterations,
+                         void* scratch, int64_t scratch_bytes, void* texels, void* stream);
+int hv_upload_frame_masked(const float* h_depth, const uint8_t* h_rgb, const uint8_t* h_mask, int H, int W,
+                           int iterations, float* d_depth, uint8_t* d_rgb, uint8_t* d_mask, void* scratch,
+                           int64_t scratch_bytes, void* texels, void* stream);
+int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scratch, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

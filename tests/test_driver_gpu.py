@@ -1,0 +1,124 @@
+"""GPU parity of the TSDF driver pieces around the volume: dilate_mask
+(hive/image_processing.py:32-48), the masked frame upload (hive/fusion.py:118-121), per-frame depth maxima
+(fusion.py:364) and the whole ``tsdf_fusion`` loop (hive/fusion.py:79-134) against oracle/driver_oracle.py.
+Bit-exact for masks; tsdf <= 1e-5, weight and colour bit-exact; mesh identical to the oracle's marching cubes."""
+import numpy as np
+import pytest
+
+from hive_b200.synthetic import Scene, SyntheticDataset
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("shape", [(60, 80), (37, 45), (33, 64), (5, 3), (480, 640)])
+@pytest.mark.parametrize("n", [0, 1, 2, 10, 40])
+def test_dilate_mask_matches_oracle(shape, n):
+    from hive_b200.image_processing import MaskDilationOptions, dilate_mask
+    from oracle import driver_oracle as drv
+    rng = np.random.default_rng(11 + n)
+    mask = (rng.random(shape) < 0.01).astype(np.uint8) * rng.integers(1, 200, size=shape).astype(np.uint8)
+    got = dilate_mask(mask, MaskDilationOptions(num_iterations=n))
+    assert got.dtype == np.bool_ and got.shape == shape
+    assert np.array_equal(got, drv.dilate_mask(mask, n))
+    # bool and float masks go through the same "non-zero" rule (image_processing.py:41-43)
+    assert np.array_equal(dilate_mask(mask > 0, MaskDilationOptions(n)), got)
+    assert np.array_equal(dilate_mask(mask.astype(np.float64) * 0.25, MaskDilationOptions(n)), got)
+
+
+def test_dilate_mask_edge_cases():
+    from hive_b200.image_processing import MaskDilationOptions, dilate_mask
+    opts = MaskDilationOptions(num_iterations=3)
+    assert not dilate_mask(np.zeros((20, 31), np.uint8), opts).any()
+    assert dilate_mask(np.ones((20, 31), np.uint8), opts).all()
+    corner = np.zeros((20, 70), np.uint8)
+    corner[0, 0] = corner[19, 69] = 2
+    assert dilate_mask(corner, opts).sum() == 2 * 16
+    with pytest.raises(AssertionError):
+        dilate_mask(np.zeros((2, 3, 4), np.uint8), opts)
+    with pytest.raises(NotImplementedError):
+        dilate_mask(corner, MaskDilationOptions(1, np.ones((5, 5), np.uint8)))
+
+
+def test_dilate_masks_batched():
+    import torch
+    from hive_b200.image_processing import dilate_masks_device
+    from oracle import driver_oracle as drv
+    sc = Scene("small", "room")
+    masks = np.stack([sc.frame(i).mask for i in range(4)])
+    out = dilate_masks_device(torch.from_numpy(masks).cuda(), 10).cpu().numpy()
+    for b in range(4):
+        assert np.array_equal(out[b].astype(bool), drv.dilate_mask(masks[b], 10))
+
+
+def test_depth_max():
+    from hive_b200.image_processing import depth_max
+    sc = Scene("small", "room")
+    depths = np.stack([sc.frame(i).depth for i in range(5)])
+    depths[3] = 0.0
+    assert np.array_equal(depth_max(depths), depths.reshape(5, -1).max(axis=1))
+
+
+def test_masked_integrate_equals_host_masking(c_oracle):
+    """integrate(..., mask=, mask_dilation_iterations=) == the reference's host-side masking followed by integrate."""
+    from hive_b200.fusion import TSDFVolume
+    from oracle import driver_oracle as drv
+    sc = Scene("small", "room")
+    gpu = TSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    orc = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    for i in range(4):
+        fr = sc.frame(i)
+        depth_before = fr.depth.copy()
+        gpu.integrate(fr.rgb, fr.depth, sc.K, fr.pose, mask=fr.mask, mask_dilation_iterations=4)
+        assert np.array_equal(fr.depth, depth_before)  # the caller's array is not modified
+        d = fr.depth.copy()
+        d[drv.dilate_mask(fr.mask, 4) > 0] = 0.0
+        orc.integrate(fr.rgb, d, sc.K, fr.pose)
+    tsdf, color = gpu.get_volume()
+    assert np.abs(tsdf - orc._tsdf_vol_cpu).max() <= 1e-5
+    assert np.array_equal(gpu.get_weight_volume(), orc._weight_vol_cpu)
+    assert np.array_equal(color, orc._color_vol_cpu)
+
+
+@pytest.mark.parametrize("max_voxels", [None, 300_000])
+@pytest.mark.parametrize("inpainted", [False, True])
+def test_tsdf_fusion_driver_matches_oracle(max_voxels, inpainted, c_oracle, monkeypatch):
+    from hive_b200 import hive_fusion
+    from oracle import driver_oracle as drv
+    from oracle import fusion_oracle as fo
+    sc = Scene("small", "room")
+    frame_set = [0, 2, 3, 5]
+    opts = hive_fusion.BackgroundMeshOptions(depth_mask_dilation_iterations=3, sdf_voxel_size=0.06,
+                                             sdf_max_voxels=max_voxels)
+    created = []
+    base = hive_fusion.fusion.TSDFVolume
+
+    class Spy(base):
+        def __init__(self, *a, **k):
+            super().__init__(*a, **k)
+            created.append(self)
+
+    monkeypatch.setattr(hive_fusion.fusion, "TSDFVolume", Spy)
+    mesh = hive_fusion.tsdf_fusion(SyntheticDataset(sc, 6, inpainted), opts, frame_set=frame_set)
+    vol, _ = drv.tsdf_fusion(SyntheticDataset(sc, 6, inpainted), 0.06, max_voxels, 3, frame_set)
+    vs, bounds = hive_fusion.adjust_voxel_size(SyntheticDataset(sc, 6), opts, frame_set)
+    ovs, obounds = drv.adjust_voxel_size(SyntheticDataset(sc, 6), 0.06, max_voxels, frame_set)
+    assert vs == ovs and np.array_equal(bounds, obounds)
+    assert (vs > 0.06) == bool(max_voxels)
+
+    # planes: the driver's volume against the oracle's driver
+    gpu = created[0]
+    tsdf, color = gpu.get_volume()
+    assert tsdf.shape == vol._tsdf_vol_cpu.shape
+    assert np.abs(tsdf - vol._tsdf_vol_cpu).max() <= 1e-5
+    assert np.array_equal(gpu.get_weight_volume(), vol._weight_vol_cpu)
+    assert np.array_equal(color, vol._color_vol_cpu)
+    # mesh: the oracle's marching cubes on the very planes the GPU meshed (signs are then equal by construction)
+    ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
+    order = np.argsort(ok, kind="stable")
+    rank = np.empty_like(order)
+    rank[order] = np.arange(len(order))
+    ow, oc = fo.mesh_postprocess(ov[order], color, gpu._voxel_size, gpu._vol_origin)
+    assert len(ov) > 1000
+    assert np.array_equal(mesh.faces, rank[of].astype(np.int32))
+    assert np.array_equal(mesh.vertices, ow) and np.array_equal(mesh.vertex_colors, oc)
+    assert np.abs(mesh.vertex_normals - on[order]).max() <= 1e-6
