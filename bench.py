@@ -252,6 +252,27 @@ def measure_mesh(vol, torch, peak, repeats=5):
             "scene": "room", "launches_per_extraction": 8}
 
 
+def measure_mesh_sharded(vol, world, rank, dist, torch, repeats=3):
+    """Seam-stitched get_mesh of the z-slab sharded volume: halo exchange + per-slab marching cubes + gather to rank 0
+    + key resolution + D2H, wall clock between barriers, max over ranks (median of `repeats` after one warm-up)."""
+    times, out = [], None
+    for r in range(repeats + 1):
+        out = None
+        _barrier(world, dist, torch)
+        t0 = time.perf_counter()
+        out = vol.get_mesh()
+        torch.cuda.synchronize()
+        ms = _max_over_ranks((time.perf_counter() - t0) * 1000.0, world, dist, torch)
+        if r > 0:
+            times.append(ms)
+    res = {"get_mesh_e2e_ms": float(np.median(times)), "scene": "room", "slabs": world,
+           "voxels": int(np.prod(vol.global_dim)), "stitched": True}
+    if rank == 0:
+        res.update(vertices=int(out[0].shape[0]), triangles=int(out[1].shape[0]),
+                   d2h_bytes=int(sum(a.nbytes for a in out)))
+    return res
+
+
 def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
     """Per-frame foreground depth-to-mesh (BASELINE config C4 shape: 640x480, frame-partitioned across ranks)."""
     from hive_b200 import geometric
@@ -434,7 +455,8 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
 
     # roofline of the dominant kernel on this rank: algorithmic bytes / event-timed launch duration
     launches = n_frames
-    bytes_per_launch = (24.0 * local_updates + 8.0 * H * W * n_frames) / launches
+    # (N > 1: the per-GPU average -- slabs of a realistic scene see very different numbers of updates)
+    bytes_per_launch = (24.0 * total_updates / world + 8.0 * H * W * n_frames) / launches
     avg_launch_ms = ms / launches
     achieved_gbs = bytes_per_launch / (avg_launch_ms / 1000.0) / 1e9
 
@@ -461,6 +483,8 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     mesh = None
     if not args.no_mesh and variant == "room" and world == 1:
         mesh = measure_mesh(vol.local, torch, peak)
+    elif not args.no_mesh and variant == "room":
+        mesh = measure_mesh_sharded(vol, world, rank, dist, torch)
 
     return {
         "value": value, "ms_per_step": ms / K, "frames_per_s": n_frames / (ms / 1000.0),
