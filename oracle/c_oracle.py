@@ -61,7 +61,7 @@ class COracleTSDFVolume:
     def integrate(self, color_im, depth_im, cam_intr, cam_pose, obs_weight=1.0):
         H, W = depth_im.shape
         folded = np.ascontiguousarray(fo.fold_color(color_im), dtype=np.float32)
-        depth = np.ascontiguousarray(depth_im, dtype=np.float32)
+        depth = np.ascontiguousarray(depth_im, dtype=np.float64)  # as given: the CPU path keeps depth_im's precision
         w2c = np.ascontiguousarray(np.linalg.inv(np.asarray(cam_pose, dtype=np.float64))[:3, :])
         k = np.asarray(cam_intr).astype(np.float32)
         intr = np.array([k[0, 0], k[1, 1], k[0, 2], k[1, 2]], dtype=np.float32)

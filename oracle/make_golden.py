@@ -11,6 +11,10 @@ synthetic inputs (``hive_b200.synthetic``).  The fixtures travel to the GPU box,
 ``frustum.npz``          get_view_frustum of three frames (fusion.py:361-375)
 ``backproject.npz``      point_cloud_from_depth / image2world / world2image of one frame (hive/geometric.py:107-206)
 
+``tsdf_7scenes.npz``     the reference's own fixture data (third_party/tsdf_fusion_python/data, read as demo.py:19-55
+                         reads it): frames 0/250/500/750/999 subsampled 4x (160x120, intrinsics scaled), bounds from the
+                         reference's get_view_frustum, 6 cm voxels; inputs and the reference's output planes
+
 Planes are stored losslessly (npz, deflate); every file also carries the SHA-256 of the raw little-endian bytes.
 """
 from __future__ import annotations
@@ -47,12 +51,47 @@ def tsdf_case(fusion, variant: str, weights):
                 sha_tsdf=sha(t), sha_weight=sha(w), sha_color=sha(c))
 
 
+def seven_scenes_case(fusion, indices=(0, 250, 500, 750, 999), step=4, voxel_size=0.06):
+    """The 7-Scenes frames shipped with the reference, read like demo.py:19-55, subsampled so the fixture stays small."""
+    import cv2
+    data = os.path.join(ref_shim.REFERENCE_ROOT, "third_party", "tsdf_fusion_python", "data")
+    cam_intr = np.loadtxt(os.path.join(data, "camera-intrinsics.txt"), delimiter=' ')
+    cam_intr[:2] /= step  # pixel (u, v) of the subsampled image = (u, v) / step of the full image
+    depths, colors, poses = [], [], []
+    vol_bnds = np.zeros((3, 2))
+    for i in indices:
+        depth_im = cv2.imread(os.path.join(data, "frame-%06d.depth.png" % i), -1).astype(float)
+        depth_im /= 1000.
+        depth_im[depth_im == 65.535] = 0
+        depth_im = np.ascontiguousarray(depth_im[::step, ::step])
+        color = cv2.cvtColor(cv2.imread(os.path.join(data, "frame-%06d.color.jpg" % i)), cv2.COLOR_BGR2RGB)
+        color = np.ascontiguousarray(color[::step, ::step])
+        pose = np.loadtxt(os.path.join(data, "frame-%06d.pose.txt" % i))
+        pts = fusion.get_view_frustum(depth_im, cam_intr, pose)
+        vol_bnds[:, 0] = np.minimum(vol_bnds[:, 0], np.amin(pts, axis=1))
+        vol_bnds[:, 1] = np.maximum(vol_bnds[:, 1], np.amax(pts, axis=1))
+        depths.append(depth_im)
+        colors.append(color)
+        poses.append(pose)
+    bounds_in = vol_bnds.copy()
+    vol = fusion.TSDFVolume(vol_bnds, voxel_size, use_gpu=False)
+    for d, c, p in zip(depths, colors, poses):
+        vol.integrate(c, d, cam_intr, p, obs_weight=1.)
+    t, w, c = vol._tsdf_vol_cpu, vol._weight_vol_cpu, vol._color_vol_cpu
+    return dict(depth=np.stack(depths), rgb=np.stack(colors), pose=np.stack(poses), cam_intr=cam_intr,
+                vol_bnds=bounds_in, voxel_size=voxel_size, indices=np.asarray(indices), tsdf=t, weight=w, color=c,
+                vol_dim=np.asarray(vol._vol_dim), vol_origin=vol._vol_origin, sha_tsdf=sha(t), sha_weight=sha(w),
+                sha_color=sha(c))
+
+
 def main():
     assert ref_shim.available(), "the reference tree is needed to generate golden vectors"
     os.makedirs(GOLDEN, exist_ok=True)
     fusion = ref_shim.reference_fusion()
     np.savez_compressed(os.path.join(GOLDEN, "tsdf_tiny_room.npz"), **tsdf_case(fusion, "room", [1.0]))
     np.savez_compressed(os.path.join(GOLDEN, "tsdf_tiny_dense.npz"), **tsdf_case(fusion, "dense", [1.0, 2.0]))
+
+    np.savez_compressed(os.path.join(GOLDEN, "tsdf_7scenes.npz"), **seven_scenes_case(fusion))
 
     scene = Scene("tiny", "room")
     fr = [scene.frame(i) for i in range(3)]

@@ -38,14 +38,15 @@ static inline void unpack(float c, float *r, float *g, float *b) {
  * tsdf/weight/color: dense C-order [X][Y][Z] float32 planes (fusion.py:54-57).
  * wx/wy/wz: per-axis float32 world coordinates, A.2 (fusion.py:183-188).
  * w2c: inv(cam_pose) rows 0..2 (3x4 float64, row-major), A.3.  intr: fx, fy, cx, cy as float32, A.4.
- * depth: (H,W) float32; color: (H,W) float32 already folded (A.1, fusion.py:231-232).
+ * depth: (H,W) float64 -- the CPU path never narrows depth_im (fusion.py:276-281; demo.py:46 feeds float64, HIVE feeds
+ * float32, hive/io.py:1032-1039: widening those is exact); color: (H,W) float32 already folded (A.1, fusion.py:231-232).
  * Returns the number of voxels updated (valid_pts.sum(), fusion.py:279).
  */
 long long hvo_integrate(float *tsdf, float *weight, float *color,
                         long long X, long long Y, long long Z,
                         const float *wx, const float *wy, const float *wz,
                         const double *w2c, const float *intr,
-                        const float *depth, const float *folded, int H, int W,
+                        const double *depth, const float *folded, int H, int W,
                         double trunc, double obs_weight) {
     const double fx = (double)intr[0], fy = (double)intr[1], cx = (double)intr[2], cy = (double)intr[3];
     const float ow32 = (float)obs_weight;
@@ -68,7 +69,7 @@ long long hvo_integrate(float *tsdf, float *weight, float *color,
                 /* A.5 */
                 if (!(u >= 0.0 && u < (double)W && v >= 0.0 && v < (double)H && qz > 0.0)) continue;
                 const size_t pix = (size_t)((long long)v * W + (long long)u);
-                const double d = (double)depth[pix];
+                const double d = depth[pix];
                 const double diff = d - qz;
                 if (!(d > 0.0 && diff >= -trunc)) continue;
                 double dist = diff / trunc;

@@ -150,3 +150,19 @@ def test_integrate_ragged_z(kernel, c_oracle):
     gpu, orc, total = _run_pair(scene, 4, c_oracle, kernel=kernel)
     assert total > 0
     _check(gpu, orc, total)
+
+
+def test_integrate_matches_reference_golden_on_7scenes_data():
+    """GPU against planes produced by the reference itself on its own 7-Scenes fixture frames (float64 depth and
+    intrinsics, real poses, real sensor noise): tests/golden/tsdf_7scenes.npz, see oracle/make_golden.py."""
+    import os
+    from hive_b200.fusion import TSDFVolume
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tsdf_7scenes.npz"))
+    vol = TSDFVolume(g["vol_bnds"].copy(), float(g["voxel_size"]))
+    for d, c, p in zip(g["depth"], g["rgb"], g["pose"]):
+        vol.integrate(c, d, g["cam_intr"], p, obs_weight=1.)
+    tsdf, color = vol.get_volume()
+    assert tsdf.shape == tuple(g["vol_dim"]) and np.array_equal(vol._vol_origin, g["vol_origin"])
+    assert np.array_equal(vol.get_weight_volume(), g["weight"])
+    assert np.abs(tsdf - g["tsdf"]).max() <= TOL
+    assert np.array_equal(color, g["color"])

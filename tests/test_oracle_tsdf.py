@@ -92,3 +92,20 @@ def test_oracle_matches_live_reference(c_oracle):
     assert np.array_equal(ref._weight_vol_cpu, orc._weight_vol_cpu)
     assert np.array_equal(ref._color_vol_cpu, orc._color_vol_cpu)
     assert np.array_equal(ref._tsdf_vol_cpu, orc._tsdf_vol_cpu)
+
+
+@pytest.mark.parametrize("impl", ["numpy", "c"])
+def test_oracle_matches_reference_on_7scenes_fixture(impl, c_oracle):
+    """Real sensor data: the reference's own 7-Scenes frames (third_party/tsdf_fusion_python/data, read as
+    demo.py:19-55 does, subsampled 4x) through the reference's CPU path -> tests/golden/tsdf_7scenes.npz."""
+    g = np.load(os.path.join(GOLDEN, "tsdf_7scenes.npz"))
+    assert _sha(g["tsdf"]) == str(g["sha_tsdf"]) and _sha(g["color"]) == str(g["sha_color"])
+    cls = fo.OracleTSDFVolume if impl == "numpy" else c_oracle.COracleTSDFVolume
+    vol = cls(g["vol_bnds"].copy(), float(g["voxel_size"]))
+    for d, c, p in zip(g["depth"], g["rgb"], g["pose"]):
+        vol.integrate(c, d, g["cam_intr"], p, 1.0)
+    assert tuple(vol._vol_dim) == tuple(g["vol_dim"]) and np.array_equal(vol._vol_origin, g["vol_origin"])
+    assert np.array_equal(vol._weight_vol_cpu, g["weight"])
+    assert np.array_equal(vol._color_vol_cpu, g["color"])
+    assert np.array_equal(vol._tsdf_vol_cpu, g["tsdf"])
+    assert (g["weight"] > 0).sum() > 30_000
