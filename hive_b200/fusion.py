@@ -335,35 +335,28 @@ def get_view_frustum(depth_im, cam_intr, cam_pose):
     return rigid_transform(view_frust_pts.T, cam_pose).T
 
 
-_PLY_VERTEX_HEADER = ("property float x\nproperty float y\nproperty float z\n")
+def _host(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a, a.ctypes.data_as(ctypes.c_void_p)
 
 
-def meshwrite(filename, verts, faces, norms, colors):
-    """Save a 3D mesh to an ASCII polygon .ply file, same format as fusion.py:378-411."""
+def meshwrite(filename, verts, faces, norms, colors, binary=False):
+    """Save a 3D mesh to a polygon .ply file (fusion.py:378-411): byte-identical ASCII output, formatted by all host
+    threads in the C library (the reference spends seconds per 10^6 vertices in a Python loop).  ``binary=True``
+    (extension) writes binary_little_endian instead."""
     verts, faces, norms, colors = (np.asarray(a) for a in (verts, faces, norms, colors))
-    with open(filename, 'w') as f:
-        f.write("ply\nformat ascii 1.0\n")
-        f.write("element vertex %d\n" % verts.shape[0])
-        f.write(_PLY_VERTEX_HEADER)
-        f.write("property float nx\nproperty float ny\nproperty float nz\n")
-        f.write("property uchar red\nproperty uchar green\nproperty uchar blue\n")
-        f.write("element face %d\n" % faces.shape[0])
-        f.write("property list uchar int vertex_index\nend_header\n")
-        lines = ["%f %f %f %f %f %f %d %d %d\n" % (v[0], v[1], v[2], n[0], n[1], n[2], c[0], c[1], c[2])
-                 for v, n, c in zip(verts.tolist(), norms.tolist(), colors.tolist())]
-        f.writelines(lines)
-        f.writelines(["3 %d %d %d\n" % (t[0], t[1], t[2]) for t in faces.tolist()])
+    n_verts, n_faces = int(verts.shape[0]), int(faces.shape[0])
+    assert norms.shape[0] >= n_verts and colors.shape[0] >= n_verts
+    v, vp = _host(verts[:, :3], np.float64)
+    n, npp = _host(norms[:n_verts, :3], np.float64)
+    c, cp = _host(colors[:n_verts, :3], np.uint8)  # '%d' of the reference's uint8 colours
+    f, fp = _host(faces[:, :3], np.int32)
+    _lib.check(_lib.load().hv_meshwrite_ply(os.fsencode(filename), vp, fp, npp, cp, n_verts, n_faces, int(bool(binary))))
 
 
-def pcwrite(filename, xyzrgb):
-    """Save a point cloud to an ASCII polygon .ply file, same format as fusion.py:414-438."""
+def pcwrite(filename, xyzrgb, binary=False):
+    """Save a point cloud to a polygon .ply file (fusion.py:414-438); ``xyzrgb`` is (N, 6) [x y z r g b]."""
     xyzrgb = np.asarray(xyzrgb)
-    xyz = xyzrgb[:, :3]
-    rgb = xyzrgb[:, 3:].astype(np.uint8)
-    with open(filename, 'w') as f:
-        f.write("ply\nformat ascii 1.0\n")
-        f.write("element vertex %d\n" % xyz.shape[0])
-        f.write(_PLY_VERTEX_HEADER)
-        f.write("property uchar red\nproperty uchar green\nproperty uchar blue\nend_header\n")
-        f.writelines(["%f %f %f %d %d %d\n" % (p[0], p[1], p[2], c[0], c[1], c[2])
-                      for p, c in zip(xyz.tolist(), rgb.tolist())])
+    xyz, xp = _host(xyzrgb[:, :3], np.float64)
+    rgb, rp = _host(xyzrgb[:, 3:6].astype(np.uint8), np.uint8)  # fusion.py:418
+    _lib.check(_lib.load().hv_pcwrite_ply(os.fsencode(filename), xp, rp, int(xyz.shape[0]), int(bool(binary))))

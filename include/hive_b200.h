@@ -211,6 +211,15 @@ int hv_upload_frame_masked(const float* h_depth, const uint8_t* h_rgb, const uin
                            int64_t scratch_bytes, void* texels, void* stream);
 int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scratch, float* out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * PLY writers (host pointers, host threads; no CUDA).  Replace meshwrite / pcwrite, fusion.py:378-438: ASCII output
+ * byte-identical to the reference's; binary != 0 writes binary_little_endian with the same elements instead.
+ * verts/norms/xyz: (n,3) float64 (the reference formats Python floats, i.e. doubles); faces (n,3) int32; colours uint8.
+ * ---------------------------------------------------------------------------------------------------------- */
+int hv_meshwrite_ply(const char* filename, const double* verts, const int32_t* faces, const double* norms,
+                     const uint8_t* colors, int64_t n_verts, int64_t n_faces, int binary);
+int hv_pcwrite_ply(const char* filename, const double* xyz, const uint8_t* rgb, int64_t n, int binary);
+
 #ifdef __cplusplus
 }
 #endif

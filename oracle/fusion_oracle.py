@@ -166,3 +166,37 @@ def mesh_postprocess(verts_vox, color_vol, voxel_size, vol_origin):
     r, g, b = unpack_color(rgb)
     colors = np.floor(np.asarray([r, g, b])).T.astype(np.uint8)
     return verts, colors
+
+
+def meshwrite(filename, verts, faces, norms, colors):
+    """fusion.py:378-411, line for line in behaviour: header, one '%'-formatted row per vertex, one per face."""
+    with open(filename, 'w') as f:
+        f.write("ply\nformat ascii 1.0\n")
+        f.write("element vertex %d\n" % (verts.shape[0]))
+        for name in ("x", "y", "z", "nx", "ny", "nz"):
+            f.write("property float %s\n" % name)
+        for name in ("red", "green", "blue"):
+            f.write("property uchar %s\n" % name)
+        f.write("element face %d\n" % (faces.shape[0]))
+        f.write("property list uchar int vertex_index\nend_header\n")
+        for i in range(verts.shape[0]):
+            f.write("%f %f %f %f %f %f %d %d %d\n" % (verts[i, 0], verts[i, 1], verts[i, 2], norms[i, 0], norms[i, 1],
+                                                      norms[i, 2], colors[i, 0], colors[i, 1], colors[i, 2]))
+        for i in range(faces.shape[0]):
+            f.write("3 %d %d %d\n" % (faces[i, 0], faces[i, 1], faces[i, 2]))
+
+
+def pcwrite(filename, xyzrgb):
+    """fusion.py:414-438."""
+    xyz = xyzrgb[:, :3]
+    rgb = xyzrgb[:, 3:].astype(np.uint8)
+    with open(filename, 'w') as f:
+        f.write("ply\nformat ascii 1.0\n")
+        f.write("element vertex %d\n" % (xyz.shape[0]))
+        for name in ("x", "y", "z"):
+            f.write("property float %s\n" % name)
+        for name in ("red", "green", "blue"):
+            f.write("property uchar %s\n" % name)
+        f.write("end_header\n")
+        for i in range(xyz.shape[0]):
+            f.write("%f %f %f %d %d %d\n" % (xyz[i, 0], xyz[i, 1], xyz[i, 2], rgb[i, 0], rgb[i, 1], rgb[i, 2]))
