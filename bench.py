@@ -59,6 +59,10 @@ def parse_args():
     ap.add_argument("--cpu-sample-frames", type=int, default=40)
     ap.add_argument("--d2m-frames", type=int, default=120, help="frames per depth-to-mesh batch")
     ap.add_argument("--no-d2m", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = one base volume per GPU along z (default); strong = the base volume cut in N slabs")
+    ap.add_argument("--no-driver", action="store_true", help="skip the hive.fusion.tsdf_fusion driver measurement")
+    ap.add_argument("--driver-frames", type=int, default=60)
     return ap.parse_args()
 
 
@@ -273,6 +277,69 @@ def measure_mesh_sharded(vol, world, rank, dist, torch, repeats=3):
     return res
 
 
+class _BenchDataset:
+    """What hive.fusion.tsdf_fusion reads from a HiveDataset (hive/fusion.py:79-134), over pre-generated host frames."""
+
+    def __init__(self, frames, K, n):
+        from hive_b200.synthetic import _Indexed, _Trajectory
+        self.num_frames = n
+        self.camera_matrix = K
+        self.has_inpainted_frame_data = False
+        self.camera_trajectory = _Trajectory([np.linalg.inv(frames[i % len(frames)][2]) for i in range(n)])
+        H, W = frames[0][1].shape
+        v, u = np.mgrid[0:H, 0:W]
+        self._masks = [(((u - W * (0.3 + 0.04 * k)) / (0.08 * W)) ** 2 + ((v - 0.55 * H) / (0.3 * H)) ** 2 < 1.0)
+                       .astype(np.uint8) for k in range(8)]  # a walking-person sized blob, 8 positions
+        self.bg_rgb_dataset = _Indexed(lambda i: frames[i % len(frames)][0])
+        self.bg_depth_dataset = _Indexed(lambda i: frames[i % len(frames)][1].copy())
+        self.mask_dataset = _Indexed(lambda i: self._masks[i % 8])
+
+
+def measure_driver(args, base_cfg, frames, torch):
+    """The reference's call site end to end: hive.fusion.tsdf_fusion(dataset, options) (hive/fusion.py:79-134) -- frustum
+    bounds + voxel budget, per-frame 10x mask dilation + depth masking + integrate from host frames, get_mesh to host."""
+    from hive_b200 import hive_fusion, synthetic
+    sc = _scene(base_cfg, "room")
+    n = args.driver_frames
+    ds = _BenchDataset(frames, sc.K, n)
+    n_vox = int(np.prod(synthetic.CONFIGS[base_cfg]["dim"]))
+    opts = hive_fusion.BackgroundMeshOptions(depth_mask_dilation_iterations=10, sdf_voxel_size=sc.voxel_size,
+                                             sdf_max_voxels=n_vox)
+    times, mesh = [], None
+    for r in range(3):
+        mesh = None
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        mesh = hive_fusion.tsdf_fusion(ds, opts)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+    s = float(np.median(times[1:]))
+    vs, bounds = hive_fusion.adjust_voxel_size(ds, opts, range(n))
+    dim = np.ceil((bounds[:, 1] - bounds[:, 0]) / vs).astype(int)
+    cpu = None
+    if not args.no_cpu_baseline:
+        # the same per-frame loop on the host cores: cv2.dilate x10 + masking as the reference does it, then the C port
+        from oracle import c_oracle, driver_oracle as drv
+        c_oracle.build()
+        vol = c_oracle.COracleTSDFVolume(bounds.copy(), vs)
+        poses = ds.camera_trajectory.inverse().to_homogenous_transforms()
+        k = 6
+        t0 = time.perf_counter()
+        for i in range(k):
+            depth = ds.bg_depth_dataset[i]
+            depth[drv.dilate_mask(ds.mask_dataset[i], 10) > 0] = 0.0
+            vol.integrate(ds.bg_rgb_dataset[i], depth, ds.camera_matrix, poses[i], 1.0)
+        cpu = {"frames_per_s": k / (time.perf_counter() - t0), "frames": k, "cores": c_oracle.num_threads(),
+               "kind": "port", "what": "per-frame part only (dilate + mask + integrate), no bounds pass, no marching cubes"}
+        del vol
+    return {"cpu_baseline": cpu, "api": "hive_b200.hive_fusion.tsdf_fusion(dataset, options) == hive.fusion.tsdf_fusion (hive/fusion.py:79-134)",
+            "frames": n, "seconds": s, "frames_per_s": n / s, "voxel_updates_per_s": float(np.prod(dim)) * n / s,
+            "volume": [int(d) for d in dim], "voxel_size": float(vs), "mask_dilation_iterations": 10,
+            "vertices": int(mesh.vertices.shape[0]), "triangles": int(mesh.faces.shape[0]),
+            "includes": "frustum bounds over all frames, volume allocation, mask dilation + depth masking (fused into "
+                        "the upload), integrate from host frames, marching cubes, mesh D2H"}
+
+
 def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
     """Per-frame foreground depth-to-mesh (BASELINE config C4 shape: 640x480, frame-partitioned across ranks)."""
     from hive_b200 import geometric
@@ -331,7 +398,10 @@ def run_ours(args):
 
     from hive_b200 import synthetic
     base_dim = synthetic.CONFIGS[base_cfg]["dim"]
-    dim = (base_dim[0], base_dim[1], base_dim[2] * n_gpus)  # weak scaling: one base volume per GPU along z
+    if args.scaling == "weak":
+        dim = (base_dim[0], base_dim[1], base_dim[2] * n_gpus)  # one base volume per GPU along z
+    else:
+        dim = tuple(base_dim)  # BASELINE configs C3 / C5: the named global volume, cut into N z-slabs
     n_distinct = max(2, min(args.distinct_frames, args.batch * (args.steps + args.warmup)))
 
     # Host-side synthetic data first (fork pool), CUDA afterwards.  Only rank 0 owns frames; others receive broadcasts.
@@ -365,6 +435,11 @@ def run_ours(args):
     if not args.no_d2m:
         d2m_res = measure_d2m(args, base_cfg, world, rank, torch, dist, peak)
 
+    driver_res = None
+    if not args.no_driver and world == 1 and "room" in frames:
+        torch.cuda.empty_cache()
+        driver_res = measure_driver(args, base_cfg, frames["room"], torch)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -373,7 +448,7 @@ def run_ours(args):
     H, W = main["H"], main["W"]
     out = {
         "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64 projection / f32 state", "data": "synthetic",
         "config": {
             "workload": f"{base_cfg}: {'x'.join(map(str, dim))} TSDF @ {sc.voxel_size * 100:g} cm, {W}x{H} synthetic frames, "
@@ -411,6 +486,8 @@ def run_ours(args):
             out["mesh"] = r["mesh"]
     if d2m_res is not None:
         out["depth_to_mesh"] = d2m_res
+    if driver_res is not None:
+        out["driver"] = driver_res
     if not args.no_cpu_baseline and n_gpus == 1:
         out["cpu_baseline"] = cpu_baseline(base_cfg, args.scene, frames[args.scene], args.cpu_sample_frames)
     print(json.dumps(out))

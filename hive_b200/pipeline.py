@@ -113,3 +113,20 @@ class Pipeline:
         if kept:
             _lib.check(lib.hv_filter_faces(*args, 1, _ptr(totals), _ptr(out), stream))
         return _xfer.to_host(out).astype(faces.dtype, copy=False)
+
+    @staticmethod
+    def _get_mesh_texture_and_uv(vertices, image, camera_matrix, rotation=geometric._EYE, translation=geometric._ZERO_T,
+                                 scale_factor=1.0):
+        """pipeline.py:782-810: project the vertices (GPU ``world2image``, int32 pixels like the reference's default),
+        crop the image to their bounding box and shift the UVs to the crop.  Returns (texture (h, w, 3), uv (N, 2))."""
+        vertices, image = np.asarray(vertices), np.asarray(image)
+        geometric.validate_shape(vertices, 'vertices', (None, 3))
+        geometric.validate_shape(image, 'image', (None, None, 3))
+        geometric.validate_camera_parameter_shapes(camera_matrix, rotation, translation)
+        uv, _ = geometric.world2image(vertices, camera_matrix, rotation, translation, scale_factor)
+        lo = np.min(np.round(uv), axis=0)
+        min_u, min_v = lo.astype(int)
+        max_u, max_v = np.max(np.round(uv), axis=0).astype(int) + 1
+        texture = image[min_v:max_v, min_u:max_u, :].copy()
+        uv -= lo
+        return texture, uv

@@ -102,3 +102,14 @@ def canonical_faces(faces):
     k = np.argmin(f, axis=1)
     rolled = np.stack([f[np.arange(len(f)), (k + i) % 3] for i in range(3)], axis=1)
     return rolled[np.lexsort((rolled[:, 2], rolled[:, 1], rolled[:, 0]))]
+
+
+def get_mesh_texture_and_uv(vertices, image, camera_matrix, rotation=np.eye(3), translation=np.zeros((3, 1)),
+                            scale_factor=1.0):
+    """hive/pipeline.py:782-810 over the oracle's world2image."""
+    uv, _ = world2image(vertices, camera_matrix, rotation, translation, scale_factor)
+    min_u, min_v = np.min(np.round(uv), axis=0).astype(int)
+    max_u, max_v = np.max(np.round(uv), axis=0).astype(int) + 1
+    texture = image[min_v:max_v, min_u:max_u, :].copy()
+    uv -= np.min(np.round(uv), axis=0)
+    return texture, uv

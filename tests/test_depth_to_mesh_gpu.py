@@ -138,3 +138,21 @@ def test_batch_equals_single_frames_and_handles_empty_frames():
         assert len(v) > 0 and f.max() < len(v)
     v, f, _, _ = batch.frame(2)
     assert v.shape == (0, 3) and f.shape == (0, 3)
+
+
+def test_texture_crop_and_uv_match_oracle():
+    """Pipeline._get_mesh_texture_and_uv (hive/pipeline.py:782-810): crop + UVs bit-exact."""
+    from hive_b200.pipeline import Pipeline
+    from hive_b200 import geometric
+    from oracle import d2m_oracle as d2m
+    sc = Scene("small", "room")
+    fr = sc.frame(3)
+    w2c = np.linalg.inv(fr.pose)
+    R, t = w2c[:3, :3], w2c[:3, 3:]
+    verts = geometric.point_cloud_from_depth(fr.depth, fr.mask == 1, sc.K, R, t)
+    assert len(verts) > 100
+    tex, uv = Pipeline._get_mesh_texture_and_uv(verts, fr.rgb, sc.K, R, t)
+    otex, ouv = d2m.get_mesh_texture_and_uv(d2m.point_cloud_from_depth(fr.depth, fr.mask == 1, sc.K, R, t), fr.rgb, sc.K, R, t)
+    assert tex.shape == otex.shape and np.array_equal(tex, otex)
+    assert uv.dtype == ouv.dtype and np.array_equal(uv, ouv)
+    assert uv.min() == 0 and tex.shape[0] == uv[:, 1].max() + 1 and tex.shape[1] == uv[:, 0].max() + 1
