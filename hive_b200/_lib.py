@@ -55,6 +55,9 @@ SIGNATURES = {
     "hv_upload_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_int64, c_void_p, c_void_p],
     "hv_depth_max": [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p],
+    "hv_cc_edge_keys": [c_void_p, c_int64, c_int64, c_void_p, c_void_p],
+    "hv_cc_scratch_bytes": [c_int64, c_void_p],
+    "hv_cc_label": [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     "hv_meshwrite_ply": [ctypes.c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int],
     "hv_pcwrite_ply": [ctypes.c_char_p, c_void_p, c_void_p, c_int64, c_int],
     "hv_filter_faces": [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_double, c_double, c_void_p, c_int64, c_int,

@@ -70,6 +70,16 @@ __device__ __forceinline__ int float_order_key(float f) {
     return i >= 0 ? i : i ^ 0x7fffffff;
 }
 
+__global__ void mc_init_kernel(unsigned long long* totals, unsigned int* n_active) {
+    if (threadIdx.x == 0) {
+        totals[0] = 0ull;
+        totals[1] = 0ull;
+        totals[2] = 0x7fffffffull;  // min key
+        totals[3] = 0x80000000ull;  // max key
+        *n_active = 0u;
+    }
+}
+
 // ---- 1. sign bits + min/max ----------------------------------------------------------------------------------------
 // A warp covers 128 consecutive zb of one column (each lane a float4 -> 4 sign bits, 8 lanes -> one 32-bit word) and
 // strides over (column, segment) tiles; whole-volume shards (no low halo, 16-byte aligned columns) take the LDG.128 path.
@@ -587,9 +597,7 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     HV_REQUIRE(totals, "hv_mc_count: null totals");
     g.totals = totals;
     cudaStream_t st = hv::as_stream(stream);
-    const unsigned long long init[4] = {0ull, 0ull, 0x7fffffffull, 0x80000000ull};
-    HV_CUDA(cudaMemcpyAsync(totals, init, sizeof(init), cudaMemcpyHostToDevice, st));
-    HV_CUDA(cudaMemsetAsync(g.n_active, 0, sizeof(unsigned int), st));
+    hv::mc_init_kernel<<<1, 32, 0, st>>>(totals, g.n_active);  // (a pageable H2D of the four counters would block the host)
     const int sms = hv::device_info().sm_count;
     hv::McSignGeom sg;
     sg.segs = (g.Zb + 127) / 128;

@@ -167,6 +167,43 @@ class McPlan:
         return mesh
 
 
+def _extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
+    """count -> (allocate the outputs while the classification kernels run) -> read the totals -> emit.  Same result as
+    ``extract``; the output allocations no longer sit between the caller and the first kernel."""
+    torch = self._torch
+    dev = self.device
+    self.count()
+    with torch.cuda.device(dev):
+        verts = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
+        verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
+        normals = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
+        colors = torch.empty((cap_verts, 3), dtype=torch.uint8, device=dev)
+        vert_keys = torch.empty((max(cap_verts, 1),), dtype=torch.int64, device=dev)
+        faces = torch.empty((cap_tris, 3), dtype=torch.int32, device=dev)
+    n_verts, n_tris, vmin, vmax = self.read_totals()
+    check_surface(self.level, vmin, vmax, n_verts)
+    if n_verts > cap_verts or n_tris > cap_tris:
+        mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
+    else:
+        origin = np.ascontiguousarray(origin, dtype=np.float32)
+        with torch.cuda.device(dev):
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_emit(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
+                _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
+                origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
+                _ptr(colors), _ptr(faces), None, None, _ptr(vert_keys), stream))
+        mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
+                          colors[:n_verts], faces[:n_tris], None, None, vert_keys[:n_verts], 0.0, 0.0)
+    mesh.vmin, mesh.vmax = vmin, vmax
+    return mesh
+
+
+McPlan.extract_overlapped = _extract_overlapped
+
+
 def check_surface(level, vmin, vmax, n_verts):
     """The two errors of skimage.measure.marching_cubes that HIVE can observe."""
     if level < vmin or level > vmax:
@@ -183,7 +220,11 @@ def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
     """Mesh of a (single-GPU, whole) ``TSDFVolume`` as device tensors."""
     X, Y, Z = (int(d) for d in vol._local_dim)
     assert min(X, Y, Z) >= 2, "Input array must be at least 2x2x2."
-    plan = McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, (X, Y, Z), vol._pitch, level=level)
+    # scratch (1.1 B/voxel) is kept with the volume: repeated extractions (HIVE meshes once, a live preview meshes often)
+    # skip the allocation and the classification can start immediately
+    plan = getattr(vol, "_mc_plan", None)
+    if plan is None or plan.level != float(level) or plan.tsdf is not vol._tsdf_vol_gpu:
+        plan = vol._mc_plan = McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, (X, Y, Z), vol._pitch, level=level)
     # capacity: a few voxel layers' worth of surface, or what the previous extraction of this shape needed
     guess = _LAST_SIZES.get((X, Y, Z))
     if guess is None:
@@ -191,7 +232,7 @@ def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
         guess = (6 * area, 12 * area)
     cap_v = min(guess[0], 3 * X * Y * Z)
     cap_t = min(guess[1], 5 * X * Y * Z)
-    mesh = plan.extract(vol._voxel_size, vol._vol_origin, cap_v, cap_t, want_voxel=want_voxel)
+    mesh = plan.extract_overlapped(vol._voxel_size, vol._vol_origin, cap_v, cap_t, want_voxel=want_voxel)
     n_v, n_t = int(mesh.verts.shape[0]), int(mesh.faces.shape[0])
     _LAST_SIZES[(X, Y, Z)] = (n_v + n_v // 2 + 1024, n_t + n_t // 2 + 1024)
     return mesh

@@ -130,3 +130,42 @@ class Pipeline:
         texture = image[min_v:max_v, min_u:max_u, :].copy()
         uv -= lo
         return texture, uv
+
+    @staticmethod
+    def _cleanup_with_connected_components(vertices, faces, is_object=True, min_components=5):
+        """pipeline.py:741-779: drop floating fragments.  Faces adjacent across an edge that exactly two faces share form
+        a graph; components with fewer than ``min_components`` faces go; for an object only the largest survives.
+        Returns (vertices, kept faces in their original order); the vertex array is returned as given (the reference's
+        ``mesh.vertices`` after ``update_faces`` also still holds the unreferenced vertices)."""
+        vertices, faces = np.asarray(vertices), np.asarray(faces)
+        geometric.validate_shape(vertices, 'vertices', (None, 3))
+        geometric.validate_shape(faces, 'faces', (None, 3))
+        if faces.shape[0] == 0:
+            return vertices, faces
+        keep = face_component_mask(faces, vertices.shape[0], min_components, largest_only=is_object)
+        return vertices, faces[keep]
+
+
+def face_component_mask(faces, n_verts, min_len=5, largest_only=True, return_labels=False):
+    """Boolean keep-mask over ``faces`` (host (F, 3) int array) from the GPU connected-components kernels."""
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n_faces = int(faces.shape[0])
+    f = _xfer.to_device(faces, dev, np.int32)
+    with torch.cuda.device(dev):
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        keys = torch.empty(3 * n_faces, dtype=torch.int64, device=dev)
+        _lib.check(lib.hv_cc_edge_keys(_ptr(f), n_faces, int(n_verts), _ptr(keys), stream))
+        sorted_keys, slot = torch.sort(keys, stable=True)  # radix sort of the 3F edge keys: library plumbing
+        nbytes = ctypes.c_int64(0)
+        _lib.check(lib.hv_cc_scratch_bytes(n_faces, ctypes.byref(nbytes)))
+        scratch = torch.empty(int(nbytes.value) // 8 + 1, dtype=torch.int64, device=dev)
+        keep = torch.empty(n_faces, dtype=torch.uint8, device=dev)
+        labels = torch.empty(n_faces, dtype=torch.int32, device=dev) if return_labels else None
+        _lib.check(lib.hv_cc_label(_ptr(sorted_keys), _ptr(slot), n_faces, int(min_len), int(bool(largest_only)),
+                                   _ptr(scratch), int(nbytes.value), _ptr(keep), _ptr(labels), stream))
+    if return_labels:
+        k, lab = _xfer.to_host(keep, labels)
+        return k.view(np.bool_), lab.view(np.uint32)
+    return _xfer.to_host(keep).view(np.bool_)

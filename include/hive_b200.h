@@ -212,6 +212,20 @@ int hv_upload_frame_masked(const float* h_depth, const uint8_t* h_rgb, const uin
 int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scratch, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Connected components over the face-adjacency graph: the body of Pipeline._cleanup_with_connected_components
+ * (hive/pipeline.py:741-779 -> trimesh.graph.connected_components(mesh.face_adjacency, min_len)).
+ *   hv_cc_edge_keys: keys[3f + k] = min(v_a, v_b) * n_verts + max(v_a, v_b) for the three edges of face f.
+ *   The caller sorts the 3F keys ascending (stable) and passes them with slot[i] = original index of sorted key i.
+ *   hv_cc_label: keep[f] = 1 iff face f survives (faces adjacent across an edge that exactly two faces use form the
+ *   graph; components below min_len faces are dropped; largest_only keeps the largest survivor, lowest face index on a
+ *   tie); labels (optional, F uint32) = component root per face, 0xffffffff for faces without any neighbour.
+ * ---------------------------------------------------------------------------------------------------------- */
+int hv_cc_edge_keys(const int32_t* faces, int64_t n_faces, int64_t n_verts, unsigned long long* keys, void* stream);
+int hv_cc_scratch_bytes(int64_t n_faces, int64_t* h_bytes);
+int hv_cc_label(const unsigned long long* sorted_keys, const int64_t* slot, int64_t n_faces, int min_len,
+                int largest_only, void* scratch, int64_t scratch_bytes, uint8_t* keep, uint32_t* labels, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * PLY writers (host pointers, host threads; no CUDA).  Replace meshwrite / pcwrite, fusion.py:378-438: ASCII output
  * byte-identical to the reference's; binary != 0 writes binary_little_endian with the same elements instead.
  * verts/norms/xyz: (n,3) float64 (the reference formats Python floats, i.e. doubles); faces (n,3) int32; colours uint8.

@@ -113,3 +113,43 @@ def get_mesh_texture_and_uv(vertices, image, camera_matrix, rotation=np.eye(3), 
     texture = image[min_v:max_v, min_u:max_u, :].copy()
     uv -= np.min(np.round(uv), axis=0)
     return texture, uv
+
+
+def face_adjacency(faces):
+    """trimesh.Trimesh.face_adjacency as HIVE uses it: pairs of faces sharing an edge that exactly two faces use."""
+    faces = np.asarray(faces)
+    edges = np.sort(faces[:, [0, 1, 1, 2, 2, 0]].reshape(-1, 2), axis=1)
+    face_of = np.repeat(np.arange(len(faces)), 3)
+    order = np.lexsort((edges[:, 1], edges[:, 0]))
+    e = edges[order]
+    start = np.ones(len(e), bool)
+    start[1:] = (e[1:] != e[:-1]).any(axis=1)
+    run_id = np.cumsum(start) - 1
+    run_len = np.bincount(run_id)
+    first = np.flatnonzero(start)[run_len == 2]
+    return np.stack([face_of[order[first]], face_of[order[first + 1]]], axis=1)
+
+
+def cleanup_with_connected_components(vertices, faces, is_object=True, min_components=5):
+    """hive/pipeline.py:741-779 with trimesh.graph.connected_components restated over scipy.sparse.csgraph (trimesh's
+    own default engine): nodes = faces with a neighbour, groups ordered by label, components below min_len dropped."""
+    from scipy.sparse import coo_matrix
+    from scipy.sparse.csgraph import connected_components
+    faces = np.asarray(faces)
+    adj = face_adjacency(faces)
+    mask = np.zeros(len(faces), dtype=bool)
+    if len(adj):
+        n = len(faces)
+        graph = coo_matrix((np.ones(len(adj), bool), (adj[:, 0], adj[:, 1])), shape=(n, n))
+        _, labels = connected_components(graph, directed=False)
+        nodes = np.unique(adj)
+        comps = {}
+        for node in nodes:
+            comps.setdefault(labels[node], []).append(node)
+        components = [np.array(c) for _, c in sorted(comps.items()) if len(c) >= min_components]
+        if components:
+            if is_object:
+                mask[components[int(np.argmax([len(c) for c in components]))]] = True
+            else:
+                mask[np.concatenate(components)] = True
+    return vertices, faces[mask]

@@ -156,3 +156,58 @@ def test_texture_crop_and_uv_match_oracle():
     assert tex.shape == otex.shape and np.array_equal(tex, otex)
     assert uv.dtype == ouv.dtype and np.array_equal(uv, ouv)
     assert uv.min() == 0 and tex.shape[0] == uv[:, 1].max() + 1 and tex.shape[1] == uv[:, 0].max() + 1
+
+
+def _strip(n_quads, v0):
+    """A strip of n_quads quads (2 triangles each) on fresh vertices starting at index v0."""
+    faces = []
+    for q in range(n_quads):
+        a, b, c, d = v0 + 2 * q, v0 + 2 * q + 1, v0 + 2 * q + 2, v0 + 2 * q + 3
+        faces += [[a, b, c], [c, b, d]]
+    return faces, v0 + 2 * n_quads + 2
+
+
+@pytest.mark.parametrize("is_object", [True, False])
+@pytest.mark.parametrize("min_components", [1, 5, 9])
+def test_connected_components_cleanup_matches_oracle(is_object, min_components):
+    """Pipeline._cleanup_with_connected_components (hive/pipeline.py:741-779) against the scipy restatement."""
+    from hive_b200.pipeline import Pipeline
+    faces, nv = [], 0
+    for n_quads in (6, 2, 6, 1, 4):  # two largest components tie (12 faces each): the first one wins for objects
+        f, nv = _strip(n_quads, nv)
+        faces += f
+    faces.append([nv, nv + 1, nv + 2])  # an isolated face: no neighbour, always dropped
+    nv += 3
+    fan, hub = [], nv  # three faces around one shared edge: that edge links nothing (trimesh requires exactly two users)
+    fan += [[hub, hub + 1, hub + 2], [hub, hub + 1, hub + 3], [hub, hub + 1, hub + 4], [hub + 2, hub + 5, hub]]
+    faces += fan
+    nv += 6
+    faces = np.array(faces, dtype=np.int32)
+    rng = np.random.default_rng(3)
+    faces = faces[rng.permutation(len(faces))]
+    verts = rng.standard_normal((nv, 3))
+    gv, gf = Pipeline._cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_components)
+    ov, of = d2m.cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_components)
+    assert gv is verts or np.array_equal(gv, verts)
+    assert np.array_equal(gf, of)
+    if is_object and min_components <= 12:
+        assert len(gf) == 12
+
+
+def test_connected_components_on_a_depth_mesh():
+    from hive_b200 import pipeline
+    from hive_b200.pipeline import Pipeline
+    sc = Scene("small", "room")
+    fr = sc.frame(1)
+    w2c = np.linalg.inv(fr.pose)
+    R, t = w2c[:3, :3], w2c[:3, 3:]
+    depth = fr.depth.copy()
+    depth[::7, ::5] = 0.0  # punch holes so that fragments and pinched regions appear
+    verts, faces, _, _ = pipeline.depth_to_mesh(depth, fr.mask > 0, sc.K, R, t)
+    assert len(faces) > 2000
+    for is_object, min_c in ((True, 5), (False, 5), (False, 40)):
+        _, gf = Pipeline._cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_c)
+        _, of = d2m.cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_c)
+        assert np.array_equal(gf, of) and 0 < len(gf) <= len(faces)
+    keep, labels = pipeline.face_component_mask(faces, len(verts), 5, largest_only=False, return_labels=True)
+    assert len(np.unique(labels[keep])) >= 2  # both instances survive as separate components
