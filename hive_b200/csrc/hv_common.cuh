@@ -36,11 +36,12 @@ const DeviceInfo& device_info();
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // hv_scan.cu: offs[i] = sum of counts[0..i) componentwise; totals[0..1] (device, optional) receive the grand totals.
-// `bsum` is scratch of scan_tiles(n) pairs.
+// `bsum` is scratch of scan_scratch_pairs(n) pairs.
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;
 long long scan_tiles(long long n);
+long long scan_scratch_pairs(long long n);  // size of `bsum` in pairs
 void exclusive_scan_u2(const uint2* counts, uint2* offs, uint2* bsum, long long n, unsigned long long* totals,
                        cudaStream_t st);
 

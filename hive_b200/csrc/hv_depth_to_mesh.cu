@@ -445,7 +445,7 @@ int d2m_layout(int B, int H, int W, D2mLayout* L) {
     L->off_bits = o;
     o = d2m_align(o + (size_t)L->n_words * sizeof(unsigned int));
     L->off_bsum = o;
-    o = d2m_align(o + (size_t)hv::scan_tiles(L->n_words) * sizeof(uint2));
+    o = d2m_align(o + (size_t)hv::scan_scratch_pairs(L->n_words) * sizeof(uint2));
     L->total = o;
     return HV_OK;
 }

@@ -89,6 +89,32 @@ struct McSignGeom {
     int vec;         // 1: z == zb and columns are float4-aligned
 };
 
+// Sign nibble of four values + running min/max.
+__device__ __forceinline__ unsigned int mc_sign4(const float (&v)[4], float level_f, bool level_exact, double level,
+                                                 float& vmin, float& vmax) {
+    unsigned int nib = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const bool pos = level_exact ? (v[k] > level_f) : ((double)v[k] > level);  // NaN (padding) -> 0
+        nib |= pos ? (1u << k) : 0u;
+    }
+    vmin = fminf(vmin, fminf(fminf(v[0], v[1]), fminf(v[2], v[3])));  // fminf / fmaxf ignore NaN
+    vmax = fmaxf(vmax, fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3])));
+    return nib;
+}
+
+__device__ __forceinline__ void mc_store_word(const McGrid& g, unsigned int nib, int lane, size_t col, int seg) {
+    unsigned int word = nib << (4 * (lane & 7));
+    word |= __shfl_xor_sync(0xffffffffu, word, 1);
+    word |= __shfl_xor_sync(0xffffffffu, word, 2);
+    word |= __shfl_xor_sync(0xffffffffu, word, 4);
+    const int gq = seg * 4 + (lane >> 3);
+    if ((lane & 7) == 0 && gq < g.G) g.bits[col * g.G + gq] = word;
+}
+
+// A warp takes whole columns (grid-stride) and walks their 128-zb segments: no tile decode, and in the vector path two
+// segments (2 x 512 B per warp) are in flight together.  r01: the tile-indexed version spent 78 warp-instructions per
+// 128 voxels, a third of them in the integer division of the tile decode, and ran at 63 % issue / 55 % DRAM.
 __global__ void __launch_bounds__(256) mc_sign_kernel(const McGrid g, const McSignGeom sg) {
     const int lane = threadIdx.x & 31;
     const int warp0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -96,34 +122,60 @@ __global__ void __launch_bounds__(256) mc_sign_kernel(const McGrid g, const McSi
     float vmin = INFINITY, vmax = -INFINITY;
     const float level_f = (float)g.level;  // exact compare needs double only when the level is not a float
     const bool level_exact = (double)level_f == g.level;
-    for (int tile = warp0; tile < sg.n_tiles; tile += n_warps) {
-        const int col = tile / sg.segs;
-        const int seg = tile - col * sg.segs;
-        const int zb0 = seg * 128 + lane * 4;
-        float v[4];
-        if (sg.vec && zb0 + 3 < g.Z) {
-            const float4 q = __ldcs(reinterpret_cast<const float4*>(g.tsdf + (size_t)col * g.pitch + zb0));
-            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+    const int n_cols = g.X * g.Y;
+    for (int col = warp0; col < n_cols; col += n_warps) {
+        if (sg.vec) {
+            const float* base = g.tsdf + (size_t)col * g.pitch + lane * 4;
+            int seg = 0;
+            for (; seg + 1 < sg.segs; seg += 2) {
+                const int za = seg * 128 + lane * 4, zb = za + 128;
+                float a[4] = {NAN, NAN, NAN, NAN}, b[4] = {NAN, NAN, NAN, NAN};
+                const bool fa = za + 3 < g.Z, fb = zb + 3 < g.Z;
+                if (fa) {
+                    const float4 q = __ldcs(reinterpret_cast<const float4*>(base + seg * 128));
+                    a[0] = q.x; a[1] = q.y; a[2] = q.z; a[3] = q.w;
+                }
+                if (fb) {
+                    const float4 q = __ldcs(reinterpret_cast<const float4*>(base + seg * 128 + 128));
+                    b[0] = q.x; b[1] = q.y; b[2] = q.z; b[3] = q.w;
+                }
+                if (!fa) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (za + k < g.Zb) a[k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, col / g.Y, col % g.Y, za + k);
+                }
+                if (!fb) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (zb + k < g.Zb) b[k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, col / g.Y, col % g.Y, zb + k);
+                }
+                mc_store_word(g, mc_sign4(a, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg);
+                mc_store_word(g, mc_sign4(b, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg + 1);
+            }
+            if (seg < sg.segs) {
+                const int za = seg * 128 + lane * 4;
+                float a[4] = {NAN, NAN, NAN, NAN};
+                if (za + 3 < g.Z) {
+                    const float4 q = __ldcs(reinterpret_cast<const float4*>(base + seg * 128));
+                    a[0] = q.x; a[1] = q.y; a[2] = q.z; a[3] = q.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (za + k < g.Zb) a[k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, col / g.Y, col % g.Y, za + k);
+                }
+                mc_store_word(g, mc_sign4(a, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg);
+            }
         } else {
             const int x = col / g.Y, y = col - x * g.Y;
+            for (int seg = 0; seg < sg.segs; ++seg) {
+                const int zb0 = seg * 128 + lane * 4;
+                float v[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                v[k] = (zb0 + k < g.Zb) ? mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb0 + k) : NAN;
+                for (int k = 0; k < 4; ++k)
+                    v[k] = (zb0 + k < g.Zb) ? mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb0 + k) : NAN;
+                mc_store_word(g, mc_sign4(v, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg);
+            }
         }
-        unsigned int nib = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const bool pos = level_exact ? (v[k] > level_f) : ((double)v[k] > g.level);  // NaN (padding) -> 0
-            nib |= pos ? (1u << k) : 0u;
-            vmin = fminf(vmin, v[k]);  // fminf / fmaxf ignore NaN
-            vmax = fmaxf(vmax, v[k]);
-        }
-        unsigned int word = nib << (4 * (lane & 7));
-        word |= __shfl_xor_sync(0xffffffffu, word, 1);
-        word |= __shfl_xor_sync(0xffffffffu, word, 2);
-        word |= __shfl_xor_sync(0xffffffffu, word, 4);
-        const int gq = seg * 4 + (lane >> 3);
-        if ((lane & 7) == 0 && gq < g.G) g.bits[(size_t)col * g.G + gq] = word;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -516,7 +568,7 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     L->G = (L->Zb + 31) / 32;
     L->n_groups = (long long)X * Y * L->G;
     HV_REQUIRE(L->n_groups < (1ll << 40) && L->Zb < (1 << 22), "marching cubes: volume too large");
-    L->n_scan_blocks = (int)((L->n_groups + hv::kScanTile - 1) / hv::kScanTile);
+    L->n_scan_blocks = (int)hv::scan_scratch_pairs(L->n_groups);
     size_t o = 0;
     L->off_gmask = o;  // 16-byte elements first
     o = align_up(o + (size_t)L->n_groups * sizeof(uint4));
@@ -605,7 +657,7 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     HV_REQUIRE(n_tiles < (1ll << 31), "hv_mc_count: too many columns");
     sg.n_tiles = (int)n_tiles;
     sg.vec = (!halo_lo && (pitch & 3) == 0 && ((uintptr_t)tsdf & 15) == 0) ? 1 : 0;
-    const long long want = (n_tiles + 7) / 8;  // 8 warps per block
+    const long long want = ((long long)g.X * g.Y + 7) / 8;  // 8 warps per block, a warp per column (grid-stride)
     const long long cap = (long long)sms * 8;
     const int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
     hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g, sg);

@@ -45,6 +45,26 @@ def main():
             torch.cuda.synchronize()
             print(f"mc rep {r}: {e0.elapsed_time(e1):.3f} ms, {mesh.verts.shape[0]} vertices, {mesh.faces.shape[0]} triangles",
                   flush=True)
+        # phase split: classification (sign + count + scans) | host read of the totals | emit + vertices
+        plan = mc.McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, tuple(int(d) for d in vol._local_dim), vol._pitch)
+        for r in range(args.reps):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ev[0].record()
+            plan.count()
+            ev[1].record()
+            t1 = time.perf_counter()
+            nv, nt, _, _ = plan.read_totals()
+            t2 = time.perf_counter()
+            ev[2].record()
+            plan.emit(nv, nt, vol._voxel_size, vol._vol_origin)
+            ev[3].record()
+            torch.cuda.synchronize()
+            t3 = time.perf_counter()
+            print(f"mc phases rep {r}: count {ev[0].elapsed_time(ev[1]):.3f} ms | totals gap {ev[1].elapsed_time(ev[2]):.3f} ms"
+                  f" | emit {ev[2].elapsed_time(ev[3]):.3f} ms || host: launch {1e3 * (t1 - t0):.3f}, wait {1e3 * (t2 - t1):.3f},"
+                  f" emit+sync {1e3 * (t3 - t2):.3f}", flush=True)
     if "d2m" in what:
         B = args.d2m_frames
         fr = [sc.frame(i) for i in range(min(12, B))]
