@@ -172,6 +172,7 @@ def cpu_baseline(config, variant, frames, n_sample, dim=None):
     """Oracle C port of fusion.py:260-303 on all host cores, bounded sample of the same workload."""
     from oracle import c_oracle
     c_oracle.build()
+    c_oracle.use_all_host_threads()
     sc = _scene(config, variant, dim)
     vol = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
     n_vox = int(np.prod(vol._vol_dim))
@@ -194,6 +195,7 @@ def run_reference(args):
         return
     from oracle import c_oracle
     c_oracle.build()
+    c_oracle.use_all_host_threads()
     n_distinct = min(args.distinct_frames, 8)
     frames = make_frames(args.config, args.scene, n_distinct)
     sc = _scene(args.config, args.scene)
@@ -210,7 +212,9 @@ def run_reference(args):
     value = n_vox * args.steps / dt
     cores = c_oracle.num_threads()
     sample = (f"each step = 1 frame (of the GPU arm's {args.batch}-frame step) of {args.config}/{args.scene} through "
-              f"oracle/tsdf_oracle.c, the C/OpenMP port of fusion.py:260-303, {cores} threads")
+              f"oracle/tsdf_oracle.c, the C/OpenMP port of fusion.py:260-303, {cores} threads"
+              + (f"; one 512^3-class slab of the {args.gpus}-slab volume (voxel-updates/s is size-normalised)"
+                 if args.gpus > 1 else ""))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True, "scaling": "weak",

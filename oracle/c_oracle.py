@@ -45,6 +45,12 @@ def num_threads() -> int:
     return int(lib().hvo_num_threads())
 
 
+def use_all_host_threads() -> int:
+    """OpenMP threads = all host cores, whatever OMP_NUM_THREADS says (torchrun sets it to 1 for every rank)."""
+    lib().hvo_set_num_threads(ctypes.c_int(os.cpu_count() or 1))
+    return num_threads()
+
+
 class COracleTSDFVolume:
     """Same contract as ``fusion_oracle.OracleTSDFVolume`` (fusion.py:21-303), executed by tsdf_oracle.c."""
 

@@ -27,6 +27,15 @@ int hvo_num_threads(void) {
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to every rank; the timed CPU arm asks for all host threads explicitly. */
+void hvo_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* fusion.py:293-295 -- float32 unpack of the b*65536+g*256+r colour */
 static inline void unpack(float c, float *r, float *g, float *b) {
     *b = floorf(c / 65536.0f);
