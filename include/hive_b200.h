@@ -78,6 +78,7 @@ int hv_upload_frame(const float* h_depth, const uint8_t* h_rgb, int H, int W, fl
 #define HV_INTEGRATE_KERNEL_PIPE 2       /* column walker: projection of tile i+1 overlapped with the loads of tile i */
 #define HV_INTEGRATE_KERNEL_PIPE_CULL 3  /* + segment-level frustum culling (switched off by the kernel itself when the
                                             whole volume is inside the frustum) */
+#define HV_INTEGRATE_KERNEL_PIPE_CULL_OCC4 4 /* the same at 64 registers / 4 CTAs per SM (A/B: spills vs occupancy) */
 #define HV_INTEGRATE_KERNEL_DEFAULT HV_INTEGRATE_KERNEL_PIPE_CULL
 #define HV_INTEGRATE_KERNEL(v) ((v) << 8)
 int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims, int64_t pitch,

@@ -39,7 +39,7 @@ def _check(gpu, orc, total):
     return float(np.abs(tsdf - orc._tsdf_vol_cpu).max())
 
 
-@pytest.mark.parametrize("kernel", [0, 1, 2, 3])  # include/hive_b200.h HV_INTEGRATE_KERNEL_*
+@pytest.mark.parametrize("kernel", [0, 1, 2, 3, 4])  # include/hive_b200.h HV_INTEGRATE_KERNEL_*
 @pytest.mark.parametrize("variant", ["room", "dense"])
 @pytest.mark.parametrize("config", ["tiny", "small"])
 def test_integrate_matches_oracle(config, variant, kernel, c_oracle):
