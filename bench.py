@@ -183,7 +183,24 @@ def cpu_baseline(config, variant, frames, n_sample, dim=None):
         rgb, depth, pose = frames[(i + 1) % len(frames)]
         vol.integrate(rgb, depth, sc.K, pose)
     dt = time.perf_counter() - t0
-    return {"value": n_vox * n_sample / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
+    # the numpy restatement (the shape of the reference's own CPU path: whole-volume numpy temporaries, one core for most
+    # of it) on two frames of the 256^3 config -- the number closest to what a HIVE user without a GPU gets
+    numpy_port = None
+    try:
+        from oracle import fusion_oracle as fo
+        sc1 = _scene("C1", variant)
+        nv = fo.OracleTSDFVolume(sc1.vol_bnds.copy(), sc1.voxel_size)
+        nv.integrate(rgb, depth, sc1.K, pose)
+        t1 = time.perf_counter()
+        for i in range(2):
+            r2, d2, p2 = frames[(i + 1) % len(frames)]
+            nv.integrate(r2, d2, sc1.K, p2)
+        numpy_port = {"value": float(np.prod(nv._vol_dim)) * 2 / (time.perf_counter() - t1), "unit": UNIT,
+                      "sample": "2 frames into a 256^3 volume through oracle/fusion_oracle.py (numpy)"}
+        del nv
+    except Exception as e:  # the C port above is the baseline of record
+        numpy_port = {"error": str(e)}
+    return {"numpy_port": numpy_port, "value": n_vox * n_sample / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
             "sample": f"{n_sample} frames of {config}/{variant} ({'x'.join(map(str, vol._vol_dim))} voxels, "
                       f"{depth.shape[1]}x{depth.shape[0]}) through oracle/tsdf_oracle.c (OpenMP), {dt:.1f} s",
             "s_per_frame": dt / n_sample}
