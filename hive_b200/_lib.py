@@ -54,6 +54,7 @@ SIGNATURES = {
     "hv_pack_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
     "hv_upload_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_keyframe_overlap": [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p],
     "hv_depth_max": [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p],
     "hv_cc_edge_keys": [c_void_p, c_int64, c_int64, c_void_p, c_void_p],
     "hv_cc_scratch_bytes": [c_int64, c_void_p],

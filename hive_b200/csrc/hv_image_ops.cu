@@ -10,6 +10,7 @@
 //     hv_pack_frame, so the dilated mask never exists as an image and the depth frame is never rewritten.
 //   * depth_max: the np.max(depth_im) of get_view_frustum (fusion.py:364) for a batch of frames.
 #include "hv_common.cuh"
+#include <limits.h>
 
 namespace hv {
 
@@ -193,6 +194,99 @@ extern "C" int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scra
     hv::depth_max_kernel<<<dim3(bx < 1 ? 1 : (bx > 64 ? 64 : bx), B), 256, 0, st>>>(depth, n, keys_scratch);
     HV_CUDA(cudaGetLastError());
     hv::depth_max_finish_kernel<<<(B + 127) / 128, 128, 0, st>>>(keys_scratch, B, out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+// ---- key-frame selection (hive/io.py:1117-1189) ---------------------------------------------------------------------------
+// For one candidate frame and K current key frames: back-project every static pixel (mask == 0, depth > 0;
+// point_cloud_from_depth, hive/geometric.py:107-126), project it into each key frame (world2image with the default int32
+// rounding, geometric.py:155-180), and reduce the bounding box of the projections that land inside the image
+// (io.py:1163-1175).  The reference materialises the point cloud and K projected copies of it per candidate; here nothing
+// is materialised: one thread per pixel, the key frames are an inner loop, boxes are reduced per warp and merged with
+// atomics.  box[k] = {min_u, min_v, max_u, max_v}, count[k] = number of visible points.
+namespace hv {
+
+__global__ void __launch_bounds__(256) keyframe_overlap_kernel(const float* __restrict__ depth, const uint8_t* __restrict__ mask,
+                                                               int H, int W, const double* __restrict__ cam /* Kinv 9, R 9, t 3 */,
+                                                               const double* __restrict__ key_cams /* K x (K 9, R 9, t 3) */,
+                                                               int n_keys, int* __restrict__ box, unsigned int* __restrict__ count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool in_image = i < H * W;
+    const float d32 = in_image ? depth[i] : 0.0f;
+    const bool valid = in_image && mask[i] == 0 && d32 > 0.0f;
+    if (__ballot_sync(0xffffffffu, valid) == 0u) return;
+    double P[3] = {0.0, 0.0, 0.0};
+    if (valid) {
+        const int v = i / W, u = i - v * W;
+        const double *Kinv = cam, *R = cam + 9, *t = cam + 18;
+        const double d = (double)d32, ud = (double)u, vd = (double)v;
+        double X[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {  // same operation order as image2world_kernel (hv_depth_to_mesh.cu)
+            const double pc = fma(Kinv[3 * k + 2], 1.0, fma(Kinv[3 * k + 1], vd, __dmul_rn(Kinv[3 * k], ud)));
+            X[k] = __dsub_rn(__dmul_rn(d, pc), t[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) P[k] = fma(R[6 + k], X[2], fma(R[3 + k], X[1], __dmul_rn(R[k], X[0])));
+    }
+    for (int kf = 0; kf < n_keys; ++kf) {
+        const double *K = key_cams + 21 * kf, *R = K + 9, *t = K + 18;
+        int pu = 0, pv = 0;
+        bool vis = false;
+        if (valid) {
+            double c[3], q[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k)  // same operation order as world2image_kernel
+                c[k] = __dadd_rn(fma(R[3 * k + 2], P[2], fma(R[3 * k + 1], P[1], __dmul_rn(R[3 * k], P[0]))), t[k]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) q[k] = fma(K[3 * k + 2], c[2], fma(K[3 * k + 1], c[1], __dmul_rn(K[3 * k], c[0])));
+            const double a = rint(q[0] / q[2]), b = rint(q[1] / q[2]);
+            // astype(int32) of the rounded value, then 0 <= u < width, 0 <= v < height (io.py:1163-1167)
+            vis = a >= 0.0 && a < (double)W && b >= 0.0 && b < (double)H;
+            pu = vis ? (int)a : 0;
+            pv = vis ? (int)b : 0;
+        }
+        const unsigned int m = __ballot_sync(0xffffffffu, vis);
+        if (m == 0u) continue;
+        int lo_u = vis ? pu : INT_MAX, lo_v = vis ? pv : INT_MAX, hi_u = vis ? pu : INT_MIN, hi_v = vis ? pv : INT_MIN;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo_u = min(lo_u, __shfl_xor_sync(0xffffffffu, lo_u, o));
+            lo_v = min(lo_v, __shfl_xor_sync(0xffffffffu, lo_v, o));
+            hi_u = max(hi_u, __shfl_xor_sync(0xffffffffu, hi_u, o));
+            hi_v = max(hi_v, __shfl_xor_sync(0xffffffffu, hi_v, o));
+        }
+        if (lane == 0) {
+            atomicMin(box + 4 * kf + 0, lo_u);
+            atomicMin(box + 4 * kf + 1, lo_v);
+            atomicMax(box + 4 * kf + 2, hi_u);
+            atomicMax(box + 4 * kf + 3, hi_v);
+            atomicAdd(count + kf, (unsigned int)__popc(m));
+        }
+    }
+}
+
+__global__ void keyframe_box_init_kernel(int* box, unsigned int* count, int n_keys) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_keys) return;
+    box[4 * k + 0] = INT_MAX;
+    box[4 * k + 1] = INT_MAX;
+    box[4 * k + 2] = INT_MIN;
+    box[4 * k + 3] = INT_MIN;
+    count[k] = 0u;
+}
+
+}  // namespace hv
+
+extern "C" int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int H, int W, const double* cam,
+                                   const double* key_cams, int n_keys, int* box, unsigned int* count, void* stream) {
+    HV_REQUIRE(depth && mask && cam && key_cams && box && count, "hv_keyframe_overlap: null pointer");
+    HV_REQUIRE(H > 0 && W > 0 && (long long)H * W < (1ll << 30) && n_keys > 0, "hv_keyframe_overlap: bad arguments");
+    cudaStream_t st = hv::as_stream(stream);
+    hv::keyframe_box_init_kernel<<<(n_keys + 127) / 128, 128, 0, st>>>(box, count, n_keys);
+    hv::keyframe_overlap_kernel<<<(H * W + 255) / 256, 256, 0, st>>>(depth, mask, H, W, cam, key_cams, n_keys, box, count);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

@@ -105,3 +105,68 @@ def tsdf_fusion(dataset, options: BackgroundMeshOptions = None, num_frames=-1, f
         return trimesh.Trimesh(vertices=verts, faces=faces, vertex_colors=colors, vertex_normals=norms)
     except ImportError:
         return Mesh(vertices=verts, faces=faces, vertex_colors=colors, vertex_normals=norms)
+
+
+def select_key_frames(dataset, threshold=0.3, frame_step=30) -> List[int]:
+    """``HiveDataset.select_key_frames`` (hive/io.py:1117-1189): frames whose static points, projected into every key
+    frame so far, cover less than ``threshold`` of the image (bounding-box area of the visible projections).
+
+    The reference materialises the candidate's point cloud and one projected copy per key frame on the host; here one
+    kernel per candidate frame back-projects, projects into all current key frames and reduces the boxes
+    (``hv_keyframe_overlap``), so a candidate costs one H2D of its depth + mask and 20 bytes per key frame back.
+    ``dataset``: ``num_frames``, ``camera_matrix``, ``camera_trajectory.to_homogenous_transforms()`` (world-to-camera),
+    ``bg_depth_dataset[i]``, ``mask_dataset[i]``.
+    """
+    import ctypes
+
+    from . import _lib, _xfer, geometric
+    logging.info(f"Selecting key frames (threshold={threshold})...")
+    if not (0.0 <= threshold <= 1.0):
+        raise ValueError(f"Threshold must be a real number between zero and one (inclusive), but got {threshold}.")
+    if threshold == 0.0:
+        return [0]
+    elif threshold == 1.0:
+        return list(range(dataset.num_frames))
+    if frame_step < 1:
+        raise ValueError(f"Frame step must be a positive integer, but got {frame_step} instead.")
+
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    K = np.asarray(dataset.camera_matrix)
+    kinv = geometric._kinv64(K)
+    K64 = np.asarray(K, dtype=np.float64)
+    poses = np.asarray(dataset.camera_trajectory.to_homogenous_transforms(), dtype=np.float64)
+
+    def cam21(M, pose):
+        return np.concatenate([M.reshape(9), pose[:3, :3].reshape(9), pose[:3, 3].reshape(3)])
+
+    key_frames = [0]
+    key_cams = [cam21(K64, poses[0])]
+    with torch.cuda.device(dev):
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for frame in range(1, dataset.num_frames, frame_step):
+            depth = np.asarray(dataset.bg_depth_dataset[frame])
+            height, width = depth.shape
+            d = _xfer.to_device(depth, dev, np.float32)
+            m = _xfer.to_device(np.asarray(dataset.mask_dataset[frame]) != 0, dev, np.uint8)  # 0 = static pixel
+            cam = _xfer.to_device(cam21(kinv, poses[frame]), dev, np.float64)
+            kc = _xfer.to_device(np.stack(key_cams), dev, np.float64)
+            n_keys = len(key_frames)
+            box = torch.empty((n_keys, 4), dtype=torch.int32, device=dev)
+            count = torch.empty((n_keys,), dtype=torch.int32, device=dev)
+            _lib.check(lib.hv_keyframe_overlap(ctypes.c_void_p(d.data_ptr()), ctypes.c_void_p(m.data_ptr()), height, width,
+                                               ctypes.c_void_p(cam.data_ptr()), ctypes.c_void_p(kc.data_ptr()), n_keys,
+                                               ctypes.c_void_p(box.data_ptr()), ctypes.c_void_p(count.data_ptr()), stream))
+            box_h, count_h = _xfer.to_host(box, count)
+            for k in range(n_keys):  # io.py:1157-1185, in key-frame order
+                if count_h[k] == 0:
+                    continue
+                lo, hi = box_h[k, :2].astype(np.int64), box_h[k, 2:].astype(np.int64)
+                overlap_ratio = np.prod(hi - lo) / (width * height)
+                if overlap_ratio >= threshold:
+                    break
+            else:
+                key_frames.append(frame)
+                key_cams.append(cam21(K64, poses[frame]))
+    return key_frames

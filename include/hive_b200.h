@@ -212,6 +212,14 @@ int hv_upload_frame_masked(const float* h_depth, const uint8_t* h_rgb, const uin
                            int64_t scratch_bytes, void* texels, void* stream);
 int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scratch, float* out, void* stream);
 
+/* Key-frame selection, the inner loop of HiveDataset.select_key_frames (hive/io.py:1149-1175): for one candidate frame
+ * (depth (H,W) f32, mask (H,W) u8 with 0 = static pixel, cam = Kinv 9 | R 9 | t 3 float64, world-to-camera) and n_keys
+ * key frames (key_cams = n_keys x (K 9 | R 9 | t 3) float64): box[k] = {min_u, min_v, max_u, max_v} of the candidate's
+ * static points projected (rounded half-even to int, as world2image does) inside key frame k's image, count[k] = how
+ * many landed inside.  All device pointers. */
+int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int H, int W, const double* cam, const double* key_cams,
+                        int n_keys, int* box, unsigned int* count, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Connected components over the face-adjacency graph: the body of Pipeline._cleanup_with_connected_components
  * (hive/pipeline.py:741-779 -> trimesh.graph.connected_components(mesh.face_adjacency, min_len)).

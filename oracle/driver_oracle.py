@@ -79,3 +79,39 @@ def tsdf_fusion(dataset, sdf_voxel_size=0.005, sdf_max_voxels=320_000_000, dilat
             depth[mask > 0] = 0.0  # hive/fusion.py:121 (in place on the array the dataset handed out)
         vol.integrate(color, depth, dataset.camera_matrix, poses[i], obs_weight=1.0)
     return vol, c_oracle.get_mesh(vol._tsdf_vol_cpu, vol._color_vol_cpu, vol._voxel_size, vol._vol_origin)
+
+
+def select_key_frames(dataset, threshold=0.3, frame_step=30):
+    """hive/io.py:1117-1189 over the verbatim numpy restatements of hive.geometric (oracle/d2m_oracle.py, pinned against
+    the real module by tests/golden/backproject.npz)."""
+    from . import d2m_oracle as geo
+    if not (0.0 <= threshold <= 1.0):
+        raise ValueError(f"Threshold must be a real number between zero and one (inclusive), but got {threshold}.")
+    if threshold == 0.0:
+        return [0]
+    elif threshold == 1.0:
+        return list(range(dataset.num_frames))
+    if frame_step < 1:
+        raise ValueError(f"Frame step must be a positive integer, but got {frame_step} instead.")
+    poses = dataset.camera_trajectory.to_homogenous_transforms()
+    K = dataset.camera_matrix
+    key_frames = [0]
+    for frame in range(1, dataset.num_frames, frame_step):
+        depth = dataset.bg_depth_dataset[frame]
+        height, width = depth.shape
+        mask = dataset.mask_dataset[frame] == 0
+        R, t = poses[frame][:3, :3], poses[frame][:3, 3:]
+        pts = geo.point_cloud_from_depth(depth, mask, K, R, t)
+        for key_frame in key_frames:
+            R, t = poses[key_frame][:3, :3], poses[key_frame][:3, 3:]
+            proj, _ = geo.world2image(pts, K, R, t)
+            vis = (proj[:, 0] >= 0) & (proj[:, 0] < width) & (proj[:, 1] >= 0) & (proj[:, 1] < height)
+            visible = proj[vis]
+            if len(visible) == 0:
+                continue
+            area = np.prod(np.max(visible, axis=0) - np.min(visible, axis=0))
+            if area / (width * height) >= threshold:
+                break
+        else:
+            key_frames.append(frame)
+    return key_frames

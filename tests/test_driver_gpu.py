@@ -122,3 +122,79 @@ def test_tsdf_fusion_driver_matches_oracle(max_voxels, inpainted, c_oracle, monk
     assert np.array_equal(mesh.faces, rank[of].astype(np.int32))
     assert np.array_equal(mesh.vertices, ow) and np.array_equal(mesh.vertex_colors, oc)
     assert np.abs(mesh.vertex_normals - on[order]).max() <= 1e-6
+
+
+def _rotating_dataset(n=12, step_deg=9.0):
+    """Frames of the small room scene behind a camera that also pans `step_deg` per frame, so that overlap with earlier
+    frames actually falls below the thresholds (the stock trajectory barely moves)."""
+    from hive_b200.synthetic import _Trajectory
+    sc = Scene("small", "room")
+    ds = SyntheticDataset(sc, n)
+
+    def rot_y(a):
+        c, s = np.cos(a), np.sin(a)
+        m = np.eye(4)
+        m[0, 0], m[0, 2], m[2, 0], m[2, 2] = c, s, -s, c
+        return m
+    ds.camera_trajectory = _Trajectory([np.linalg.inv(sc.pose(i) @ rot_y(np.deg2rad(step_deg * i))) for i in range(n)])
+    return ds
+
+
+@pytest.mark.parametrize("frame_step", [1, 3])
+@pytest.mark.parametrize("threshold", [0.2, 0.3, 0.5, 0.7, 0.9])
+def test_select_key_frames_matches_oracle(threshold, frame_step):
+    """HiveDataset.select_key_frames (hive/io.py:1117-1189): same key-frame list as the numpy restatement."""
+    from hive_b200 import hive_fusion
+    from oracle import driver_oracle as drv
+    ds = _rotating_dataset()
+    want = drv.select_key_frames(ds, threshold, frame_step)
+    assert hive_fusion.select_key_frames(ds, threshold, frame_step) == want
+    assert 1 < len(want) <= 12
+
+
+def test_select_key_frames_edge_cases():
+    from hive_b200 import hive_fusion
+    ds = _rotating_dataset(5)
+    assert hive_fusion.select_key_frames(ds, 0.0) == [0]
+    assert hive_fusion.select_key_frames(ds, 1.0) == [0, 1, 2, 3, 4]
+    with pytest.raises(ValueError):
+        hive_fusion.select_key_frames(ds, 1.5)
+    with pytest.raises(ValueError):
+        hive_fusion.select_key_frames(ds, 0.5, frame_step=0)
+    # a fully masked candidate has no static point: it can never overlap, so it becomes a key frame (io.py:1169-1170)
+    ds.mask_dataset = type(ds.mask_dataset)(lambda i: np.ones((ds.scene.H, ds.scene.W), np.uint8))
+    assert hive_fusion.select_key_frames(ds, 0.5, frame_step=2) == [0, 1, 3]
+
+
+def test_keyframe_boxes_match_oracle_projection():
+    """The per-key-frame boxes and counts themselves, not only the decisions."""
+    import ctypes
+    import torch
+    from hive_b200 import _lib, geometric
+    from oracle import d2m_oracle as geo
+    ds = _rotating_dataset(6)
+    poses = ds.camera_trajectory.to_homogenous_transforms()
+    K = ds.camera_matrix
+    depth, mask = ds.bg_depth_dataset[4], ds.mask_dataset[4]
+    H, W = depth.shape
+    keys = [0, 2, 3]
+
+    def cam21(M, p):
+        return np.concatenate([np.asarray(M, np.float64).reshape(9), p[:3, :3].reshape(9), p[:3, 3].reshape(3)])
+    dev = torch.device("cuda")
+    d = torch.from_numpy(depth).to(dev)
+    m = torch.from_numpy((mask != 0).astype(np.uint8)).to(dev)
+    cam = torch.from_numpy(cam21(geometric._kinv64(K), poses[4])).to(dev)
+    kc = torch.from_numpy(np.stack([cam21(K, poses[k]) for k in keys])).to(dev)
+    box = torch.empty((3, 4), dtype=torch.int32, device=dev)
+    cnt = torch.empty(3, dtype=torch.int32, device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    _lib.check(_lib.load().hv_keyframe_overlap(p(d), p(m), H, W, p(cam), p(kc), 3, p(box), p(cnt),
+                                               ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    box, cnt = box.cpu().numpy(), cnt.cpu().numpy()
+    pts = geo.point_cloud_from_depth(depth, mask == 0, K, poses[4][:3, :3], poses[4][:3, 3:])
+    for j, k in enumerate(keys):
+        uv, _ = geo.world2image(pts, K, poses[k][:3, :3], poses[k][:3, 3:])
+        vis = (uv[:, 0] >= 0) & (uv[:, 0] < W) & (uv[:, 1] >= 0) & (uv[:, 1] < H)
+        assert cnt[j] == vis.sum() > 0
+        assert np.array_equal(box[j], np.concatenate([uv[vis].min(axis=0), uv[vis].max(axis=0)]))
