@@ -110,11 +110,21 @@ __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(const uint2*
     const long long base = (long long)tile * kScanTile + (long long)threadIdx.x * kScanItems;
     uint2 item[kScanItems];
     uint2 s = make_uint2(0, 0);
+    const bool full = base + kScanItems <= n;  // the thread's 64 bytes as four 16-byte accesses (arrays are 256-byte aligned)
+    if (full) {
+        const uint4* src = reinterpret_cast<const uint4*>(counts + base);
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        item[i] = (base + i < n) ? counts[base + i] : make_uint2(0, 0);
-        s = add2(s, item[i]);
+        for (int i = 0; i < kScanItems / 2; ++i) {
+            const uint4 q = __ldg(src + i);
+            item[2 * i] = make_uint2(q.x, q.y);
+            item[2 * i + 1] = make_uint2(q.z, q.w);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; ++i) item[i] = (base + i < n) ? counts[base + i] : make_uint2(0, 0);
     }
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) s = add2(s, item[i]);
     uint2 total;
     const uint2 ex = block_exclusive_scan(s, total);
     if (threadIdx.x < 32) {
@@ -154,10 +164,21 @@ __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(const uint2*
     }
     __syncthreads();
     uint2 run = add2(ex, s_prefix);
+    if (full) {
+        uint4* dst = reinterpret_cast<uint4*>(offs + base);
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        if (base + i < n) offs[base + i] = run;
-        run = add2(run, item[i]);
+        for (int i = 0; i < kScanItems / 2; ++i) {
+            const uint2 a = run;
+            const uint2 b = add2(run, item[2 * i]);
+            dst[i] = make_uint4(a.x, a.y, b.x, b.y);
+            run = add2(b, item[2 * i + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; ++i) {
+            if (base + i < n) offs[base + i] = run;
+            run = add2(run, item[i]);
+        }
     }
 }
 
