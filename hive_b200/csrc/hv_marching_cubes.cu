@@ -269,6 +269,29 @@ __device__ __forceinline__ int cube_variant(int idx, const double v[8]) {
     return variant;
 }
 
+// The asymptotic decider needs the eight corner values in float64 (16 registers): out of line, so that the common
+// unambiguous path of the count / emit kernels keeps a small register footprint (count: 64 -> 40 registers, 4 -> 6 CTAs/SM).
+// (scalars by value: a reference to the kernel-parameter struct would make every thread spill the struct to its stack)
+__device__ __noinline__ int cube_variant_ambiguous(const float* tsdf, const float* halo_lo, const float* halo_hi, int Y,
+                                                   int pitch, int Z, int hl, double level, int idx, int x, int y, int zb) {
+    double v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int cx = x + kMcCornerOff[3 * i], cy = y + kMcCornerOff[3 * i + 1], cz = zb + kMcCornerOff[3 * i + 2] - hl;
+        const size_t col = (size_t)cx * Y + cy;
+        const float f = cz < 0 ? __ldg(halo_lo + col) : (cz >= Z ? __ldg(halo_hi + col) : __ldg(tsdf + col * (size_t)pitch + cz));
+        v[i] = (double)f - level;
+    }
+    return cube_variant(idx, v);
+}
+
+// count kernel: one thread per group, nearly all of them with nothing ambiguous -> occupancy matters, call out of line
+__device__ __forceinline__ int cube_variant_at_ool(const McGrid& g, int idx, int x, int y, int zb) {
+    if (kMcAmbCount[idx] == 0) return kMcVariantBase[idx];
+    return cube_variant_ambiguous(g.tsdf, g.halo_lo, g.halo_hi, g.Y, g.pitch, g.Z, g.hl, g.level, idx, x, y, zb);
+}
+
+// emit kernel: works on surface cubes only; inlined (the call cost 30 us at 512^3 there)
 __device__ __forceinline__ int cube_variant_at(const McGrid& g, int idx, int x, int y, int zb) {
     if (kMcAmbCount[idx] == 0) return kMcVariantBase[idx];
     double v[8];
@@ -280,9 +303,18 @@ __device__ __forceinline__ int cube_variant_at(const McGrid& g, int idx, int x, 
 __global__ void __launch_bounds__(256) mc_count_kernel(const McGrid g) {
     const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (gi >= g.n_groups) return;
-    const long long col = gi / g.G;
-    const int gq = (int)(gi - col * g.G);
-    const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+    int x, y, gq;
+    if (gi < 0x100000000ll) {  // 32-bit decode (a 64-bit division is ~100 instructions; this kernel has 4.2 M threads at 512^3)
+        const unsigned int g32 = (unsigned int)gi, col = g32 / (unsigned int)g.G;
+        gq = (int)(g32 - col * (unsigned int)g.G);
+        x = (int)(col / (unsigned int)g.Y);
+        y = (int)(col - (unsigned int)x * (unsigned int)g.Y);
+    } else {
+        const long long col = gi / g.G;
+        gq = (int)(gi - col * g.G);
+        x = (int)(col / g.Y);
+        y = (int)(col - (long long)x * g.Y);
+    }
     const CubeWords c = load_cube_words(g, x, y, gq);
     const int base = gq * 32;
     uint4 m;
@@ -294,7 +326,7 @@ __global__ void __launch_bounds__(256) mc_count_kernel(const McGrid g) {
     for (unsigned int rest = c.active; rest; rest &= rest - 1) {
         const int k = __ffs(rest) - 1;
         const int idx = cube_index(c, k);
-        const int variant = cube_variant_at(g, idx, x, y, base + k);
+        const int variant = cube_variant_at_ool(g, idx, x, y, base + k);
         ntri += kMcVarNtri[variant];
         if ((kMcVarMult[variant] >> 48) & 15ull) m.w |= 1u << k;
     }
@@ -375,12 +407,12 @@ __global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, c
         __syncthreads();
         const unsigned int a = base + threadIdx.x;
         if (a < n_active) {
-            const long long gi = g.active[a];
+            const unsigned int gi = g.active[a];
             const uint2 cnt = g.gcount[gi];
             const uint2 off = g.goff[gi];
-            const long long col = gi / g.G;
-            const int gq = (int)(gi - col * g.G);
-            const int x = (int)(col / g.Y), y = (int)(col - (long long)x * g.Y);
+            const unsigned int col = gi / (unsigned int)g.G;
+            const int gq = (int)(gi - col * (unsigned int)g.G);
+            const int x = (int)(col / (unsigned int)g.Y), y = (int)(col - (unsigned int)x * (unsigned int)g.Y);
             if (cnt.x) {  // vertex keys, order inside the group: (voxel, axis)
                 const uint4 m = g.gmask[gi];
                 size_t vi = off.x;
@@ -477,9 +509,21 @@ __global__ void __launch_bounds__(128) mc_vertex_kernel(const McGrid g, const Mc
     const unsigned long long key = out.vert_keys[vi];
     const int axis = (int)(key & 3ull);
     const unsigned long long lin = key >> 2;
-    const long long zg = (long long)(lin % (unsigned long long)g.Zg);
-    const unsigned long long col = lin / (unsigned long long)g.Zg;
-    const int y = (int)(col % (unsigned long long)g.Y), x = (int)(col / (unsigned long long)g.Y);
+    // key -> (x, y, zg): 32-bit divisions whenever the linear index fits (volumes below 2^32 voxels); the four 64-bit
+    // divisions this replaces were ~400 instructions per vertex
+    long long zg;
+    int x, y;
+    if (lin < 0x100000000ull) {
+        const unsigned int l32 = (unsigned int)lin, c32 = l32 / (unsigned int)g.Zg;
+        zg = (long long)(l32 - c32 * (unsigned int)g.Zg);
+        x = (int)(c32 / (unsigned int)g.Y);
+        y = (int)(c32 - (unsigned int)x * (unsigned int)g.Y);
+    } else {
+        const unsigned long long col = lin / (unsigned long long)g.Zg;
+        zg = (long long)(lin - col * (unsigned long long)g.Zg);
+        x = (int)(col / (unsigned long long)g.Y);
+        y = (int)(col - (unsigned long long)x * (unsigned long long)g.Y);
+    }
     const int zb = (int)(zg - g.zoff);
     const int p[3] = {x, y, zb};
     const int dim[3] = {g.X, g.Y, g.Zb};
@@ -567,7 +611,7 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     L->Zb = (int)Z + (lo ? 1 : 0) + (hi ? 1 : 0);
     L->G = (L->Zb + 31) / 32;
     L->n_groups = (long long)X * Y * L->G;
-    HV_REQUIRE(L->n_groups < (1ll << 40) && L->Zb < (1 << 22), "marching cubes: volume too large");
+    HV_REQUIRE(L->n_groups < (1ll << 32) && L->Zb < (1 << 22), "marching cubes: volume too large");
     L->n_scan_blocks = (int)hv::scan_scratch_pairs(L->n_groups);
     size_t o = 0;
     L->off_gmask = o;  // 16-byte elements first
