@@ -66,28 +66,47 @@ struct Row {
     unsigned int bits;     // warp-uniform: vertices of the word
 };
 
-__device__ __forceinline__ Row load_row(const D2mGrid& g, int b, int v, int cw, int lane) {
-    Row r;
+// The loads of a row and what is derived from them are separate steps, so that a kernel can issue row v + 2 before it
+// works on row v: with load-then-use in one call every row cost a full memory round trip per warp (r01 ncu of the
+// one-step version: 12 long-scoreboard stall cycles per issued instruction in d2m_count_kernel).
+struct RawRow {
+    float d, dh;
+    unsigned int m, mh;
+};
+
+__device__ __forceinline__ RawRow load_raw(const D2mGrid& g, int b, int v, int cw, int lane) {
+    RawRow r;
     // the four loads (own depth + mask, halo depth + mask) are independent and issued together
     const int u = cw * 32 + lane;
     const int hu = lane == 0 ? cw * 32 + 32 : cw * 32 - 1;
     const bool row_in = v >= 0 && v < g.H;
     const bool in = row_in && u < g.W, hin = row_in && lane < 2 && hu >= 0 && hu < g.W;
     const size_t row = ((size_t)b * g.H + (row_in ? v : 0)) * g.W;
-    float d = 0.0f, dh = 0.0f;
-    unsigned int m = 1u, mh = 1u;
-    if (in) d = __ldg(g.depth + row + u);
-    if (hin) dh = __ldg(g.depth + row + hu);
+    r.d = 0.0f;
+    r.dh = 0.0f;
+    r.m = 1u;
+    r.mh = 1u;
+    if (in) r.d = __ldg(g.depth + row + u);
+    if (hin) r.dh = __ldg(g.depth + row + hu);
     if (g.mask) {
-        if (in) m = __ldg(g.mask + row + u);
-        if (hin) mh = __ldg(g.mask + row + hu);
+        if (in) r.m = __ldg(g.mask + row + u);
+        if (hin) r.mh = __ldg(g.mask + row + hu);
     }
-    r.c = (m != 0u && d > 0.0f) ? d : 0.0f;
-    const float halo = (mh != 0u && dh > 0.0f) ? dh : 0.0f;
+    return r;
+}
+
+__device__ __forceinline__ Row finish_row(const RawRow& q) {
+    Row r;
+    r.c = (q.m != 0u && q.d > 0.0f) ? q.d : 0.0f;
+    const float halo = (q.mh != 0u && q.dh > 0.0f) ? q.dh : 0.0f;
     r.halo_r = __shfl_sync(0xffffffffu, halo, 0);
     r.halo_l = __shfl_sync(0xffffffffu, halo, 1);
     r.bits = __ballot_sync(0xffffffffu, r.c > 0.0f);
     return r;
+}
+
+__device__ __forceinline__ Row load_row(const D2mGrid& g, int b, int v, int cw, int lane) {
+    return finish_row(load_raw(g, b, v, cw, lane));
 }
 
 struct Hood {
@@ -189,10 +208,14 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_count_kernel(const D2mGrid g)
     const int b = (int)blockIdx.z;
     const int v0 = (int)blockIdx.y * kD2mRows, v1 = min(v0 + kD2mRows, g.H);
     const bool faces = !g.verts_only;
-    Row prev = load_row(g, b, v0 - 1, cw, lane), cur = load_row(g, b, v0, cw, lane);
+    const RawRow q0 = load_raw(g, b, v0 - 1, cw, lane), q1 = load_raw(g, b, v0, cw, lane);
+    RawRow raw_next = load_raw(g, b, v0 + 1, cw, lane);
+    Row prev = finish_row(q0), cur = finish_row(q1);
     size_t w = (size_t)b * g.words_per_frame + (size_t)v0 * g.wpr + cw;
     for (int v = v0; v < v1; ++v) {
-        const Row next = load_row(g, b, v + 1, cw, lane);
+        const RawRow raw_next2 = load_raw(g, b, v + 2 <= v1 ? v + 2 : -1, cw, lane);  // in flight while row v is processed
+        const Row next = finish_row(raw_next);
+        raw_next = raw_next2;
         unsigned int nf = 0;
         if (faces && !hood_empty(cur, next)) {
             const Hood h = make_hood(prev, cur, next, lane);
@@ -259,23 +282,35 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
     const unsigned int vbase = g.woff[wframe].x;
 
     Row prev, cur, next;
-    unsigned int first_prev = 0u, first_cur = 0u, first_next = 0u;  // frame-local rank of the first pixel of the word per row
+    RawRow raw_next;
     if (has_f) {
-        prev = load_row(g, b, v0 - 1, cw, lane);
-        cur = load_row(g, b, v0, cw, lane);
-        if (v0 > 0) first_prev = g.woff[w0 - g.wpr].x - vbase;
-        first_cur = g.woff[w0].x - vbase;
+        const RawRow q0 = load_raw(g, b, v0 - 1, cw, lane), q1 = load_raw(g, b, v0, cw, lane);
+        raw_next = load_raw(g, b, v0 + 1, cw, lane);
+        prev = finish_row(q0);
+        cur = finish_row(q1);
+    }
+    // prefix offsets of the word in rows v0 - 1 .. v1 (lane l holds row v0 - 1 + l): one load up front instead of three
+    // dependent loads per row inside the loop
+    uint2 my_off = make_uint2(0u, 0u);
+    {
+        const int row = v0 - 1 + lane;
+        if (lane < (v1 - v0) + 2 && row >= 0 && row < g.H) my_off = g.woff[wframe + (size_t)row * g.wpr + cw];
     }
     const int u = cw * 32 + lane;
     for (int r = 0; r < v1 - v0; ++r) {
         const int v = v0 + r;
         const size_t w = w0 + (size_t)r * g.wpr;
         if (has_f) {
-            next = load_row(g, b, v + 1, cw, lane);
-            if (v + 1 < g.H) first_next = g.woff[w + g.wpr].x - vbase;
+            const RawRow raw_next2 = load_raw(g, b, v + 2 <= v1 ? v + 2 : -1, cw, lane);  // prefetch, used next iteration
+            next = finish_row(raw_next);
+            raw_next = raw_next2;
         }
         if (((has_v | has_f) >> r) & 1u) {
-            const uint2 off = g.woff[w];
+            const uint2 off = make_uint2(__shfl_sync(0xffffffffu, my_off.x, r + 1), __shfl_sync(0xffffffffu, my_off.y, r + 1));
+            // frame-local rank of the first pixel of the word in the rows above / of / below v
+            const unsigned int first_prev = v > 0 ? __shfl_sync(0xffffffffu, my_off.x, r) - vbase : 0u;
+            const unsigned int first_cur = off.x - vbase;
+            const unsigned int first_next = v + 1 < g.H ? __shfl_sync(0xffffffffu, my_off.x, r + 2) - vbase : 0u;
             if ((has_f >> r) & 1u) {
                 const Hood h = make_hood(prev, cur, next, lane);
                 PixelFaces f;
@@ -297,9 +332,9 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
                         out.faces[3 * fi + c] = corner_rank(q.x, cw * 32, rb, rf);
                     }
             }
-            const unsigned int bits = g.wbits[w];
+            const unsigned int bits = has_f ? cur.bits : g.wbits[w];  // (the count kernel stored exactly cur.bits)
             if ((bits >> lane) & 1u) {  // image2world, hive/geometric.py:200-204 (float64)
-                const float d = __ldg(g.depth + ((size_t)b * g.H + v) * g.W + u);
+                const float d = has_f ? cur.c : __ldg(g.depth + ((size_t)b * g.H + v) * g.W + u);
                 const size_t vi = off.x + __popc(bits & ((1u << lane) - 1u));
                 const double* R = out.cams + 12 * (size_t)b;
                 const double* t = R + 9;
@@ -323,8 +358,6 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
         if (has_f) {
             prev = cur;
             cur = next;
-            first_prev = first_cur;
-            first_cur = first_next;
         }
     }
 }
