@@ -395,8 +395,8 @@ __device__ __forceinline__ void emit_cube(const McGrid& g, const McEmit& out, in
 // group owns, and one record per surface cube (position, tiling, triangle offset) pushed into a shared-memory list.
 // Phase 2, one thread per record: the triangles.  (r01: with one warp per group and one lane per cube, 75-90 % of the
 // lanes idled in the triangle loop -- a group of 32 cubes is crossed by the surface in only a handful of them.)
-constexpr int kEmitThreads = 256;
-constexpr int kEmitCap = 2048;  // records per round; cubes beyond it are written by their phase-1 thread directly
+constexpr int kEmitThreads = 128;
+constexpr int kEmitCap = 1024;  // records per round; cubes beyond it are written by their phase-1 thread directly
 
 __global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, const McEmit out) {
     __shared__ uint4 s_list[kEmitCap];
