@@ -166,42 +166,38 @@ class McPlan:
         mesh.vmin, mesh.vmax = vmin, vmax
         return mesh
 
-
-def _extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
-    """count -> (allocate the outputs while the classification kernels run) -> read the totals -> emit.  Same result as
-    ``extract``; the output allocations no longer sit between the caller and the first kernel."""
-    torch = self._torch
-    dev = self.device
-    self.count()
-    with torch.cuda.device(dev):
-        verts = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
-        verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
-        normals = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
-        colors = torch.empty((cap_verts, 3), dtype=torch.uint8, device=dev)
-        vert_keys = torch.empty((max(cap_verts, 1),), dtype=torch.int64, device=dev)
-        faces = torch.empty((cap_tris, 3), dtype=torch.int32, device=dev)
-    n_verts, n_tris, vmin, vmax = self.read_totals()
-    check_surface(self.level, vmin, vmax, n_verts)
-    if n_verts > cap_verts or n_tris > cap_tris:
-        mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
-    else:
-        origin = np.ascontiguousarray(origin, dtype=np.float32)
+    def extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
+        """count -> (allocate the outputs while the classification kernels run) -> read the totals -> emit.  Same result as
+        ``extract``; the output allocations no longer sit between the caller and the first kernel."""
+        torch = self._torch
+        dev = self.device
+        self.count()
         with torch.cuda.device(dev):
-            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-            _lib.check(self._lib.hv_mc_emit(
-                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
-                _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
-                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
-                self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
-                origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
-                _ptr(colors), _ptr(faces), None, None, _ptr(vert_keys), stream))
-        mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
-                          colors[:n_verts], faces[:n_tris], None, None, vert_keys[:n_verts], 0.0, 0.0)
-    mesh.vmin, mesh.vmax = vmin, vmax
-    return mesh
-
-
-McPlan.extract_overlapped = _extract_overlapped
+            verts = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
+            verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
+            normals = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
+            colors = torch.empty((cap_verts, 3), dtype=torch.uint8, device=dev)
+            vert_keys = torch.empty((max(cap_verts, 1),), dtype=torch.int64, device=dev)
+            faces = torch.empty((cap_tris, 3), dtype=torch.int32, device=dev)
+        n_verts, n_tris, vmin, vmax = self.read_totals()
+        check_surface(self.level, vmin, vmax, n_verts)
+        if n_verts > cap_verts or n_tris > cap_tris:
+            mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
+        else:
+            origin = np.ascontiguousarray(origin, dtype=np.float32)
+            with torch.cuda.device(dev):
+                stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+                _lib.check(self._lib.hv_mc_emit(
+                    _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
+                    _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
+                    ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                    self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
+                    origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
+                    _ptr(colors), _ptr(faces), None, None, _ptr(vert_keys), stream))
+            mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
+                              colors[:n_verts], faces[:n_tris], None, None, vert_keys[:n_verts], 0.0, 0.0)
+        mesh.vmin, mesh.vmax = vmin, vmax
+        return mesh
 
 
 def check_surface(level, vmin, vmax, n_verts):
