@@ -278,6 +278,36 @@ __global__ void keyframe_box_init_kernel(int* box, unsigned int* count, int n_ke
     count[k] = 0u;
 }
 
+// ---- vertex colours through a 256-entry table (hive/pipeline.py:281-282) --------------------------------------------------
+// The reference converts the TSDF mesh's vertex colours for the renderer with
+//     vertex_colors[:, :3] = (255 * np.power(vertex_colors / 255, 2.2)).astype(int)
+// a pure function of one byte.  The table is built on the host by that very numpy expression (so it is the reference's
+// arithmetic by construction) and applied in place here: 16 bytes per thread, table in shared memory.
+__global__ void __launch_bounds__(256) byte_lut_kernel(uint8_t* __restrict__ bytes, long long n,
+                                                       const uint8_t* __restrict__ lut) {
+    __shared__ uint8_t s_lut[256];
+    s_lut[threadIdx.x] = lut[threadIdx.x];
+    __syncthreads();
+    const long long n16 = n >> 4;
+    uint4* v = reinterpret_cast<uint4*>(bytes);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) {
+        uint4 w = v[i];
+        unsigned int* c = &w.x;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned int x = c[k];
+            c[k] = (unsigned int)s_lut[x & 255u] | ((unsigned int)s_lut[(x >> 8) & 255u] << 8) |
+                   ((unsigned int)s_lut[(x >> 16) & 255u] << 16) | ((unsigned int)s_lut[x >> 24] << 24);
+        }
+        v[i] = w;
+    }
+    // ragged tail (< 16 bytes), by the first threads of block 0
+    if (blockIdx.x == 0) {
+        const long long i = (n16 << 4) + threadIdx.x;
+        if (threadIdx.x < 16 && i < n) bytes[i] = s_lut[bytes[i]];
+    }
+}
+
 }  // namespace hv
 
 extern "C" int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int H, int W, const double* cam,
@@ -287,6 +317,18 @@ extern "C" int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int 
     cudaStream_t st = hv::as_stream(stream);
     hv::keyframe_box_init_kernel<<<(n_keys + 127) / 128, 128, 0, st>>>(box, count, n_keys);
     hv::keyframe_overlap_kernel<<<(H * W + 255) / 256, 256, 0, st>>>(depth, mask, H, W, cam, key_cams, n_keys, box, count);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_byte_lut(uint8_t* bytes, int64_t n, const uint8_t* lut, void* stream) {
+    HV_REQUIRE(bytes && lut && n >= 0, "hv_byte_lut: bad arguments");
+    HV_REQUIRE(((uintptr_t)bytes & 15) == 0, "hv_byte_lut: bytes must be 16-byte aligned");
+    if (n == 0) return HV_OK;
+    const long long blocks = (n / 16 + 255) / 256;
+    const int cap = hv::device_info().sm_count * 8;
+    hv::byte_lut_kernel<<<(unsigned)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks)), 256, 0, hv::as_stream(stream)>>>(
+        bytes, n, lut);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

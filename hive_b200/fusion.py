@@ -308,10 +308,11 @@ class TSDFVolume:
         verts, _, _, colors = self.get_mesh()
         return np.hstack([verts, colors])
 
-    def get_mesh(self):
-        """Compute a mesh from the voxel volume using marching cubes (fusion.py:332-350)."""
+    def get_mesh(self, srgb_colors=False):
+        """Compute a mesh from the voxel volume using marching cubes (fusion.py:332-350).  ``srgb_colors=True`` also
+        applies HIVE's vertex-colour conversion (hive/pipeline.py:281-282) before the colours leave the device."""
         from . import marching_cubes
-        return marching_cubes.extract_mesh(self)
+        return marching_cubes.extract_mesh(self, srgb_colors=srgb_colors)
 
 
 def rigid_transform(xyz, transform):

@@ -72,8 +72,13 @@ def adjust_voxel_size(dataset, options: BackgroundMeshOptions, frame_set: List[i
     return voxel_size, vol_bnds
 
 
-def tsdf_fusion(dataset, options: BackgroundMeshOptions = None, num_frames=-1, frame_set: Optional[List[int]] = None):
-    """hive/fusion.py:79-134: fuse the (masked) frames of ``dataset`` and return the marching-cubes mesh."""
+def tsdf_fusion(dataset, options: BackgroundMeshOptions = None, num_frames=-1, frame_set: Optional[List[int]] = None,
+                srgb_vertex_colors=False):
+    """hive/fusion.py:79-134: fuse the (masked) frames of ``dataset`` and return the marching-cubes mesh.
+
+    ``srgb_vertex_colors=True`` folds in what the only caller does to the result next (hive/pipeline.py:281-282,
+    ``vertex_colors[:, :3] = (255 * np.power(vertex_colors / 255, 2.2)).astype(int)``) while the colours are still in HBM.
+    """
     options = options if options is not None else BackgroundMeshOptions()
     if num_frames == -1:
         num_frames = dataset.num_frames
@@ -99,7 +104,7 @@ def tsdf_fusion(dataset, options: BackgroundMeshOptions = None, num_frames=-1, f
         else:
             tsdf_vol.integrate(color_image, depth_im, dataset.camera_matrix, cam_pose, obs_weight=1.)
 
-    verts, faces, norms, colors = tsdf_vol.get_mesh()
+    verts, faces, norms, colors = tsdf_vol.get_mesh(srgb_colors=srgb_vertex_colors)
     try:
         import trimesh
         return trimesh.Trimesh(vertices=verts, faces=faces, vertex_colors=colors, vertex_normals=norms)

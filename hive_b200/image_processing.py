@@ -10,7 +10,8 @@ import numpy as np
 from . import _lib
 from . import _xfer
 
-__all__ = ["MaskDilationOptions", "dilate_mask", "dilate_masks_device", "depth_max"]
+__all__ = ["MaskDilationOptions", "dilate_mask", "dilate_masks_device", "depth_max", "srgb_vertex_color_lut",
+           "apply_byte_lut_device", "vertex_colors_to_srgb"]
 
 _RECT3 = np.ones((3, 3), dtype=np.uint8)  # cv2.getStructuringElement(cv2.MORPH_RECT, (3, 3)), hive/options.py:248
 
@@ -80,3 +81,44 @@ def depth_max(depths):
         _lib.check(lib.hv_depth_max(_ptr(depths), B, n, _ptr(keys), _ptr(out),
                                     ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
     return _xfer.to_host(out)
+
+
+def srgb_vertex_color_lut():
+    """The colour-space conversion of hive/pipeline.py:281-282 tabulated over its whole domain (one uint8 in, one out):
+    ``(255 * np.power(vertex_colors / 255, 2.2)).astype(int)`` stored back into the uint8 colour array."""
+    vertex_colors = np.arange(256, dtype=np.uint8)
+    return (255 * np.power(vertex_colors / 255, 2.2)).astype(int).astype(np.uint8)
+
+
+_LUT_CACHE = {}
+
+
+def apply_byte_lut_device(bytes_tensor, lut):
+    """In place ``t[...] = lut[t[...]]`` on a contiguous uint8 device tensor (``hv_byte_lut``)."""
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    assert bytes_tensor.dtype == torch.uint8 and bytes_tensor.is_contiguous(), "contiguous uint8 tensor expected"
+    lut = np.ascontiguousarray(lut, dtype=np.uint8)
+    assert lut.shape == (256,), "lut must have 256 entries"
+    dev = bytes_tensor.device
+    key = (dev.index, lut.tobytes())
+    d_lut = _LUT_CACHE.get(key)
+    if d_lut is None:
+        d_lut = _LUT_CACHE[key] = _xfer.to_device(lut, dev, np.uint8)
+    with torch.cuda.device(dev):
+        _lib.check(lib.hv_byte_lut(_ptr(bytes_tensor), int(bytes_tensor.numel()), _ptr(d_lut),
+                                   ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return bytes_tensor
+
+
+def vertex_colors_to_srgb(vertex_colors):
+    """hive/pipeline.py:281-282 for a host (V, 3|4) uint8 colour array: returns the converted r, g, b (alpha, if any, is
+    left alone as in the reference, which only assigns ``[:, :3]``)."""
+    torch = _lib.require_cuda()
+    vertex_colors = np.asarray(vertex_colors)
+    assert vertex_colors.dtype == np.uint8 and vertex_colors.ndim == 2, "(V, 3) or (V, 4) uint8 colours expected"
+    dev = torch.device("cuda", torch.cuda.current_device())
+    rgb = _xfer.to_device(np.ascontiguousarray(vertex_colors[:, :3]), dev, np.uint8)
+    out = vertex_colors.copy()
+    out[:, :3] = _xfer.to_host(apply_byte_lut_device(rgb, srgb_vertex_color_lut()))
+    return out

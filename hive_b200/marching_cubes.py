@@ -234,10 +234,15 @@ def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
     return mesh
 
 
-def extract_mesh(vol):
+def extract_mesh(vol, srgb_colors=False):
     """``TSDFVolume.get_mesh`` (fusion.py:332-350): verts (V,3) f32 world, faces (F,3) i32, norms (V,3) f32,
-    colors (V,3) u8."""
-    return extract_device_mesh(vol).to_host()
+    colors (V,3) u8.  ``srgb_colors`` applies the vertex-colour conversion of hive/pipeline.py:281-282 on the device,
+    before the download."""
+    mesh = extract_device_mesh(vol)
+    if srgb_colors and mesh.colors.numel():
+        from . import image_processing
+        image_processing.apply_byte_lut_device(mesh.colors, image_processing.srgb_vertex_color_lut())
+    return mesh.to_host()
 
 
 def marching_cubes(volume, level=None, *, spacing=(1., 1., 1.), gradient_direction='descent', step_size=1,

@@ -220,6 +220,12 @@ int hv_depth_max(const float* depth, int B, int64_t n, int* keys_scratch, float*
 int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int H, int W, const double* cam, const double* key_cams,
                         int n_keys, int* box, unsigned int* count, void* stream);
 
+/* Vertex colours of the TSDF mesh to the renderer's colour space, hive/pipeline.py:281-282
+ * (`vertex_colors[:, :3] = (255 * np.power(vertex_colors / 255, 2.2)).astype(int)`): a function of one byte, applied
+ * in place through a 256-entry table the host builds with that expression.  bytes: n device bytes, 16-byte aligned;
+ * lut: 256 device bytes. */
+int hv_byte_lut(uint8_t* bytes, int64_t n, const uint8_t* lut, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Connected components over the face-adjacency graph: the body of Pipeline._cleanup_with_connected_components
  * (hive/pipeline.py:741-779 -> trimesh.graph.connected_components(mesh.face_adjacency, min_len)).

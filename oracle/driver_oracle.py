@@ -115,3 +115,12 @@ def select_key_frames(dataset, threshold=0.3, frame_step=30):
         else:
             key_frames.append(frame)
     return key_frames
+
+
+def vertex_colors_to_srgb(vertex_colors):
+    """hive/pipeline.py:281-282, on a copy: ``vertex_colors[:, :3] = (255 * np.power(vertex_colors / 255, 2.2)).astype(int)``
+    (float64 power, truncation, stored back into the uint8 colour array)."""
+    out = np.array(vertex_colors, copy=True)
+    rgb = out[:, :3]
+    out[:, :3] = (255 * np.power(rgb / 255, 2.2)).astype(int)
+    return out

@@ -198,3 +198,39 @@ def test_keyframe_boxes_match_oracle_projection():
         vis = (uv[:, 0] >= 0) & (uv[:, 0] < W) & (uv[:, 1] >= 0) & (uv[:, 1] < H)
         assert cnt[j] == vis.sum() > 0
         assert np.array_equal(box[j], np.concatenate([uv[vis].min(axis=0), uv[vis].max(axis=0)]))
+
+
+@pytest.mark.parametrize("n_verts", [1, 5, 16, 1000, 100_003])
+@pytest.mark.parametrize("cols", [3, 4])
+def test_vertex_colors_to_srgb_matches_oracle(n_verts, cols):
+    """hive/pipeline.py:281-282 through hv_byte_lut, ragged sizes around the 16-byte vector width; bit-exact."""
+    from hive_b200 import image_processing
+    from oracle import driver_oracle as drv
+    rng = np.random.default_rng(n_verts + cols)
+    c = rng.integers(0, 256, (n_verts, cols), dtype=np.uint8)
+    before = c.copy()
+    got = image_processing.vertex_colors_to_srgb(c)
+    assert np.array_equal(c, before), "input must not be modified"
+    assert got.dtype == np.uint8 and np.array_equal(got, drv.vertex_colors_to_srgb(c))
+
+
+def test_get_mesh_srgb_colors_equals_conversion_of_plain_mesh():
+    from hive_b200.fusion import TSDFVolume
+    from oracle import driver_oracle as drv
+    sc = Scene("small", "room")
+    vol = TSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    for i in range(3):
+        fr = sc.frame(i)
+        vol.integrate(fr.rgb, fr.depth, sc.K, fr.pose)
+    v0, f0, n0, c0 = vol.get_mesh()
+    v1, f1, n1, c1 = vol.get_mesh(srgb_colors=True)
+    assert np.array_equal(v0, v1) and np.array_equal(f0, f1) and np.array_equal(n0, n1)
+    assert len(c0) > 1000 and len(np.unique(c0)) > 50
+    assert np.array_equal(c1, drv.vertex_colors_to_srgb(c0))
+    # and through the driver
+    from hive_b200 import hive_fusion
+    opts = hive_fusion.BackgroundMeshOptions(depth_mask_dilation_iterations=2, sdf_voxel_size=0.06, sdf_max_voxels=None)
+    plain = hive_fusion.tsdf_fusion(SyntheticDataset(sc, 4), opts)
+    srgb = hive_fusion.tsdf_fusion(SyntheticDataset(sc, 4), opts, srgb_vertex_colors=True)
+    assert np.array_equal(srgb.vertex_colors, drv.vertex_colors_to_srgb(plain.vertex_colors))
+    assert np.array_equal(srgb.faces, plain.faces)

@@ -35,3 +35,21 @@ def test_voxel_budget_rule():
     vs2, bounds2 = drv.adjust_voxel_size(ds, 0.01, 100_000, range(3))
     assert np.array_equal(bounds, bounds2)
     assert vs2 > 0.01 and np.isclose(np.prod((bounds[:, 1] - bounds[:, 0]) / vs2), 100_000)
+
+
+def test_srgb_table_is_the_reference_expression_over_its_domain():
+    """hive/pipeline.py:281-282 is a function of one uint8; the table the CUDA path applies must equal the oracle's
+    whole-array restatement for every input byte, in (V, 3) and (V, 4) layouts (alpha untouched)."""
+    from hive_b200 import image_processing
+    lut = image_processing.srgb_vertex_color_lut()
+    assert lut.dtype == np.uint8 and lut.shape == (256,)
+    assert lut[0] == 0 and lut[255] == 255 and np.all(np.diff(lut.astype(int)) >= 0)
+    rng = np.random.default_rng(5)
+    for cols in (3, 4):
+        c = rng.integers(0, 256, (5000, cols), dtype=np.uint8)
+        c[:256, 0] = np.arange(256)
+        want = drv.vertex_colors_to_srgb(c)
+        got = c.copy()
+        got[:, :3] = lut[c[:, :3]]
+        assert np.array_equal(got, want)
+        assert want.dtype == np.uint8
