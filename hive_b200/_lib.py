@@ -57,6 +57,8 @@ SIGNATURES = {
     "hv_keyframe_overlap": [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p],
     "hv_depth_max": [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_void_p],
     "hv_byte_lut": [c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_atlas_pack": [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int64,
+                      c_void_p, c_void_p],
     "hv_cc_edge_keys": [c_void_p, c_int64, c_int64, c_void_p, c_void_p],
     "hv_cc_scratch_bytes": [c_int64, c_void_p],
     "hv_cc_label": [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],

@@ -132,6 +132,61 @@ class Pipeline:
         return texture, uv
 
     @staticmethod
+    def _pack_textures(textures_atlas, uvs_atlas, n_rows=1):
+        """pipeline.py:810-868: the crops of a frame's objects side by side on one black canvas (``n_rows`` rows of
+        ``len // n_rows + 1`` slots, row height = tallest crop, canvas width = widest row) and their UVs shifted to the
+        crop's place and normalised (``u / canvas_w``, ``1 - v / canvas_h``).  Returns (atlas (H, W, 3) uint8,
+        final_uvs (sum N_k, 2) float64).
+
+        The placement is a few integers per crop (host); pixels and UVs move on the GPU (``hv_atlas_pack``).  One
+        documented difference: the reference also shifts the caller's ``uvs_atlas`` arrays in place as a side effect
+        (pipeline.py:837, 857); both of its call sites drop them right after, and here they are left untouched."""
+        torch = _lib.require_cuda()
+        lib = _lib.load()
+        n = len(textures_atlas)
+        assert len(uvs_atlas) == n, "one uv array per texture"
+        n_columns = n // n_rows + 1
+        textures = [np.asarray(t) for t in textures_atlas]
+        for t in textures:
+            geometric.validate_shape(t, 'texture', (None, None, 3))
+        desc = np.zeros((max(n, 1), 6), dtype=np.int64)  # src byte offset, x0, y0, w, h, first uv row
+        row_first, row_y0 = np.zeros(n_rows + 1, dtype=np.int64), np.zeros(n_rows + 1, dtype=np.int64)
+        src_off = uv_row = canvas_h = canvas_w = 0
+        for i in range(n_rows):
+            first, end = i * n_columns, min((i + 1) * n_columns, n)
+            if first >= n:  # the reference indexes textures_atlas[i * n_columns] of a row that received no crop
+                raise IndexError("list index out of range")
+            x0 = row_h = 0
+            for k in range(first, end):
+                h, w = textures[k].shape[:2]
+                desc[k] = (src_off, x0, canvas_h, w, h, uv_row)
+                src_off += h * w * 3
+                uv_row += len(uvs_atlas[k])
+                x0 += w
+                row_h = max(row_h, h)
+            row_first[i], row_y0[i] = first, canvas_h
+            canvas_w = max(canvas_w, x0)
+            canvas_h += row_h
+        row_first[n_rows], row_y0[n_rows] = n, canvas_h
+
+        dev = torch.device("cuda", torch.cuda.current_device())
+        src_h = np.concatenate([t.reshape(-1) for t in textures]) if src_off else np.zeros(0, dtype=np.uint8)
+        uv_h = np.vstack([np.zeros((0, 2))] + [np.asarray(u) for u in uvs_atlas])
+        with torch.cuda.device(dev):
+            src = _xfer.to_device(src_h, dev, np.uint8)
+            uv = _xfer.to_device(uv_h, dev, np.float64)
+            d_desc = _xfer.to_device(desc, dev, np.int64)
+            d_rows = _xfer.to_device(np.concatenate([row_first, row_y0]), dev, np.int64)
+            atlas = torch.empty((canvas_h, canvas_w, 3), dtype=torch.uint8, device=dev)
+            uv_out = torch.empty((uv_row, 2), dtype=torch.float64, device=dev)
+            _lib.check(lib.hv_atlas_pack(_ptr(src) if src_off else None, _ptr(d_desc), n, _ptr(d_rows),
+                                         ctypes.c_void_p(d_rows.data_ptr() + 8 * (n_rows + 1)), n_rows, canvas_h, canvas_w,
+                                         _ptr(atlas) if atlas.numel() else None, _ptr(uv) if uv_row else None, uv_row,
+                                         _ptr(uv_out) if uv_row else None,
+                                         ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            return _xfer.to_host(atlas, uv_out)
+
+    @staticmethod
     def _cleanup_with_connected_components(vertices, faces, is_object=True, min_components=5):
         """pipeline.py:741-779: drop floating fragments.  Faces adjacent across an edge that exactly two faces share form
         a graph; components with fewer than ``min_components`` faces go; for an object only the largest survives.

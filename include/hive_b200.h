@@ -226,6 +226,17 @@ int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int H, int W, c
  * lut: 256 device bytes. */
 int hv_byte_lut(uint8_t* bytes, int64_t n, const uint8_t* lut, void* stream);
 
+/* Texture atlas of a frame's objects, the pixel and UV work of Pipeline._pack_textures (hive/pipeline.py:810-868); the
+ * placement (a few integers per crop) is the host's.  src: the crops' (h, w, 3) uint8 pixels back to back; desc[t] =
+ * {byte offset in src, x0, y0, w, h, first row of the crop's UVs in `uv`} (int64 x 6); rows r = 0..n_rows-1 hold crops
+ * row_first[r] .. row_first[r+1]-1 (in x order) and start at canvas row row_y0[r] (both n_rows+1 entries).
+ * atlas: (canvas_h, canvas_w, 3) uint8, every byte written (black where no crop lies).  uv: (n_uv, 2) float64 crop-local
+ * pixel coordinates; uv_out[i] = ((u + x0) / canvas_w, 1 - (v + y0) / canvas_h) (pipeline.py:837, 857, 865-866).
+ * All pointers device. */
+int hv_atlas_pack(const uint8_t* src, const int64_t* desc, int n_tex, const int64_t* row_first, const int64_t* row_y0,
+                  int n_rows, int canvas_h, int canvas_w, uint8_t* atlas, const double* uv, int64_t n_uv, double* uv_out,
+                  void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Connected components over the face-adjacency graph: the body of Pipeline._cleanup_with_connected_components
  * (hive/pipeline.py:741-779 -> trimesh.graph.connected_components(mesh.face_adjacency, min_len)).

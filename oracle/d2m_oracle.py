@@ -115,6 +115,53 @@ def get_mesh_texture_and_uv(vertices, image, camera_matrix, rotation=np.eye(3), 
     return texture, uv
 
 
+def atlas_layout(shapes, n_rows=1):
+    """Placement rule of hive/pipeline.py:814-858: crops go into ``n_rows`` rows of ``len // n_rows + 1`` slots each, left
+    to right; a row is as tall as its tallest crop and the canvas as wide as its widest row.  Returns
+    (per-crop (x0, y0), per-row (first index, end index, y0), canvas_h, canvas_w).  A row that receives no crop makes the
+    reference index past the end of the list: IndexError."""
+    n = len(shapes)
+    n_columns = n // n_rows + 1
+    places, rows = [None] * n, []
+    y0 = canvas_w = 0
+    for i in range(n_rows):
+        first, end = i * n_columns, min((i + 1) * n_columns, n)
+        if first >= n:
+            raise IndexError("list index out of range")
+        x0 = row_h = 0
+        for k in range(first, end):
+            h, w = shapes[k][:2]
+            places[k] = (x0, y0)
+            x0 += w
+            row_h = max(row_h, h)
+        rows.append((first, end, y0))
+        canvas_w = max(canvas_w, x0)
+        y0 += row_h
+    return places, rows, y0, canvas_w
+
+
+def pack_textures(textures_atlas, uvs_atlas, n_rows=1):
+    """hive/pipeline.py:810-868 without the side effect on ``uvs_atlas`` (the reference shifts the caller's arrays in
+    place; both call sites, pipeline.py:469 and :619, drop them afterwards)."""
+    places, rows, canvas_h, canvas_w = atlas_layout([t.shape for t in textures_atlas], n_rows)
+    atlas = np.zeros((canvas_h, canvas_w, 3), dtype=np.uint8)
+    shifted = []
+    for k, (tex, uv) in enumerate(zip(textures_atlas, uvs_atlas)):
+        uv = np.array(uv, copy=True)
+        x0, y0 = places[k]
+        h, w = tex.shape[:2]
+        atlas[y0:y0 + h, x0:x0 + w, :] = tex
+        uv[:, 0] += x0
+        uv[:, 1] += y0
+        shifted.append(uv)
+    final_uvs = np.zeros((0, 2))
+    for uv in shifted:
+        final_uvs = np.vstack((final_uvs, uv))
+    final_uvs[:, 0] /= canvas_w
+    final_uvs[:, 1] = 1. - final_uvs[:, 1] / canvas_h
+    return atlas, final_uvs
+
+
 def face_adjacency(faces):
     """trimesh.Trimesh.face_adjacency as HIVE uses it: pairs of faces sharing an edge that exactly two faces use."""
     faces = np.asarray(faces)

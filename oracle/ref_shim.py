@@ -57,3 +57,31 @@ def reference_geometric():
         sys.path.insert(0, REFERENCE_ROOT)
     import hive.geometric as geometric
     return geometric
+
+
+def reference_pipeline_statics(names=("_triangulate_faces", "_filter_faces", "_get_mesh_texture_and_uv", "_pack_textures")):
+    """The reference's own ``Pipeline`` static methods, executed from ``hive/pipeline.py`` where it lies.
+
+    ``hive.pipeline`` cannot be imported here (trimesh, openmesh, detectron2 ...), but these methods only use numpy,
+    scipy's Delaunay and ``hive.geometric`` / ``hive.utils`` helpers: their ``FunctionDef`` nodes are taken out of the
+    parsed source (decorators dropped) and compiled in a namespace holding exactly those names.  Nothing is copied into
+    this repository; the functions exist only in the calling process."""
+    import ast
+    import numpy as np
+    from scipy.spatial import Delaunay
+    geometric = reference_geometric()
+    import hive.utils as utils  # noqa: importable once hive.geometric is (same shims)
+    path = os.path.join(REFERENCE_ROOT, "hive", "pipeline.py")
+    with open(path) as f:
+        tree = ast.parse(f.read(), filename=path)
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "Pipeline")
+    picked = [n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name in names]
+    assert len(picked) == len(names), f"missing in {path}: {set(names) - {n.name for n in picked}}"
+    for n in picked:
+        n.decorator_list = []
+    module = ast.Module(body=picked, type_ignores=[])
+    ns = {"np": np, "Delaunay": Delaunay, "world2image": geometric.world2image,
+          "validate_shape": utils.validate_shape, "validate_camera_parameter_shapes": utils.validate_camera_parameter_shapes,
+          "MeshFilteringOptions": object}
+    exec(compile(module, path, "exec"), ns)
+    return {name: ns[name] for name in names}

@@ -211,3 +211,64 @@ def test_connected_components_on_a_depth_mesh():
         assert np.array_equal(gf, of) and 0 < len(gf) <= len(faces)
     keep, labels = pipeline.face_component_mask(faces, len(verts), 5, largest_only=False, return_labels=True)
     assert len(np.unique(labels[keep])) >= 2  # both instances survive as separate components
+
+
+# ---- against the reference's own static methods (tests/golden/pipeline_statics.npz, oracle/make_pipeline_golden.py) ----
+
+def _statics_gold():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "pipeline_statics.npz"))
+
+
+def test_filter_faces_matches_reference_golden():
+    """Pipeline._filter_faces (pipeline.py:670-694) on the reference's own Delaunay faces: kept faces equal, in order."""
+    from hive_b200.pipeline import MeshFilteringOptions, Pipeline
+    g = _statics_gold()
+    got = Pipeline._filter_faces(g["ff_points2d"], g["ff_depth"], g["ff_raw"], MeshFilteringOptions())
+    assert np.array_equal(got, g["ff_kept"])
+
+
+def test_texture_and_uv_match_reference_golden():
+    """Pipeline._get_mesh_texture_and_uv (pipeline.py:782-808): crop and UVs bit-equal to the reference's."""
+    from hive_b200.pipeline import Pipeline
+    from hive_b200.synthetic import Scene
+    g = _statics_gold()
+    sc = Scene("small", "room")
+    texture, uv = Pipeline._get_mesh_texture_and_uv(g["tx_vertices"], sc.frame(2).rgb, sc.K, g["tx_R"], g["tx_t"])
+    assert np.array_equal(texture, g["tx_texture"])
+    assert uv.dtype == g["tx_uv"].dtype and np.array_equal(uv, g["tx_uv"])
+
+
+def test_pack_textures_matches_reference_golden():
+    """Pipeline._pack_textures (pipeline.py:810-868): atlas bytes and float64 UVs bit-equal on all golden layouts
+    (one row, one crop, two rows, float UVs, crops of zero width / without vertices)."""
+    from hive_b200.pipeline import Pipeline
+    g = _statics_gold()
+    for i in range(int(g["pk_cases"])):
+        n = int(g[f"pk{i}_n"])
+        tex = [g[f"pk{i}_tex{k}"] for k in range(n)]
+        uvs = [g[f"pk{i}_uv{k}"] for k in range(n)]
+        atlas, final = Pipeline._pack_textures(tex, uvs, n_rows=int(g[f"pk{i}_rows"]))
+        assert atlas.dtype == np.uint8 and atlas.shape == g[f"pk{i}_atlas"].shape, i
+        assert np.array_equal(atlas, g[f"pk{i}_atlas"]), i
+        assert final.dtype == np.float64 and np.array_equal(final, g[f"pk{i}_final"]), i
+
+
+def test_pack_textures_large_and_errors():
+    """Frame-sized crops against the numpy restatement; the reference's IndexError for a row without crops."""
+    from hive_b200.pipeline import Pipeline
+    from oracle import d2m_oracle as d2m
+    rng = np.random.default_rng(9)
+    shapes = [(480, 300), (217, 640), (1, 1), (333, 129)]
+    tex = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in shapes]
+    uvs = [np.stack([rng.integers(0, w, 5000), rng.integers(0, h, 5000)], axis=1).astype(np.int32) for h, w in shapes]
+    for n_rows in (1, 2):
+        atlas, final = Pipeline._pack_textures(tex, uvs, n_rows=n_rows)
+        want_atlas, want_final = d2m.pack_textures(tex, uvs, n_rows)
+        assert np.array_equal(atlas, want_atlas) and np.array_equal(final, want_final)
+    with pytest.raises(IndexError):
+        Pipeline._pack_textures(tex, uvs, n_rows=3)  # 2 slots per row: the third row receives nothing
+    with pytest.raises(IndexError):
+        Pipeline._pack_textures(tex[:2], uvs[:2], n_rows=2)
+    with pytest.raises(IndexError):
+        Pipeline._pack_textures([], [], n_rows=1)
