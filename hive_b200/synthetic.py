@@ -241,6 +241,18 @@ class _Indexed:
         return self._fn(i)  # a fresh array per access, like decoding a PNG (hive/io.py:550)
 
 
+def panning_poses(scene: "Scene", n: int, step_deg: float = 9.0):
+    """World-to-camera matrices of the scene's trajectory with an extra pan of ``step_deg`` per frame about the camera's
+    y axis, so that the overlap with earlier frames really falls (the stock trajectory barely moves): the trajectory the
+    key-frame selection tests and goldens run on."""
+    def rot_y(a):
+        c, s = np.cos(a), np.sin(a)
+        m = np.eye(4)
+        m[0, 0], m[0, 2], m[2, 0], m[2, 2] = c, s, -s, c
+        return m
+    return [np.linalg.inv(scene.pose(i) @ rot_y(np.deg2rad(step_deg * i))) for i in range(n)]
+
+
 class SyntheticDataset:
     """Duck-typed stand-in for ``hive.io.HiveDataset`` as read by ``hive.fusion.tsdf_fusion`` (hive/fusion.py:79-134):
     world-to-camera trajectory, RGB / depth / instance-mask frame accessors, float32 camera matrix."""

@@ -85,3 +85,59 @@ def reference_pipeline_statics(names=("_triangulate_faces", "_filter_faces", "_g
           "MeshFilteringOptions": object}
     exec(compile(module, path, "exec"), ns)
     return {name: ns[name] for name in names}
+
+
+def _compile_from_source(rel_path, names, namespace, class_name=None):
+    """Compile the named functions (or methods of ``class_name``) of a reference source file in ``namespace``."""
+    import ast
+    path = os.path.join(REFERENCE_ROOT, rel_path)
+    with open(path) as f:
+        tree = ast.parse(f.read(), filename=path)
+    body = tree.body
+    if class_name is not None:
+        body = next(n for n in body if isinstance(n, ast.ClassDef) and n.name == class_name).body
+    picked = [n for n in body if isinstance(n, ast.FunctionDef) and n.name in names]
+    assert len(picked) == len(names), f"missing in {path}: {set(names) - {n.name for n in picked}}"
+    for n in picked:
+        n.decorator_list = []
+    exec(compile(ast.Module(body=picked, type_ignores=[]), path, "exec"), namespace)
+    return {name: namespace[name] for name in names}
+
+
+def reference_tsdf_driver(volume_class=None):
+    """The reference's own ``adjust_voxel_size`` and ``tsdf_fusion`` (hive/fusion.py:37-134), compiled from the source
+    file (the module imports trimesh and hive.io at the top and cannot be imported) over the real reference
+    ``fusion`` module (CPU mode), the real ``hive.image_processing.dilate_mask`` and ``hive.options``.
+
+    ``volume_class``: replaces ``fusion.TSDFVolume`` inside the driver (a subclass of the reference's, used by the golden
+    generator to keep hold of the volume and to answer ``get_mesh``, which needs the absent scikit-image)."""
+    import logging
+    import typing
+    import numpy as np
+    fusion = reference_fusion()
+    reference_geometric()  # numpy-1 aliases + matplotlib stub, puts the reference root on sys.path
+    import hive.image_processing as image_processing
+    import hive.options as options
+    fusion_ns = types.SimpleNamespace(TSDFVolume=volume_class or fusion.TSDFVolume, get_view_frustum=fusion.get_view_frustum)
+    trimesh = types.SimpleNamespace(Trimesh=lambda **kw: kw)
+    ns = {"np": np, "logging": logging, "tqdm": lambda it, *a, **k: it, "fusion": fusion_ns, "trimesh": trimesh,
+          "dilate_mask": image_processing.dilate_mask, "MaskDilationOptions": options.MaskDilationOptions,
+          "BackgroundMeshOptions": options.BackgroundMeshOptions, "HiveDataset": object, "Optional": typing.Optional,
+          "List": typing.List, "Tuple": typing.Tuple}
+    out = _compile_from_source(os.path.join("hive", "fusion.py"), ("adjust_voxel_size", "tsdf_fusion"), ns)
+    out["BackgroundMeshOptions"] = options.BackgroundMeshOptions
+    out["fusion"] = fusion
+    return out
+
+
+def reference_select_key_frames():
+    """``HiveDataset.select_key_frames`` (hive/io.py:1117-1189) as a plain function of a stand-in ``self``."""
+    import logging
+    import typing
+    import numpy as np
+    geo = reference_geometric()
+    ns = {"np": np, "logging": logging, "tqdm": lambda it, *a, **k: it, "List": typing.List,
+          "get_pose_components": geo.get_pose_components, "pose_vec2mat": geo.pose_vec2mat,
+          "point_cloud_from_depth": geo.point_cloud_from_depth, "world2image": geo.world2image}
+    return _compile_from_source(os.path.join("hive", "io.py"), ("select_key_frames",), ns,
+                                class_name="HiveDataset")["select_key_frames"]

@@ -125,18 +125,11 @@ def test_tsdf_fusion_driver_matches_oracle(max_voxels, inpainted, c_oracle, monk
 
 
 def _rotating_dataset(n=12, step_deg=9.0):
-    """Frames of the small room scene behind a camera that also pans `step_deg` per frame, so that overlap with earlier
-    frames actually falls below the thresholds (the stock trajectory barely moves)."""
-    from hive_b200.synthetic import _Trajectory
+    """Frames of the small room scene behind a camera that also pans `step_deg` per frame."""
+    from hive_b200.synthetic import _Trajectory, panning_poses
     sc = Scene("small", "room")
     ds = SyntheticDataset(sc, n)
-
-    def rot_y(a):
-        c, s = np.cos(a), np.sin(a)
-        m = np.eye(4)
-        m[0, 0], m[0, 2], m[2, 0], m[2, 2] = c, s, -s, c
-        return m
-    ds.camera_trajectory = _Trajectory([np.linalg.inv(sc.pose(i) @ rot_y(np.deg2rad(step_deg * i))) for i in range(n)])
+    ds.camera_trajectory = _Trajectory(panning_poses(sc, n, step_deg))
     return ds
 
 
@@ -234,3 +227,56 @@ def test_get_mesh_srgb_colors_equals_conversion_of_plain_mesh():
     srgb = hive_fusion.tsdf_fusion(SyntheticDataset(sc, 4), opts, srgb_vertex_colors=True)
     assert np.array_equal(srgb.vertex_colors, drv.vertex_colors_to_srgb(plain.vertex_colors))
     assert np.array_equal(srgb.faces, plain.faces)
+
+
+# ---- against the reference's own driver (tests/golden/driver_reference.npz, oracle/make_driver_golden.py) -------------
+
+def _driver_gold():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "driver_reference.npz"))
+
+
+@pytest.mark.parametrize("case", [0, 1, 2])
+def test_tsdf_fusion_driver_matches_reference_golden(case, monkeypatch):
+    """hive_b200.hive_fusion.tsdf_fusion (device dilation fused into the upload) against the planes the reference's own
+    driver produced with cv2.dilate + its CPU TSDFVolume: voxel size and bounds equal, tsdf <= 1e-5, weight and colour
+    bit-exact."""
+    from hive_b200 import hive_fusion
+    g = _driver_gold()
+    sc = Scene("small", "room")
+    max_voxels = int(g[f"fu{case}_max_voxels"]) or None
+    inpainted = bool(g[f"fu{case}_inpainted"])
+    frame_set = [int(i) for i in g["fu_frame_set"]]
+    opts = hive_fusion.BackgroundMeshOptions(depth_mask_dilation_iterations=3, sdf_voxel_size=0.06,
+                                             sdf_max_voxels=max_voxels)
+    vs, bounds = hive_fusion.adjust_voxel_size(SyntheticDataset(sc, 6, inpainted), opts, frame_set)
+    assert vs == float(g[f"fu{case}_voxel_size"]) and np.array_equal(bounds, g[f"fu{case}_bounds"])
+    created = []
+    base = hive_fusion.fusion.TSDFVolume
+
+    class Spy(base):
+        def __init__(self, *a, **k):
+            super().__init__(*a, **k)
+            created.append(self)
+
+    monkeypatch.setattr(hive_fusion.fusion, "TSDFVolume", Spy)
+    hive_fusion.tsdf_fusion(SyntheticDataset(sc, 6, inpainted), opts, frame_set=frame_set)
+    tsdf, color = created[0].get_volume()
+    assert tsdf.shape == g[f"fu{case}_tsdf"].shape
+    assert np.abs(tsdf - g[f"fu{case}_tsdf"]).max() <= 1e-5
+    assert np.array_equal(created[0].get_weight_volume(), g[f"fu{case}_weight"])
+    assert np.array_equal(color, g[f"fu{case}_color"])
+
+
+def test_select_key_frames_matches_reference_golden():
+    """hive_fusion.select_key_frames against the lists HiveDataset.select_key_frames itself returned."""
+    from hive_b200 import hive_fusion
+    from hive_b200.synthetic import _Trajectory
+    g = _driver_gold()
+    mats = g["kf_world_to_camera"]
+    ds = SyntheticDataset(Scene("small", "room"), len(mats))
+    ds.camera_trajectory = _Trajectory(list(mats))
+    for a, thr in enumerate(g["kf_thresholds"]):
+        for b, step in enumerate(g["kf_steps"]):
+            want = [int(k) for k in g[f"kf_{a}_{b}"]]
+            assert hive_fusion.select_key_frames(ds, float(thr), int(step)) == want, (thr, step)
