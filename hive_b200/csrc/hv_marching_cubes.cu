@@ -371,35 +371,48 @@ __device__ __forceinline__ int vertex_index(const McGrid& g, int x, int y, int z
     return r;
 }
 
-// Writes the triangles of one cube (x, y, zb) with tiling `variant` at triangle offset ti.
-__device__ __forceinline__ void emit_cube(const McGrid& g, const McEmit& out, int x, int y, int zb, int variant, size_t ti) {
-    const int n = 3 * (int)kMcVarNtri[variant];
-    const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
-    for (int t = 0; t < n; ++t) {
-        const int e = tri[t];
-        int ox = 0, oy = 0, oz = 0, axis = 3;
+// Writes triangle `j` of the cube (x, y, zb) with tiling `variant` as face `ti`: three independent look-ups (edge ->
+// owning voxel -> that voxel's group mask and offset), unrolled so that all of their loads are in flight together.
+__device__ __forceinline__ void emit_triangle(const McGrid& g, const McEmit& out, int x, int y, int zb, int variant, int j,
+                                              size_t ti) {
+    const uint8_t* tri = kMcTris + 3 * ((size_t)kMcVarTriOff[variant] + (size_t)j);
+    int ox[3], oy[3], oz[3], axis[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const int e = tri[c];
+        ox[c] = oy[c] = oz[c] = 0;
+        axis[c] = 3;
         if (e < 12) {
-            ox = kMcEdgeOwner[4 * e], oy = kMcEdgeOwner[4 * e + 1], oz = kMcEdgeOwner[4 * e + 2];
-            axis = kMcEdgeOwner[4 * e + 3];
+            ox[c] = kMcEdgeOwner[4 * e], oy[c] = kMcEdgeOwner[4 * e + 1], oz[c] = kMcEdgeOwner[4 * e + 2];
+            axis[c] = kMcEdgeOwner[4 * e + 3];
         }
-        if (out.face_keys) {
-            out.face_keys[3 * ti + t] = vertex_key(g, x + ox, y + oy, zb + oz, axis);
-            if (out.face_cubes && t % 3 == 0) out.face_cubes[ti + t / 3] = vertex_key(g, x, y, zb, 0) >> 2;
-        } else {
-            out.faces[3 * ti + t] = vertex_index(g, x + ox, y + oy, zb + oz, axis);
-        }
+    }
+    if (out.face_keys) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) out.face_keys[3 * ti + c] = vertex_key(g, x + ox[c], y + oy[c], zb + oz[c], axis[c]);
+        if (out.face_cubes) out.face_cubes[ti] = vertex_key(g, x, y, zb, 0) >> 2;
+    } else {
+        int v[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) v[c] = vertex_index(g, x + ox[c], y + oy[c], zb + oz[c], axis[c]);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) out.faces[3 * ti + c] = v[c];
     }
 }
 
-// A block takes 256 entries of the active-group list.  Phase 1, one thread per group: the keys of the vertices the
-// group owns, and one record per surface cube (position, tiling, triangle offset) pushed into a shared-memory list.
-// Phase 2, one thread per record: the triangles.  (r01: with one warp per group and one lane per cube, 75-90 % of the
-// lanes idled in the triangle loop -- a group of 32 cubes is crossed by the surface in only a handful of them.)
+// A block takes kEmitThreads entries of the active-group list.  Phase 1, one thread per group: the keys of the vertices
+// the group owns, and one 8-byte record per *triangle* of its surface cubes (phase-1 slot, voxel, tiling, triangle number,
+// face index) pushed into a shared-memory list.  Phase 2, one thread per record: one triangle = three independent
+// vertex look-ups.  (r01 history: one warp per group / one lane per cube left 75-90 % of the lanes idle in the triangle
+// loop; one thread per cube record still walked up to 12 triangles x 3 dependent look-ups serially -- 47 % of the
+// kernel's stall samples were long-scoreboard waits inside that loop.)
 constexpr int kEmitThreads = 128;
-constexpr int kEmitCap = 1024;  // records per round; cubes beyond it are written by their phase-1 thread directly
+constexpr int kEmitCap = 2048;  // triangle records per round (16 KB); triangles beyond it are written by phase 1 directly
+static_assert(HV_MC_NUM_VARIANTS <= 1024 && kEmitThreads <= 128, "record packing: 7 bits slot, 5 voxel, 10 tiling, 4+ triangle");
 
 __global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, const McEmit out) {
-    __shared__ uint4 s_list[kEmitCap];
+    __shared__ uint2 s_tri[kEmitCap];
+    __shared__ int s_x[kEmitThreads], s_y[kEmitThreads], s_z0[kEmitThreads];
     __shared__ unsigned int s_n;
     const unsigned int n_active = *g.n_active;
     for (unsigned int base = blockIdx.x * kEmitThreads; base < n_active; base += gridDim.x * kEmitThreads) {
@@ -413,6 +426,9 @@ __global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, c
             const unsigned int col = gi / (unsigned int)g.G;
             const int gq = (int)(gi - col * (unsigned int)g.G);
             const int x = (int)(col / (unsigned int)g.Y), y = (int)(col - (unsigned int)x * (unsigned int)g.Y);
+            s_x[threadIdx.x] = x;
+            s_y[threadIdx.x] = y;
+            s_z0[threadIdx.x] = gq * 32;
             if (cnt.x) {  // vertex keys, order inside the group: (voxel, axis)
                 const uint4 m = g.gmask[gi];
                 size_t vi = off.x;
@@ -430,15 +446,17 @@ __global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, c
                 unsigned int toff = off.y;
                 for (unsigned int rest = c.active; rest; rest &= rest - 1) {
                     const int k = __ffs(rest) - 1;
-                    const int zb = gq * 32 + k;
-                    const int variant = cube_variant_at(g, cube_index(c, k), x, y, zb);
+                    const int variant = cube_variant_at(g, cube_index(c, k), x, y, gq * 32 + k);
                     const unsigned int ntri = kMcVarNtri[variant];
                     if (ntri == 0u) continue;
-                    const unsigned int slot = atomicAdd(&s_n, 1u);
-                    if (slot < (unsigned int)kEmitCap)
-                        s_list[slot] = make_uint4((unsigned int)x, (unsigned int)y, (unsigned int)zb | ((unsigned int)variant << 22), toff);
-                    else
-                        emit_cube(g, out, x, y, zb, variant, toff);
+                    const unsigned int slot = atomicAdd(&s_n, ntri);
+                    const unsigned int head = threadIdx.x | ((unsigned int)k << 7) | ((unsigned int)variant << 12);
+                    for (unsigned int j = 0; j < ntri; ++j) {
+                        if (slot + j < (unsigned int)kEmitCap)
+                            s_tri[slot + j] = make_uint2(head | (j << 22), toff + j);
+                        else
+                            emit_triangle(g, out, x, y, gq * 32 + k, variant, (int)j, toff + j);
+                    }
                     toff += ntri;
                 }
             }
@@ -446,8 +464,10 @@ __global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, c
         __syncthreads();
         const unsigned int n = min(s_n, (unsigned int)kEmitCap);
         for (unsigned int i = threadIdx.x; i < n; i += kEmitThreads) {
-            const uint4 r = s_list[i];
-            emit_cube(g, out, (int)r.x, (int)r.y, (int)(r.z & 0x3fffffu), (int)(r.z >> 22), r.w);
+            const uint2 r = s_tri[i];
+            const unsigned int t = r.x & 127u;
+            emit_triangle(g, out, s_x[t], s_y[t], s_z0[t] + (int)((r.x >> 7) & 31u), (int)((r.x >> 12) & 1023u),
+                          (int)(r.x >> 22), r.y);
         }
         __syncthreads();
     }
