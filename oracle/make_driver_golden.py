@@ -9,6 +9,8 @@ from the source files by ``oracle/ref_shim.py``, on the seeded synthetic dataset
 ``fu<i>_*``  driver runs on ``small``/``room``, frames 0, 2, 3, 5, three dilation iterations, 6 cm voxels: (0) masks applied,
              no voxel budget; (1) masks applied, budget 300 000 voxels (voxel size raised); (2) inpainted data (no masks).
              Stored: voxel size, bounds as returned, and the three planes of the reference volume after the loop.
+``mp_*``     the reference's ``get_mesh`` / ``get_point_cloud`` post-processing (fusion.py:311-350) of run 0's volume, with the
+             absent scikit-image call answered by the C restatement of marching cubes
 ``kf_*``     key-frame lists of a 12-frame panning trajectory for thresholds 0.2-0.9 and frame steps 1 and 3; the
              world-to-camera matrices are stored as the reference derives them from its 7-vectors (pose_vec2mat).
 """
@@ -65,8 +67,27 @@ def fusion_cases(out):
         out[f"fu{i}_color"] = vol._color_vol_cpu
         print(f"fusion case {i}: voxel {voxel_size:.4f}, dims {vol._vol_dim}, "
               f"{int((vol._weight_vol_cpu > 0).sum())} voxels observed")
+        if i == 0:
+            mesh_post_case(out, vol, fusion)
     out["fu_cases"] = len(FUSION_CASES)
     out["fu_frame_set"] = np.array(FRAME_SET)
+
+
+def mesh_post_case(out, vol, fusion):
+    """The reference's own ``get_mesh`` / ``get_point_cloud`` (fusion.py:311-350) on the volume of driver run 0.  The
+    marching cubes inside them is scikit-image's (absent): ``measure.marching_cubes`` is answered by the C restatement, so
+    what this pins is everything the reference does *after* it -- voxel rounding, world transform, colour gather and
+    unpacking, the (V, 6) point-cloud layout -- in the reference's own arithmetic and dtypes."""
+    from oracle import c_oracle
+    c_oracle.build()
+    fusion.measure.marching_cubes = lambda tsdf, level=0: c_oracle.marching_cubes(tsdf, float(level))
+    fusion.measure.marching_cubes_lewiner = fusion.measure.marching_cubes
+    vol.ctx = types.SimpleNamespace(pop=lambda: None)  # get_mesh pops the PyCUDA context even in CPU mode (fusion.py:349)
+    verts, faces, norms, colors = fusion.TSDFVolume.get_mesh(vol)
+    pc = fusion.TSDFVolume.get_point_cloud(vol)
+    out.update(mp_verts=verts, mp_faces=faces, mp_norms=norms, mp_colors=colors, mp_pc=pc)
+    print(f"get_mesh: verts {verts.dtype}{verts.shape}, faces {faces.dtype}{faces.shape}, colors {colors.dtype}, "
+          f"point cloud {pc.dtype}{pc.shape}")
 
 
 def key_frame_cases(out):

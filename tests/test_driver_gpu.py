@@ -280,3 +280,33 @@ def test_select_key_frames_matches_reference_golden():
         for b, step in enumerate(g["kf_steps"]):
             want = [int(k) for k in g[f"kf_{a}_{b}"]]
             assert hive_fusion.select_key_frames(ds, float(thr), int(step)) == want, (thr, step)
+
+
+def test_get_mesh_and_point_cloud_match_reference_golden(c_oracle):
+    """TSDFVolume.get_mesh / get_point_cloud on exactly the planes the reference's driver produced, against what the
+    reference's own get_mesh / get_point_cloud returned for them (fusion.py:311-350; the skimage call inside was answered
+    by the C marching cubes, so topology parity is that of tests/test_marching_cubes_gpu.py -- what is pinned here is the
+    post-processing: dtypes, world transform, colour gather and unpacking, the (V, 6) layout)."""
+    import torch
+    from hive_b200.fusion import TSDFVolume
+    g = _driver_gold()
+    tsdf, color = g["fu0_tsdf"], g["fu0_color"]
+    vol = TSDFVolume(g["fu0_bounds"].copy(), float(g["fu0_voxel_size"]))
+    X, Y, Z = tsdf.shape
+    assert tuple(int(d) for d in vol._vol_dim) == (X, Y, Z)
+    vol._tsdf_vol_gpu[:, :, :Z].copy_(torch.from_numpy(tsdf))
+    vol._color_vol_gpu[:, :, :Z].copy_(torch.from_numpy(color))
+    verts, faces, norms, colors = vol.get_mesh()
+    # the golden is in the C oracle's vertex order, the GPU emits in (owner voxel, axis) order: renumber through the keys
+    _, _, _, _, keys = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
+    order = np.argsort(keys, kind="stable")
+    rank = np.empty_like(order)
+    rank[order] = np.arange(len(order))
+    assert verts.dtype == np.float32 and faces.dtype == np.int32 and colors.dtype == np.uint8
+    assert np.array_equal(verts, g["mp_verts"][order])
+    assert np.array_equal(colors, g["mp_colors"][order])
+    assert np.array_equal(faces, rank[g["mp_faces"]].astype(np.int32))
+    assert np.abs(norms - g["mp_norms"][order]).max() <= 1e-6
+    pc = vol.get_point_cloud()
+    assert pc.dtype == g["mp_pc"].dtype and pc.shape == g["mp_pc"].shape
+    assert np.array_equal(pc, g["mp_pc"][order])

@@ -50,3 +50,20 @@ def test_select_key_frames_restatement_equals_the_reference(gold):
             assert drv.select_key_frames(ds, float(thr), int(step)) == want
             seen.add(tuple(want))
     assert len(seen) >= 6  # the cases really differ
+
+
+def test_mesh_postprocess_restatement_equals_the_reference_get_mesh(gold, c_oracle):
+    """fusion.py:339-348 / :318-329 (everything after the marching-cubes call) in the reference's own arithmetic: the
+    golden was produced by the reference's get_mesh / get_point_cloud with the C marching cubes standing in for skimage."""
+    from oracle import fusion_oracle as fo
+    tsdf, color = gold["fu0_tsdf"], gold["fu0_color"]
+    voxel_size = float(gold["fu0_voxel_size"])
+    origin = gold["fu0_bounds"][:, 0].copy(order='C').astype(np.float32)  # fusion.py:46
+    ov, of, on, _ = c_oracle.marching_cubes(tsdf, 0.0)
+    verts, colors = fo.mesh_postprocess(ov, color, voxel_size, origin)
+    assert verts.dtype == gold["mp_verts"].dtype == np.float32
+    assert np.array_equal(verts, gold["mp_verts"]) and np.array_equal(colors, gold["mp_colors"])
+    assert np.array_equal(of, gold["mp_faces"]) and np.array_equal(on, gold["mp_norms"])
+    pc = np.hstack([verts, colors])
+    assert pc.dtype == gold["mp_pc"].dtype and np.array_equal(pc, gold["mp_pc"])
+    assert len(verts) > 10_000 and len(np.unique(colors)) > 50
