@@ -20,7 +20,7 @@ from . import _lib
 from . import _xfer
 from . import geometric
 
-__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh"]
+__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh", "FrameMesh", "process_frame"]
 
 
 def _ptr(t):
@@ -224,3 +224,65 @@ def face_component_mask(faces, n_verts, min_len=5, largest_only=True, return_lab
         k, lab = _xfer.to_host(keep, labels)
         return k.view(np.bool_), lab.view(np.uint32)
     return _xfer.to_host(keep).view(np.bool_)
+
+
+@dataclass
+class FrameMesh:
+    """What ``process_frame`` hands to ``trimesh.Trimesh(frame_vertices, frame_faces, TextureVisuals(uv, texture))``
+    (pipeline.py:472-482).  ``faces`` is float64 like the reference's (it stacks onto ``np.zeros((0, 3))``)."""
+    vertices: np.ndarray
+    faces: np.ndarray
+    texture: np.ndarray = None
+    uv: np.ndarray = None
+    object_ids: tuple = ()
+
+    @property
+    def is_empty(self):
+        return self.texture is None
+
+
+def process_frame(rgb, depth, mask_encoded, pose, camera_matrix, dilation_options=None, filtering_options=None,
+                  disable_coverage_constraint=False, diags=None) -> FrameMesh:
+    """The per-frame foreground mesh step, ``process_frame`` of pipeline.py:340-484, for the dynamic objects
+    (``include_background=False``): for every instance id in the mask -- dilate its mask, skip it below 1 % coverage,
+    back-project + triangulate + filter (one fused CUDA call), skip below 9 vertices or without faces, drop floaters
+    (largest face component), crop the texture and the UVs -- then pack the crops into the frame's atlas.
+
+    Every step is the GPU drop-in of this package; the loop, the three skip rules and the stacking are the reference's.
+    Not performed: mesh decimation (``_decimate_mesh`` is OpenMesh's sequential edge collapse, out of scope: the meshes
+    are passed on undecimated) and the optional billboard flattening.  ``diags``: per-object diagonal bitmaps for the
+    co-circular lattice quads (tests inject the oracle's Qhull choices; ``None`` = this package's rule).
+    """
+    from . import image_processing
+    dilation_options = dilation_options or image_processing.MaskDilationOptions(num_iterations=0)
+    filtering_options = filtering_options or MeshFilteringOptions()
+    rgb = np.ascontiguousarray(np.asarray(rgb)[:, :, :3])
+    depth, mask_encoded = np.asarray(depth), np.asarray(mask_encoded)
+    rotation, translation = geometric.get_pose_components(np.asarray(pose))
+
+    frame_vertices = np.zeros((0, 3))
+    frame_faces = np.zeros((0, 3))
+    uv_atlas, texture_atlas, kept_ids = [], [], []
+    vertex_count = 0
+    for object_id in range(1, int(mask_encoded.max()) + 1):
+        mask = image_processing.dilate_mask(mask_encoded == object_id, dilation_options)
+        coverage_ratio = np.count_nonzero(mask) / mask.size  # == mask.mean()
+        if coverage_ratio < 0.01 and not disable_coverage_constraint:
+            continue
+        vertices, faces, _, _ = depth_to_mesh(depth, mask, camera_matrix, rotation, translation, filtering_options,
+                                              None if diags is None else diags.get(object_id))
+        if len(vertices) < 9 or len(faces) < 1:
+            continue
+        vertices, faces = Pipeline._cleanup_with_connected_components(vertices, faces, True,
+                                                                     min_components=filtering_options.min_num_components)
+        texture, uv = Pipeline._get_mesh_texture_and_uv(vertices, rgb, camera_matrix, rotation, translation)
+        texture_atlas.append(texture)
+        uv_atlas.append(uv)
+        frame_vertices = np.vstack((frame_vertices, vertices))
+        frame_faces = np.vstack((frame_faces, faces + vertex_count))
+        vertex_count += len(vertices)
+        kept_ids.append(object_id)
+    if len(texture_atlas) == 0:
+        return FrameMesh(frame_vertices, frame_faces)
+    packed_textures, packed_uv = Pipeline._pack_textures(texture_atlas, uv_atlas, n_rows=1)
+    return FrameMesh(frame_vertices, frame_faces, packed_textures, packed_uv, tuple(kept_ids))

@@ -200,3 +200,42 @@ def cleanup_with_connected_components(vertices, faces, is_object=True, min_compo
             else:
                 mask[np.concatenate(components)] = True
     return vertices, faces[mask]
+
+
+def process_frame(rgb, depth, mask_encoded, pose, camera_matrix, dilation_iterations=0, max_pixel_distance=2,
+                  max_depth_distance=0.1, min_num_components=5, disable_coverage_constraint=False):
+    """hive/pipeline.py:340-484 for the dynamic objects (object ids >= 1), decimation and billboard off, composed from the
+    restatements above.  Returns (frame_vertices, frame_faces, atlas or None, uv or None, kept ids, {id: (points2d, raw)})."""
+    from . import driver_oracle as drv
+    rgb = np.ascontiguousarray(rgb[:, :, :3])
+    rotation, translation = pose[:3, :3], pose[:3, 3:]
+    frame_vertices, frame_faces = np.zeros((0, 3)), np.zeros((0, 3))
+    uv_atlas, texture_atlas, kept, raws = [], [], [], {}
+    vertex_count = 0
+    for object_id in range(1, int(mask_encoded.max()) + 1):
+        mask = drv.dilate_mask(mask_encoded == object_id, dilation_iterations)
+        if mask.mean() < 0.01 and not disable_coverage_constraint:
+            continue
+        vertices = point_cloud_from_depth(depth, mask, camera_matrix, rotation, translation)
+        if len(vertices) < 9:
+            continue
+        valid = mask & (depth > 0.0)
+        v, u = valid.nonzero()
+        points2d = np.vstack((u, v)).T
+        raw = triangulate_faces(points2d)
+        raws[object_id] = (points2d, raw)
+        faces = filter_faces(points2d, depth[valid], raw, max_pixel_distance, max_depth_distance)
+        if len(faces) < 1:
+            continue
+        vertices, faces = cleanup_with_connected_components(vertices, faces, True, min_num_components)
+        texture, uv = get_mesh_texture_and_uv(vertices, rgb, camera_matrix, rotation, translation)
+        texture_atlas.append(texture)
+        uv_atlas.append(uv)
+        frame_vertices = np.vstack((frame_vertices, vertices))
+        frame_faces = np.vstack((frame_faces, faces + vertex_count))
+        vertex_count += len(vertices)
+        kept.append(object_id)
+    if not texture_atlas:
+        return frame_vertices, frame_faces, None, None, kept, raws
+    atlas, final_uv = pack_textures(texture_atlas, uv_atlas, n_rows=1)
+    return frame_vertices, frame_faces, atlas, final_uv, kept, raws

@@ -272,3 +272,61 @@ def test_pack_textures_large_and_errors():
         Pipeline._pack_textures(tex[:2], uvs[:2], n_rows=2)
     with pytest.raises(IndexError):
         Pipeline._pack_textures([], [], n_rows=1)
+
+
+# ---- the composed per-frame step (pipeline.py:340-484) -----------------------------------------------------------------
+
+def _with_small_blobs(mask, depth):
+    """Adds instance 3 (a 3x3 blob: below 1 % coverage, exactly 9 vertices) and instance 4 (2x2: below 9 vertices) on
+    background pixels with valid depth."""
+    mask = mask.copy()
+    free = (mask == 0) & (depth > 0)
+    H, W = mask.shape
+    placed = []
+    for size, obj in ((3, 3), (2, 4)):
+        for v in range(2, H - 4):
+            u = next((u for u in range(2, W - 4) if free[v - 1:v + size + 1, u - 1:u + size + 1].all()), None)
+            if u is not None:
+                mask[v:v + size, u:u + size] = obj
+                free[v - 1:v + size + 1, u - 1:u + size + 1] = False
+                placed.append(obj)
+                break
+    assert placed == [3, 4]
+    return mask
+
+
+@pytest.mark.parametrize("config,index,dilation", [("small", 2, 2), ("small", 5, 0), ("tiny", 1, 1)])
+@pytest.mark.parametrize("disable_coverage", [False, True])
+def test_process_frame_matches_oracle(config, index, dilation, disable_coverage):
+    """Objects kept / skipped, stacked vertices and faces, atlas and UVs of the whole per-frame step equal the composed
+    numpy restatement (Qhull's diagonals injected per object; faces compared as sets, everything else element-wise)."""
+    from hive_b200 import image_processing, pipeline
+    scene, fr, R, t = _frame(config, index)
+    pose = np.eye(4)
+    pose[:3, :3], pose[:3, 3:] = R, t
+    mask = _with_small_blobs(fr.mask, fr.depth)
+    ov, of, oatlas, ouv, okept, raws = d2m.process_frame(fr.rgb, fr.depth, mask, pose, scene.K, dilation,
+                                                         disable_coverage_constraint=disable_coverage)
+    diags = {k: d2m.diagonals(p2, raw, scene.H, scene.W) for k, (p2, raw) in raws.items()}
+    got = pipeline.process_frame(fr.rgb, fr.depth, mask, pose, scene.K,
+                                 image_processing.MaskDilationOptions(num_iterations=dilation),
+                                 pipeline.MeshFilteringOptions(), disable_coverage_constraint=disable_coverage, diags=diags)
+    assert list(got.object_ids) == okept
+    if not disable_coverage:
+        assert 3 not in okept and 4 not in okept      # both blobs fall to the 1 % coverage rule
+    elif dilation == 0:
+        assert 3 in okept and 4 not in okept          # 3x3 = exactly 9 vertices stays, 2x2 falls to the 9-vertex rule
+    assert got.vertices.dtype == np.float64 and got.faces.dtype == np.float64
+    assert got.vertices.shape == ov.shape and _close(got.vertices, ov)
+    assert np.array_equal(d2m.canonical_faces(got.faces), d2m.canonical_faces(of))
+    assert np.array_equal(got.texture, oatlas)
+    assert got.uv.dtype == np.float64 and np.array_equal(got.uv, ouv)
+
+
+def test_process_frame_without_objects_is_empty():
+    from hive_b200 import pipeline
+    scene, fr, R, t = _frame("tiny", 1)
+    pose = np.eye(4)
+    pose[:3, :3], pose[:3, 3:] = R, t
+    got = pipeline.process_frame(fr.rgb, fr.depth, np.zeros_like(fr.mask), pose, scene.K)
+    assert got.is_empty and got.vertices.shape == (0, 3) and got.faces.shape == (0, 3)
