@@ -523,7 +523,7 @@ __device__ __forceinline__ void add_cube_gradient(const double v[8], int e, int 
     }
 }
 
-__global__ void __launch_bounds__(128) mc_vertex_kernel(const McGrid g, const McVerts out) {
+__global__ void __launch_bounds__(128, 8) mc_vertex_kernel(const McGrid g, const McVerts out) {
     const long long vi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (vi >= out.n_verts) return;
     const unsigned long long key = out.vert_keys[vi];
