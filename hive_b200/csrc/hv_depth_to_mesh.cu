@@ -41,8 +41,16 @@ struct D2mGrid {
 
 struct PixelFaces {
     int n;
-    int2 p[4][3];  // pixel coordinates (u, v) of the corners, winding with negative signed area in (u, v)
+    // Corners of the (at most four) faces, winding with negative signed area in (u, v).  Every corner lies within one
+    // pixel of the owner, so a corner is 4 bits ((du + 1) | (dv + 1) << 2), a face 12, and the whole set one register
+    // pair -- as int2 p[4][3] indexed by the running face count it lived in local memory (104-byte stack frame, a
+    // store and a load per corner in the emit loop).
+    unsigned long long codes;
 };
+
+__device__ __forceinline__ unsigned int corner_code(int2 p, int u, int v) {
+    return (unsigned int)(p.x - u + 1) | ((unsigned int)(p.y - v + 1) << 2);
+}
 
 // Depth of pixel (u, v) if it is a vertex (inside the image, mask set, depth > 0: geometric.py:117), else 0.
 __device__ __forceinline__ float d2m_vdepth(const D2mGrid& g, int b, int u, int v) {
@@ -137,13 +145,12 @@ __device__ __forceinline__ bool depth_ok(const D2mGrid& g, float a, float b, flo
            fabsf(__fsub_rn(a, c)) <= g.max_depth_distance;
 }
 
-__device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, bool keep_coords, int2 a, float da, int2 b,
-                                          float db, int2 c, float dc) {
+__device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, bool keep_coords, int u, int v, int2 a,
+                                          float da, int2 b, float db, int2 c, float dc) {
     if (!depth_ok(g, da, db, dc)) return;
     if (keep_coords) {
-        f.p[f.n][0] = a;
-        f.p[f.n][1] = b;
-        f.p[f.n][2] = c;
+        const unsigned int face = corner_code(a, u, v) | (corner_code(b, u, v) << 4) | (corner_code(c, u, v) << 8);
+        f.codes |= (unsigned long long)face << (12 * f.n);
     }
     ++f.n;
 }
@@ -153,6 +160,7 @@ __device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, bool 
 __device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int v, const Hood& h, bool keep_coords,
                                             PixelFaces& f) {
     f.n = 0;
+    f.codes = 0ull;
     if (u >= g.W) return;
     const unsigned int ov = g.diag ? g.diag[((size_t)b * g.H + v) * g.W + u] : 0u;
     const float d_self = h.c, db = h.e, dc = h.s, dd = h.se;
@@ -162,17 +170,17 @@ __device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int 
     if (nq == 4) {
         const bool anti = g.diag ? (ov & 1u) : !(fabsf(__fsub_rn(d_self, dd)) <= fabsf(__fsub_rn(db, dc)));
         if (!anti) {
-            push_face(g, f, keep_coords, A, d_self, D, dd, Bp, db);
-            push_face(g, f, keep_coords, A, d_self, C, dc, D, dd);
+            push_face(g, f, keep_coords, u, v, A, d_self, D, dd, Bp, db);
+            push_face(g, f, keep_coords, u, v, A, d_self, C, dc, D, dd);
         } else {
-            push_face(g, f, keep_coords, A, d_self, C, dc, Bp, db);
-            push_face(g, f, keep_coords, Bp, db, C, dc, D, dd);
+            push_face(g, f, keep_coords, u, v, A, d_self, C, dc, Bp, db);
+            push_face(g, f, keep_coords, u, v, Bp, db, C, dc, D, dd);
         }
     } else if (nq == 3) {
-        if (!vd) push_face(g, f, keep_coords, A, d_self, C, dc, Bp, db);
-        else if (!self_valid) push_face(g, f, keep_coords, Bp, db, C, dc, D, dd);
-        else if (!vb) push_face(g, f, keep_coords, A, d_self, C, dc, D, dd);
-        else push_face(g, f, keep_coords, A, d_self, D, dd, Bp, db);
+        if (!vd) push_face(g, f, keep_coords, u, v, A, d_self, C, dc, Bp, db);
+        else if (!self_valid) push_face(g, f, keep_coords, u, v, Bp, db, C, dc, D, dd);
+        else if (!vb) push_face(g, f, keep_coords, u, v, A, d_self, C, dc, D, dd);
+        else push_face(g, f, keep_coords, u, v, A, d_self, D, dd, Bp, db);
     }
     if (!self_valid && g.bridges) {
         const float dn = h.n, de = h.e, ds = h.s, dw = h.w;
@@ -182,17 +190,17 @@ __device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int 
         if (nh == 4) {
             const bool vertical = g.diag ? ((ov >> 1) & 1u) : !(fabsf(__fsub_rn(dw, de)) <= fabsf(__fsub_rn(dn, ds)));
             if (!vertical) {
-                push_face(g, f, keep_coords, Wp, dw, E, de, N, dn);
-                push_face(g, f, keep_coords, Wp, dw, S, ds, E, de);
+                push_face(g, f, keep_coords, u, v, Wp, dw, E, de, N, dn);
+                push_face(g, f, keep_coords, u, v, Wp, dw, S, ds, E, de);
             } else {
-                push_face(g, f, keep_coords, N, dn, S, ds, E, de);
-                push_face(g, f, keep_coords, N, dn, Wp, dw, S, ds);
+                push_face(g, f, keep_coords, u, v, N, dn, S, ds, E, de);
+                push_face(g, f, keep_coords, u, v, N, dn, Wp, dw, S, ds);
             }
         } else if (nh == 3) {
-            if (!vn) push_face(g, f, keep_coords, Wp, dw, S, ds, E, de);
-            else if (!vs) push_face(g, f, keep_coords, Wp, dw, E, de, N, dn);
-            else if (!ve) push_face(g, f, keep_coords, N, dn, Wp, dw, S, ds);
-            else push_face(g, f, keep_coords, N, dn, S, ds, E, de);
+            if (!vn) push_face(g, f, keep_coords, u, v, Wp, dw, S, ds, E, de);
+            else if (!vs) push_face(g, f, keep_coords, u, v, Wp, dw, E, de, N, dn);
+            else if (!ve) push_face(g, f, keep_coords, u, v, N, dn, Wp, dw, S, ds);
+            else push_face(g, f, keep_coords, u, v, N, dn, S, ds, E, de);
         }
     }
 }
@@ -322,14 +330,15 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
                     if (lane >= o) inc += up;
                 }
                 size_t fi = (size_t)off.y + inc - (unsigned int)f.n;
-                for (int k = 0; k < f.n; ++k, ++fi)
+                unsigned long long codes = f.codes;
+                for (int k = 0; k < f.n; ++k, ++fi, codes >>= 12)
 #pragma unroll
                     for (int c = 0; c < 3; ++c) {
-                        const int2 q = f.p[k][c];
-                        const int dv = q.y - v;
+                        const unsigned int nib = ((unsigned int)codes >> (4 * c)) & 15u;
+                        const int qx = u + (int)(nib & 3u) - 1, dv = (int)(nib >> 2) - 1;
                         const unsigned int rb = dv < 0 ? prev.bits : (dv > 0 ? next.bits : cur.bits);
                         const unsigned int rf = dv < 0 ? first_prev : (dv > 0 ? first_next : first_cur);
-                        out.faces[3 * fi + c] = corner_rank(q.x, cw * 32, rb, rf);
+                        out.faces[3 * fi + c] = corner_rank(qx, cw * 32, rb, rf);
                     }
             }
             const unsigned int bits = has_f ? cur.bits : g.wbits[w];  // (the count kernel stored exactly cur.bits)
