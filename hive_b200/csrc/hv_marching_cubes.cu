@@ -252,9 +252,60 @@ __device__ __forceinline__ void load_cube_values(const McGrid& g, int x, int y, 
     }
 }
 
-// Resolves the ambiguous faces with the asymptotic decider (same statement as oracle/mc_oracle.c:mc_variant).
+// Lewiner's test_interior (same statement as oracle/mc_oracle.c:interior_says_tunnel): slab form
+// for cases 4 / 10, reference-edge form for 6 / 7 / 12 / 13.5.  `word`: kMcInterior descriptor.  Returns true when the
+// tube tiling is to be used.  Plain double arithmetic; the TU is compiled with -fmad=false, so no contraction.
+__device__ __noinline__ bool cube_interior_tunnel(unsigned int word, const double v[8]) {
+    const bool inverted = (word >> 2) & 1u, tunnel_if_test = (word >> 3) & 1u;
+    const bool ret_pos = !inverted, ret_neg = inverted;  // Lewiner's "return s > 0" / "return s < 0"
+    int c[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i] = (int)((word >> (4 + 3 * i)) & 7u);
+    double a0 = 0, a1 = 0, b0 = 0, b1 = 0, c0 = 0, c1 = 0, d0 = 0, d1 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {  // select by compare: keeps v[] in registers
+        const double vi = v[i];
+        if (c[0] == i) a0 = vi;
+        if (c[1] == i) a1 = vi;
+        if (c[2] == i) b0 = vi;
+        if (c[3] == i) b1 = vi;
+        if (c[4] == i) c0 = vi;
+        if (c[5] == i) c1 = vi;
+        if (c[6] == i) d0 = vi;
+        if (c[7] == i) d1 = vi;
+    }
+    double t, At, Bt, Ct, Dt;
+    bool result;
+    if ((word & 3u) == 1u) {
+        const double dA = a1 - a0, dB = b1 - b0, dC = c1 - c0, dD = d1 - d0;
+        const double qa = dA * dC - dB * dD;
+        const double qb = c0 * dA + a0 * dC - d0 * dB - b0 * dD;
+        t = -qb / (2 * qa);
+        if (t < 0 || t > 1) return tunnel_if_test ? ret_pos : !ret_pos;
+        At = a0 + dA * t;
+        Bt = b0 + dB * t;
+        Ct = c0 + dC * t;
+        Dt = d0 + dD * t;
+    } else {
+        t = a0 / (a0 - a1);
+        At = 0;
+        Bt = b0 + (b1 - b0) * t;
+        Ct = c0 + (c1 - c0) * t;
+        Dt = d0 + (d1 - d0) * t;
+    }
+    const int test = (At >= 0 ? 1 : 0) | (Bt >= 0 ? 2 : 0) | (Ct >= 0 ? 4 : 0) | (Dt >= 0 ? 8 : 0);
+    if (test == 5) result = (At * Ct - Bt * Dt < (double)FLT_EPSILON) ? ret_pos : ret_neg;
+    else if (test == 10) result = (At * Ct - Bt * Dt >= (double)FLT_EPSILON) ? ret_pos : ret_neg;
+    else if (test == 7 || test == 11 || test >= 13) result = ret_neg;
+    else result = ret_pos;
+    return tunnel_if_test ? result : !result;
+}
+
+// Tiling of one cube: each ambiguous face is resolved with Lewiner's face test, p =
+// "the positive corners are joined" = (pos - neg > -FLT_EPSILON); where his decision tree evaluates the interior
+// test, a tunnel selects the tube tiling stored after the 2^namb plain ones.
 __device__ __forceinline__ int cube_variant(int idx, const double v[8]) {
-    int variant = kMcVariantBase[idx];
+    int p_bits = 0;
     const int namb = kMcAmbCount[idx];
     const unsigned int faces = kMcAmbFaces[idx];
     for (int k = 0; k < namb; ++k) {
@@ -264,7 +315,16 @@ __device__ __forceinline__ int cube_variant(int idx, const double v[8]) {
             const int t = a; a = b; b = c; c = d; d = t;
         }
         const double pos = __dmul_rn(v[a], v[c]), neg = __dmul_rn(v[b], v[d]);
-        if (pos > neg) variant += 1 << k;
+        if (__dsub_rn(pos, neg) > -(double)FLT_EPSILON) p_bits |= 1 << k;
+    }
+    int variant = kMcVariantBase[idx] + p_bits;
+    const int ib = kMcInteriorBase[idx];
+    if (ib != 255) {
+        const unsigned long long mask = kMcInteriorMask[idx];
+        if ((mask >> p_bits) & 1ull) {
+            const int rank = __popcll(mask & ((1ull << p_bits) - 1ull));
+            if (cube_interior_tunnel(kMcInterior[ib + rank], v)) variant = kMcVariantBase[idx] + (1 << namb) + rank;
+        }
     }
     return variant;
 }
@@ -287,13 +347,13 @@ __device__ __noinline__ int cube_variant_ambiguous(const float* tsdf, const floa
 
 // count kernel: one thread per group, nearly all of them with nothing ambiguous -> occupancy matters, call out of line
 __device__ __forceinline__ int cube_variant_at_ool(const McGrid& g, int idx, int x, int y, int zb) {
-    if (kMcAmbCount[idx] == 0) return kMcVariantBase[idx];
+    if (kMcAmbCount[idx] == 0 && kMcInteriorBase[idx] == 255) return kMcVariantBase[idx];  // (case 4: no face, one interior test)
     return cube_variant_ambiguous(g.tsdf, g.halo_lo, g.halo_hi, g.Y, g.pitch, g.Z, g.hl, g.level, idx, x, y, zb);
 }
 
 // emit kernel: works on surface cubes only; inlined (the call cost 30 us at 512^3 there)
 __device__ __forceinline__ int cube_variant_at(const McGrid& g, int idx, int x, int y, int zb) {
-    if (kMcAmbCount[idx] == 0) return kMcVariantBase[idx];
+    if (kMcAmbCount[idx] == 0 && kMcInteriorBase[idx] == 255) return kMcVariantBase[idx];
     double v[8];
     load_cube_values(g, x, y, zb, v);
     return cube_variant(idx, v);

@@ -20,7 +20,7 @@ _LIB = None
 def build(force: bool = False) -> str:
     """Compile the C restatements (gcc, a second or two)."""
     so = os.path.join(_HERE, "libhive_oracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("tsdf_oracle.c", "mc_oracle.c", "mc_tables.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("tsdf_oracle.c", "mc_oracle.c")]
     stale = force or not os.path.exists(so) or any(
         os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if stale:
@@ -127,3 +127,40 @@ def get_mesh(tsdf_vol, color_vol, voxel_size, vol_origin):
     verts, faces, norms, _ = marching_cubes(tsdf_vol, 0.0)
     verts_w, colors = fo.mesh_postprocess(verts, color_vol, voxel_size, vol_origin)
     return verts_w, faces, norms, colors
+
+
+def mc_face_corners():
+    """Corner ids (Lewiner numbering) of the six cube faces in mc_oracle.c's own face order."""
+    out = np.zeros((6, 4), np.int32)
+    for f in range(6):
+        lib().hvo_mc_face_corners(ctypes.c_int(f), _p(out[f]))
+    return out
+
+
+def mc_tiling(config, pmask, tunnel):
+    """Triangles (edge ids, 12 = centre vertex) and sub-case label mc_oracle.c derives for a (configuration, face
+    resolution, tunnel) triple; ``pmask`` bit f = "the positive corners of oracle face f are joined".  None if the
+    triple is not valid (a tunnel where Lewiner's decision tree has no interior test)."""
+    tris = np.zeros(48, np.uint8)
+    label = ctypes.create_string_buffer(32)
+    L = lib()
+    L.hvo_mc_tiling.restype = ctypes.c_int
+    n = L.hvo_mc_tiling(ctypes.c_int(int(config)), ctypes.c_int(int(pmask)), ctypes.c_int(int(bool(tunnel))), _p(tris), label)
+    if n < 0:
+        return None
+    return tris[:3 * n].reshape(n, 3).copy(), label.value.decode()
+
+
+def mc_cube(values):
+    """Decision of mc_oracle.c for one cube from its eight corner values (Lewiner corner order, level already
+    subtracted): (configuration, pmask, tunnel, triangles, label)."""
+    v = np.ascontiguousarray(values, dtype=np.float64)
+    assert v.shape == (8,)
+    tris = np.zeros(48, np.uint8)
+    label = ctypes.create_string_buffer(32)
+    cfg, pm, tn = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    L = lib()
+    L.hvo_mc_cube.restype = ctypes.c_int
+    n = L.hvo_mc_cube(_p(v), ctypes.byref(cfg), ctypes.byref(pm), ctypes.byref(tn), _p(tris), label)
+    assert n >= 0
+    return cfg.value, pm.value, tn.value, tris[:3 * n].reshape(n, 3).copy(), label.value.decode()

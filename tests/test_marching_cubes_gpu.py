@@ -59,6 +59,36 @@ def test_noise_volume_exercises_every_ambiguous_case(shape, c_oracle):
     _compare(rng.standard_normal(shape).astype(np.float32), 0.0, c_oracle)
 
 
+def test_every_reachable_lewiner_subcase_gives_the_app_c_triangle_count(c_oracle):
+    """Crafted corner values for every (case, sub-case) of Lewiner's decision tree that values can reach, laid out as
+    2x2x2 blocks along z: per-cube triangle counts equal SURVEY.md App. C's inventory (the only reference-derived
+    numbers on this box), and the GPU mesh equals the oracle's, triangle for triangle."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import gen_mc_tables as gen
+    from test_mc_tables import APP_C_TRIANGLES, _random_cubes
+    per_label = {}
+    for v in _random_cubes(60000, 11):
+        label = gen.decide(v)[3]
+        if label != "0" and len(per_label.setdefault(label, [])) < 6:
+            per_label[label].append(v.astype(np.float32))
+    assert set(APP_C_TRIANGLES) - set(per_label) <= {"12.1.2", "13.5.2", "7.4.2"}  # see tests/test_mc_tables.py
+    blocks = [(label, v) for label in sorted(per_label) for v in per_label[label]]
+    vol = np.zeros((2, 2, 2 * len(blocks)), np.float32)
+    for b, (label, v) in enumerate(blocks):
+        for i in range(8):
+            o = gen.CORNERS[i]
+            vol[o[0], o[1], 2 * b + o[2]] = v[i]
+    _compare(vol, 0.0, c_oracle)
+    _, faces, _, _, _, cubes = c_oracle.marching_cubes(vol, 0.0, with_cubes=True)
+    per_cube = np.bincount(cubes, minlength=2 * len(blocks))
+    for b, (label, v) in enumerate(blocks):
+        # float32 storage can move a value across a decision boundary only if the float64 decision was a near-tie
+        if gen.decide(v.astype(np.float64))[3] == label:
+            assert per_cube[2 * b] == APP_C_TRIANGLES[label], (label, v)
+
+
 def test_nonzero_level_and_exact_zeros(c_oracle):
     rng = np.random.default_rng(3)
     vol = rng.integers(-3, 4, size=(17, 19, 40)).astype(np.float32)  # many voxels exactly on the level

@@ -93,8 +93,8 @@ def test_noise_volume_gives_a_closed_oriented_manifold(shape, seed, c_oracle):
     # every vertex sits on a lattice edge whose end points straddle the level
     frac = verts - np.floor(verts)
     on_axis = (frac > 0).sum(axis=1)
-    # (the 12-gon tilings add a vertex inside the cube -- Lewiner's "c-vertex": three fractional coordinates)
-    assert np.isin(on_axis, (0, 1, 3)).all() and (on_axis == 3).mean() < 0.02
+    # (tilings 6.1.2, 7.3, 10.2, 12.2, 13.3, 13.4 add a vertex inside the cube -- Lewiner's "c-vertex")
+    assert np.isin(on_axis, (0, 1, 3)).all() and (on_axis == 3).mean() < 0.05
     edge = on_axis <= 1
     verts, on_axis, frac = verts[edge], on_axis[edge], frac[edge]
     lo = np.floor(verts).astype(int)
