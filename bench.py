@@ -20,8 +20,15 @@ For N > 1 GPUs the volume is z-slab sharded (one 512^3 slab per GPU: weak scalin
              over its CUDA-event launch duration, against MEASURED_PEAKS.json's HBM copy bandwidth.
 ``cpu_baseline``: the oracle's C/OpenMP port of the reference's CPU path (oracle/tsdf_oracle.c) on the host cores.
 
-``--impl reference`` times that same CPU port (the reference is Python/numba and cannot be compiled into
-``oracle/_ref``; the port is several times faster than the reference's numpy path, so the ratio is conservative).
+``parity_checked``: after the timed loops, random blocks of the volume the loops produced are compared with the oracle
+             run over the same frame sequence (tsdf <= 1e-5, weight and colour bit-exact).
+``build``   : hash compiled into the library that ran vs hash of the sources lying next to it.
+
+``--impl reference`` times the reference's CPU path.  The reference is Python (numpy + numba): it cannot be compiled
+into ``oracle/_ref`` and ``/root/reference`` does not travel, so the arm runs ``oracle/fusion_numba.py`` -- a restatement
+with the reference's own memory and loop structure, measured at 0.99-1.06x the real reference's speed in the build
+container (profiles/r02_reference_speed.json) -- when numba imports on the box, else the C/OpenMP port (42-69x faster
+than the reference).  The line says which one ran.
 """
 from __future__ import annotations
 
@@ -32,6 +39,10 @@ import subprocess
 import sys
 import threading
 import time
+
+if "reference" in sys.argv:  # the reference arm uses every host thread (torchrun exports OMP_NUM_THREADS=1 to all ranks)
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS", "NUMBA_NUM_THREADS"):
+        os.environ[_v] = str(os.cpu_count() or 1)
 
 import numpy as np
 
@@ -96,6 +107,31 @@ def make_frames(config, variant, n, dim=None):
         return [_gen_frame(j) for j in jobs]
     with mp.get_context("fork").Pool(procs) as pool:
         return pool.map(_gen_frame, jobs)
+
+
+def config_dict(args, sc, dim, n_gpus, n_distinct):
+    """`config` of the JSON line -- the same for both arms (what differs, the reference arm's bounded sample, is
+    described in its `cpu_baseline.sample`)."""
+    return {
+        "workload": f"{args.config}: {'x'.join(map(str, dim))} TSDF @ {sc.voxel_size * 100:g} cm, {sc.W}x{sc.H} synthetic "
+                    f"frames, scene={args.scene}, {args.batch} frames/step",
+        "voxels": int(np.prod(dim)), "frames_per_step": args.batch, "scene": args.scene,
+        "parallelism": "single GPU" if n_gpus == 1 else f"z-slab x{n_gpus}, NCCL frame broadcast",
+        "l2": "volume planes (12 B/voxel, >= 1.6 GB per GPU) are far larger than the 126 MB L2; no flush needed",
+        "distinct_frames": n_distinct,
+    }
+
+
+def global_dim(args, n_gpus):
+    from hive_b200 import synthetic
+    base_dim = synthetic.CONFIGS[args.config]["dim"]
+    if args.scaling == "weak":
+        return (base_dim[0], base_dim[1], base_dim[2] * n_gpus)  # one base volume per GPU along z
+    return tuple(base_dim)  # BASELINE configs C3 / C5: the named global volume, cut into N z-slabs
+
+
+def n_distinct_frames(args):
+    return max(2, min(args.distinct_frames, args.batch * (args.steps + args.warmup)))
 
 
 class ClockSampler:
@@ -167,6 +203,54 @@ def load_traffic():
         return None
 
 
+def reference_speed_record():
+    """What oracle/measure_reference_speed.py measured in the build container, where /root/reference exists."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_reference_speed.json")) as f:
+            rec = json.load(f)
+        return {"source": "profiles/r02_reference_speed.json (build container, real reference vs restatements, C1)",
+                "cores": rec["cores"], **{k: {m: v[m] for m in ("reference_numpy_numba", "restatement_numba",
+                                                                "c_port_openmp", "c_port_vs_reference",
+                                                                "numba_restatement_vs_reference")}
+                                          for k, v in rec["scenes"].items()}}
+    except Exception as e:
+        return {"error": str(e)}
+
+
+def host_cpu():
+    try:
+        with open("/proc/cpuinfo") as f:
+            model = f.read().split("model name")[1].split("\n")[0].strip(": \t")
+    except Exception:
+        model = "unknown"
+    return {"model": model, "logical_cores": os.cpu_count()}
+
+
+def numba_restatement_speed(variant, frames, n_sample=2):
+    """The reference-shaped numpy + numba restatement (oracle/fusion_numba.py) on a bounded sample: `n_sample` frames
+    into the central 256^3 voxels of the C2 volume (same 1 cm voxels, same frames)."""
+    try:
+        import numba
+        from oracle import fusion_numba
+    except Exception as e:
+        return {"numba_imported": False, "error": str(e)}
+    sc = _scene("C2", variant)
+    lo = sc.vol_bnds[:, 0] + 128 * sc.voxel_size
+    bnds = np.stack([lo, lo + (256 - 0.5) * sc.voxel_size], axis=1)
+    vol = fusion_numba.NumbaTSDFVolume(bnds, sc.voxel_size)
+    rgb, depth, pose = frames[0]
+    vol.integrate(rgb, depth, sc.K, pose, 1.0)  # numba JIT + page faults
+    t0 = time.perf_counter()
+    for i in range(n_sample):
+        rgb, depth, pose = frames[(i + 1) % len(frames)]
+        vol.integrate(rgb, depth, sc.K, pose, 1.0)
+    dt = time.perf_counter() - t0
+    return {"numba_imported": True, "numba": numba.__version__, "threads": numba.get_num_threads(),
+            "value": float(np.prod(vol._vol_dim)) * n_sample / dt, "unit": UNIT,
+            "sample": f"{n_sample} frames of C2/{variant} into the central 256^3 voxels through oracle/fusion_numba.py "
+                      f"(the reference's structure: (N,3) voxel table, numba prange kernels, numpy gather/scatter), {dt:.1f} s"}
+
+
 # ----------------------------------------------------------------------------------------------------------------------
 def cpu_baseline(config, variant, frames, n_sample, dim=None):
     """Oracle C port of fusion.py:260-303 on all host cores, bounded sample of the same workload."""
@@ -183,30 +267,18 @@ def cpu_baseline(config, variant, frames, n_sample, dim=None):
         rgb, depth, pose = frames[(i + 1) % len(frames)]
         vol.integrate(rgb, depth, sc.K, pose)
     dt = time.perf_counter() - t0
-    # the numpy restatement (the shape of the reference's own CPU path: whole-volume numpy temporaries, one core for most
-    # of it) on two frames of the 256^3 config -- the number closest to what a HIVE user without a GPU gets
-    numpy_port = None
-    try:
-        from oracle import fusion_oracle as fo
-        sc1 = _scene("C1", variant)
-        nv = fo.OracleTSDFVolume(sc1.vol_bnds.copy(), sc1.voxel_size)
-        nv.integrate(rgb, depth, sc1.K, pose)
-        t1 = time.perf_counter()
-        for i in range(2):
-            r2, d2, p2 = frames[(i + 1) % len(frames)]
-            nv.integrate(r2, d2, sc1.K, p2)
-        numpy_port = {"value": float(np.prod(nv._vol_dim)) * 2 / (time.perf_counter() - t1), "unit": UNIT,
-                      "sample": "2 frames into a 256^3 volume through oracle/fusion_oracle.py (numpy)"}
-        del nv
-    except Exception as e:  # the C port above is the baseline of record
-        numpy_port = {"error": str(e)}
-    return {"numpy_port": numpy_port, "value": n_vox * n_sample / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
+    return {"value": n_vox * n_sample / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
             "sample": f"{n_sample} frames of {config}/{variant} ({'x'.join(map(str, vol._vol_dim))} voxels, "
                       f"{depth.shape[1]}x{depth.shape[0]}) through oracle/tsdf_oracle.c (OpenMP), {dt:.1f} s",
-            "s_per_frame": dt / n_sample}
+            "s_per_frame": dt / n_sample, "host": host_cpu(),
+            # what a HIVE user without a GPU runs is far slower than this C port: the reference-shaped restatement
+            # measured here, and the real reference measured in the build container
+            "reference_shaped": numba_restatement_speed(variant, frames),
+            "port_vs_reference_speed": reference_speed_record()}
 
 
 def run_reference(args):
+    """The reference arm: the reference's CPU path on the host cores, one frame of the workload per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -216,37 +288,107 @@ def run_reference(args):
     n_distinct = min(args.distinct_frames, 8)
     frames = make_frames(args.config, args.scene, n_distinct)
     sc = _scene(args.config, args.scene)
-    vol = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    try:
+        import numba
+        from oracle import fusion_numba
+        numba_note = {"numba_imported": True, "numba": numba.__version__, "threads": numba.get_num_threads()}
+    except Exception as e:
+        fusion_numba, numba_note = None, {"numba_imported": False, "error": str(e)}
+
+    # the C/OpenMP port on the full volume, a few frames: context for the headline below
+    cvol = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+    n_vox_full = int(np.prod(cvol._vol_dim))
+    cvol.integrate(frames[0][0], frames[0][1], sc.K, frames[0][2])
+    t0 = time.perf_counter()
+    for i in range(4):
+        rgb, depth, pose = frames[(i + 1) % len(frames)]
+        cvol.integrate(rgb, depth, sc.K, pose)
+    c_port = {"value": n_vox_full * 4 / (time.perf_counter() - t0), "unit": UNIT, "cores": c_oracle.num_threads(),
+              "sample": f"4 frames into the full {'x'.join(map(str, cvol._vol_dim))} volume through oracle/tsdf_oracle.c"}
+    del cvol
+
+    if fusion_numba is not None:
+        # bounded sample: the central 256^3 voxels of the volume (the reference's CPU mode needs ~200 B/voxel and
+        # ~4 s per frame for them); same voxel size, same frames, one frame per step
+        sub = 256 if args.steps + args.warmup <= 40 else 160
+        dim0 = np.array(sc.dim)
+        sub_dim = np.minimum(dim0, sub)
+        lo = sc.vol_bnds[:, 0] + ((dim0 - sub_dim) // 2) * sc.voxel_size
+        bnds = np.stack([lo, lo + (sub_dim - 0.5) * sc.voxel_size], axis=1)
+        vol = fusion_numba.NumbaTSDFVolume(bnds, sc.voxel_size)
+        vol.integrate(frames[0][0], frames[0][1], sc.K, frames[0][2], 1.0)  # numba JIT, excluded like any warm-up
+        what = (f"oracle/fusion_numba.py: the reference's CPU path restated with its own structure (fusion.py:166-215, "
+                f"260-303: (N,3) voxel table, three numba prange kernels, numpy gather/scatter), "
+                f"{numba_note['threads']} numba threads; 0.99-1.06x the real reference's speed where both can run")
+        cores = int(numba_note["threads"])
+    else:
+        vol = c_oracle.COracleTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size)
+        what = f"oracle/tsdf_oracle.c, the C/OpenMP port of fusion.py:260-303 (numba does not import on this box)"
+        cores = c_oracle.num_threads()
     n_vox = int(np.prod(vol._vol_dim))
-    for i in range(args.warmup):  # one frame per step: a bounded sample of the 30-frame step of the GPU arm
+    for i in range(args.warmup):
         rgb, depth, pose = frames[i % len(frames)]
-        vol.integrate(rgb, depth, sc.K, pose)
+        vol.integrate(rgb, depth, sc.K, pose, 1.0)
     t0 = time.perf_counter()
     for i in range(args.steps):
         rgb, depth, pose = frames[(args.warmup + i) % len(frames)]
-        vol.integrate(rgb, depth, sc.K, pose)
+        vol.integrate(rgb, depth, sc.K, pose, 1.0)
     dt = time.perf_counter() - t0
     value = n_vox * args.steps / dt
-    cores = c_oracle.num_threads()
-    sample = (f"each step = 1 frame (of the GPU arm's {args.batch}-frame step) of {args.config}/{args.scene} through "
-              f"oracle/tsdf_oracle.c, the C/OpenMP port of fusion.py:260-303, {cores} threads"
-              + (f"; one 512^3-class slab of the {args.gpus}-slab volume (voxel-updates/s is size-normalised)"
-                 if args.gpus > 1 else ""))
+    sample = (f"each step = 1 frame (of the GPU arm's {args.batch}-frame step) of {args.config}/{args.scene} into "
+              f"{'x'.join(map(str, vol._vol_dim))} voxels (voxel-updates/s is size-normalised) through {what}")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64/f32", "data": "synthetic",
-        "config": {"workload": f"{args.config} {'x'.join(map(str, vol._vol_dim))} TSDF, 640x480 frames, scene={args.scene}"},
+        "vs_baseline": None, "dtype": "f64 projection / f32 state", "data": "synthetic",
+        "config": config_dict(args, sc, global_dim(args, max(args.gpus, 1)), max(args.gpus, 1), n_distinct_frames(args)),
         "frames_per_s": args.steps / dt,
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "host": host_cpu(), **numba_note},
+        "c_port": c_port,
+        "port_vs_reference_speed": reference_speed_record(),
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
 
 
+def parity_check(local, sc, frames, sequence, n_blocks=8, block=(16, 16, 64)):
+    """Random blocks of the volume the timed loops left behind against the oracle (oracle/tsdf_oracle.c over the blocks'
+    slices of the global world tables, the whole frame sequence, obs_weight 1).  Runs after the timing, on rank 0."""
+    from oracle import c_oracle
+    from hive_b200.fusion import _world_table
+    c_oracle.build()
+    X, Y, Z = (int(d) for d in local._local_dim)
+    bx, by, bz = (min(b, d) for b, d in zip(block, (X, Y, Z)))
+    rng = np.random.default_rng(1)
+    seen = (local._weight_vol_gpu[::bx, ::by, :Z:bz] > 0).nonzero().cpu().numpy() * np.array([bx, by, bz])
+    if len(seen) == 0:
+        return {"parity_checked": False, "why": "no voxel was updated"}
+    picks = seen[rng.choice(len(seen), min(n_blocks, len(seen)), replace=False)]
+    picks = np.minimum(picks, np.array([X - bx, Y - by, Z - bz]))
+    tables = [_world_table(local._vol_origin[0], local._voxel_size, X), _world_table(local._vol_origin[1], local._voxel_size, Y),
+              _world_table(local._vol_origin[2], local._voxel_size, Z, local._z0)]
+    prepared = {i: c_oracle.prepare_frame(frames[i][0], frames[i][1], sc.K, frames[i][2]) for i in sorted(set(sequence))}
+    worst, ok_w, ok_c, n_vox, n_upd = 0.0, True, True, 0, 0
+    for x0, y0, z0 in picks:
+        orc = c_oracle.COracleBlock([tables[0][x0:x0 + bx], tables[1][y0:y0 + by], tables[2][z0:z0 + bz]], local._voxel_size)
+        for i in sequence:
+            orc.integrate_prepared(prepared[i])
+        sl = (slice(x0, x0 + bx), slice(y0, y0 + by), slice(z0, z0 + bz))
+        worst = max(worst, float(np.abs(local._tsdf_vol_gpu[sl].cpu().numpy() - orc._tsdf_vol_cpu).max()))
+        ok_w &= bool(np.array_equal(local._weight_vol_gpu[sl].cpu().numpy(), orc._weight_vol_cpu))
+        ok_c &= bool(np.array_equal(local._color_vol_gpu[sl].cpu().numpy(), orc._color_vol_cpu))
+        n_vox += bx * by * bz
+        n_upd += int((orc._weight_vol_cpu > 0).sum())
+    passed = worst <= 1e-5 and ok_w and ok_c
+    return {"parity_checked": bool(passed), "voxels_compared": n_vox, "of_which_updated": n_upd,
+            "frames_integrated": len(sequence), "max_abs_tsdf_err": worst, "weight_bit_exact": ok_w,
+            "colour_bit_exact": ok_c, "blocks": f"{len(picks)} random {bx}x{by}x{bz} blocks with weight > 0",
+            "oracle": "oracle/tsdf_oracle.c (fusion.py:260-303) over the same frame sequence"}
+
 
 # ----------------------------------------------------------------------------------------------------------------------
-def measure_mesh(vol, torch, peak, repeats=5):
+def measure_mesh(vol, torch, peak, repeats=5, cpu=True):
     """get_mesh device time (count + scan + host read of the two totals + emit + vertices), median of `repeats`."""
     from hive_b200 import marching_cubes as mc
     times, mesh = [], None
@@ -271,10 +413,30 @@ def measure_mesh(vol, torch, peak, repeats=5):
         verts, faces, norms, colors = vol.get_mesh()
         e2e.append((time.perf_counter() - t0) * 1000.0)
     e2e_ms = float(np.median(e2e[1:]))
-    return {"mc_ms": ms, "vertices": V, "triangles": F, "voxels": n, "algorithmic_bytes": algo,
-            "achieved_gbs": algo / (ms / 1e3) / 1e9, "roofline_frac": algo / (ms / 1e3) / 1e9 / peak,
-            "get_mesh_e2e_ms": e2e_ms, "d2h_bytes": int(verts.nbytes + faces.nbytes + norms.nbytes + colors.nbytes),
-            "scene": "room", "launches_per_extraction": 8}
+    res = {"mc_ms": ms, "vertices": V, "triangles": F, "voxels": n, "algorithmic_bytes": algo,
+           "achieved_gbs": algo / (ms / 1e3) / 1e9, "roofline_frac": algo / (ms / 1e3) / 1e9 / peak,
+           "get_mesh_e2e_ms": e2e_ms, "d2h_bytes": int(verts.nbytes + faces.nbytes + norms.nbytes + colors.nbytes),
+           "scene": "room", "launches_per_extraction": mc.LAUNCHES_PER_EXTRACTION}
+    if cpu:
+        # the C restatement of the skimage call, single thread, on the same volume -- and the checker
+        from oracle import c_oracle, fusion_oracle as fo
+        c_oracle.build()
+        tsdf, color = vol.get_volume()
+        t0 = time.perf_counter()
+        ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
+        cpu_s = time.perf_counter() - t0
+        order = np.argsort(ok, kind="stable")
+        rank = np.empty_like(order)
+        rank[order] = np.arange(len(order))
+        ow, oc = fo.mesh_postprocess(ov[order], color, vol._voxel_size, vol._vol_origin)
+        same = bool(faces.shape == of.shape and np.array_equal(faces, rank[of].astype(np.int32))
+                    and np.array_equal(verts, ow) and np.array_equal(colors, oc))
+        res["cpu_baseline"] = {"ms": cpu_s * 1e3, "cores": 1, "kind": "port", "host": host_cpu(),
+                               "what": "oracle/mc_oracle.c: serial C restatement of skimage.measure.marching_cubes "
+                                       "(fusion.py:338) on the same volume; skimage itself is on neither box",
+                               "speedup_device": cpu_s * 1e3 / ms, "speedup_e2e": cpu_s * 1e3 / e2e_ms}
+        res["parity_checked"] = same
+    return res
 
 
 def measure_mesh_sharded(vol, world, rank, dist, torch, repeats=3):
@@ -402,9 +564,41 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
         del batch
     e2e_s = float(np.median(e2e[1:]))
     e2e_fps = _sum_over_ranks(int(B / e2e_s), world, dist, torch)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # the reference's per-frame code (point_cloud_from_depth + scipy Delaunay + _filter_faces,
+        # hive/pipeline.py:386-409) single thread on 20 frames, and through a ThreadPool over all cores as
+        # hive/pipeline.py:491 runs it
+        from multiprocessing.pool import ThreadPool
+        from oracle import d2m_oracle as d2m
+
+        def one(i):
+            w2c = poses[i]
+            return d2m.frame_mesh(depths[i], masks[i] > 0, sc.K, w2c[:3, :3], w2c[:3, 3:])[0].shape[0]
+
+        one(0)
+        n1 = min(20, B)
+        t0 = time.perf_counter()
+        for i in range(n1):
+            one(i)
+        single = n1 / (time.perf_counter() - t0)
+        threads = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        with ThreadPool(threads) as pool:
+            pool.map(one, range(B))
+        pooled = B / (time.perf_counter() - t0)
+        cpu = {"frames_per_s_single_thread": single, "frames_per_s_threadpool": pooled, "threads": threads,
+               "kind": "port", "host": host_cpu(), "frames": [n1, B],
+               "what": "oracle/d2m_oracle.py = hive.geometric.point_cloud_from_depth + scipy.spatial.Delaunay + "
+                       "Pipeline._filter_faces (hive/pipeline.py:386-409), ThreadPool as hive/pipeline.py:491"}
+    algo_survey = 5.0 * H * W * B + 24.0 * V + 12.0 * F  # without the optional (u, v, depth) outputs
     return {"frames_per_s": world * B / (ms / 1e3), "ms_per_batch": ms, "frames_per_batch_per_gpu": B,
-            "vertices": V, "faces": F, "achieved_gbs": algo / (ms / 1e3) / 1e9,
-            "roofline_frac": algo / (ms / 1e3) / 1e9 / peak, "e2e_frames_per_s": float(e2e_fps),
+            "vertices": V, "faces": F, "achieved_gbs": algo_survey / (ms / 1e3) / 1e9,
+            "roofline_frac": algo_survey / (ms / 1e3) / 1e9 / peak,
+            "roofline_frac_with_points2d": algo / (ms / 1e3) / 1e9 / peak,
+            "roofline_note": "roofline_frac uses SURVEY 8(d)'s 5*H*W + 24*V + 12*F; the kernel also writes 12 B/vertex of "
+                             "(u, v, depth) for _filter_faces' callers, counted in roofline_frac_with_points2d",
+            "cpu_baseline": cpu, "e2e_frames_per_s": float(e2e_fps),
             "h2d_bytes": int(depths.nbytes + masks.nbytes), "d2h_bytes": int(hv.nbytes + hf.nbytes + hp.nbytes + hd.nbytes),
             "workload": f"{B} frames/GPU of {W}x{H}, instance masks of the room scene, frame-partitioned"}
 
@@ -417,13 +611,8 @@ def run_ours(args):
     n_gpus = max(world, 1)
     base_cfg = args.config
 
-    from hive_b200 import synthetic
-    base_dim = synthetic.CONFIGS[base_cfg]["dim"]
-    if args.scaling == "weak":
-        dim = (base_dim[0], base_dim[1], base_dim[2] * n_gpus)  # one base volume per GPU along z
-    else:
-        dim = tuple(base_dim)  # BASELINE configs C3 / C5: the named global volume, cut into N z-slabs
-    n_distinct = max(2, min(args.distinct_frames, args.batch * (args.steps + args.warmup)))
+    dim = global_dim(args, n_gpus)
+    n_distinct = n_distinct_frames(args)
 
     # Host-side synthetic data first (fork pool), CUDA afterwards.  Only rank 0 owns frames; others receive broadcasts.
     scenes = [args.scene] + ([] if args.no_room or args.scene == "room" else ["room"])
@@ -471,14 +660,7 @@ def run_ours(args):
         "metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64 projection / f32 state", "data": "synthetic",
-        "config": {
-            "workload": f"{base_cfg}: {'x'.join(map(str, dim))} TSDF @ {sc.voxel_size * 100:g} cm, {W}x{H} synthetic frames, "
-                        f"scene={args.scene}, {args.batch} frames/step",
-            "voxels": int(np.prod(dim)), "frames_per_step": args.batch, "scene": args.scene,
-            "parallelism": "single GPU" if n_gpus == 1 else f"z-slab x{n_gpus}, NCCL frame broadcast",
-            "l2": "volume planes (12 B/voxel, >= 1.6 GB per GPU) are far larger than the 126 MB L2; no flush needed",
-            "distinct_frames": n_distinct,
-        },
+        "config": config_dict(args, sc, dim, n_gpus, n_distinct),
         "frames_per_s": main["frames_per_s"],
         "updated_fraction": main["updated_fraction"],
         "e2e": main["e2e"],
@@ -493,6 +675,12 @@ def run_ours(args):
             "frac_of_8000_spec": main["achieved_gbs"] / 8000.0,
         },
     }
+    from hive_b200 import _lib as hv_lib
+    src_hash = hv_build.source_hash()
+    out["build"] = {"binary_id": hv_lib.build_id(), "source_hash": src_hash, "binary_matches_sources": hv_lib.build_id() == src_hash,
+                    "library": os.path.relpath(hv_lib.LIB_PATH, ROOT)}
+    out["parity_checked"] = bool(main["parity"].get("parity_checked", False))
+    out["parity"] = main["parity"]
     tr = load_traffic()
     if tr is not None:
         out["roofline"]["traffic"] = tr.get("dram_bytes_per_launch")
@@ -526,8 +714,11 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     dev_frames = vol.upload_frames(frames, sc.K)  # rank 0 uploads; other ranks get an empty receiver of the same shape
     n_f = dev_frames.num_frames
 
+    sequence = []  # every frame integrated into this volume, in order (for the parity check after the timing)
+
     def step_device(s):
         idx = [(s * B + j) % n_f for j in range(B)]
+        sequence.extend(idx)
         vol.integrate_batch_device(dev_frames, idx)
 
     vol.count_updates(False)
@@ -561,6 +752,7 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     # ---- end-to-end path: host numpy frames through TSDFVolume.integrate -------------------------------------------
     vol.count_updates(True)
     for s in range(min(Wm, 3)):
+        sequence.extend((s * B + j) % n_f for j in range(B))
         vol.integrate_batch_host(frames, [(s * B + j) % n_f for j in range(B)], sc.K)
     vol.read_update_counter()
     _barrier(world, dist, torch)
@@ -568,6 +760,7 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     t0 = time.perf_counter()
     e2.record()
     for s in range(K):
+        sequence.extend(((Wm + s) * B + j) % n_f for j in range(B))
         vol.integrate_batch_host(frames, [((Wm + s) * B + j) % n_f for j in range(B)], sc.K)
         vol.read_update_counter_pipelined()  # D2H read of the step's result (async snapshot, consumed one step later)
     vol.read_update_counter()  # drains the pipeline: the last step's result
@@ -578,9 +771,13 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     ms_e2e = _max_over_ranks(max(e2.elapsed_time(e3), wall_ms), world, dist, torch)
     e2e_value = n_vox_global * n_frames / (ms_e2e / 1000.0)
 
+    parity = {"parity_checked": False, "why": "not rank 0"}
+    if rank == 0:
+        parity = parity_check(vol.local, sc, frames, sequence)
+
     mesh = None
     if not args.no_mesh and variant == "room" and world == 1:
-        mesh = measure_mesh(vol.local, torch, peak)
+        mesh = measure_mesh(vol.local, torch, peak, cpu=not args.no_cpu_baseline)
     elif not args.no_mesh and variant == "room":
         mesh = measure_mesh_sharded(vol, world, rank, dist, torch)
 
@@ -588,7 +785,7 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
         "value": value, "ms_per_step": ms / K, "frames_per_s": n_frames / (ms / 1000.0),
         "updated_fraction": total_updates / float(n_vox_global * n_frames),
         "achieved_gbs": achieved_gbs, "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_launch_ms,
-        "gpu_launches": launches, "clocks": clocks, "H": H, "W": W, "mesh": mesh,
+        "gpu_launches": launches, "clocks": clocks, "H": H, "W": W, "mesh": mesh, "parity": parity,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * (H * W * 7 + 12 * 8 + 16),
                 "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e / K,
                 "api": "TSDFVolume.integrate(color_im, depth_im, cam_intr, cam_pose) with host numpy buffers"},

@@ -27,6 +27,7 @@ c_void_p, c_int, c_int64, c_double, c_float = (ctypes.c_void_p, ctypes.c_int, ct
 # name -> argtypes; every function returns int.  Kept in step with include/hive_b200.h (tests/test_abi.py checks it).
 SIGNATURES = {
     "hv_version": [],
+    "hv_build_id": [ctypes.c_char_p, c_int],
     "hv_last_error": [ctypes.c_char_p, c_int],
     "hv_sm_count": [],
     "hv_pack_frame": [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p],
@@ -88,6 +89,13 @@ def load():
                 fn.restype = c_int
             _lib = lib
     return _lib
+
+
+def build_id() -> str:
+    """Hash of the sources the loaded library was compiled from (compare with ``build.source_hash()``)."""
+    buf = ctypes.create_string_buffer(64)
+    load().hv_build_id(buf, 64)
+    return buf.value.decode()
 
 
 def last_error() -> str:

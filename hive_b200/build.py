@@ -6,6 +6,7 @@ snapshot.  Usage: ``python -m hive_b200.build [--force] [--verbose]``.
 from __future__ import annotations
 
 import glob
+import hashlib
 import os
 import shutil
 import subprocess
@@ -35,24 +36,49 @@ def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
+def _inputs():
+    return sources() + sorted(glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.h")) +
+                              glob.glob(os.path.join(HERE, "..", "include", "*.h")))
+
+
+def source_hash() -> str:
+    """sha256 (first 16 hex digits) over the names and contents of every file the library is compiled from, plus the
+    compiler flags.  The same string is compiled into the library (``hv_build_id``), so a binary can be attributed to
+    the sources that are lying next to it -- bench.py prints both."""
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for path in _inputs():
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def built_id() -> str | None:
+    """Build id of the library on disk (sidecar written next to it by ``build``), None if there is none."""
+    try:
+        with open(LIB_PATH + ".id") as f:
+            return f.read().strip()
+    except OSError:
+        return None
+
+
 def is_stale() -> bool:
-    if not os.path.exists(LIB_PATH):
-        return True
-    t = os.path.getmtime(LIB_PATH)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(CSRC, "*.h")) + \
-        glob.glob(os.path.join(HERE, "..", "include", "*.h"))
-    return any(os.path.getmtime(d) > t for d in deps)
+    return not os.path.exists(LIB_PATH) or built_id() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB_PATH
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + sources()
+    bid = source_hash()
+    cmd = [_nvcc()] + NVCC_FLAGS + [f'-DHV_BUILD_ID="{bid}"'] + (["-Xptxas", "-v"] if verbose else []) + \
+        ["-o", LIB_PATH] + sources()
     res = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed building libhive_b200.so")
+    with open(LIB_PATH + ".id", "w") as f:
+        f.write(bid + "\n")
     return LIB_PATH
 
 

@@ -42,6 +42,20 @@ const DeviceInfo& device_info() {
 
 extern "C" int hv_version(void) { return HV_VERSION; }
 
+#ifndef HV_BUILD_ID
+#define HV_BUILD_ID "unknown"
+#endif
+extern "C" int hv_build_id(char* buf, int n) {
+    static const char id[] = HV_BUILD_ID;
+    const int len = (int)sizeof(id) - 1;
+    if (buf && n > 0) {
+        const int c = len < n - 1 ? len : n - 1;
+        memcpy(buf, id, c);
+        buf[c] = 0;
+    }
+    return len;
+}
+
 extern "C" int hv_last_error(char* buf, int n) {
     int len = (int)strlen(hv::g_err);
     if (buf && n > 0) {

@@ -227,9 +227,11 @@ class TSDFVolume:
             st["consumed"][slot] = ev
 
     def _weights_flag(self, obs_weight) -> int:
-        """HV_INTEGRATE_INTEGER_WEIGHTS while every weight ever integrated was a small positive integer."""
+        """HV_INTEGRATE_INTEGER_WEIGHTS while every weight ever integrated was a small positive integer and the
+        accumulated weight keeps ``w * 255`` exactly representable in float32 (w <= 65793): only
+        then does the fast path's single-rounding blend equal the reference's mul / mul / add / div bit for bit."""
         ow = float(obs_weight)
-        if self._integer_weights and ow >= 1.0 and ow == int(ow) and self._weight_sum + ow < 2 ** 20:
+        if self._integer_weights and ow >= 1.0 and ow == int(ow) and self._weight_sum + ow <= 65793:
             self._weight_sum += ow
             return 1
         self._integer_weights = False

@@ -18,6 +18,10 @@ from . import _lib
 from . import _xfer
 
 
+#: kernels launched by one extraction (init, sign, count, scan x3, emit, vertex); bench.py reports it
+LAUNCHES_PER_EXTRACTION = 8
+
+
 def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else None
 

@@ -29,6 +29,9 @@ extern "C" {
 #define HV_E_CAPACITY (-5)    /* caller-provided output / scratch buffer too small        -> RuntimeError */
 
 int hv_version(void);
+/* Copies the build id (hash of the sources and flags the library was compiled from, hive_b200/build.py:source_hash)
+ * into buf; returns its length. */
+int hv_build_id(char* buf, int n);
 /* Copies the calling thread's last error text into buf (NUL-terminated, at most n bytes); returns its length. */
 int hv_last_error(char* buf, int n);
 /* Number of SMs of the current device (grid sizing is in multiples of it); <0 on error. */

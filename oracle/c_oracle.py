@@ -65,12 +65,12 @@ class COracleTSDFVolume:
         self.last_updated = 0
 
     def integrate(self, color_im, depth_im, cam_intr, cam_pose, obs_weight=1.0):
-        H, W = depth_im.shape
-        folded = np.ascontiguousarray(fo.fold_color(color_im), dtype=np.float32)
-        depth = np.ascontiguousarray(depth_im, dtype=np.float64)  # as given: the CPU path keeps depth_im's precision
-        w2c = np.ascontiguousarray(np.linalg.inv(np.asarray(cam_pose, dtype=np.float64))[:3, :])
-        k = np.asarray(cam_intr).astype(np.float32)
-        intr = np.array([k[0, 0], k[1, 1], k[0, 2], k[1, 2]], dtype=np.float32)
+        self.integrate_prepared(prepare_frame(color_im, depth_im, cam_intr, cam_pose), obs_weight)
+
+    def integrate_prepared(self, frame, obs_weight=1.0):
+        """``frame`` = prepare_frame(...): lets a caller that integrates the same frames into many volumes (the
+        block-sampled parity checks) pay the colour fold and the pose inverse once."""
+        folded, depth, w2c, intr, H, W = frame
         X, Y, Z = (int(d) for d in self._vol_dim)
         wx, wy, wz = self._tables
         self.last_updated = int(lib().hvo_integrate(
@@ -82,6 +82,34 @@ class COracleTSDFVolume:
 
     def get_volume(self):
         return self._tsdf_vol_cpu, self._color_vol_cpu
+
+
+def prepare_frame(color_im, depth_im, cam_intr, cam_pose):
+    """Per-frame inputs of hvo_integrate: folded colour (fusion.py:231-232), depth as given (the CPU path keeps
+    depth_im's precision), inv(cam_pose)[:3] (fusion.py:263), float32 intrinsics (fusion.py:196)."""
+    H, W = depth_im.shape
+    folded = np.ascontiguousarray(fo.fold_color(color_im), dtype=np.float32)
+    depth = np.ascontiguousarray(depth_im, dtype=np.float64)
+    w2c = np.ascontiguousarray(np.linalg.inv(np.asarray(cam_pose, dtype=np.float64))[:3, :])
+    k = np.asarray(cam_intr).astype(np.float32)
+    intr = np.array([k[0, 0], k[1, 1], k[0, 2], k[1, 2]], dtype=np.float32)
+    return folded, depth, w2c, intr, H, W
+
+
+class COracleBlock(COracleTSDFVolume):
+    """A box of a larger volume: the caller passes the box's slices of the GLOBAL world-coordinate tables
+    (float32(float64(origin) + voxel_size * global_index), fusion.py:183-188), so the oracle sees exactly the voxels
+    the product holds at those indices -- how volumes too large for the host (2048^3) are checked block by block."""
+
+    def __init__(self, tables, voxel_size):
+        self._tables = tuple(np.ascontiguousarray(t, dtype=np.float32) for t in tables)
+        self._vol_dim = np.array([len(t) for t in self._tables])
+        self._voxel_size = float(voxel_size)
+        self._trunc_margin = 5 * self._voxel_size
+        self._tsdf_vol_cpu = np.ones(self._vol_dim, dtype=np.float32)
+        self._weight_vol_cpu = np.zeros(self._vol_dim, dtype=np.float32)
+        self._color_vol_cpu = np.zeros(self._vol_dim, dtype=np.float32)
+        self.last_updated = 0
 
 
 def marching_cubes(volume, level=0.0, with_keys=False, with_cubes=False):

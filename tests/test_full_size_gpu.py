@@ -1,12 +1,14 @@
-"""BASELINE config C2 at full size (512^3 voxels, 640x480 frames): too large for the oracle to finish in seconds, so the
-CUDA path is checked through size-independent properties of the domain (task statement, parity rule 3):
+"""Parity at the sizes the benchmark numbers are quoted on (BASELINE.json configs C2, C3, C5).
 
-* integrate: all kernel variants agree (weight/colour bit-identical), integrating the same observation twice leaves
-  the running mean where it was and doubles the weight, untouched voxels keep their initial state, the update counter
-  equals the number of voxels whose weight changed;
-* marching cubes: one vertex per sign-changing lattice edge (counted independently with numpy), every triangle edge is
-  used by at most two triangles and by exactly two away from the volume border, vertex colours equal the nearest
-  voxel's unpacked colour.
+* C2 in full -- 512^3 voxels, 640x480 frames, `room` and `dense` scenes -- against the C oracle
+  (oracle/tsdf_oracle.c restating fusion.py:260-303; 0.2 s per frame on the box's host cores): tsdf <= 1e-5,
+  weight and colour bit-exact, update counts equal.
+* C3-shaped frames (1920x1440, Kinect intrinsics x 3) and C5-shaped frames (1920x1080, 90 degree field of view) at
+  their voxel sizes (5 mm, 2.5 mm) into a sub-volume the host can hold: same gates.
+* the 2048^3 volume itself (103 GB of voxel state on one B200; 64-bit voxel indexing): the oracle cannot hold it
+  (SURVEY.md hard part 4), so it is run over random 64^3 blocks with the blocks' slices of the global world-coordinate
+  tables and compared with the same blocks of the device planes.
+* size-independent properties at C2: idempotence of a repeated observation, untouched voxels, manifoldness of the mesh.
 """
 import numpy as np
 import pytest
@@ -14,6 +16,104 @@ import pytest
 from hive_b200.synthetic import Scene
 
 pytestmark = pytest.mark.gpu
+
+
+def _assert_planes(gpu_tsdf, gpu_weight, gpu_color, orc, what):
+    err = float(np.abs(gpu_tsdf - orc._tsdf_vol_cpu).max())
+    assert err <= 1e-5, f"{what}: tsdf differs by {err}"
+    assert np.array_equal(gpu_weight, orc._weight_vol_cpu), f"{what}: weight plane differs"
+    assert np.array_equal(gpu_color, orc._color_vol_cpu), f"{what}: colour plane differs"
+
+
+@pytest.mark.parametrize("variant", ["room", "dense"])
+def test_c2_full_size_equals_the_oracle(variant, c_oracle):
+    from hive_b200.fusion import TSDFVolume
+    c_oracle.use_all_host_threads()
+    scene = Scene("C2", variant)
+    gpu = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    assert tuple(gpu._vol_dim) == (512, 512, 512)
+    gpu.count_updates = True
+    orc = c_oracle.COracleTSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    updated = 0
+    for i, w in ((0, 1.0), (7, 1.0), (13, 2.0)):
+        fr = scene.frame(i)
+        gpu.integrate(fr.rgb, fr.depth, scene.K, fr.pose, obs_weight=w)
+        orc.integrate(fr.rgb, fr.depth, scene.K, fr.pose, obs_weight=w)
+        updated += orc.last_updated
+    assert gpu.num_updated() == updated > 10_000_000
+    tsdf, color = gpu.get_volume()
+    _assert_planes(tsdf, gpu.get_weight_volume(), color, orc, f"C2/{variant}")
+
+
+def _sub_volume(config, lo, dims):
+    """Bounds of a `dims`-voxel box of the named config's voxel size whose lower corner is `lo`."""
+    scene = Scene(config, "room")
+    lo = np.asarray(lo, dtype=np.float64)
+    hi = lo + (np.asarray(dims) - 0.5) * scene.voxel_size
+    return scene, np.stack([lo, hi], axis=1)
+
+
+@pytest.mark.parametrize("config,lo,dims", [
+    ("C3", (-0.6, -1.3, 3.3), (320, 288, 352)),    # 1920x1440 frames, 5 mm voxels: a sphere and the wall behind it
+    ("C5", (0.90, 0.62, 2.25), (352, 320, 384)),   # 1920x1080 frames, 2.5 mm voxels
+])
+def test_c3_and_c5_shaped_frames_equal_the_oracle(config, lo, dims, c_oracle):
+    from hive_b200.fusion import TSDFVolume
+    c_oracle.use_all_host_threads()
+    scene, bnds = _sub_volume(config, lo, dims)
+    gpu = TSDFVolume(bnds.copy(), scene.voxel_size)
+    assert tuple(gpu._vol_dim) == dims
+    gpu.count_updates = True
+    orc = c_oracle.COracleTSDFVolume(bnds.copy(), scene.voxel_size)
+    updated = 0
+    for i in (0, 5, 11):
+        fr = scene.frame(i)
+        assert fr.depth.shape == (scene.H, scene.W) and scene.W == 1920
+        gpu.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+        orc.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+        updated += orc.last_updated
+    assert gpu.num_updated() == updated > 1_000_000
+    tsdf, color = gpu.get_volume()
+    _assert_planes(tsdf, gpu.get_weight_volume(), color, orc, config)
+
+
+def test_c5_2048_cubed_block_sampled_against_the_oracle(c_oracle):
+    """The whole 2048^3 volume on one GPU; 24 random 64^3 blocks (plus the two extreme corners) against the oracle."""
+    import torch
+    from hive_b200.fusion import TSDFVolume, _world_table
+    torch.cuda.empty_cache()
+    free, _ = torch.cuda.mem_get_info()
+    if free < 115 * 2 ** 30:
+        pytest.skip(f"needs 103 GB of HBM for the 2048^3 planes, {free / 2 ** 30:.0f} GiB free")
+    c_oracle.use_all_host_threads()
+    scene = Scene("C5", "room")
+    gpu = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    assert tuple(gpu._vol_dim) == (2048, 2048, 2048)
+    gpu.count_updates = True
+    frames = [scene.frame(i) for i in (0, 9)]
+    for fr in frames:
+        gpu.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+    assert gpu.num_updated() > 2 ** 31  # the counter and the voxel index are 64-bit
+    tables = [_world_table(gpu._vol_origin[k], gpu._voxel_size, 2048) for k in range(3)]
+    rng = np.random.default_rng(5)
+    B = 64
+    corners = [(0, 0, 0), (2048 - B, 2048 - B, 2048 - B)]
+    # blocks around the surfaces the camera sees (pure free space / unseen blocks would compare 1.0 with 1.0)
+    w_any = (gpu._weight_vol_gpu[::B, ::B, ::B] > 0).nonzero().cpu().numpy() * B
+    picks = [tuple(int(v) for v in np.minimum(w_any[k], 2048 - B)) for k in rng.choice(len(w_any), 24, replace=False)]
+    touched = 0
+    prepared = [c_oracle.prepare_frame(fr.rgb, fr.depth, scene.K, fr.pose) for fr in frames]
+    for bx, by, bz in corners + picks:
+        orc = c_oracle.COracleBlock([t[o:o + B] for t, o in zip(tables, (bx, by, bz))], scene.voxel_size)
+        for fr in prepared:
+            orc.integrate_prepared(fr)
+        sl = (slice(bx, bx + B), slice(by, by + B), slice(bz, bz + B))
+        _assert_planes(gpu._tsdf_vol_gpu[sl].cpu().numpy(), gpu._weight_vol_gpu[sl].cpu().numpy(),
+                       gpu._color_vol_gpu[sl].cpu().numpy(), orc, f"block {bx},{by},{bz}")
+        touched += int((orc._weight_vol_cpu > 0).sum())
+    assert touched > 100_000
+    del gpu
+    torch.cuda.empty_cache()
 
 
 @pytest.fixture(scope="module")
@@ -67,7 +167,7 @@ def test_c2_mesh_properties(c2_frames):
     tsdf, color = vol.get_volume()
     pos = tsdf > 0
     expected = int((pos[1:] != pos[:-1]).sum() + (pos[:, 1:] != pos[:, :-1]).sum() + (pos[:, :, 1:] != pos[:, :, :-1]).sum())
-    assert len(verts) >= expected  # + the few cube-centre vertices of the 12-gon tilings
+    assert len(verts) >= expected  # + the few cube-centre vertices of the tilings that use one
     assert len(verts) - expected < 0.001 * expected + 16
     assert faces.min() == 0 and faces.max() == len(verts) - 1 and len(faces) > 500_000
     # manifoldness: directed edges are unique; an undirected edge without a partner lies on the volume border
@@ -91,3 +191,23 @@ def test_c2_mesh_properties(c2_frames):
     assert match.mean() > 0.999  # (the world -> voxel round trip above is float64; the product rounds the float32 voxel coordinate)
     ln = np.linalg.norm(norms, axis=1)
     assert np.isfinite(norms).all() and ln.max() < 1.0 + 1e-3 and (np.abs(ln - 1.0) < 1e-3).mean() > 0.999
+
+
+def test_c2_mesh_equals_the_oracle(c2_frames, c_oracle):
+    """get_mesh at 512^3 against the serial C marching cubes on the same planes: same vertices, triangles, colours."""
+    from hive_b200.fusion import TSDFVolume
+    from oracle import fusion_oracle as fo
+    scene, frames = c2_frames
+    vol = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    for fr in frames:
+        vol.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+    verts, faces, norms, colors = vol.get_mesh()
+    tsdf, color = vol.get_volume()
+    ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
+    order = np.argsort(ok, kind="stable")
+    rank = np.empty_like(order)
+    rank[order] = np.arange(len(order))
+    ow, oc = fo.mesh_postprocess(ov[order], color, vol._voxel_size, vol._vol_origin)
+    assert np.array_equal(faces, rank[of].astype(np.int32))
+    assert np.array_equal(verts, ow) and np.array_equal(colors, oc)
+    assert np.abs(norms - on[order]).max() <= 1e-6

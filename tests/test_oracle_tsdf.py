@@ -29,12 +29,16 @@ def _run(vol, variant, weights):
 
 
 @pytest.mark.parametrize("variant", ["room", "dense"])
-@pytest.mark.parametrize("impl", ["numpy", "c"])
+@pytest.mark.parametrize("impl", ["numpy", "c", "numba"])
 def test_oracle_matches_reference_golden(variant, impl, c_oracle):
     g = np.load(os.path.join(GOLDEN, f"tsdf_tiny_{variant}.npz"))
     assert _sha(g["tsdf"]) == str(g["sha_tsdf"]) and _sha(g["color"]) == str(g["sha_color"])
     scene = Scene("tiny", variant)
-    cls = fo.OracleTSDFVolume if impl == "numpy" else c_oracle.COracleTSDFVolume
+    if impl == "numba":
+        fnb = pytest.importorskip("oracle.fusion_numba")  # the reference-shaped restatement bench.py --impl reference times
+        cls = fnb.NumbaTSDFVolume
+    else:
+        cls = fo.OracleTSDFVolume if impl == "numpy" else c_oracle.COracleTSDFVolume
     vol = _run(cls(scene.vol_bnds.copy(), scene.voxel_size), variant, list(g["weights"]))
     assert tuple(vol._vol_dim) == tuple(g["vol_dim"])
     assert np.array_equal(vol._vol_origin, g["vol_origin"])
@@ -94,13 +98,17 @@ def test_oracle_matches_live_reference(c_oracle):
     assert np.array_equal(ref._tsdf_vol_cpu, orc._tsdf_vol_cpu)
 
 
-@pytest.mark.parametrize("impl", ["numpy", "c"])
+@pytest.mark.parametrize("impl", ["numpy", "c", "numba"])
 def test_oracle_matches_reference_on_7scenes_fixture(impl, c_oracle):
     """Real sensor data: the reference's own 7-Scenes frames (third_party/tsdf_fusion_python/data, read as
     demo.py:19-55 does, subsampled 4x) through the reference's CPU path -> tests/golden/tsdf_7scenes.npz."""
     g = np.load(os.path.join(GOLDEN, "tsdf_7scenes.npz"))
     assert _sha(g["tsdf"]) == str(g["sha_tsdf"]) and _sha(g["color"]) == str(g["sha_color"])
-    cls = fo.OracleTSDFVolume if impl == "numpy" else c_oracle.COracleTSDFVolume
+    if impl == "numba":
+        fnb = pytest.importorskip("oracle.fusion_numba")  # the reference-shaped restatement bench.py --impl reference times
+        cls = fnb.NumbaTSDFVolume
+    else:
+        cls = fo.OracleTSDFVolume if impl == "numpy" else c_oracle.COracleTSDFVolume
     vol = cls(g["vol_bnds"].copy(), float(g["voxel_size"]))
     for d, c, p in zip(g["depth"], g["rgb"], g["pose"]):
         vol.integrate(c, d, g["cam_intr"], p, 1.0)
