@@ -425,7 +425,7 @@ def measure_mesh(vol, torch, peak, repeats=5, cpu=True):
         t0 = time.perf_counter()
         ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
         cpu_s = time.perf_counter() - t0
-        order = np.argsort(ok, kind="stable")
+        order = c_oracle.product_order(ok)
         rank = np.empty_like(order)
         rank[order] = np.arange(len(order))
         ow, oc = fo.mesh_postprocess(ov[order], color, vol._voxel_size, vol._vol_origin)

@@ -38,7 +38,7 @@ SIGNATURES = {
     "hv_mc_count": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p, c_int64, c_void_p, c_void_p],
     "hv_mc_emit": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
                    c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
-                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_mc_extract": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
                       c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],

@@ -5,17 +5,22 @@
 // nearest-voxel colour gather, b/g/r unpack, voxel -> world transform).  The arithmetic contract is the one restated in
 // oracle/mc_oracle.c (scikit-image itself is not available anywhere on the box: parity unpinned).
 //
-// Pipeline (all HBM-bound streaming / compaction, no tensor cores):
-//   1. mc_sign_kernel    one pass over the TSDF plane (4 B/voxel): one bit per voxel (v > level) and min/max.  The bit
-//                        volume is N/8 bytes (16 MB for 512^3) and stays L2-resident for everything that follows.
-//   2. mc_count_kernel   one thread per group of 32 z-consecutive voxels: bit-parallel edge masks (which voxels own a
-//                        vertex on their +axis0/+axis1/+axis2 edge or a cube-centre vertex) and the triangle count of
-//                        the group's active cubes.  TSDF values are only touched for cubes with an ambiguous face.
-//   3. scan kernels      exclusive prefix sums of the per-group (vertex, triangle) counts.
-//   4. mc_emit_kernel    re-walks the active cubes and writes triangles; a vertex index is recovered from the owner
-//                        group's prefix + popcounts of its masks, so no per-voxel index volume exists.  Vertices come out
-//                        sorted by (owner voxel in scan order, axis) and triangles in cube scan order: deterministic.
-//   5. mc_vertex_kernel  one thread per vertex: position, accumulated normal, colour, world transform.
+// Pipeline (HBM-bound streaming + sparse compaction, no tensor cores), DESIGN.md 4.2:
+//   1. mc_classify_kernel  the one pass over the TSDF plane (4 B/voxel).  A CTA sweeps a strip of TY columns along
+//                          axis 0; the sign bits of planes x and x + 1 sit in shared memory, so the per-group vertex /
+//                          triangle counts are taken from the bits the same CTA has just produced.  Writes the bit volume
+//                          (N/8 bytes), one packed count word per 32-voxel group, and the totals of every run (= one
+//                          plane of one strip, a contiguous range of the global group order); min / max for the
+//                          skimage level-range check.
+//   2. mc_run_scan_kernel  exclusive scan of the run totals (X * ceil(Y/TY) entries), one CTA.
+//   3. mc_emit_kernel      sweeps the same strips: bits of three planes + count words of two planes in shared memory,
+//                          block scans turn them into the index base of every group in reach, so a triangle corner's
+//                          vertex index is run base + shared-memory prefix + popcounts -- no index volume, no global
+//                          look-ups.  One thread per triangle record, one thread per vertex record (position, normal
+//                          accumulated over the <= 4 cubes around the edge in scan order, colour, world transform) with
+//                          the edge's 2x3x3 neighbourhood in registers.
+// Vertex order: edge vertices sorted by (owner voxel in scan order, axis), then the cube-centre vertices by cube;
+// triangles in cube scan order.  Deterministic; no dedup pass because each lattice edge has exactly one owner.
 //
 // z-slab shards pass one halo plane below / above the slab (`halo_lo` / `halo_hi`); keys carry global voxel indices so
 // per-slab meshes can be stitched exactly (hive_b200/sharded.py).
@@ -44,15 +49,14 @@ struct McGrid {
     long long zoff;      // global z of zb = 0
     long long Zg;        // global Z
     double level;
+    // sweep geometry: a strip = TY columns (axis 1), a run = one plane (axis 0) of one strip
+    int TY, S, GP;        // columns per strip, strips per plane, G + 2 (row pitch of the shared bit tables)
     // scratch
     unsigned int* bits;   // [X*Y*G]
-    uint4* gmask;         // [X*Y*G] owner masks: axis0, axis1, axis2, centre
-    uint2* gcount;        // [X*Y*G] (vertices, triangles)
-    uint2* goff;          // [X*Y*G] exclusive prefix of gcount
-    uint2* bsum;          // scratch of the scan
-    unsigned int* active; // [n_groups] compacted ids of the groups that own a vertex or a triangle (any order)
-    unsigned int* n_active;
-    unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float)
+    unsigned int* gcnt;   // [X*Y*G] edge vertices | centre vertices << 8 | triangles << 16 of the group
+    uint4* run_tot;       // [X*S] (edge vertices, triangles, centre vertices, 0) of every run
+    uint4* run_base;      // [X*S] exclusive prefix of run_tot
+    unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float) [4] edge vertices
     long long n_groups;
 };
 
@@ -70,24 +74,15 @@ __device__ __forceinline__ int float_order_key(float f) {
     return i >= 0 ? i : i ^ 0x7fffffff;
 }
 
-__global__ void mc_init_kernel(unsigned long long* totals, unsigned int* n_active) {
+__global__ void mc_init_kernel(unsigned long long* totals) {
     if (threadIdx.x == 0) {
         totals[0] = 0ull;
         totals[1] = 0ull;
         totals[2] = 0x7fffffffull;  // min key
         totals[3] = 0x80000000ull;  // max key
-        *n_active = 0u;
+        totals[4] = 0ull;
     }
 }
-
-// ---- 1. sign bits + min/max ----------------------------------------------------------------------------------------
-// A warp covers 128 consecutive zb of one column (each lane a float4 -> 4 sign bits, 8 lanes -> one 32-bit word) and
-// strides over (column, segment) tiles; whole-volume shards (no low halo, 16-byte aligned columns) take the LDG.128 path.
-struct McSignGeom {
-    int segs;        // 128-zb segments per column
-    int n_tiles;     // columns * segs
-    int vec;         // 1: z == zb and columns are float4-aligned
-};
 
 // Sign nibble of four values + running min/max.
 __device__ __forceinline__ unsigned int mc_sign4(const float (&v)[4], float level_f, bool level_exact, double level,
@@ -103,99 +98,11 @@ __device__ __forceinline__ unsigned int mc_sign4(const float (&v)[4], float leve
     return nib;
 }
 
-__device__ __forceinline__ void mc_store_word(const McGrid& g, unsigned int nib, int lane, size_t col, int seg) {
-    unsigned int word = nib << (4 * (lane & 7));
-    word |= __shfl_xor_sync(0xffffffffu, word, 1);
-    word |= __shfl_xor_sync(0xffffffffu, word, 2);
-    word |= __shfl_xor_sync(0xffffffffu, word, 4);
-    const int gq = seg * 4 + (lane >> 3);
-    if ((lane & 7) == 0 && gq < g.G) g.bits[col * g.G + gq] = word;
-}
-
-// A warp takes whole columns (grid-stride) and walks their 128-zb segments: no tile decode, and in the vector path two
-// segments (2 x 512 B per warp) are in flight together.  r01: the tile-indexed version spent 78 warp-instructions per
-// 128 voxels, a third of them in the integer division of the tile decode, and ran at 63 % issue / 55 % DRAM.
-__global__ void __launch_bounds__(256) mc_sign_kernel(const McGrid g, const McSignGeom sg) {
-    const int lane = threadIdx.x & 31;
-    const int warp0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    const int n_warps = (int)((gridDim.x * blockDim.x) >> 5);
-    float vmin = INFINITY, vmax = -INFINITY;
-    const float level_f = (float)g.level;  // exact compare needs double only when the level is not a float
-    const bool level_exact = (double)level_f == g.level;
-    const int n_cols = g.X * g.Y;
-    for (int col = warp0; col < n_cols; col += n_warps) {
-        if (sg.vec) {
-            const float* base = g.tsdf + (size_t)col * g.pitch + lane * 4;
-            int seg = 0;
-            for (; seg + 1 < sg.segs; seg += 2) {
-                const int za = seg * 128 + lane * 4, zb = za + 128;
-                float a[4] = {NAN, NAN, NAN, NAN}, b[4] = {NAN, NAN, NAN, NAN};
-                const bool fa = za + 3 < g.Z, fb = zb + 3 < g.Z;
-                if (fa) {
-                    const float4 q = __ldcs(reinterpret_cast<const float4*>(base + seg * 128));
-                    a[0] = q.x; a[1] = q.y; a[2] = q.z; a[3] = q.w;
-                }
-                if (fb) {
-                    const float4 q = __ldcs(reinterpret_cast<const float4*>(base + seg * 128 + 128));
-                    b[0] = q.x; b[1] = q.y; b[2] = q.z; b[3] = q.w;
-                }
-                if (!fa) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (za + k < g.Zb) a[k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, col / g.Y, col % g.Y, za + k);
-                }
-                if (!fb) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (zb + k < g.Zb) b[k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, col / g.Y, col % g.Y, zb + k);
-                }
-                mc_store_word(g, mc_sign4(a, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg);
-                mc_store_word(g, mc_sign4(b, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg + 1);
-            }
-            if (seg < sg.segs) {
-                const int za = seg * 128 + lane * 4;
-                float a[4] = {NAN, NAN, NAN, NAN};
-                if (za + 3 < g.Z) {
-                    const float4 q = __ldcs(reinterpret_cast<const float4*>(base + seg * 128));
-                    a[0] = q.x; a[1] = q.y; a[2] = q.z; a[3] = q.w;
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (za + k < g.Zb) a[k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, col / g.Y, col % g.Y, za + k);
-                }
-                mc_store_word(g, mc_sign4(a, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg);
-            }
-        } else {
-            const int x = col / g.Y, y = col - x * g.Y;
-            for (int seg = 0; seg < sg.segs; ++seg) {
-                const int zb0 = seg * 128 + lane * 4;
-                float v[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    v[k] = (zb0 + k < g.Zb) ? mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb0 + k) : NAN;
-                mc_store_word(g, mc_sign4(v, level_f, level_exact, g.level, vmin, vmax), lane, (size_t)col, seg);
-            }
-        }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
-        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-    }
-    if (lane == 0) {
-        if (vmin <= vmax) {  // at least one real value seen
-            atomicMin(reinterpret_cast<int*>(g.totals + 2), float_order_key(vmin));
-            atomicMax(reinterpret_cast<int*>(g.totals + 3), float_order_key(vmax));
-        }
-    }
-}
-
 // ---- cube helpers -----------------------------------------------------------------------------------------------------
 struct CubeWords {
     unsigned int w[8];    // per corner: the word whose bit k is that corner of cube (x, y, 32*gq + k)
     unsigned int active;  // cubes of this group that exist, are owned and are crossed by the surface
-    unsigned int own;     // owned voxels of this group
-    unsigned int b00, b01, b10, u00;
+    unsigned int mx, my, mz;  // voxels of the group owning a vertex on their +axis0 / +axis1 / +axis2 edge
 };
 
 __device__ __forceinline__ unsigned int range_mask(int lo, int hi, int base) {
@@ -204,36 +111,6 @@ __device__ __forceinline__ unsigned int range_mask(int lo, int hi, int base) {
     if (a >= b) return 0u;
     const unsigned int upto_b = (b >= 32) ? 0xffffffffu : ((1u << b) - 1u);
     return upto_b & ~((1u << a) - 1u);
-}
-
-__device__ __forceinline__ void load_pair(const McGrid& g, int x, int y, int gq, bool in, unsigned int& b, unsigned int& u) {
-    b = 0u;
-    u = 0u;
-    if (!in) return;
-    const size_t gi = ((size_t)x * g.Y + y) * g.G + gq;
-    b = g.bits[gi];
-    const unsigned int nxt = (gq + 1 < g.G) ? g.bits[gi + 1] : 0u;
-    u = (b >> 1) | (nxt << 31);
-}
-
-__device__ __forceinline__ CubeWords load_cube_words(const McGrid& g, int x, int y, int gq) {
-    CubeWords c;
-    const bool x1 = x + 1 < g.X, y1 = y + 1 < g.Y;
-    unsigned int b00, b01, b10, b11, u00, u01, u10, u11;
-    load_pair(g, x, y, gq, true, b00, u00);
-    load_pair(g, x, y + 1, gq, y1, b01, u01);
-    load_pair(g, x + 1, y, gq, x1, b10, u10);
-    load_pair(g, x + 1, y + 1, gq, x1 && y1, b11, u11);
-    // corner i offsets (axis0, axis1, axis2): see kMcCornerOff
-    c.w[0] = b00; c.w[1] = u00; c.w[2] = u01; c.w[3] = b01;
-    c.w[4] = b10; c.w[5] = u10; c.w[6] = u11; c.w[7] = b11;
-    c.b00 = b00; c.b01 = b01; c.b10 = b10; c.u00 = u00;
-    const int base = gq * 32;
-    c.own = range_mask(g.own_lo, g.own_hi, base);
-    const unsigned int all8 = b00 & b01 & b10 & b11 & u00 & u01 & u10 & u11;
-    const unsigned int any8 = b00 | b01 | b10 | b11 | u00 | u01 | u10 | u11;
-    c.active = (x1 && y1) ? (any8 & ~all8 & c.own & range_mask(0, g.Zb - 1, base)) : 0u;
-    return c;
 }
 
 __device__ __forceinline__ int cube_index(const CubeWords& c, int k) {
@@ -359,59 +236,235 @@ __device__ __forceinline__ int cube_variant_at(const McGrid& g, int idx, int x, 
     return cube_variant(idx, v);
 }
 
-// ---- 2. per-group owner masks and counts ------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) mc_count_kernel(const McGrid g) {
-    const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gi >= g.n_groups) return;
-    int x, y, gq;
-    if (gi < 0x100000000ll) {  // 32-bit decode (a 64-bit division is ~100 instructions; this kernel has 4.2 M threads at 512^3)
-        const unsigned int g32 = (unsigned int)gi, col = g32 / (unsigned int)g.G;
-        gq = (int)(g32 - col * (unsigned int)g.G);
-        x = (int)(col / (unsigned int)g.Y);
-        y = (int)(col - (unsigned int)x * (unsigned int)g.Y);
-    } else {
-        const long long col = gi / g.G;
-        gq = (int)(gi - col * g.G);
-        x = (int)(col / g.Y);
-        y = (int)(col - (long long)x * g.Y);
-    }
-    const CubeWords c = load_cube_words(g, x, y, gq);
+// ---- shared-memory bit tables ---------------------------------------------------------------------------------------------
+// One table = the sign words of one plane (axis 0) for TY + 2 columns of a strip (its own columns, then up to two columns of
+// the next strip), GP = G + 2 words per column; words past the last group, columns past Y and planes past X read as zero.
+constexpr int kSweepThreads = 256;
+
+// Sign words around group (column c of the tables, word gq) of plane x: p0 = table of plane x, p1 = of plane x + 1.
+__device__ __forceinline__ CubeWords cube_words(const McGrid& g, const unsigned int* p0, const unsigned int* p1, int x, int y,
+                                                int c, int gq) {
+    CubeWords w;
+    const int i = c * g.GP + gq;
+    const unsigned int b00 = p0[i], b01 = p0[i + g.GP], b10 = p1[i], b11 = p1[i + g.GP];
+    const unsigned int u00 = (b00 >> 1) | (p0[i + 1] << 31), u01 = (b01 >> 1) | (p0[i + g.GP + 1] << 31);
+    const unsigned int u10 = (b10 >> 1) | (p1[i + 1] << 31), u11 = (b11 >> 1) | (p1[i + g.GP + 1] << 31);
+    // corner i offsets (axis0, axis1, axis2): see kMcCornerOff
+    w.w[0] = b00; w.w[1] = u00; w.w[2] = u01; w.w[3] = b01;
+    w.w[4] = b10; w.w[5] = u10; w.w[6] = u11; w.w[7] = b11;
+    const bool x1 = x + 1 < g.X, y1 = y + 1 < g.Y;
     const int base = gq * 32;
-    uint4 m;
-    m.x = (x + 1 < g.X) ? ((c.b00 ^ c.b10) & c.own) : 0u;
-    m.y = (y + 1 < g.Y) ? ((c.b00 ^ c.b01) & c.own) : 0u;
-    m.z = (c.b00 ^ c.u00) & c.own & range_mask(0, g.Zb - 1, base);
-    m.w = 0u;
-    unsigned int ntri = 0;
-    for (unsigned int rest = c.active; rest; rest &= rest - 1) {
-        const int k = __ffs(rest) - 1;
-        const int idx = cube_index(c, k);
-        const int variant = cube_variant_at_ool(g, idx, x, y, base + k);
-        ntri += kMcVarNtri[variant];
-        if ((kMcVarMult[variant] >> 48) & 15ull) m.w |= 1u << k;
-    }
-    g.gmask[gi] = m;
-    const unsigned int nv = __popc(m.x) + __popc(m.y) + __popc(m.z) + __popc(m.w);
-    g.gcount[gi] = make_uint2(nv, ntri);
-    // warp-aggregated append to the work list of mc_emit_kernel
-    const bool has_work = (nv | ntri) != 0u;
-    const unsigned int vote = __ballot_sync(__activemask(), has_work);
-    if (has_work) {
-        const int lane = threadIdx.x & 31;
-        const int leader = __ffs(vote) - 1;
-        unsigned int base0 = 0;
-        if (lane == leader) base0 = atomicAdd(g.n_active, (unsigned int)__popc(vote));
-        base0 = __shfl_sync(vote, base0, leader);
-        g.active[base0 + __popc(vote & ((1u << lane) - 1u))] = (unsigned int)gi;
+    const unsigned int own = range_mask(g.own_lo, g.own_hi, base), zin = range_mask(0, g.Zb - 1, base);
+    w.mx = x1 ? ((b00 ^ b10) & own) : 0u;
+    w.my = y1 ? ((b00 ^ b01) & own) : 0u;
+    w.mz = (b00 ^ u00) & own & zin;
+    const unsigned int all8 = b00 & b01 & b10 & b11 & u00 & u01 & u10 & u11;
+    const unsigned int any8 = b00 | b01 | b10 | b11 | u00 | u01 | u10 | u11;
+    w.active = (x1 && y1) ? (any8 & ~all8 & own & zin) : 0u;
+    return w;
+}
+
+__device__ __forceinline__ unsigned int warp_sum(unsigned int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- 1. classify: sign bits, per-group counts, run totals, min / max -------------------------------------------------------
+// Loads the sign words of plane x (columns y0 .. y0 + ny of the strip; column ny belongs to the next strip) into `tab`;
+// `owned`: this CTA is the one that publishes the plane's bits (and takes its values into min / max).
+__device__ __forceinline__ void classify_load_plane(const McGrid& g, unsigned int* tab, int x, int y0, int ny, bool owned,
+                                                    int vec, float level_f, bool level_exact, float& vmin, float& vmax) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int segs = (g.Zb + 127) >> 7;
+    const int tiles = (ny + 1) * segs;
+    for (int tb = warp; tb < tiles; tb += 4 * (kSweepThreads / 32)) {
+        float v[4][4];
+        int cc[4], sg[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {  // four 512-byte column segments of this warp in flight together
+            const int t = tb + u * (kSweepThreads / 32);
+            v[u][0] = v[u][1] = v[u][2] = v[u][3] = NAN;
+            cc[u] = -1;
+            if (t < tiles) {
+                const int c = t / segs, seg = t - c * segs, y = y0 + c;
+                cc[u] = c;
+                sg[u] = seg;
+                if (x < g.X && y < g.Y) {
+                    const int z0 = seg * 128 + lane * 4;
+                    const size_t col = (size_t)x * g.Y + y;
+                    if (vec && z0 + 3 < g.Z) {
+                        const float4* p = reinterpret_cast<const float4*>(g.tsdf + col * (size_t)g.pitch + z0);
+                        const float4 q = (owned && c < ny) ? __ldcs(p) : __ldg(p);
+                        v[u][0] = q.x; v[u][1] = q.y; v[u][2] = q.z; v[u][3] = q.w;
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (z0 + k < g.Zb) v[u][k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, z0 + k);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (cc[u] < 0) continue;  // warp-uniform
+            float lmin = INFINITY, lmax = -INFINITY;
+            const unsigned int nib = mc_sign4(v[u], level_f, level_exact, g.level, lmin, lmax);
+            unsigned int word = nib << (4 * (lane & 7));
+            word |= __shfl_xor_sync(0xffffffffu, word, 1);
+            word |= __shfl_xor_sync(0xffffffffu, word, 2);
+            word |= __shfl_xor_sync(0xffffffffu, word, 4);
+            const int gq = sg[u] * 4 + (lane >> 3);
+            if ((lane & 7) == 0 && gq < g.G) {
+                tab[cc[u] * g.GP + gq] = word;
+                if (owned && cc[u] < ny) g.bits[((size_t)x * g.Y + (y0 + cc[u])) * g.G + gq] = word;
+            }
+            if (owned && cc[u] < ny) {
+                vmin = fminf(vmin, lmin);
+                vmax = fmaxf(vmax, lmax);
+            }
+        }
     }
 }
 
-// ---- 4. emit triangles and vertex keys ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSweepThreads) mc_classify_kernel(const McGrid g, const int CX, const int vec) {
+    extern __shared__ unsigned int s_mem[];
+    __shared__ unsigned int s_tot[3];
+    const int tabw = (g.TY + 2) * g.GP;
+    const int strip = blockIdx.x % g.S, chunk = blockIdx.x / g.S;
+    const int y0 = strip * g.TY, ny = min(g.TY, g.Y - y0);
+    const int xa = chunk * CX, xb = min(g.X, xa + CX);
+    if (xa >= xb) return;
+    const float level_f = (float)g.level;  // exact compare needs double only when the level is not a float
+    const bool level_exact = (double)level_f == g.level;
+    float vmin = INFINITY, vmax = -INFINITY;
+    for (int i = threadIdx.x; i < 2 * tabw; i += kSweepThreads) s_mem[i] = 0u;
+    if (threadIdx.x < 3) s_tot[threadIdx.x] = 0u;
+    __syncthreads();
+    unsigned int* cur = s_mem;
+    unsigned int* nxt = s_mem + tabw;
+    classify_load_plane(g, cur, xa, y0, ny, true, vec, level_f, level_exact, vmin, vmax);
+    for (int x = xa; x < xb; ++x) {
+        classify_load_plane(g, nxt, x + 1, y0, ny, x + 1 < xb, vec, level_f, level_exact, vmin, vmax);
+        __syncthreads();
+        unsigned int a_nv = 0, a_nt = 0, a_nc = 0;
+        for (int t = threadIdx.x; t < ny * g.G; t += kSweepThreads) {
+            const int c = t / g.G, gq = t - c * g.G, y = y0 + c;
+            const CubeWords w = cube_words(g, cur, nxt, x, y, c, gq);
+            const unsigned int nv = __popc(w.mx) + __popc(w.my) + __popc(w.mz);
+            unsigned int nt = 0, nc = 0;
+            for (unsigned int rest = w.active; rest; rest &= rest - 1) {
+                const int k = __ffs(rest) - 1;
+                const int variant = cube_variant_at_ool(g, cube_index(w, k), x, y, gq * 32 + k);
+                nt += kMcVarNtri[variant];
+                nc += ((kMcVarMult[variant] >> 48) & 15ull) ? 1u : 0u;
+            }
+            g.gcnt[((size_t)x * g.Y + y) * g.G + gq] = nv | (nc << 8) | (nt << 16);
+            a_nv += nv;
+            a_nt += nt;
+            a_nc += nc;
+        }
+        a_nv = warp_sum(a_nv);
+        a_nt = warp_sum(a_nt);
+        a_nc = warp_sum(a_nc);
+        if ((threadIdx.x & 31) == 0 && (a_nv | a_nt | a_nc)) {
+            atomicAdd(&s_tot[0], a_nv);
+            atomicAdd(&s_tot[1], a_nt);
+            atomicAdd(&s_tot[2], a_nc);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            g.run_tot[(size_t)x * g.S + strip] = make_uint4(s_tot[0], s_tot[1], s_tot[2], 0u);
+            s_tot[0] = s_tot[1] = s_tot[2] = 0u;
+        }
+        unsigned int* t = cur;
+        cur = nxt;
+        nxt = t;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    }
+    if ((threadIdx.x & 31) == 0 && vmin <= vmax) {  // at least one real value seen
+        atomicMin(reinterpret_cast<int*>(g.totals + 2), float_order_key(vmin));
+        atomicMax(reinterpret_cast<int*>(g.totals + 3), float_order_key(vmax));
+    }
+}
+
+// ---- 2. exclusive scan of the run totals (one CTA) ----------------------------------------------------------------------------
+constexpr int kRunScanThreads = 1024;
+
+__global__ void __launch_bounds__(kRunScanThreads) mc_run_scan_kernel(const uint4* __restrict__ tot, uint4* __restrict__ base,
+                                                                      int n, unsigned long long* totals) {
+    __shared__ unsigned long long s_w[3][kRunScanThreads / 32];
+    const int per = (n + kRunScanThreads - 1) / kRunScanThreads;
+    const int i0 = threadIdx.x * per, i1 = min(n, i0 + per);
+    unsigned long long a = 0, b = 0, c = 0;
+    for (int i = i0; i < i1; ++i) {
+        const uint4 v = tot[i];
+        a += v.x;
+        b += v.y;
+        c += v.z;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long ia = a, ib = b, ic = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long ua = __shfl_up_sync(0xffffffffu, ia, o), ub = __shfl_up_sync(0xffffffffu, ib, o),
+                                 uc = __shfl_up_sync(0xffffffffu, ic, o);
+        if (lane >= o) {
+            ia += ua;
+            ib += ub;
+            ic += uc;
+        }
+    }
+    if (lane == 31) {
+        s_w[0][warp] = ia;
+        s_w[1][warp] = ib;
+        s_w[2][warp] = ic;
+    }
+    __syncthreads();
+    unsigned long long ca = 0, cb = 0, cc = 0, ta = 0, tb = 0, tc = 0;
+    for (int w = 0; w < kRunScanThreads / 32; ++w) {
+        if (w < warp) {
+            ca += s_w[0][w];
+            cb += s_w[1][w];
+            cc += s_w[2][w];
+        }
+        ta += s_w[0][w];
+        tb += s_w[1][w];
+        tc += s_w[2][w];
+    }
+    unsigned long long ea = ca + ia - a, eb = cb + ib - b, ec = cc + ic - c;  // exclusive prefix of this thread's range
+    for (int i = i0; i < i1; ++i) {
+        const uint4 v = tot[i];
+        base[i] = make_uint4((unsigned int)ea, (unsigned int)eb, (unsigned int)ec, 0u);
+        ea += v.x;
+        eb += v.y;
+        ec += v.z;
+    }
+    if (threadIdx.x == 0) {
+        totals[0] = ta + tc;  // vertices: edge vertices, then the cube-centre vertices
+        totals[1] = tb;
+        totals[4] = ta;
+    }
+}
+
+// ---- 3. emit -----------------------------------------------------------------------------------------------------------------
 struct McEmit {
     int32_t* faces;                  // [T][3] local vertex indices, or null
     unsigned long long* face_keys;   // [T][3] global vertex keys, or null
-    unsigned long long* vert_keys;   // [V]
+    unsigned long long* vert_keys;   // [V], or null
     unsigned long long* face_cubes;  // [T] global linear index of the cube that produced the face, or null
+    float* verts_world;              // [V][3]
+    float* verts_voxel;              // [V][3] or null
+    float* normals;                  // [V][3]
+    uint8_t* colors;                 // [V][3] r, g, b
+    long long cap_verts, cap_tris;   // capacity of the buffers above: anything beyond is counted, not written
+    float voxel_size;
+    float origin[3];
+    int CX;
 };
 
 __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x, int y, int zb, int axis) {
@@ -419,247 +472,278 @@ __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x,
     return lin * 4ull + (unsigned long long)axis;
 }
 
-__device__ __forceinline__ int vertex_index(const McGrid& g, int x, int y, int zb, int axis) {
-    const size_t og = ((size_t)x * g.Y + y) * g.G + (zb >> 5);
-    const int bit = zb & 31;
-    const uint4 m = g.gmask[og];
+// Exclusive block scan of one value per thread, with a running carry kept in shared memory (s_carry); `s_warp`: 8 words.
+__device__ __forceinline__ unsigned int block_scan_carry(unsigned int v, unsigned int* s_warp, unsigned int* s_carry) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    unsigned int before = *s_carry, total = 0;
+#pragma unroll
+    for (int w = 0; w < kSweepThreads / 32; ++w) {
+        const unsigned int sw = s_warp[w];
+        if (w < warp) before += sw;
+        total += sw;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *s_carry += total;
+    return before + inc - v;
+}
+
+// Tables the emit kernel keeps in shared memory.
+struct EmitTables {
+    unsigned int* bits[3];  // planes x, x + 1, x + 2 (rotating): [(TY + 2) * GP]
+    unsigned int* vpre[2];  // planes x, x + 1: global index of the first edge vertex of every group, [(TY + 1) * G]
+    unsigned int* tpre;     // own groups of plane x: run-local index of the group's first triangle, [TY * G]
+    unsigned int* cpre;     //   ... of its first centre vertex
+    unsigned int* cnt;      //   ... its packed counts
+    unsigned int* mw;       //   ... mask of its cubes that have a centre vertex
+    uint2* rec;             // record list of one round
+    unsigned int* s_warp;   // 8 words of scan scratch
+    unsigned int* s_misc;   // [0] carry, [1] own total of a scan, [2..4] run totals (edge vertices, triangles, centres)
+};
+
+constexpr int kRecCap = 2048;  // records per round (16 KB)
+
+__device__ __forceinline__ void emit_load_bits(const McGrid& g, unsigned int* tab, int p, int y0) {
+    const int rows = g.TY + 2;
+    for (int i = threadIdx.x; i < rows * g.GP; i += kSweepThreads) {
+        const int c = i / g.GP, gq = i - c * g.GP, y = y0 + c;
+        tab[i] = (p < g.X && y < g.Y && gq < g.G) ? __ldg(g.bits + ((size_t)p * g.Y + y) * g.G + gq) : 0u;
+    }
+}
+
+// Global index of the first edge vertex of every group of plane p in reach: the strip's own columns continue the run
+// (p, strip); column ny is the first column of the run (p, strip + 1).
+__device__ __forceinline__ void emit_build_vpre(const McGrid& g, const EmitTables& T, unsigned int* vpre, int p, int strip,
+                                                int y0, int ny) {
+    const int n_own = ny * g.G, n_all = (y0 + ny < g.Y) ? n_own + g.G : n_own;
+    if (p >= g.X) return;  // never referenced
+    const unsigned int base_own = g.run_base[(size_t)p * g.S + strip].x;
+    const unsigned int base_next = (y0 + ny < g.Y) ? g.run_base[(size_t)p * g.S + strip + 1].x : 0u;
+    if (threadIdx.x == 0) T.s_misc[0] = 0u;
+    __syncthreads();
+    for (int t0 = 0; t0 < n_all; t0 += kSweepThreads) {
+        const int t = t0 + threadIdx.x;
+        unsigned int v = 0;
+        if (t < n_all) {
+            const int c = t / g.G, gq = t - c * g.G;
+            v = __ldg(g.gcnt + ((size_t)p * g.Y + (y0 + c)) * g.G + gq) & 255u;
+        }
+        const unsigned int ex = block_scan_carry(v, T.s_warp, T.s_misc);
+        if (t == n_own) T.s_misc[1] = ex;  // total of the own columns
+        if (t < n_all) vpre[t] = ex;       // rebased below
+    }
+    __syncthreads();
+    const unsigned int own_total = T.s_misc[1];
+    for (int t = threadIdx.x; t < n_all; t += kSweepThreads)
+        vpre[t] = (t < n_own) ? base_own + vpre[t] : base_next + (vpre[t] - own_total);
+}
+
+// Run-local prefixes of the triangles and centre vertices of the own groups of plane x; run totals into s_misc[2..4].
+__device__ __forceinline__ void emit_build_own(const McGrid& g, const EmitTables& T, int x, int y0, int ny) {
+    const int n_own = ny * g.G;
+    unsigned int nv_total = 0;
+    for (int comp = 0; comp < 2; ++comp) {  // 0: triangles, 1: centre vertices
+        if (threadIdx.x == 0) T.s_misc[0] = 0u;
+        __syncthreads();
+        for (int t0 = 0; t0 < n_own; t0 += kSweepThreads) {
+            const int t = t0 + threadIdx.x;
+            unsigned int word = 0;
+            if (t < n_own) {
+                const int c = t / g.G, gq = t - c * g.G;
+                word = __ldg(g.gcnt + ((size_t)x * g.Y + (y0 + c)) * g.G + gq);
+                if (comp == 0) T.cnt[t] = word;
+            }
+            const unsigned int v = comp == 0 ? (word >> 16) : ((word >> 8) & 255u);
+            const unsigned int ex = block_scan_carry(v, T.s_warp, T.s_misc);
+            if (t < n_own) (comp == 0 ? T.tpre : T.cpre)[t] = ex;
+            if (comp == 0) nv_total += word & 255u;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) T.s_misc[comp == 0 ? 3 : 4] = T.s_misc[0];
+    }
+    nv_total = warp_sum(nv_total);
+    if (threadIdx.x == 0) T.s_misc[2] = 0u;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0 && nv_total) atomicAdd(&T.s_misc[2], nv_total);
+    __syncthreads();
+}
+
+// Index of the edge vertex owned by voxel (column co of the tables, z = zo) of the plane whose tables are (bp, bq = the
+// plane after it), on `axis`: the group's base from `vpre`, plus the vertices of lower voxels, plus lower axes of its own.
+__device__ __forceinline__ unsigned int edge_vertex_index(const McGrid& g, const unsigned int* bp, const unsigned int* bq,
+                                                          const unsigned int* vpre, int xo, int yo, int co, int zo, int axis) {
+    const int og = zo >> 5, bit = zo & 31;
+    const int i = co * g.GP + og;
+    const unsigned int b00 = bp[i], u00 = (b00 >> 1) | (bp[i + 1] << 31), b01 = bp[i + g.GP], b10 = bq[i];
+    const unsigned int own = range_mask(g.own_lo, g.own_hi, og * 32), zin = range_mask(0, g.Zb - 1, og * 32);
+    const unsigned int mx = (xo + 1 < g.X) ? ((b00 ^ b10) & own) : 0u;
+    const unsigned int my = (yo + 1 < g.Y) ? ((b00 ^ b01) & own) : 0u;
+    const unsigned int mz = (b00 ^ u00) & own & zin;
     const unsigned int low = (1u << bit) - 1u;
-    int r = (int)g.goff[og].x + __popc(m.x & low) + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
-    if (axis > 0) r += (m.x >> bit) & 1u;
-    if (axis > 1) r += (m.y >> bit) & 1u;
-    if (axis > 2) r += (m.z >> bit) & 1u;
+    unsigned int r = vpre[co * g.G + og] + __popc(mx & low) + __popc(my & low) + __popc(mz & low);
+    if (axis > 0) r += (mx >> bit) & 1u;
+    if (axis > 1) r += (my >> bit) & 1u;
     return r;
 }
 
-// Writes triangle `j` of the cube (x, y, zb) with tiling `variant` as face `ti`: three independent look-ups (edge ->
-// owning voxel -> that voxel's group mask and offset), unrolled so that all of their loads are in flight together.
-__device__ __forceinline__ void emit_triangle(const McGrid& g, const McEmit& out, int x, int y, int zb, int variant, int j,
-                                              size_t ti) {
+// One triangle record: rec.x = column | word << 5 | voxel << 13 | tiling << 18 | triangle << 28, rec.y = run-local index.
+__device__ __forceinline__ void emit_triangle(const McGrid& g, const McEmit& out, const EmitTables& T, int s0, int x, int y0,
+                                              uint2 rec, unsigned int tri_base, unsigned int centre_base) {
+    const int c = (int)(rec.x & 31u), gq = (int)((rec.x >> 5) & 255u), k = (int)((rec.x >> 13) & 31u);
+    const int variant = (int)((rec.x >> 18) & 1023u), j = (int)(rec.x >> 28);
+    const int y = y0 + c, zb = gq * 32 + k;
+    const size_t ti = (size_t)tri_base + rec.y;
+    if ((long long)ti >= out.cap_tris) return;
     const uint8_t* tri = kMcTris + 3 * ((size_t)kMcVarTriOff[variant] + (size_t)j);
-    int ox[3], oy[3], oz[3], axis[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const int e = tri[c];
-        ox[c] = oy[c] = oz[c] = 0;
-        axis[c] = 3;
-        if (e < 12) {
-            ox[c] = kMcEdgeOwner[4 * e], oy[c] = kMcEdgeOwner[4 * e + 1], oz[c] = kMcEdgeOwner[4 * e + 2];
-            axis[c] = kMcEdgeOwner[4 * e + 3];
-        }
-    }
     if (out.face_keys) {
 #pragma unroll
-        for (int c = 0; c < 3; ++c) out.face_keys[3 * ti + c] = vertex_key(g, x + ox[c], y + oy[c], zb + oz[c], axis[c]);
+        for (int q = 0; q < 3; ++q) {
+            const int e = tri[q];
+            unsigned long long key;
+            if (e < 12)
+                key = vertex_key(g, x + kMcEdgeOwner[4 * e], y + kMcEdgeOwner[4 * e + 1], zb + kMcEdgeOwner[4 * e + 2],
+                                 kMcEdgeOwner[4 * e + 3]);
+            else
+                key = vertex_key(g, x, y, zb, 3);
+            out.face_keys[3 * ti + q] = key;
+        }
         if (out.face_cubes) out.face_cubes[ti] = vertex_key(g, x, y, zb, 0) >> 2;
-    } else {
-        int v[3];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) v[c] = vertex_index(g, x + ox[c], y + oy[c], zb + oz[c], axis[c]);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) out.faces[3 * ti + c] = v[c];
+        return;
     }
-}
-
-// A block takes kEmitThreads entries of the active-group list.  Phase 1, one thread per group: the keys of the vertices
-// the group owns, and one 8-byte record per *triangle* of its surface cubes (phase-1 slot, voxel, tiling, triangle number,
-// face index) pushed into a shared-memory list.  Phase 2, one thread per record: one triangle = three independent
-// vertex look-ups.  (r01 history: one warp per group / one lane per cube left 75-90 % of the lanes idle in the triangle
-// loop; one thread per cube record still walked up to 12 triangles x 3 dependent look-ups serially -- 47 % of the
-// kernel's stall samples were long-scoreboard waits inside that loop.)
-constexpr int kEmitThreads = 128;
-constexpr int kEmitCap = 2048;  // triangle records per round (16 KB); triangles beyond it are written by phase 1 directly
-static_assert(HV_MC_NUM_VARIANTS <= 1024 && kEmitThreads <= 128, "record packing: 7 bits slot, 5 voxel, 10 tiling, 4+ triangle");
-
-__global__ void __launch_bounds__(kEmitThreads) mc_emit_kernel(const McGrid g, const McEmit out) {
-    __shared__ uint2 s_tri[kEmitCap];
-    __shared__ int s_x[kEmitThreads], s_y[kEmitThreads], s_z0[kEmitThreads];
-    __shared__ unsigned int s_n;
-    const unsigned int n_active = *g.n_active;
-    for (unsigned int base = blockIdx.x * kEmitThreads; base < n_active; base += gridDim.x * kEmitThreads) {
-        if (threadIdx.x == 0) s_n = 0u;
-        __syncthreads();
-        const unsigned int a = base + threadIdx.x;
-        if (a < n_active) {
-            const unsigned int gi = g.active[a];
-            const uint2 cnt = g.gcount[gi];
-            const uint2 off = g.goff[gi];
-            const unsigned int col = gi / (unsigned int)g.G;
-            const int gq = (int)(gi - col * (unsigned int)g.G);
-            const int x = (int)(col / (unsigned int)g.Y), y = (int)(col - (unsigned int)x * (unsigned int)g.Y);
-            s_x[threadIdx.x] = x;
-            s_y[threadIdx.x] = y;
-            s_z0[threadIdx.x] = gq * 32;
-            if (cnt.x) {  // vertex keys, order inside the group: (voxel, axis)
-                const uint4 m = g.gmask[gi];
-                size_t vi = off.x;
-                for (unsigned int rest = m.x | m.y | m.z | m.w; rest; rest &= rest - 1) {
-                    const int k = __ffs(rest) - 1;
-                    const int zb = gq * 32 + k;
-                    if ((m.x >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 0);
-                    if ((m.y >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 1);
-                    if ((m.z >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 2);
-                    if ((m.w >> k) & 1u) out.vert_keys[vi++] = vertex_key(g, x, y, zb, 3);
-                }
-            }
-            if (cnt.y) {
-                const CubeWords c = load_cube_words(g, x, y, gq);
-                unsigned int toff = off.y;
-                for (unsigned int rest = c.active; rest; rest &= rest - 1) {
-                    const int k = __ffs(rest) - 1;
-                    const int variant = cube_variant_at(g, cube_index(c, k), x, y, gq * 32 + k);
-                    const unsigned int ntri = kMcVarNtri[variant];
-                    if (ntri == 0u) continue;
-                    const unsigned int slot = atomicAdd(&s_n, ntri);
-                    const unsigned int head = threadIdx.x | ((unsigned int)k << 7) | ((unsigned int)variant << 12);
-                    for (unsigned int j = 0; j < ntri; ++j) {
-                        if (slot + j < (unsigned int)kEmitCap)
-                            s_tri[slot + j] = make_uint2(head | (j << 22), toff + j);
-                        else
-                            emit_triangle(g, out, x, y, gq * 32 + k, variant, (int)j, toff + j);
-                    }
-                    toff += ntri;
-                }
-            }
-        }
-        __syncthreads();
-        const unsigned int n = min(s_n, (unsigned int)kEmitCap);
-        for (unsigned int i = threadIdx.x; i < n; i += kEmitThreads) {
-            const uint2 r = s_tri[i];
-            const unsigned int t = r.x & 127u;
-            emit_triangle(g, out, s_x[t], s_y[t], s_z0[t] + (int)((r.x >> 7) & 31u), (int)((r.x >> 12) & 1023u),
-                          (int)(r.x >> 22), r.y);
-        }
-        __syncthreads();
-    }
-}
-
-// ---- 5. vertices: position, normal, colour ----------------------------------------------------------------------------
-struct McVerts {
-    const unsigned long long* vert_keys;
-    long long n_verts;
-    float* verts_world;  // [V][3]
-    float* verts_voxel;  // [V][3] or null
-    float* normals;      // [V][3]
-    uint8_t* colors;     // [V][3] r, g, b
-    float voxel_size;
-    float origin[3];
-};
-
-// Adds `mult` times this cube's interpolated down-hill gradient at edge `e` (12 = centre) to the float32 accumulator.
-__device__ __forceinline__ void add_cube_gradient(const double v[8], int e, int mult, float acc[3]) {
-    if (mult == 0) return;
-    // weights 1 / (FLT_EPSILON + |v|): only the edge's two end corners are needed for e < 12 (all 8 for the centre);
-    // computing all eight per cube cost 32 double divisions per vertex (r01 ncu: mc_vertex_kernel 100 us)
-    double w[8];
-    int lo = 0, hi = 0, clo = 0, chi = 0;
-    if (e < 12) {
-        lo = kMcEdgeCorner[2 * e], hi = kMcEdgeCorner[2 * e + 1];
-        clo = kMcCornerOff[3 * lo] * 4 + kMcCornerOff[3 * lo + 1] * 2 + kMcCornerOff[3 * lo + 2];
-        chi = kMcCornerOff[3 * hi] * 4 + kMcCornerOff[3 * hi + 1] * 2 + kMcCornerOff[3 * hi + 2];
-        w[0] = 1.0 / ((double)FLT_EPSILON + fabs(v[lo]));
-        w[1] = 1.0 / ((double)FLT_EPSILON + fabs(v[hi]));
-    } else {
+    unsigned int v[3];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) w[i] = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
-    }
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int bitk = 4 >> k;  // offset bit of axis k in the d0*4 + d1*2 + d2 code
-        double gk;
+    for (int q = 0; q < 3; ++q) {
+        const int e = tri[q];
         if (e < 12) {
-            const double g_lo = v[kMcCornerAt[clo & ~bitk]] - v[kMcCornerAt[clo | bitk]];
-            const double g_hi = v[kMcCornerAt[chi & ~bitk]] - v[kMcCornerAt[chi | bitk]];
-            gk = __dadd_rn(__dmul_rn(g_lo, w[0]), __dmul_rn(g_hi, w[1]));
+            const int ox = kMcEdgeOwner[4 * e], oy = kMcEdgeOwner[4 * e + 1], oz = kMcEdgeOwner[4 * e + 2];
+            const unsigned int* bp = T.bits[(s0 + ox) % 3];
+            const unsigned int* bq = T.bits[(s0 + ox + 1) % 3];
+            v[q] = edge_vertex_index(g, bp, bq, T.vpre[(x + ox) & 1], x + ox, y + oy, c + oy, zb + oz, kMcEdgeOwner[4 * e + 3]);
         } else {
-            gk = 0.0;
-            for (int i = 0; i < 8; ++i) {
-                const int ci = kMcCornerOff[3 * i] * 4 + kMcCornerOff[3 * i + 1] * 2 + kMcCornerOff[3 * i + 2];
-                const double gi = v[kMcCornerAt[ci & ~bitk]] - v[kMcCornerAt[ci | bitk]];
-                gk = __dadd_rn(gk, __dmul_rn(w[i], gi));
-            }
+            const int t = c * g.G + gq;
+            v[q] = centre_base + T.cpre[t] + __popc(T.mw[t] & ((1u << k) - 1u));
         }
-        const float gf = (float)gk;
-        for (int j = 0; j < mult; ++j) acc[k] = __fadd_rn(acc[k], gf);
     }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) out.faces[3 * ti + q] = (int32_t)v[q];
 }
 
-__global__ void __launch_bounds__(128, 8) mc_vertex_kernel(const McGrid g, const McVerts out) {
-    const long long vi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (vi >= out.n_verts) return;
-    const unsigned long long key = out.vert_keys[vi];
-    const int axis = (int)(key & 3ull);
-    const unsigned long long lin = key >> 2;
-    // key -> (x, y, zg): 32-bit divisions whenever the linear index fits (volumes below 2^32 voxels); the four 64-bit
-    // divisions this replaces were ~400 instructions per vertex
-    long long zg;
-    int x, y;
-    if (lin < 0x100000000ull) {
-        const unsigned int l32 = (unsigned int)lin, c32 = l32 / (unsigned int)g.Zg;
-        zg = (long long)(l32 - c32 * (unsigned int)g.Zg);
-        x = (int)(c32 / (unsigned int)g.Y);
-        y = (int)(c32 - (unsigned int)x * (unsigned int)g.Y);
-    } else {
-        const unsigned long long col = lin / (unsigned long long)g.Zg;
-        zg = (long long)(lin - col * (unsigned long long)g.Zg);
-        x = (int)(col / (unsigned long long)g.Y);
-        y = (int)(col - (unsigned long long)x * (unsigned long long)g.Y);
-    }
-    const int zb = (int)(zg - g.zoff);
-    const int p[3] = {x, y, zb};
-    const int dim[3] = {g.X, g.Y, g.Zb};
+// Bits (i0 | i1 << 1 | ... ) -> Lewiner configuration index: corner i of the cube sits at cube-local (ia, ib, ic) along
+// (edge axis, lower other axis, upper other axis); kCornerPos[axis] holds ia * 4 + ib * 2 + ic for i = 0..7, 3 bits each.
+__device__ __forceinline__ unsigned int corner_positions(int axis) {
+    // corner offsets (axis0, axis1, axis2): 0:(0,0,0) 1:(0,0,1) 2:(0,1,1) 3:(0,1,0) 4:(1,0,0) 5:(1,0,1) 6:(1,1,1) 7:(1,1,0)
+    // axis 0: (ia, ib, ic) = (o0, o1, o2); axis 1: (o1, o0, o2); axis 2: (o2, o0, o1)   [tools/gen_mc_tables.py CORNERS]
+    return axis == 0 ? 0xdec4c8u : (axis == 1 ? 0xdda948u : 0x7f2360u);
+}
 
-    double pos[3] = {(double)x, (double)y, (double)zg};
-    float acc[3] = {0.0f, 0.0f, 0.0f};
-    double v[8];
-    if (axis == 3) {
-        load_cube_values(g, x, y, zb, v);
-        int idx = 0;
-        for (int i = 0; i < 8; ++i) idx |= (v[i] > 0.0 ? 1 : 0) << i;
-        const int variant = cube_variant(idx, v);
-        double f[3] = {0.0, 0.0, 0.0}, ff = 0.0;
-        for (int i = 0; i < 8; ++i) {
-            const double w = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
-            for (int k = 0; k < 3; ++k) f[k] = __dadd_rn(f[k], __dmul_rn((double)kMcCornerOff[3 * i + k], w));
-            ff = __dadd_rn(ff, w);
-        }
-        for (int k = 0; k < 3; ++k) pos[k] = __dadd_rn(pos[k], f[k] / ff);
-        add_cube_gradient(v, 12, (int)((kMcVarMult[variant] >> 48) & 15ull), acc);
-    } else {
-        int q[3] = {x, y, zb};
-        q[axis] += 1;
-        const double v_lo = (double)mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, zb) - g.level;
-        const double v_hi = (double)mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, q[0], q[1], q[2]) - g.level;
-        const double w_lo = 1.0 / ((double)FLT_EPSILON + fabs(v_lo)), w_hi = 1.0 / ((double)FLT_EPSILON + fabs(v_hi));
-        pos[axis] = __dadd_rn(pos[axis], w_hi / __dadd_rn(w_lo, w_hi));
-        // the (up to four) cubes around the edge, in scan order (axis0 outermost): larger offsets first
-        const int b = (axis == 0) ? 1 : 0, c = (axis == 2) ? 1 : 2;
-        for (int db = 1; db >= 0; --db) {
-            for (int dc = 1; dc >= 0; --dc) {
-                int base[3] = {p[0], p[1], p[2]};
-                base[b] -= db;
-                base[c] -= dc;
-                if (base[b] < 0 || base[c] < 0 || base[b] + 1 >= dim[b] || base[c] + 1 >= dim[c]) continue;
-                int d[3] = {0, 0, 0};
-                d[b] = db;
-                d[c] = dc;
-                const int e = kMcEdgeAt[axis * 8 + d[0] * 4 + d[1] * 2 + d[2]];
-                load_cube_values(g, base[0], base[1], base[2], v);
-                int idx = 0;
-                for (int i = 0; i < 8; ++i) idx |= (v[i] > 0.0 ? 1 : 0) << i;
-                const int variant = cube_variant(idx, v);
-                add_cube_gradient(v, e, (int)((kMcVarMult[variant] >> (4 * e)) & 15ull), acc);
+// One edge vertex (fusion.py:338-348 for one vertex): position on the edge, normal accumulated over the (up to four) cubes
+// around the edge in scan order, colour of the nearest voxel, world transform.  The edge's 2 x 3 x 3 neighbourhood lives in
+// registers in an edge-relative frame (a = along the edge, b < c the other two axes), so nothing is indexed dynamically.
+__device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& out, int x, int y, int zb, int axis, size_t vi) {
+    const int bax = axis == 0 ? 1 : 0, cax = axis == 2 ? 1 : 2;
+    const int pb = bax == 0 ? x : y, pc = cax == 1 ? y : zb;
+    const int db_dim = bax == 0 ? g.X : g.Y, dc_dim = cax == 1 ? g.Y : g.Zb;
+    float n[2][3][3];
+#pragma unroll
+    for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+        for (int ib = 0; ib < 3; ++ib)
+#pragma unroll
+            for (int ic = 0; ic < 3; ++ic) {
+                const int qb = pb + ib - 1, qc = pc + ic - 1;
+                float f = 0.0f;
+                if (qb >= 0 && qb < db_dim && qc >= 0 && qc < dc_dim) {
+                    // (x, y, zb) of the neighbour: the three coordinates are (a, b, c) permuted by `axis`
+                    const int qx = axis == 0 ? x + ia : qb;                      // bax == 0 whenever axis != 0
+                    const int qy = axis == 1 ? y + ia : (axis == 0 ? qb : qc);    // axis 0: b = y; axis 2: c = y
+                    const int qz = axis == 2 ? zb + ia : qc;                     // cax == 2 whenever axis != 2
+                    f = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, qx, qy, qz);
+                }
+                n[ia][ib][ic] = f;
+            }
+    const double level = g.level;
+    const double v_lo = (double)n[0][1][1] - level, v_hi = (double)n[1][1][1] - level;
+    const double w_lo = 1.0 / ((double)FLT_EPSILON + fabs(v_lo)), w_hi = 1.0 / ((double)FLT_EPSILON + fabs(v_hi));
+    const double frac = w_hi / __dadd_rn(w_lo, w_hi);
+    const unsigned int cpos = corner_positions(axis);
+    float acc_a = 0.0f, acc_b = 0.0f, acc_c = 0.0f;
+    // the cubes around the edge in scan order (axis0 outermost): larger offsets first; b is the lower axis
+#pragma unroll
+    for (int db = 1; db >= 0; --db) {
+#pragma unroll
+        for (int dc = 1; dc >= 0; --dc) {
+            const int bb = pb - db, bc = pc - dc;  // base of the cube along b, c
+            if (bb < 0 || bc < 0 || bb + 1 >= db_dim || bc + 1 >= dc_dim) continue;
+            // sign bits of the cube's corners at cube-local (ia, ib, ic)
+            unsigned int loc = 0;
+#pragma unroll
+            for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+                for (int ib = 0; ib < 2; ++ib)
+#pragma unroll
+                    for (int ic = 0; ic < 2; ++ic)
+                        loc |= (((double)n[ia][ib + 1 - db][ic + 1 - dc] - level) > 0.0 ? 1u : 0u) << (ia * 4 + ib * 2 + ic);
+            int idx = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) idx |= (int)((loc >> ((cpos >> (3 * i)) & 7u)) & 1u) << i;
+            int variant;
+            if (kMcAmbCount[idx] == 0 && kMcInteriorBase[idx] == 255) {
+                variant = kMcVariantBase[idx];
+            } else {
+                const int cx = axis == 0 ? x : bb;
+                const int cy = axis == 1 ? y : (axis == 0 ? bb : bc);
+                const int cz = axis == 2 ? zb : bc;
+                variant = cube_variant_ambiguous(g.tsdf, g.halo_lo, g.halo_hi, g.Y, g.pitch, g.Z, g.hl, g.level, idx, cx, cy, cz);
+            }
+            // the edge inside this cube: lower corner at cube-local (0, db, dc)
+            const int d0 = axis == 0 ? 0 : db, d1 = axis == 1 ? 0 : (axis == 0 ? db : dc), d2 = axis == 2 ? 0 : dc;
+            const int e = kMcEdgeAt[axis * 8 + d0 * 4 + d1 * 2 + d2];
+            const int mult = (int)((kMcVarMult[variant] >> (4 * e)) & 15ull);
+            if (mult == 0) continue;
+            // down-hill in-cube finite differences at the edge's two end corners, weighted like the position
+            const double ga = v_lo - v_hi;
+            const double gb_lo = ((double)n[0][1 - db][1] - level) - ((double)n[0][2 - db][1] - level);
+            const double gb_hi = ((double)n[1][1 - db][1] - level) - ((double)n[1][2 - db][1] - level);
+            const double gc_lo = ((double)n[0][1][1 - dc] - level) - ((double)n[0][1][2 - dc] - level);
+            const double gc_hi = ((double)n[1][1][1 - dc] - level) - ((double)n[1][1][2 - dc] - level);
+            const float fa = (float)__dadd_rn(__dmul_rn(ga, w_lo), __dmul_rn(ga, w_hi));
+            const float fb = (float)__dadd_rn(__dmul_rn(gb_lo, w_lo), __dmul_rn(gb_hi, w_hi));
+            const float fc = (float)__dadd_rn(__dmul_rn(gc_lo, w_lo), __dmul_rn(gc_hi, w_hi));
+            for (int j = 0; j < mult; ++j) {
+                acc_a = __fadd_rn(acc_a, fa);
+                acc_b = __fadd_rn(acc_b, fb);
+                acc_c = __fadd_rn(acc_c, fc);
             }
         }
     }
+    float acc[3];
+    acc[0] = axis == 0 ? acc_a : acc_b;                     // axis 0 is a for axis 0, else b
+    acc[1] = axis == 1 ? acc_a : (axis == 0 ? acc_b : acc_c);  // axis 1: a for axis 1, b for axis 0, c for axis 2
+    acc[2] = axis == 2 ? acc_a : acc_c;
+    const long long zg = (long long)zb + g.zoff;
+    double pos[3] = {(double)x, (double)y, (double)zg};
+    if (axis == 0) pos[0] = __dadd_rn(pos[0], frac);
+    else if (axis == 1) pos[1] = __dadd_rn(pos[1], frac);
+    else pos[2] = __dadd_rn(pos[2], frac);
     const float pv[3] = {(float)pos[0], (float)pos[1], (float)pos[2]};
     const double len = sqrt(__dadd_rn(__dadd_rn(__dmul_rn((double)acc[0], (double)acc[0]), __dmul_rn((double)acc[1], (double)acc[1])),
                                       __dmul_rn((double)acc[2], (double)acc[2])));
-    if (len > 0.0)
+    if (len > 0.0) {
+#pragma unroll
         for (int k = 0; k < 3; ++k) acc[k] = (float)((double)acc[k] / len);
+    }
     // colour of the nearest voxel (fusion.py:339,343-348), half-to-even like np.round
     const int i0 = (int)rintf(pv[0]), i1 = (int)rintf(pv[1]);
     const int i2 = (int)((long long)rintf(pv[2]) - g.zoff);
     const unsigned int packed = (unsigned int)mc_fetch(g, g.color, g.chalo_lo, g.chalo_hi, i0, i1, i2);
+#pragma unroll
     for (int k = 0; k < 3; ++k) {
         out.verts_world[3 * vi + k] = __fadd_rn(__fmul_rn(pv[k], out.voxel_size), out.origin[k]);  // fusion.py:340
         if (out.verts_voxel) out.verts_voxel[3 * vi + k] = pv[k];
@@ -668,6 +752,175 @@ __global__ void __launch_bounds__(128, 8) mc_vertex_kernel(const McGrid g, const
     out.colors[3 * vi + 0] = (uint8_t)(packed & 255u);
     out.colors[3 * vi + 1] = (uint8_t)((packed >> 8) & 255u);
     out.colors[3 * vi + 2] = (uint8_t)((packed >> 16) & 255u);
+    if (out.vert_keys) out.vert_keys[vi] = vertex_key(g, x, y, zb, axis);
+}
+
+// Adds `mult` times this cube's interpolated down-hill gradient at the centre vertex to the float32 accumulator.
+__device__ __noinline__ void emit_centre_vertex(const McGrid& g, const McEmit& out, int x, int y, int zb, size_t vi) {
+    double v[8];
+    load_cube_values(g, x, y, zb, v);
+    int idx = 0;
+    for (int i = 0; i < 8; ++i) idx |= (v[i] > 0.0 ? 1 : 0) << i;
+    const int variant = cube_variant(idx, v);
+    const int mult = (int)((kMcVarMult[variant] >> 48) & 15ull);
+    double w[8], f[3] = {0.0, 0.0, 0.0}, ff = 0.0;
+    for (int i = 0; i < 8; ++i) {
+        w[i] = 1.0 / ((double)FLT_EPSILON + fabs(v[i]));
+        for (int k = 0; k < 3; ++k) f[k] = __dadd_rn(f[k], __dmul_rn((double)kMcCornerOff[3 * i + k], w[i]));
+        ff = __dadd_rn(ff, w[i]);
+    }
+    const long long zg = (long long)zb + g.zoff;
+    double pos[3] = {(double)x, (double)y, (double)zg};
+    float acc[3] = {0.0f, 0.0f, 0.0f};
+    for (int k = 0; k < 3; ++k) {
+        pos[k] = __dadd_rn(pos[k], f[k] / ff);
+        const int bitk = 4 >> k;  // offset bit of axis k in the d0*4 + d1*2 + d2 code
+        double gk = 0.0;
+        for (int i = 0; i < 8; ++i) {
+            const int ci = kMcCornerOff[3 * i] * 4 + kMcCornerOff[3 * i + 1] * 2 + kMcCornerOff[3 * i + 2];
+            const double gi = v[kMcCornerAt[ci & ~bitk]] - v[kMcCornerAt[ci | bitk]];
+            gk = __dadd_rn(gk, __dmul_rn(w[i], gi));
+        }
+        const float gf = (float)gk;
+        for (int j = 0; j < mult; ++j) acc[k] = __fadd_rn(acc[k], gf);
+    }
+    const float pv[3] = {(float)pos[0], (float)pos[1], (float)pos[2]};
+    const double len = sqrt(__dadd_rn(__dadd_rn(__dmul_rn((double)acc[0], (double)acc[0]), __dmul_rn((double)acc[1], (double)acc[1])),
+                                      __dmul_rn((double)acc[2], (double)acc[2])));
+    if (len > 0.0)
+        for (int k = 0; k < 3; ++k) acc[k] = (float)((double)acc[k] / len);
+    const int i0 = (int)rintf(pv[0]), i1 = (int)rintf(pv[1]);
+    const int i2 = (int)((long long)rintf(pv[2]) - g.zoff);
+    const unsigned int packed = (unsigned int)mc_fetch(g, g.color, g.chalo_lo, g.chalo_hi, i0, i1, i2);
+    for (int k = 0; k < 3; ++k) {
+        out.verts_world[3 * vi + k] = __fadd_rn(__fmul_rn(pv[k], out.voxel_size), out.origin[k]);
+        if (out.verts_voxel) out.verts_voxel[3 * vi + k] = pv[k];
+        out.normals[3 * vi + k] = acc[k];
+    }
+    out.colors[3 * vi + 0] = (uint8_t)(packed & 255u);
+    out.colors[3 * vi + 1] = (uint8_t)((packed >> 8) & 255u);
+    out.colors[3 * vi + 2] = (uint8_t)((packed >> 16) & 255u);
+    if (out.vert_keys) out.vert_keys[vi] = vertex_key(g, x, y, zb, 3);
+}
+
+__global__ void __launch_bounds__(kSweepThreads, 2) mc_emit_kernel(const McGrid g, const McEmit out) {
+    extern __shared__ unsigned int s_mem[];
+    EmitTables T;
+    {
+        const int tabw = (g.TY + 2) * g.GP, vw = (g.TY + 1) * g.G, ow = g.TY * g.G;
+        unsigned int* p = s_mem;
+        for (int i = 0; i < 3; ++i, p += tabw) T.bits[i] = p;
+        for (int i = 0; i < 2; ++i, p += vw) T.vpre[i] = p;
+        T.tpre = p; p += ow;
+        T.cpre = p; p += ow;
+        T.cnt = p; p += ow;
+        T.mw = p; p += ow;
+        T.s_warp = p; p += 8;
+        T.s_misc = p; p += 8;
+        T.rec = reinterpret_cast<uint2*>(p + ((reinterpret_cast<uintptr_t>(p) & 4) ? 1 : 0));
+    }
+    const int strip = blockIdx.x % g.S, chunk = blockIdx.x / g.S;
+    const int y0 = strip * g.TY, ny = min(g.TY, g.Y - y0);
+    const int xa = chunk * out.CX, xb = min(g.X, xa + out.CX);
+    const int n_own = ny * g.G;
+    const unsigned int n_edge_total = (unsigned int)g.totals[4];
+    int held_bits[3] = {-1, -1, -1}, held_v[2] = {-1, -1};
+    for (int x = xa; x < xb; ++x) {
+        const uint4 rt = g.run_tot[(size_t)x * g.S + strip];
+        if ((rt.x | rt.y | rt.z) == 0u) continue;  // nothing owned by this run (uniform over the block)
+        __syncthreads();                           // the previous plane's readers are done with the tables
+        for (int d = 0; d < 3; ++d)
+            if (held_bits[(x + d) % 3] != x + d) {
+                emit_load_bits(g, T.bits[(x + d) % 3], x + d, y0);
+                held_bits[(x + d) % 3] = x + d;
+            }
+        for (int d = 0; d < 2; ++d)
+            if (held_v[(x + d) & 1] != x + d) {
+                emit_build_vpre(g, T, T.vpre[(x + d) & 1], x + d, strip, y0, ny);
+                held_v[(x + d) & 1] = x + d;
+            }
+        emit_build_own(g, T, x, y0, ny);
+        __syncthreads();
+        const uint4 rb = g.run_base[(size_t)x * g.S + strip];
+        const unsigned int run_nv = T.s_misc[2], run_nt = T.s_misc[3], run_nc = T.s_misc[4];
+        const int s0 = x % 3;
+        const unsigned int* B0 = T.bits[s0];
+        const unsigned int* B1 = T.bits[(s0 + 1) % 3];
+        // ---- triangles: one record per triangle, then one thread per record
+        for (unsigned int lo = 0; lo < run_nt; lo += kRecCap) {
+            const unsigned int hi = lo + kRecCap;
+            for (int t = threadIdx.x; t < n_own; t += kSweepThreads) {
+                const unsigned int nt = T.cnt[t] >> 16;
+                unsigned int o = T.tpre[t];
+                if (nt == 0u || o + nt <= lo || o >= hi) continue;
+                const int c = t / g.G, gq = t - c * g.G;
+                const CubeWords w = cube_words(g, B0, B1, x, y0 + c, c, gq);
+                unsigned int mw = 0u;
+                for (unsigned int rest = w.active; rest; rest &= rest - 1) {
+                    const int k = __ffs(rest) - 1;
+                    const int variant = cube_variant_at(g, cube_index(w, k), x, y0 + c, gq * 32 + k);
+                    const unsigned int ntri = kMcVarNtri[variant];
+                    if ((kMcVarMult[variant] >> 48) & 15ull) mw |= 1u << k;
+                    const unsigned int head = (unsigned int)c | ((unsigned int)gq << 5) | ((unsigned int)k << 13) |
+                                              ((unsigned int)variant << 18);
+                    for (unsigned int j = 0; j < ntri; ++j)
+                        if (o + j >= lo && o + j < hi) T.rec[o + j - lo] = make_uint2(head | (j << 28), o + j);
+                    o += ntri;
+                }
+                T.mw[t] = mw;
+            }
+            __syncthreads();
+            const unsigned int n = min(run_nt - lo, (unsigned int)kRecCap);
+            for (unsigned int i = threadIdx.x; i < n; i += kSweepThreads)
+                emit_triangle(g, out, T, s0, x, y0, T.rec[i], rb.y, n_edge_total + rb.z);
+            __syncthreads();
+        }
+        // ---- edge vertices
+        for (unsigned int lo = 0; lo < run_nv; lo += kRecCap) {
+            const unsigned int hi = lo + kRecCap;
+            for (int t = threadIdx.x; t < n_own; t += kSweepThreads) {
+                const unsigned int nv = T.cnt[t] & 255u;
+                unsigned int o = T.vpre[x & 1][t] - rb.x;  // run-local
+                if (nv == 0u || o + nv <= lo || o >= hi) continue;
+                const int c = t / g.G, gq = t - c * g.G;
+                const CubeWords w = cube_words(g, B0, B1, x, y0 + c, c, gq);
+                const unsigned int head = (unsigned int)c | ((unsigned int)gq << 5);
+                for (unsigned int rest = w.mx | w.my | w.mz; rest; rest &= rest - 1) {
+                    const int k = __ffs(rest) - 1;
+#pragma unroll
+                    for (int axis = 0; axis < 3; ++axis) {
+                        const unsigned int m = axis == 0 ? w.mx : (axis == 1 ? w.my : w.mz);
+                        if ((m >> k) & 1u) {
+                            if (o >= lo && o < hi) T.rec[o - lo] = make_uint2(head | ((unsigned int)k << 13) | ((unsigned int)axis << 18), o);
+                            ++o;
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+            const unsigned int n = min(run_nv - lo, (unsigned int)kRecCap);
+            for (unsigned int i = threadIdx.x; i < n; i += kSweepThreads) {
+                const uint2 r = T.rec[i];
+                const size_t vi = (size_t)rb.x + r.y;
+                if ((long long)vi < out.cap_verts)
+                    emit_edge_vertex(g, out, x, y0 + (int)(r.x & 31u), (int)((r.x >> 5) & 255u) * 32 + (int)((r.x >> 13) & 31u),
+                                     (int)((r.x >> 18) & 3u), vi);
+            }
+            __syncthreads();
+        }
+        // ---- cube-centre vertices (tilings 6.1.2, 7.3, 10.2, 12.2, 13.3, 13.4): after all edge vertices
+        if (run_nc) {
+            for (int t = threadIdx.x; t < n_own; t += kSweepThreads) {
+                unsigned int m = ((T.cnt[t] >> 8) & 255u) ? T.mw[t] : 0u;
+                unsigned int o = T.cpre[t];
+                const int c = t / g.G, gq = t - c * g.G;
+                for (; m; m &= m - 1, ++o) {
+                    const size_t vi = (size_t)n_edge_total + rb.z + o;
+                    if ((long long)vi < out.cap_verts) emit_centre_vertex(g, out, x, y0 + c, gq * 32 + (__ffs(m) - 1), vi);
+                }
+            }
+        }
+    }
 }
 
 }  // namespace hv
@@ -676,9 +929,9 @@ __global__ void __launch_bounds__(128, 8) mc_vertex_kernel(const McGrid g, const
 namespace {
 
 struct McLayout {
-    long long n_groups;
-    int G, Zb, n_scan_blocks;
-    size_t off_bits, off_gmask, off_gcount, off_goff, off_bsum, off_active, off_nactive, total;
+    long long n_groups, n_runs;
+    int G, Zb, TY, S, GP;
+    size_t off_bits, off_gcnt, off_run_tot, off_run_base, total;
 };
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -690,24 +943,26 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
                "marching cubes: bad dims %lld x %lld x %lld", (long long)X, (long long)Y, (long long)Z);
     L->Zb = (int)Z + (lo ? 1 : 0) + (hi ? 1 : 0);
     L->G = (L->Zb + 31) / 32;
+    HV_REQUIRE(L->G <= 256, "marching cubes: more than 8192 voxels along axis 2 per shard (%d): cut the volume into z-slabs", L->Zb);
     L->n_groups = (long long)X * Y * L->G;
-    HV_REQUIRE(L->n_groups < (1ll << 32) && L->Zb < (1 << 22), "marching cubes: volume too large");
-    L->n_scan_blocks = (int)hv::scan_scratch_pairs(L->n_groups);
+    HV_REQUIRE(L->n_groups < (1ll << 32), "marching cubes: volume too large");
+    int ty = 512 / L->G;  // about two rounds of the 256 threads per plane of a strip
+    ty = ty < 1 ? 1 : (ty > 30 ? 30 : ty);
+    if (ty > Y) ty = (int)Y;
+    L->TY = ty;
+    L->S = (int)((Y + ty - 1) / ty);
+    L->GP = L->G + 2;
+    L->n_runs = (long long)X * L->S;
+    HV_REQUIRE(L->n_runs < (1ll << 31), "marching cubes: too many runs");
     size_t o = 0;
-    L->off_gmask = o;  // 16-byte elements first
-    o = align_up(o + (size_t)L->n_groups * sizeof(uint4));
-    L->off_gcount = o;
-    o = align_up(o + (size_t)L->n_groups * sizeof(uint2));
-    L->off_goff = o;
-    o = align_up(o + (size_t)L->n_groups * sizeof(uint2));
+    L->off_run_tot = o;
+    o = align_up(o + (size_t)L->n_runs * sizeof(uint4));
+    L->off_run_base = o;
+    o = align_up(o + (size_t)L->n_runs * sizeof(uint4));
     L->off_bits = o;
     o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
-    L->off_bsum = o;
-    o = align_up(o + (size_t)L->n_scan_blocks * sizeof(uint2));
-    L->off_active = o;
+    L->off_gcnt = o;
     o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
-    L->off_nactive = o;
-    o = align_up(o + sizeof(unsigned int));
     L->total = o;
     return HV_OK;
 }
@@ -740,16 +995,24 @@ int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float*
     g->zoff = -(long long)g->hl;
     g->Zg = g->Z;
     g->level = level;
+    g->TY = L->TY;
+    g->S = L->S;
+    g->GP = L->GP;
     g->bits = reinterpret_cast<unsigned int*>(s + L->off_bits);
-    g->gmask = reinterpret_cast<uint4*>(s + L->off_gmask);
-    g->gcount = reinterpret_cast<uint2*>(s + L->off_gcount);
-    g->goff = reinterpret_cast<uint2*>(s + L->off_goff);
-    g->bsum = reinterpret_cast<uint2*>(s + L->off_bsum);
-    g->active = reinterpret_cast<unsigned int*>(s + L->off_active);
-    g->n_active = reinterpret_cast<unsigned int*>(s + L->off_nactive);
+    g->gcnt = reinterpret_cast<unsigned int*>(s + L->off_gcnt);
+    g->run_tot = reinterpret_cast<uint4*>(s + L->off_run_tot);
+    g->run_base = reinterpret_cast<uint4*>(s + L->off_run_base);
     g->totals = nullptr;
     g->n_groups = L->n_groups;
     return HV_OK;
+}
+
+// planes per chunk so that about `target` CTAs exist
+int planes_per_chunk(int X, int S, long long target) {
+    long long chunks = (target + S - 1) / S;
+    if (chunks < 1) chunks = 1;
+    if (chunks > X) chunks = X;
+    return (int)((X + chunks - 1) / chunks);
 }
 
 }  // namespace
@@ -773,21 +1036,14 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     HV_REQUIRE(totals, "hv_mc_count: null totals");
     g.totals = totals;
     cudaStream_t st = hv::as_stream(stream);
-    hv::mc_init_kernel<<<1, 32, 0, st>>>(totals, g.n_active);  // (a pageable H2D of the four counters would block the host)
+    hv::mc_init_kernel<<<1, 32, 0, st>>>(totals);  // (a pageable H2D of the counters would block the host)
     const int sms = hv::device_info().sm_count;
-    hv::McSignGeom sg;
-    sg.segs = (g.Zb + 127) / 128;
-    const long long n_tiles = (long long)g.X * g.Y * sg.segs;
-    HV_REQUIRE(n_tiles < (1ll << 31), "hv_mc_count: too many columns");
-    sg.n_tiles = (int)n_tiles;
-    sg.vec = (!halo_lo && (pitch & 3) == 0 && ((uintptr_t)tsdf & 15) == 0) ? 1 : 0;
-    const long long want = ((long long)g.X * g.Y + 7) / 8;  // 8 warps per block, a warp per column (grid-stride)
-    const long long cap = (long long)sms * 8;
-    const int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
-    hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g, sg);
-    const unsigned int group_blocks = (unsigned int)((g.n_groups + 255) / 256);
-    hv::mc_count_kernel<<<group_blocks, 256, 0, st>>>(g);
-    hv::exclusive_scan_u2(g.gcount, g.goff, g.bsum, g.n_groups, totals, st);
+    const int vec = (!halo_lo && (pitch & 3) == 0 && ((uintptr_t)tsdf & 15) == 0) ? 1 : 0;
+    const int CX = planes_per_chunk(g.X, g.S, (long long)sms * 4);
+    const int chunks = (g.X + CX - 1) / CX;
+    const size_t smem = (size_t)2 * (g.TY + 2) * g.GP * sizeof(unsigned int);
+    hv::mc_classify_kernel<<<(unsigned int)(g.S * chunks), hv::kSweepThreads, smem, st>>>(g, CX, vec);
+    hv::mc_run_scan_kernel<<<1, hv::kRunScanThreads, 0, st>>>(g.run_tot, g.run_base, (int)L.n_runs, totals);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }
@@ -798,14 +1054,14 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
                           float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
                           float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces,
                           unsigned long long* face_keys, unsigned long long* face_cubes, unsigned long long* vert_keys,
-                          void* stream) {
+                          unsigned long long* totals, void* stream) {
     hv::McGrid g;
     McLayout L;
     int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, &L);
     if (rc != HV_OK) return rc;
     HV_REQUIRE(n_verts >= 0 && n_tris >= 0 && n_verts < (1ll << 31) && n_tris < (1ll << 31), "hv_mc_emit: bad counts");
-    if (n_verts == 0 && n_tris == 0) return HV_OK;  // a shard the surface does not cross
-    HV_REQUIRE(color && h_origin && vert_keys && verts_world && normals && colors, "hv_mc_emit: null pointer");
+    if (n_verts == 0 && n_tris == 0) return HV_OK;  // a shard the surface does not cross / no capacity at all
+    HV_REQUIRE(color && h_origin && verts_world && normals && colors && totals, "hv_mc_emit: null pointer");
     HV_REQUIRE((faces != nullptr) != (face_keys != nullptr), "hv_mc_emit: pass exactly one of faces / face_keys");
     HV_REQUIRE((halo_lo != nullptr) == (color_halo_lo != nullptr) && (halo_hi != nullptr) == (color_halo_hi != nullptr),
                "hv_mc_emit: tsdf and colour halos must come in pairs");
@@ -816,34 +1072,35 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     g.chalo_hi = color_halo_hi;
     g.zoff = z_global_offset - g.hl;
     g.Zg = z_global_dim;
+    g.totals = totals;
     cudaStream_t st = hv::as_stream(stream);
-    hv::McEmit em{faces, face_keys, vert_keys, face_keys ? face_cubes : nullptr};
-    // one thread per active group; the list length lives on the device, so size the grid by what the outputs imply
-    long long emit_groups = n_verts + n_tris;  // >= number of active groups
-    if (emit_groups > g.n_groups) emit_groups = g.n_groups;
-    const long long max_blocks = (long long)hv::device_info().sm_count * 8;
-    long long emit_blocks = (emit_groups + hv::kEmitThreads - 1) / hv::kEmitThreads;
-    if (emit_blocks > max_blocks) emit_blocks = max_blocks;
-    if (emit_blocks < 1) emit_blocks = 1;
-    hv::mc_emit_kernel<<<(unsigned int)emit_blocks, hv::kEmitThreads, 0, st>>>(g, em);
-    if (n_verts > 0) {
-        hv::McVerts mv;
-        mv.vert_keys = vert_keys;
-        mv.n_verts = n_verts;
-        mv.verts_world = verts_world;
-        mv.verts_voxel = verts_voxel;
-        mv.normals = normals;
-        mv.colors = colors;
-        mv.voxel_size = voxel_size;
-        for (int k = 0; k < 3; ++k) mv.origin[k] = h_origin[k];
-        hv::mc_vertex_kernel<<<(unsigned int)((n_verts + 127) / 128), 128, 0, st>>>(g, mv);
-    }
+    hv::McEmit em;
+    em.faces = faces;
+    em.face_keys = face_keys;
+    em.vert_keys = vert_keys;
+    em.face_cubes = face_keys ? face_cubes : nullptr;
+    em.verts_world = verts_world;
+    em.verts_voxel = verts_voxel;
+    em.normals = normals;
+    em.colors = colors;
+    em.cap_verts = n_verts;
+    em.cap_tris = n_tris;
+    em.voxel_size = voxel_size;
+    for (int k = 0; k < 3; ++k) em.origin[k] = h_origin[k];
+    const int sms = hv::device_info().sm_count;
+    em.CX = planes_per_chunk(g.X, g.S, (long long)sms * 16);
+    if (em.CX < 4 && g.X >= 4) em.CX = 4;
+    const int chunks = (g.X + em.CX - 1) / em.CX;
+    const size_t words = (size_t)3 * (g.TY + 2) * g.GP + (size_t)2 * (g.TY + 1) * g.G + (size_t)4 * g.TY * g.G + 16 + 2;
+    const size_t smem = words * sizeof(unsigned int) + (size_t)hv::kRecCap * sizeof(uint2);
+    HV_REQUIRE(smem <= 48 * 1024, "hv_mc_emit: %lld bytes of shared memory", (long long)smem);
+    hv::mc_emit_kernel<<<(unsigned int)(g.S * chunks), hv::kSweepThreads, smem, st>>>(g, em);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }
 
 // Count + emit in one call: the only host round trip (the output sizes are data dependent) is a stream synchronise on
-// four counters copied into the caller's pinned `h_totals`; the caller provides output buffers with a capacity and gets
+// the counters copied into the caller's pinned `h_totals`; the caller provides output buffers with a capacity and gets
 // HV_E_CAPACITY (with h_totals filled, scratch still valid for a plain hv_mc_emit) if the surface is larger.
 extern "C" int hv_mc_extract(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
                              const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
@@ -883,5 +1140,5 @@ extern "C" int hv_mc_extract(const float* tsdf, const float* halo_lo, const floa
     }
     return hv_mc_emit(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch,
                       scratch_bytes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris, verts_world,
-                      verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys, stream);
+                      verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys, totals, stream);
 }

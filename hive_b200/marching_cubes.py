@@ -18,8 +18,8 @@ from . import _lib
 from . import _xfer
 
 
-#: kernels launched by one extraction (init, sign, count, scan x3, emit, vertex); bench.py reports it
-LAUNCHES_PER_EXTRACTION = 8
+#: kernels launched by one extraction (init, classify, run scan, emit); bench.py reports it
+LAUNCHES_PER_EXTRACTION = 4
 
 
 def _ptr(t):
@@ -60,7 +60,7 @@ def _pinned_totals(torch, device):
     key = (threading.get_ident(), str(device))
     buf = _PINNED.get(key)
     if buf is None:
-        buf = _PINNED[key] = torch.empty(4, dtype=torch.int64).pin_memory()
+        buf = _PINNED[key] = torch.empty(8, dtype=torch.int64).pin_memory()
     return buf
 
 
@@ -88,7 +88,7 @@ class McPlan:
             self.scratch = torch.empty(self.scratch_bytes + 256, dtype=torch.uint8, device=self.device)
             pad = (-self.scratch.data_ptr()) % 256
             self.scratch_ptr = ctypes.c_void_p(self.scratch.data_ptr() + pad)
-            self.totals = torch.zeros(4, dtype=torch.int64, device=self.device)
+            self.totals = torch.zeros(8, dtype=torch.int64, device=self.device)
 
     def count(self):
         """Launch the classification; returns the device tensor of totals (no sync)."""
@@ -109,7 +109,7 @@ class McPlan:
         with torch.cuda.device(self.device):
             host.copy_(self.totals, non_blocking=True)
             torch.cuda.current_stream().synchronize()
-        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist())
+        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist()[:4])
         return n_verts, n_tris, _key_to_float(kmin), _key_to_float(kmax)
 
     def emit(self, n_verts, n_tris, voxel_size, origin, want_voxel=False, keys=False) -> DeviceMesh:
@@ -121,7 +121,7 @@ class McPlan:
             verts_voxel = torch.empty((n_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
             normals = torch.empty((n_verts, 3), dtype=torch.float32, device=dev)
             colors = torch.empty((n_verts, 3), dtype=torch.uint8, device=dev)
-            vert_keys = torch.empty((max(n_verts, 1),), dtype=torch.int64, device=dev)
+            vert_keys = torch.empty((max(n_verts, 1),), dtype=torch.int64, device=dev) if keys else None
             faces = None if keys else torch.empty((n_tris, 3), dtype=torch.int32, device=dev)
             face_keys = torch.empty((n_tris, 3), dtype=torch.int64, device=dev) if keys else None
             face_cubes = torch.empty((n_tris,), dtype=torch.int64, device=dev) if keys else None
@@ -132,8 +132,9 @@ class McPlan:
                 ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
                 self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
                 origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
-                _ptr(colors), _ptr(faces), _ptr(face_keys), _ptr(face_cubes), _ptr(vert_keys), stream))
-        return DeviceMesh(verts, verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys[:n_verts], 0.0, 0.0)
+                _ptr(colors), _ptr(faces), _ptr(face_keys), _ptr(face_cubes), _ptr(vert_keys), _ptr(self.totals), stream))
+        return DeviceMesh(verts, verts_voxel, normals, colors, faces, face_keys, face_cubes,
+                          vert_keys[:n_verts] if keys else None, 0.0, 0.0)
 
 
     def extract(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
@@ -148,7 +149,6 @@ class McPlan:
             verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
             normals = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
             colors = torch.empty((cap_verts, 3), dtype=torch.uint8, device=dev)
-            vert_keys = torch.empty((max(cap_verts, 1),), dtype=torch.int64, device=dev)
             faces = torch.empty((cap_tris, 3), dtype=torch.int32, device=dev)
             stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
             rc = self._lib.hv_mc_extract(
@@ -157,22 +157,24 @@ class McPlan:
                 ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
                 self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
                 origin.ctypes.data_as(ctypes.c_void_p), cap_verts, cap_tris, _ptr(verts), _ptr(verts_voxel),
-                _ptr(normals), _ptr(colors), _ptr(faces), None, None, _ptr(vert_keys), _ptr(self.totals),
+                _ptr(normals), _ptr(colors), _ptr(faces), None, None, None, _ptr(self.totals),
                 ctypes.c_void_p(host.data_ptr()), stream)
-        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist())
+        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist()[:4])
         vmin, vmax = _key_to_float(kmin), _key_to_float(kmax)
         if rc == _lib.HV_E_CAPACITY:
             mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
         else:
             _lib.check(rc)
             mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
-                              colors[:n_verts], faces[:n_tris], None, None, vert_keys[:n_verts], 0.0, 0.0)
+                              colors[:n_verts], faces[:n_tris], None, None, None, 0.0, 0.0)
         mesh.vmin, mesh.vmax = vmin, vmax
         return mesh
 
-    def extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
-        """count -> (allocate the outputs while the classification kernels run) -> read the totals -> emit.  Same result as
-        ``extract``; the output allocations no longer sit between the caller and the first kernel."""
+    def extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False, speculative=False) -> DeviceMesh:
+        """count -> (allocate the outputs while the classification runs) -> emit.  ``speculative``: the capacity comes from
+        an earlier extraction of the same volume, so emit is launched right behind the classification and the totals are
+        read afterwards -- no host round trip between the kernels; a surface that outgrew the capacity is emitted again
+        into exactly sized buffers."""
         torch = self._torch
         dev = self.device
         self.count()
@@ -181,14 +183,10 @@ class McPlan:
             verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
             normals = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
             colors = torch.empty((cap_verts, 3), dtype=torch.uint8, device=dev)
-            vert_keys = torch.empty((max(cap_verts, 1),), dtype=torch.int64, device=dev)
             faces = torch.empty((cap_tris, 3), dtype=torch.int32, device=dev)
-        n_verts, n_tris, vmin, vmax = self.read_totals()
-        check_surface(self.level, vmin, vmax, n_verts)
-        if n_verts > cap_verts or n_tris > cap_tris:
-            mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
-        else:
-            origin = np.ascontiguousarray(origin, dtype=np.float32)
+        origin = np.ascontiguousarray(origin, dtype=np.float32)
+
+        def launch():
             with torch.cuda.device(dev):
                 stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
                 _lib.check(self._lib.hv_mc_emit(
@@ -196,10 +194,20 @@ class McPlan:
                     _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
                     ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
                     self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
-                    origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
-                    _ptr(colors), _ptr(faces), None, None, _ptr(vert_keys), stream))
+                    origin.ctypes.data_as(ctypes.c_void_p), cap_verts, cap_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
+                    _ptr(colors), _ptr(faces), None, None, None, _ptr(self.totals), stream))
+
+        if speculative:
+            launch()
+        n_verts, n_tris, vmin, vmax = self.read_totals()
+        check_surface(self.level, vmin, vmax, n_verts)
+        if n_verts > cap_verts or n_tris > cap_tris:
+            mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
+        else:
+            if not speculative:
+                launch()
             mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
-                              colors[:n_verts], faces[:n_tris], None, None, vert_keys[:n_verts], 0.0, 0.0)
+                              colors[:n_verts], faces[:n_tris], None, None, None, 0.0, 0.0)
         mesh.vmin, mesh.vmax = vmin, vmax
         return mesh
 
@@ -232,7 +240,8 @@ def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
         guess = (6 * area, 12 * area)
     cap_v = min(guess[0], 3 * X * Y * Z)
     cap_t = min(guess[1], 5 * X * Y * Z)
-    mesh = plan.extract_overlapped(vol._voxel_size, vol._vol_origin, cap_v, cap_t, want_voxel=want_voxel)
+    mesh = plan.extract_overlapped(vol._voxel_size, vol._vol_origin, cap_v, cap_t, want_voxel=want_voxel,
+                                   speculative=(X, Y, Z) in _LAST_SIZES)
     n_v, n_t = int(mesh.verts.shape[0]), int(mesh.faces.shape[0])
     _LAST_SIZES[(X, Y, Z)] = (n_v + n_v // 2 + 1024, n_t + n_t // 2 + 1024)
     return mesh
@@ -258,7 +267,7 @@ def marching_cubes(volume, level=None, *, spacing=(1., 1., 1.), gradient_directi
     """
     torch = _lib.require_cuda()
     if (tuple(spacing) != (1., 1., 1.) or gradient_direction != 'descent' or step_size != 1 or not allow_degenerate
-            or mask is not None or method not in ('lewiner', '_lorensen', 'lorensen')):
+            or mask is not None or method != 'lewiner'):
         raise NotImplementedError("hive_b200.marching_cubes supports the reference's call only (fusion.py:338)")
     volume = np.asarray(volume)
     if volume.ndim != 3:

@@ -308,6 +308,8 @@ def stitch_mesh_parts(parts):
     sorted by the cube that produced them (stable: the in-cube triangle order is kept), face keys -> vertex indices."""
     import torch
     keys = torch.cat([p["vert_keys"] for p in parts])
+    # whole-volume vertex order: lattice-edge vertices by key, then the vertices inside cubes (axis 3) by cube
+    keys = keys + ((keys & 3) == 3).to(keys.dtype) * (1 << 62)
     order = torch.argsort(keys, stable=True)
     sorted_keys = keys[order]
     assert bool((sorted_keys[1:] != sorted_keys[:-1]).all()), "a seam vertex was emitted by two slabs"
@@ -318,6 +320,7 @@ def stitch_mesh_parts(parts):
     face_cubes = torch.cat([p["face_cubes"] for p in parts])
     forder = torch.argsort(face_cubes, stable=True)
     face_keys = face_keys[forder]
+    face_keys = face_keys + ((face_keys & 3) == 3).to(face_keys.dtype) * (1 << 62)
     idx = torch.searchsorted(sorted_keys, face_keys.reshape(-1))
     assert bool((sorted_keys[idx.clamp(max=sorted_keys.numel() - 1)] == face_keys.reshape(-1)).all()), \
         "a face references a vertex no slab emitted"

@@ -95,13 +95,16 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * in-tree post-processing fusion.py:339-348 (nearest-voxel colour gather, b/g/r unpack, voxel -> world transform).
  *
  * Two calls with a host read of two counters in between (the output size is data dependent):
- *   hv_mc_count  classifies the volume into `scratch` and writes totals[0] = #vertices, totals[1] = #triangles,
- *                totals[2] / totals[3] = min / max of the volume as order-preserving int32 keys of the floats
+ *   hv_mc_count  classifies the volume into `scratch` and writes totals (DEVICE, 8 x uint64): [0] = #vertices,
+ *                [1] = #triangles, [2] / [3] = min / max of the volume as order-preserving int32 keys of the floats
  *                (key = bits >= 0 ? bits : bits ^ 0x7fffffff) for skimage's "level within data range" check
- *                (ValueError, relied on by scripts/experiments.py:167).
- *   hv_mc_emit   writes the mesh.  Vertices are sorted by (owner voxel in C scan order, edge axis); triangles by cube
- *                scan order; right-hand normals of the faces point towards increasing values (what skimage returns
- *                for its default gradient_direction='descent').
+ *                (ValueError, relied on by scripts/experiments.py:167), [4] = #vertices that lie on lattice edges.
+ *   hv_mc_emit   writes the mesh: at most n_verts vertices / n_tris triangles (the capacity of the output buffers;
+ *                `totals` as left by hv_mc_count says how many there are -- a caller that reuses a capacity from an
+ *                earlier extraction can launch both calls back to back and read the totals afterwards).  Vertices on
+ *                lattice edges come first, sorted by (owner voxel in C scan order, edge axis), then the vertices
+ *                inside cubes (Lewiner's c-vertex) by cube; triangles by cube scan order; right-hand normals of the
+ *                faces point towards increasing values (what skimage returns for gradient_direction='descent').
  *
  * tsdf / color : float32 planes [X][Y][pitch] (z fastest), h_dims = {X, Y, Z}.
  * halo_lo / halo_hi (and the colour pair): optional [X][Y] planes just below z = 0 / above z = Z-1 of a z-slab
@@ -114,6 +117,7 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * face_cubes   : optional, with face_keys: uint64 [T] global linear index ((x*Y + y)*z_global_dim + z) of the cube each
  *                face came from -- the merge key that restores the whole-volume face order when shards are stitched.
  * verts_voxel  : optional [V][3] positions in voxel units (what skimage itself returns); NULL to skip.
+ * vert_keys    : optional uint64 [V] key of every vertex (shards: what face_keys refer to); NULL to skip.
  * ---------------------------------------------------------------------------------------------------------- */
 int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, int64_t* h_bytes);
 int hv_mc_count(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims, int64_t pitch,
@@ -123,7 +127,7 @@ int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, co
                double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
                float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
                float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
-               unsigned long long* face_cubes, unsigned long long* vert_keys, void* stream);
+               unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals, void* stream);
 
 /* hv_mc_count + hv_mc_emit in one call with caller-provided capacity (cap_verts vertices, cap_tris triangles in every
  * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 4 x uint64, pinned memory

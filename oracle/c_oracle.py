@@ -150,6 +150,14 @@ def marching_cubes(volume, level=0.0, with_keys=False, with_cubes=False):
     return (verts, faces, normals, values, keys) if with_keys else (verts, faces, normals, values)
 
 
+def product_order(keys):
+    """Permutation that brings the oracle's vertices (numbered in first-touch order like skimage's) into the order the
+    CUDA product emits: vertices on lattice edges sorted by key = (owner voxel in scan order, axis), then the vertices
+    inside cubes (key axis 3) sorted by cube.  skimage's own numbering is not reproduced by either (App. C)."""
+    keys = np.asarray(keys, dtype=np.int64)
+    return np.argsort(keys + ((keys & 3) == 3).astype(np.int64) * (1 << 62), kind="stable")
+
+
 def get_mesh(tsdf_vol, color_vol, voxel_size, vol_origin):
     """TSDFVolume.get_mesh (fusion.py:332-350): marching cubes at level 0, then the in-tree post-processing."""
     verts, faces, norms, _ = marching_cubes(tsdf_vol, 0.0)

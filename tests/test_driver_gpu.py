@@ -114,7 +114,7 @@ def test_tsdf_fusion_driver_matches_oracle(max_voxels, inpainted, c_oracle, monk
     assert np.array_equal(color, vol._color_vol_cpu)
     # mesh: the oracle's marching cubes on the very planes the GPU meshed (signs are then equal by construction)
     ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
-    order = np.argsort(ok, kind="stable")
+    order = c_oracle.product_order(ok)
     rank = np.empty_like(order)
     rank[order] = np.arange(len(order))
     ow, oc = fo.mesh_postprocess(ov[order], color, gpu._voxel_size, gpu._vol_origin)
@@ -299,7 +299,7 @@ def test_get_mesh_and_point_cloud_match_reference_golden(c_oracle):
     verts, faces, norms, colors = vol.get_mesh()
     # the golden is in the C oracle's vertex order, the GPU emits in (owner voxel, axis) order: renumber through the keys
     _, _, _, _, keys = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
-    order = np.argsort(keys, kind="stable")
+    order = c_oracle.product_order(keys)
     rank = np.empty_like(order)
     rank[order] = np.arange(len(order))
     assert verts.dtype == np.float32 and faces.dtype == np.int32 and colors.dtype == np.uint8

@@ -204,7 +204,7 @@ def test_c2_mesh_equals_the_oracle(c2_frames, c_oracle):
     verts, faces, norms, colors = vol.get_mesh()
     tsdf, color = vol.get_volume()
     ov, of, on, _, ok = c_oracle.marching_cubes(tsdf, 0.0, with_keys=True)
-    order = np.argsort(ok, kind="stable")
+    order = c_oracle.product_order(ok)
     rank = np.empty_like(order)
     rank[order] = np.arange(len(order))
     ow, oc = fo.mesh_postprocess(ov[order], color, vol._voxel_size, vol._vol_origin)

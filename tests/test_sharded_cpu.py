@@ -47,7 +47,7 @@ def _oracle_parts(world):
         parts.append({"verts": verts[vs], "normals": normals[vs], "colors": colors[vs], "vert_keys": keys[vs],
                       "face_keys": keys[faces[fs]], "face_cubes": cubes[fs]})
     # the whole-volume reference in the product's order: vertices by key, faces by cube (stable)
-    order = np.argsort(keys, kind="stable")
+    order = c_oracle.product_order(keys)
     rank = np.empty_like(order)
     rank[order] = np.arange(len(order))
     forder = np.argsort(cubes, kind="stable")
