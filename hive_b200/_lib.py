@@ -35,12 +35,14 @@ SIGNATURES = {
     "hv_integrate": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                      c_void_p, c_int, c_int, c_double, c_double, c_int, c_void_p, c_void_p],
     "hv_mc_scratch_bytes": [c_void_p, c_int, c_int, c_void_p],
-    "hv_mc_count": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_mc_work_bytes": [c_int64, c_int64, c_void_p],
+    "hv_mc_count": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p, c_int64, c_void_p, c_int64,
+                    c_int64, c_void_p, c_void_p],
     "hv_mc_emit": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
-                   c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                   c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_mc_extract": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
-                      c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
+                      c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_d2m_scratch_bytes": [c_int, c_int, c_int, c_void_p],
     "hv_d2m_count": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_int64, c_void_p,

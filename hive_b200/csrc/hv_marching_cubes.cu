@@ -6,19 +6,20 @@
 // oracle/mc_oracle.c (scikit-image itself is not available anywhere on the box: parity unpinned).
 //
 // Pipeline (HBM-bound streaming + sparse compaction, no tensor cores), DESIGN.md 4.2:
-//   1. mc_classify_kernel  the one pass over the TSDF plane (4 B/voxel).  A CTA sweeps a strip of TY columns along
-//                          axis 0; the sign bits of planes x and x + 1 sit in shared memory, so the per-group vertex /
-//                          triangle counts are taken from the bits the same CTA has just produced.  Writes the bit volume
-//                          (N/8 bytes), one packed count word per 32-voxel group, and the totals of every run (= one
-//                          plane of one strip, a contiguous range of the global group order); min / max for the
-//                          skimage level-range check.
-//   2. mc_run_scan_kernel  exclusive scan of the run totals (X * ceil(Y/TY) entries), one CTA.
-//   3. mc_emit_kernel      sweeps the same strips: bits of three planes + count words of two planes in shared memory,
-//                          block scans turn them into the index base of every group in reach, so a triangle corner's
-//                          vertex index is run base + shared-memory prefix + popcounts -- no index volume, no global
-//                          look-ups.  One thread per triangle record, one thread per vertex record (position, normal
-//                          accumulated over the <= 4 cubes around the edge in scan order, colour, world transform) with
-//                          the edge's 2x3x3 neighbourhood in registers.
+//   1. mc_sign_kernel   the one pass over the TSDF plane (4 B/voxel): one sign bit per voxel (N/8 bytes, L2 resident)
+//                       + min / max for the skimage level-range check.
+//   2. mc_count_kernel  one thread per 32-voxel z-group over the bit volume: masks of the voxels owning a vertex on
+//                       their +axis0 / +axis1 / +axis2 edge, triangles of the group's surface cubes (TSDF values are
+//                       fetched only for cubes with an ambiguous face or an interior test).  A tile of 256 groups is
+//                       scanned in the block; written: a 16-byte record {first vertex, mx, my, mz} in place for every
+//                       group that owns a vertex (`gtab`, sparse: the index look-up of a triangle corner is ONE load
+//                       plus a hot small-table entry), one work record per surface cube and per edge vertex, the
+//                       tile totals.  The last tile to finish scans the tile totals (no extra launch, no look-back).
+//   3. mc_tri_kernel    one thread per cube record: its triangles (three `gtab` look-ups each) and its centre vertex.
+//   4. mc_vert_kernel   one thread per vertex record: position, normal accumulated over the <= 4 cubes around the
+//                       edge in scan order, colour, world transform -- the edge's 2x3x3 neighbourhood in registers.
+// The emit kernels read the totals on the device, so all launches can be queued back to back; the host reads the totals
+// once, afterwards.
 // Vertex order: edge vertices sorted by (owner voxel in scan order, axis), then the cube-centre vertices by cube;
 // triangles in cube scan order.  Deterministic; no dedup pass because each lattice edge has exactly one owner.
 //
@@ -49,15 +50,21 @@ struct McGrid {
     long long zoff;      // global z of zb = 0
     long long Zg;        // global Z
     double level;
-    // sweep geometry: a strip = TY columns (axis 1), a run = one plane (axis 0) of one strip
-    int TY, S, GP;        // columns per strip, strips per plane, G + 2 (row pitch of the shared bit tables)
     // scratch
-    unsigned int* bits;   // [X*Y*G]
-    unsigned int* gcnt;   // [X*Y*G] edge vertices | centre vertices << 8 | triangles << 16 of the group
-    uint4* run_tot;       // [X*S] (edge vertices, triangles, centre vertices, 0) of every run
-    uint4* run_base;      // [X*S] exclusive prefix of run_tot
+    unsigned int* bits;          // [n_groups] sign words
+    uint4* gtab;                 // [n_groups], written only where the group owns a vertex: {batch-local first vertex, mx, my, mz}
+    uint4* batch_base;           // [n_batches] {edge vertices, triangles, centre vertices} of the tile before this batch of 32 groups
+    uint4* tile_tot;             // [n_tiles] {edge vertices, triangles, centre vertices, cubes} of every tile of 32 batches
+    uint4* tile_base;            // [n_tiles] exclusive prefix of tile_tot (x, y, z)
+    unsigned int* ctrl;          // [0] tiles done, [1] / [2] cursors of the record arrays
+    // work records (caller-sized: hv_mc_work_bytes)
+    uint4* cube_rec;             // {group, voxel | tiling << 5, batch-local first triangle, batch-local centre vertex}
+    unsigned long long* vert_rec;  // pack_vertex_record()
+    long long cap_cubes, cap_vrec;
     unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float) [4] edge vertices
-    long long n_groups;
+                                 // [5] surface cubes [6] 1 if the records did not fit
+    long long n_groups, n_batches;
+    int n_tiles;
 };
 
 __device__ __forceinline__ float mc_fetch(const McGrid& g, const float* vol, const float* lo, const float* hi, int x,
@@ -72,16 +79,6 @@ __device__ __forceinline__ float mc_fetch(const McGrid& g, const float* vol, con
 __device__ __forceinline__ int float_order_key(float f) {
     const int i = __float_as_int(f);
     return i >= 0 ? i : i ^ 0x7fffffff;
-}
-
-__global__ void mc_init_kernel(unsigned long long* totals) {
-    if (threadIdx.x == 0) {
-        totals[0] = 0ull;
-        totals[1] = 0ull;
-        totals[2] = 0x7fffffffull;  // min key
-        totals[3] = 0x80000000ull;  // max key
-        totals[4] = 0ull;
-    }
 }
 
 // Sign nibble of four values + running min/max.
@@ -236,23 +233,91 @@ __device__ __forceinline__ int cube_variant_at(const McGrid& g, int idx, int x, 
     return cube_variant(idx, v);
 }
 
-// ---- shared-memory bit tables ---------------------------------------------------------------------------------------------
-// One table = the sign words of one plane (axis 0) for TY + 2 columns of a strip (its own columns, then up to two columns of
-// the next strip), GP = G + 2 words per column; words past the last group, columns past Y and planes past X read as zero.
-constexpr int kSweepThreads = 256;
+// ---- 1. sign bits + min/max ----------------------------------------------------------------------------------------
+// A warp takes whole columns (grid-stride).  Lane l reads the voxels zb = 32 w + l of sixteen sign words w at a time (sixteen
+// coalesced 128-byte loads in flight), and a word is one warp vote -- no nibble packing, no shuffles.  (r01: the float4 /
+// shuffle form spent 79 warp-instructions per 128 voxels and sat at 73 % issue utilisation with DRAM at 66 %.)
+constexpr int kSignBatch = 16;
 
-// Sign words around group (column c of the tables, word gq) of plane x: p0 = table of plane x, p1 = of plane x + 1.
-__device__ __forceinline__ CubeWords cube_words(const McGrid& g, const unsigned int* p0, const unsigned int* p1, int x, int y,
-                                                int c, int gq) {
+__global__ void __launch_bounds__(256) mc_sign_kernel(const __grid_constant__ McGrid g) {
+    const int lane = threadIdx.x & 31;
+    const int warp0 = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int n_warps = (int)((gridDim.x * blockDim.x) >> 5);
+    float vmin = INFINITY, vmax = -INFINITY;
+    const float level_f = (float)g.level;  // exact compare needs double only when the level is not a float
+    const bool level_exact = (double)level_f == g.level;
+    const int n_cols = g.X * g.Y;
+    for (int col = warp0; col < n_cols; col += n_warps) {
+        const float* base = g.tsdf + (size_t)col * g.pitch + lane;
+        unsigned int* dst = g.bits + (size_t)col * g.G;
+        for (int w0 = 0; w0 < g.G; w0 += kSignBatch) {
+            float v[kSignBatch];
+            if (g.hl == 0 && (w0 + kSignBatch) * 32 <= g.Z) {
+#pragma unroll
+                for (int k = 0; k < kSignBatch; ++k) v[k] = __ldcs(base + (w0 + k) * 32);
+            } else {
+#pragma unroll
+                for (int k = 0; k < kSignBatch; ++k) {
+                    const int zb = (w0 + k) * 32 + lane, z = zb - g.hl;
+                    v[k] = NAN;  // padding: compares false, ignored by fminf / fmaxf
+                    if (zb < g.Zb) v[k] = z < 0 ? __ldg(g.halo_lo + col) : (z >= g.Z ? __ldg(g.halo_hi + col) : __ldcs(g.tsdf + (size_t)col * g.pitch + z));
+                }
+            }
+            unsigned int mine = 0u;
+#pragma unroll
+            for (int k = 0; k < kSignBatch; ++k) {
+                const bool pos = level_exact ? (v[k] > level_f) : ((double)v[k] > g.level);
+                const unsigned int word = __ballot_sync(0xffffffffu, pos);
+                if (lane == k) mine = word;
+                vmin = fminf(vmin, v[k]);
+                vmax = fmaxf(vmax, v[k]);
+            }
+            if (lane < kSignBatch && w0 + lane < g.G) dst[w0 + lane] = mine;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
+        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    }
+    if (lane == 0 && vmin <= vmax) {  // at least one real value seen
+        atomicMin(reinterpret_cast<int*>(g.totals + 2), float_order_key(vmin));
+        atomicMax(reinterpret_cast<int*>(g.totals + 3), float_order_key(vmax));
+    }
+}
+
+// ---- group helpers ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned int decode_group(const McGrid& g, unsigned int gid, int& x, int& y, int& gq) {
+    const unsigned int col = gid / (unsigned int)g.G;
+    gq = (int)(gid - col * (unsigned int)g.G);
+    x = (int)(col / (unsigned int)g.Y);
+    y = (int)(col - (unsigned int)x * (unsigned int)g.Y);
+    return col;
+}
+
+__device__ __forceinline__ void load_pair(const McGrid& g, size_t gi, int gq, bool in, unsigned int& b, unsigned int& u) {
+    b = 0u;
+    u = 0u;
+    if (!in) return;
+    b = __ldg(g.bits + gi);
+    const unsigned int nxt = (gq + 1 < g.G) ? __ldg(g.bits + gi + 1) : 0u;
+    u = (b >> 1) | (nxt << 31);
+}
+
+// Sign words around group (x, y, gq) from the bit volume, the masks of the vertices its voxels own and of its surface cubes.
+__device__ __forceinline__ CubeWords load_cube_words(const McGrid& g, int x, int y, int gq) {
     CubeWords w;
-    const int i = c * g.GP + gq;
-    const unsigned int b00 = p0[i], b01 = p0[i + g.GP], b10 = p1[i], b11 = p1[i + g.GP];
-    const unsigned int u00 = (b00 >> 1) | (p0[i + 1] << 31), u01 = (b01 >> 1) | (p0[i + g.GP + 1] << 31);
-    const unsigned int u10 = (b10 >> 1) | (p1[i + 1] << 31), u11 = (b11 >> 1) | (p1[i + g.GP + 1] << 31);
+    const bool x1 = x + 1 < g.X, y1 = y + 1 < g.Y;
+    const size_t gi = ((size_t)x * g.Y + y) * g.G + gq;
+    const size_t dx = (size_t)g.Y * g.G;
+    unsigned int b00, b01, b10, b11, u00, u01, u10, u11;
+    load_pair(g, gi, gq, true, b00, u00);
+    load_pair(g, gi + g.G, gq, y1, b01, u01);
+    load_pair(g, gi + dx, gq, x1, b10, u10);
+    load_pair(g, gi + dx + g.G, gq, x1 && y1, b11, u11);
     // corner i offsets (axis0, axis1, axis2): see kMcCornerOff
     w.w[0] = b00; w.w[1] = u00; w.w[2] = u01; w.w[3] = b01;
     w.w[4] = b10; w.w[5] = u10; w.w[6] = u11; w.w[7] = b11;
-    const bool x1 = x + 1 < g.X, y1 = y + 1 < g.Y;
     const int base = gq * 32;
     const unsigned int own = range_mask(g.own_lo, g.own_hi, base), zin = range_mask(0, g.Zb - 1, base);
     w.mx = x1 ? ((b00 ^ b10) & own) : 0u;
@@ -264,194 +329,235 @@ __device__ __forceinline__ CubeWords cube_words(const McGrid& g, const unsigned 
     return w;
 }
 
-__device__ __forceinline__ unsigned int warp_sum(unsigned int v) {
+// ---- warp-level expansion helpers ----------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned int warp_excl_scan(unsigned int v, unsigned int& total) {
+    const int lane = threadIdx.x & 31;
+    unsigned int inc = v;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    total = __shfl_sync(0xffffffffu, inc, 31);
+    return inc - v;
 }
 
-// ---- 1. classify: sign bits, per-group counts, run totals, min / max -------------------------------------------------------
-// Loads the sign words of plane x (columns y0 .. y0 + ny of the strip; column ny belongs to the next strip) into `tab`;
-// `owned`: this CTA is the one that publishes the plane's bits (and takes its values into min / max).
-__device__ __forceinline__ void classify_load_plane(const McGrid& g, unsigned int* tab, int x, int y0, int ny, bool owned,
-                                                    int vec, float level_f, bool level_exact, float& vmin, float& vmax) {
+// Largest lane s with off[s] <= q, `off` being an exclusive scan over the lanes: the lane whose items cover ordinal q.
+__device__ __forceinline__ int warp_owner(unsigned int off, unsigned int q) {
+    int s = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+        const unsigned int v = __shfl_sync(0xffffffffu, off, s + step);
+        if (v <= q) s += step;
+    }
+    return s;
+}
+
+// Position of the r-th (0-based) set bit of `mask` (r < popc(mask)).
+__device__ __forceinline__ int select_bit(unsigned int mask, int r) {
+    int pos = 0;
+#pragma unroll
+    for (int w = 16; w > 0; w >>= 1) {
+        const int cnt = __popc((mask >> pos) & ((1u << w) - 1u));
+        if (r >= cnt) {
+            r -= cnt;
+            pos += w;
+        }
+    }
+    return pos;
+}
+
+// ---- 2. count: per-group masks, work records, scan -------------------------------------------------------------------------
+// The unit of work is a batch of 32 consecutive groups (the global group order is the vertex / triangle order), one per
+// lane: sign words of the four columns around the group, owner masks, surface-cube mask.  Nearly all batches are empty
+// and end there.  The cubes of a batch are then spread over the lanes with a warp scan -- 32 cubes at a time whatever the
+// shape of the surface (one thread per group walked up to 32 cubes serially, one thread per column up to Z: 315 us and
+// 370 us at 512^3 with a wall parallel to z in the scene) -- so every tiling decision (face and interior tests included)
+// is made ONCE, lane-parallel, and lands in the cube's work record together with the cube's batch-local triangle offset.
+// A tile = 32 batches (16 warps x 2); the batch totals are scanned in the tile, the last tile to finish scans the tile
+// totals: a consumer adds two hot small-table entries per look-up.  (A decoupled look-back over tiles of 256 groups was
+// measured at 520 us: with ~600 tiles in flight every tile walks back ~20 windows.)  Records go to a bump-allocated range
+// per batch: their order in the record arrays is arbitrary, the indices they carry are not.
+constexpr int kCountThreads = 512;
+constexpr int kBatchesPerWarp = 2;
+constexpr int kTileBatches = (kCountThreads / 32) * kBatchesPerWarp;
+static_assert(kTileBatches == 32, "the batch totals of a tile are scanned by one warp");
+
+__global__ void mc_init_kernel(unsigned long long* totals, unsigned int* ctrl) {
+    if (threadIdx.x == 0) {
+        totals[0] = 0ull;
+        totals[1] = 0ull;
+        totals[2] = 0x7fffffffull;  // min key
+        totals[3] = 0x80000000ull;  // max key
+        totals[4] = 0ull;
+        totals[5] = 0ull;
+        totals[6] = 0ull;
+    }
+    if (threadIdx.x < 8) ctrl[threadIdx.x] = 0u;
+}
+
+// vertex record: group (31 bits) | voxel << 31 (5) | axis << 36 (2) | batch-local vertex index << 38 (<= 32 * 96)
+__device__ __forceinline__ unsigned long long pack_vertex_record(unsigned int gid, int k, int axis, unsigned int local) {
+    return (unsigned long long)gid | ((unsigned long long)k << 31) | ((unsigned long long)axis << 36) | ((unsigned long long)local << 38);
+}
+
+__global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_constant__ McGrid g) {
+    __shared__ uint4 s_batch[kTileBatches];
+    __shared__ unsigned long long s_wa[kCountThreads / 32], s_wb[kCountThreads / 32];
+    __shared__ unsigned int s_last;
+    const unsigned int tile = blockIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int segs = (g.Zb + 127) >> 7;
-    const int tiles = (ny + 1) * segs;
-    for (int tb = warp; tb < tiles; tb += 4 * (kSweepThreads / 32)) {
-        float v[4][4];
-        int cc[4], sg[4];
+    const unsigned int lt = (1u << lane) - 1u;
+#pragma unroll 1
+    for (int b = 0; b < kBatchesPerWarp; ++b) {
+        const int slot = warp * kBatchesPerWarp + b;
+        const long long gid64 = ((long long)tile * kTileBatches + slot) * 32 + lane;
+        const unsigned int gid = (unsigned int)gid64;
+        uint4 tot = make_uint4(0u, 0u, 0u, 0u);
+        int x = 0, y = 0, gq = 0;
+        CubeWords c;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {  // four 512-byte column segments of this warp in flight together
-            const int t = tb + u * (kSweepThreads / 32);
-            v[u][0] = v[u][1] = v[u][2] = v[u][3] = NAN;
-            cc[u] = -1;
-            if (t < tiles) {
-                const int c = t / segs, seg = t - c * segs, y = y0 + c;
-                cc[u] = c;
-                sg[u] = seg;
-                if (x < g.X && y < g.Y) {
-                    const int z0 = seg * 128 + lane * 4;
-                    const size_t col = (size_t)x * g.Y + y;
-                    if (vec && z0 + 3 < g.Z) {
-                        const float4* p = reinterpret_cast<const float4*>(g.tsdf + col * (size_t)g.pitch + z0);
-                        const float4 q = (owned && c < ny) ? __ldcs(p) : __ldg(p);
-                        v[u][0] = q.x; v[u][1] = q.y; v[u][2] = q.z; v[u][3] = q.w;
-                    } else {
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            if (z0 + k < g.Zb) v[u][k] = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, x, y, z0 + k);
+        for (int i = 0; i < 8; ++i) c.w[i] = 0u;
+        c.active = c.mx = c.my = c.mz = 0u;
+        if (gid64 < g.n_groups) {
+            decode_group(g, gid, x, y, gq);
+            c = load_cube_words(g, x, y, gq);
+        }
+        if (__ballot_sync(0xffffffffu, (c.active | c.mx | c.my | c.mz) != 0u)) {
+            // ---- edge vertices: the group's record in place, one work record per vertex
+            const unsigned int nv = __popc(c.mx) + __popc(c.my) + __popc(c.mz);
+            unsigned int NV;
+            const unsigned int vpre = warp_excl_scan(nv, NV);
+            if (nv) g.gtab[gid] = make_uint4(vpre, c.mx, c.my, c.mz);
+            if (NV) {
+                unsigned int vbase = 0;
+                if (lane == 0) vbase = atomicAdd(g.ctrl + 2, NV);
+                vbase = __shfl_sync(0xffffffffu, vbase, 0);
+                if ((long long)vbase + NV <= g.cap_vrec) {
+                    unsigned long long* dst = g.vert_rec + vbase;
+                    unsigned int o = vpre;
+                    for (unsigned int rest = c.mx | c.my | c.mz; rest; rest &= rest - 1) {
+                        const int k = __ffs(rest) - 1;
+                        if ((c.mx >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 0, o); ++o; }
+                        if ((c.my >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 1, o); ++o; }
+                        if ((c.mz >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 2, o); ++o; }
                     }
                 }
             }
-        }
+            // ---- surface cubes, one lane per cube
+            unsigned int C;
+            const unsigned int coff = warp_excl_scan(__popc(c.active), C);
+            unsigned int cbase = 0;
+            if (C && lane == 0) cbase = atomicAdd(g.ctrl + 1, C);
+            cbase = __shfl_sync(0xffffffffu, cbase, 0);
+            const bool write_ok = (long long)cbase + C <= g.cap_cubes;
+            unsigned int tri_run = 0, cen_run = 0;
+            for (unsigned int c0 = 0; c0 < C; c0 += 32u) {
+                const unsigned int q = c0 + (unsigned int)lane;
+                const bool cv = q < C;
+                const int s = warp_owner(coff, cv ? q : C - 1u);
+                const unsigned int r = q - __shfl_sync(0xffffffffu, coff, s);
+                const unsigned int am = __shfl_sync(0xffffffffu, c.active, s);
+                unsigned int w[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (cc[u] < 0) continue;  // warp-uniform
-            float lmin = INFINITY, lmax = -INFINITY;
-            const unsigned int nib = mc_sign4(v[u], level_f, level_exact, g.level, lmin, lmax);
-            unsigned int word = nib << (4 * (lane & 7));
-            word |= __shfl_xor_sync(0xffffffffu, word, 1);
-            word |= __shfl_xor_sync(0xffffffffu, word, 2);
-            word |= __shfl_xor_sync(0xffffffffu, word, 4);
-            const int gq = sg[u] * 4 + (lane >> 3);
-            if ((lane & 7) == 0 && gq < g.G) {
-                tab[cc[u] * g.GP + gq] = word;
-                if (owned && cc[u] < ny) g.bits[((size_t)x * g.Y + (y0 + cc[u])) * g.G + gq] = word;
-            }
-            if (owned && cc[u] < ny) {
-                vmin = fminf(vmin, lmin);
-                vmax = fmaxf(vmax, lmax);
-            }
-        }
-    }
-}
-
-__global__ void __launch_bounds__(kSweepThreads) mc_classify_kernel(const McGrid g, const int CX, const int vec) {
-    extern __shared__ unsigned int s_mem[];
-    __shared__ unsigned int s_tot[3];
-    const int tabw = (g.TY + 2) * g.GP;
-    const int strip = blockIdx.x % g.S, chunk = blockIdx.x / g.S;
-    const int y0 = strip * g.TY, ny = min(g.TY, g.Y - y0);
-    const int xa = chunk * CX, xb = min(g.X, xa + CX);
-    if (xa >= xb) return;
-    const float level_f = (float)g.level;  // exact compare needs double only when the level is not a float
-    const bool level_exact = (double)level_f == g.level;
-    float vmin = INFINITY, vmax = -INFINITY;
-    for (int i = threadIdx.x; i < 2 * tabw; i += kSweepThreads) s_mem[i] = 0u;
-    if (threadIdx.x < 3) s_tot[threadIdx.x] = 0u;
-    __syncthreads();
-    unsigned int* cur = s_mem;
-    unsigned int* nxt = s_mem + tabw;
-    classify_load_plane(g, cur, xa, y0, ny, true, vec, level_f, level_exact, vmin, vmax);
-    for (int x = xa; x < xb; ++x) {
-        classify_load_plane(g, nxt, x + 1, y0, ny, x + 1 < xb, vec, level_f, level_exact, vmin, vmax);
-        __syncthreads();
-        unsigned int a_nv = 0, a_nt = 0, a_nc = 0;
-        for (int t = threadIdx.x; t < ny * g.G; t += kSweepThreads) {
-            const int c = t / g.G, gq = t - c * g.G, y = y0 + c;
-            const CubeWords w = cube_words(g, cur, nxt, x, y, c, gq);
-            const unsigned int nv = __popc(w.mx) + __popc(w.my) + __popc(w.mz);
-            unsigned int nt = 0, nc = 0;
-            for (unsigned int rest = w.active; rest; rest &= rest - 1) {
-                const int k = __ffs(rest) - 1;
-                const int variant = cube_variant_at_ool(g, cube_index(w, k), x, y, gq * 32 + k);
-                nt += kMcVarNtri[variant];
-                nc += ((kMcVarMult[variant] >> 48) & 15ull) ? 1u : 0u;
-            }
-            g.gcnt[((size_t)x * g.Y + y) * g.G + gq] = nv | (nc << 8) | (nt << 16);
-            a_nv += nv;
-            a_nt += nt;
-            a_nc += nc;
-        }
-        a_nv = warp_sum(a_nv);
-        a_nt = warp_sum(a_nt);
-        a_nc = warp_sum(a_nc);
-        if ((threadIdx.x & 31) == 0 && (a_nv | a_nt | a_nc)) {
-            atomicAdd(&s_tot[0], a_nv);
-            atomicAdd(&s_tot[1], a_nt);
-            atomicAdd(&s_tot[2], a_nc);
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            g.run_tot[(size_t)x * g.S + strip] = make_uint4(s_tot[0], s_tot[1], s_tot[2], 0u);
-            s_tot[0] = s_tot[1] = s_tot[2] = 0u;
-        }
-        unsigned int* t = cur;
-        cur = nxt;
-        nxt = t;
-    }
+                for (int i = 0; i < 8; ++i) w[i] = __shfl_sync(0xffffffffu, c.w[i], s);
+                const int cx = __shfl_sync(0xffffffffu, x, s), cy = __shfl_sync(0xffffffffu, y, s);
+                const int cgq = __shfl_sync(0xffffffffu, gq, s);
+                int variant = 0, k = 0;
+                unsigned int ntri = 0;
+                bool hasc = false;
+                if (cv) {
+                    k = select_bit(am, (int)r);
+                    int idx = 0;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
-        vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-    }
-    if ((threadIdx.x & 31) == 0 && vmin <= vmax) {  // at least one real value seen
-        atomicMin(reinterpret_cast<int*>(g.totals + 2), float_order_key(vmin));
-        atomicMax(reinterpret_cast<int*>(g.totals + 3), float_order_key(vmax));
-    }
-}
-
-// ---- 2. exclusive scan of the run totals (one CTA) ----------------------------------------------------------------------------
-constexpr int kRunScanThreads = 1024;
-
-__global__ void __launch_bounds__(kRunScanThreads) mc_run_scan_kernel(const uint4* __restrict__ tot, uint4* __restrict__ base,
-                                                                      int n, unsigned long long* totals) {
-    __shared__ unsigned long long s_w[3][kRunScanThreads / 32];
-    const int per = (n + kRunScanThreads - 1) / kRunScanThreads;
-    const int i0 = threadIdx.x * per, i1 = min(n, i0 + per);
-    unsigned long long a = 0, b = 0, c = 0;
-    for (int i = i0; i < i1; ++i) {
-        const uint4 v = tot[i];
-        a += v.x;
-        b += v.y;
-        c += v.z;
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned long long ia = a, ib = b, ic = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long ua = __shfl_up_sync(0xffffffffu, ia, o), ub = __shfl_up_sync(0xffffffffu, ib, o),
-                                 uc = __shfl_up_sync(0xffffffffu, ic, o);
-        if (lane >= o) {
-            ia += ua;
-            ib += ub;
-            ic += uc;
+                    for (int i = 0; i < 8; ++i) idx |= (int)((w[i] >> k) & 1u) << i;
+                    variant = cube_variant_at_ool(g, idx, cx, cy, cgq * 32 + k);
+                    ntri = kMcVarNtri[variant];
+                    hasc = ((kMcVarMult[variant] >> 48) & 15ull) != 0ull;
+                }
+                unsigned int T;
+                const unsigned int toff = warp_excl_scan(ntri, T);
+                const unsigned int cb = __ballot_sync(0xffffffffu, hasc);
+                if (cv && write_ok)
+                    g.cube_rec[cbase + q] = make_uint4(gid - (unsigned int)lane + (unsigned int)s, (unsigned int)k | ((unsigned int)variant << 5),
+                                                       tri_run + toff, cen_run + __popc(cb & lt));
+                tri_run += T;
+                cen_run += __popc(cb);
+            }
+            tot = make_uint4(NV, tri_run, cen_run, C);
         }
-    }
-    if (lane == 31) {
-        s_w[0][warp] = ia;
-        s_w[1][warp] = ib;
-        s_w[2][warp] = ic;
+        if (lane == 0) s_batch[slot] = tot;
     }
     __syncthreads();
-    unsigned long long ca = 0, cb = 0, cc = 0, ta = 0, tb = 0, tc = 0;
-    for (int w = 0; w < kRunScanThreads / 32; ++w) {
-        if (w < warp) {
-            ca += s_w[0][w];
-            cb += s_w[1][w];
-            cc += s_w[2][w];
-        }
-        ta += s_w[0][w];
-        tb += s_w[1][w];
-        tc += s_w[2][w];
+    if (warp == 0) {  // scan of the tile's batch totals
+        const uint4 v = s_batch[lane];
+        unsigned int sx, sy, sz, sw;
+        const unsigned int ex = warp_excl_scan(v.x, sx), ey = warp_excl_scan(v.y, sy), ez = warp_excl_scan(v.z, sz);
+        warp_excl_scan(v.w, sw);
+        const long long batch = (long long)tile * kTileBatches + lane;
+        if (batch < g.n_batches) g.batch_base[batch] = make_uint4(ex, ey, ez, 0u);
+        if (lane == 0) g.tile_tot[tile] = make_uint4(sx, sy, sz, sw);
     }
-    unsigned long long ea = ca + ia - a, eb = cb + ib - b, ec = cc + ic - c;  // exclusive prefix of this thread's range
-    for (int i = i0; i < i1; ++i) {
-        const uint4 v = tot[i];
-        base[i] = make_uint4((unsigned int)ea, (unsigned int)eb, (unsigned int)ec, 0u);
-        ea += v.x;
-        eb += v.y;
-        ec += v.z;
+    // the last tile to get here turns the tile totals into bases
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(g.ctrl, 1u) == gridDim.x - 1u) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int n_tiles = g.n_tiles;
+    unsigned long long carry_a = 0, carry_b = 0;  // (edge vertices | triangles << 32), (centre vertices | cubes << 32): all < 2^31
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if ((int)threadIdx.x < n_tiles) v = __ldcg(g.tile_tot + threadIdx.x);
+    for (int i0 = 0; i0 < n_tiles; i0 += kCountThreads) {
+        const int i = i0 + (int)threadIdx.x;
+        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+        if (i + kCountThreads < n_tiles) nxt = __ldcg(g.tile_tot + i + kCountThreads);  // next round's entry, requested early
+        const unsigned long long a = (unsigned long long)v.x | ((unsigned long long)v.y << 32);
+        const unsigned long long bb = (unsigned long long)v.z | ((unsigned long long)v.w << 32);
+        unsigned long long ia = a, ib = bb;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long ua = __shfl_up_sync(0xffffffffu, ia, o), ub = __shfl_up_sync(0xffffffffu, ib, o);
+            if (lane >= o) {
+                ia += ua;
+                ib += ub;
+            }
+        }
+        if (lane == 31) {
+            s_wa[warp] = ia;
+            s_wb[warp] = ib;
+        }
+        __syncthreads();
+        unsigned long long ca = 0, cb = 0, ta = 0, tb = 0;
+#pragma unroll
+        for (int w = 0; w < kCountThreads / 32; ++w) {
+            const unsigned long long xa = s_wa[w], xb = s_wb[w];
+            if (w < warp) {
+                ca += xa;
+                cb += xb;
+            }
+            ta += xa;
+            tb += xb;
+        }
+        __syncthreads();
+        const unsigned long long ea = carry_a + ca + ia - a, eb = carry_b + cb + ib - bb;
+        if (i < n_tiles) g.tile_base[i] = make_uint4((unsigned int)ea, (unsigned int)(ea >> 32), (unsigned int)eb, 0u);
+        carry_a += ta;
+        carry_b += tb;
+        v = nxt;
     }
     if (threadIdx.x == 0) {
-        totals[0] = ta + tc;  // vertices: edge vertices, then the cube-centre vertices
-        totals[1] = tb;
-        totals[4] = ta;
+        const unsigned long long n_edge = carry_a & 0xffffffffull, n_tri = carry_a >> 32, n_centre = carry_b & 0xffffffffull, n_cube = carry_b >> 32;
+        g.totals[0] = n_edge + n_centre;  // edge vertices, then the cube-centre vertices
+        g.totals[1] = n_tri;
+        g.totals[4] = n_edge;
+        g.totals[5] = n_cube;
+        g.totals[6] = ((long long)n_cube > g.cap_cubes || (long long)n_edge > g.cap_vrec) ? 1ull : 0ull;  // records incomplete
     }
 }
 
-// ---- 3. emit -----------------------------------------------------------------------------------------------------------------
+// ---- 3. / 4. emit ----------------------------------------------------------------------------------------------------------
 struct McEmit {
     int32_t* faces;                  // [T][3] local vertex indices, or null
     unsigned long long* face_keys;   // [T][3] global vertex keys, or null
@@ -464,7 +570,6 @@ struct McEmit {
     long long cap_verts, cap_tris;   // capacity of the buffers above: anything beyond is counted, not written
     float voxel_size;
     float origin[3];
-    int CX;
 };
 
 __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x, int y, int zb, int axis) {
@@ -472,215 +577,157 @@ __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x,
     return lin * 4ull + (unsigned long long)axis;
 }
 
-// Exclusive block scan of one value per thread, with a running carry kept in shared memory (s_carry); `s_warp`: 8 words.
-__device__ __forceinline__ unsigned int block_scan_carry(unsigned int v, unsigned int* s_warp, unsigned int* s_carry) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned int inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned int u = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += u;
-    }
-    if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();
-    unsigned int before = *s_carry, total = 0;
-#pragma unroll
-    for (int w = 0; w < kSweepThreads / 32; ++w) {
-        const unsigned int sw = s_warp[w];
-        if (w < warp) before += sw;
-        total += sw;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) *s_carry += total;
-    return before + inc - v;
-}
-
-// Tables the emit kernel keeps in shared memory.
-struct EmitTables {
-    unsigned int* bits[3];  // planes x, x + 1, x + 2 (rotating): [(TY + 2) * GP]
-    unsigned int* vpre[2];  // planes x, x + 1: global index of the first edge vertex of every group, [(TY + 1) * G]
-    unsigned int* tpre;     // own groups of plane x: run-local index of the group's first triangle, [TY * G]
-    unsigned int* cpre;     //   ... of its first centre vertex
-    unsigned int* cnt;      //   ... its packed counts
-    unsigned int* mw;       //   ... mask of its cubes that have a centre vertex
-    uint2* rec;             // record list of one round
-    unsigned int* s_warp;   // 8 words of scan scratch
-    unsigned int* s_misc;   // [0] carry, [1] own total of a scan, [2..4] run totals (edge vertices, triangles, centres)
-};
-
-constexpr int kRecCap = 2048;  // records per round (16 KB)
-
-__device__ __forceinline__ void emit_load_bits(const McGrid& g, unsigned int* tab, int p, int y0) {
-    const int rows = g.TY + 2;
-    for (int i = threadIdx.x; i < rows * g.GP; i += kSweepThreads) {
-        const int c = i / g.GP, gq = i - c * g.GP, y = y0 + c;
-        tab[i] = (p < g.X && y < g.Y && gq < g.G) ? __ldg(g.bits + ((size_t)p * g.Y + y) * g.G + gq) : 0u;
-    }
-}
-
-// Global index of the first edge vertex of every group of plane p in reach: the strip's own columns continue the run
-// (p, strip); column ny is the first column of the run (p, strip + 1).
-__device__ __forceinline__ void emit_build_vpre(const McGrid& g, const EmitTables& T, unsigned int* vpre, int p, int strip,
-                                                int y0, int ny) {
-    const int n_own = ny * g.G, n_all = (y0 + ny < g.Y) ? n_own + g.G : n_own;
-    if (p >= g.X) return;  // never referenced
-    const unsigned int base_own = g.run_base[(size_t)p * g.S + strip].x;
-    const unsigned int base_next = (y0 + ny < g.Y) ? g.run_base[(size_t)p * g.S + strip + 1].x : 0u;
-    if (threadIdx.x == 0) T.s_misc[0] = 0u;
-    __syncthreads();
-    for (int t0 = 0; t0 < n_all; t0 += kSweepThreads) {
-        const int t = t0 + threadIdx.x;
-        unsigned int v = 0;
-        if (t < n_all) {
-            const int c = t / g.G, gq = t - c * g.G;
-            v = __ldg(g.gcnt + ((size_t)p * g.Y + (y0 + c)) * g.G + gq) & 255u;
-        }
-        const unsigned int ex = block_scan_carry(v, T.s_warp, T.s_misc);
-        if (t == n_own) T.s_misc[1] = ex;  // total of the own columns
-        if (t < n_all) vpre[t] = ex;       // rebased below
-    }
-    __syncthreads();
-    const unsigned int own_total = T.s_misc[1];
-    for (int t = threadIdx.x; t < n_all; t += kSweepThreads)
-        vpre[t] = (t < n_own) ? base_own + vpre[t] : base_next + (vpre[t] - own_total);
-}
-
-// Run-local prefixes of the triangles and centre vertices of the own groups of plane x; run totals into s_misc[2..4].
-__device__ __forceinline__ void emit_build_own(const McGrid& g, const EmitTables& T, int x, int y0, int ny) {
-    const int n_own = ny * g.G;
-    unsigned int nv_total = 0;
-    for (int comp = 0; comp < 2; ++comp) {  // 0: triangles, 1: centre vertices
-        if (threadIdx.x == 0) T.s_misc[0] = 0u;
-        __syncthreads();
-        for (int t0 = 0; t0 < n_own; t0 += kSweepThreads) {
-            const int t = t0 + threadIdx.x;
-            unsigned int word = 0;
-            if (t < n_own) {
-                const int c = t / g.G, gq = t - c * g.G;
-                word = __ldg(g.gcnt + ((size_t)x * g.Y + (y0 + c)) * g.G + gq);
-                if (comp == 0) T.cnt[t] = word;
-            }
-            const unsigned int v = comp == 0 ? (word >> 16) : ((word >> 8) & 255u);
-            const unsigned int ex = block_scan_carry(v, T.s_warp, T.s_misc);
-            if (t < n_own) (comp == 0 ? T.tpre : T.cpre)[t] = ex;
-            if (comp == 0) nv_total += word & 255u;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) T.s_misc[comp == 0 ? 3 : 4] = T.s_misc[0];
-    }
-    nv_total = warp_sum(nv_total);
-    if (threadIdx.x == 0) T.s_misc[2] = 0u;
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0 && nv_total) atomicAdd(&T.s_misc[2], nv_total);
-    __syncthreads();
-}
-
-// Index of the edge vertex owned by voxel (column co of the tables, z = zo) of the plane whose tables are (bp, bq = the
-// plane after it), on `axis`: the group's base from `vpre`, plus the vertices of lower voxels, plus lower axes of its own.
-__device__ __forceinline__ unsigned int edge_vertex_index(const McGrid& g, const unsigned int* bp, const unsigned int* bq,
-                                                          const unsigned int* vpre, int xo, int yo, int co, int zo, int axis) {
-    const int og = zo >> 5, bit = zo & 31;
-    const int i = co * g.GP + og;
-    const unsigned int b00 = bp[i], u00 = (b00 >> 1) | (bp[i + 1] << 31), b01 = bp[i + g.GP], b10 = bq[i];
-    const unsigned int own = range_mask(g.own_lo, g.own_hi, og * 32), zin = range_mask(0, g.Zb - 1, og * 32);
-    const unsigned int mx = (xo + 1 < g.X) ? ((b00 ^ b10) & own) : 0u;
-    const unsigned int my = (yo + 1 < g.Y) ? ((b00 ^ b01) & own) : 0u;
-    const unsigned int mz = (b00 ^ u00) & own & zin;
+// Index of the edge vertex owned by voxel (xo, yo, zo) on `axis`: the tile's and the batch's base + the group's first vertex,
+// plus the vertices of lower voxels, plus lower axes of its own -- one 16-byte load and two hot small-table entries.
+__device__ __forceinline__ unsigned int edge_vertex_index(const McGrid& g, int xo, int yo, int zo, int axis) {
+    const size_t og = ((size_t)xo * g.Y + yo) * g.G + (zo >> 5);
+    const int bit = zo & 31;
+    const uint4 m = __ldg(g.gtab + og);
+    const unsigned int base = __ldg(&g.tile_base[og / (32 * kTileBatches)].x) + __ldg(&g.batch_base[og / 32].x);
     const unsigned int low = (1u << bit) - 1u;
-    unsigned int r = vpre[co * g.G + og] + __popc(mx & low) + __popc(my & low) + __popc(mz & low);
-    if (axis > 0) r += (mx >> bit) & 1u;
-    if (axis > 1) r += (my >> bit) & 1u;
+    unsigned int r = base + m.x + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
+    if (axis > 0) r += (m.y >> bit) & 1u;
+    if (axis > 1) r += (m.z >> bit) & 1u;
     return r;
 }
 
-// One triangle record: rec.x = column | word << 5 | voxel << 13 | tiling << 18 | triangle << 28, rec.y = run-local index.
-__device__ __forceinline__ void emit_triangle(const McGrid& g, const McEmit& out, const EmitTables& T, int s0, int x, int y0,
-                                              uint2 rec, unsigned int tri_base, unsigned int centre_base) {
-    const int c = (int)(rec.x & 31u), gq = (int)((rec.x >> 5) & 255u), k = (int)((rec.x >> 13) & 31u);
-    const int variant = (int)((rec.x >> 18) & 1023u), j = (int)(rec.x >> 28);
-    const int y = y0 + c, zb = gq * 32 + k;
-    const size_t ti = (size_t)tri_base + rec.y;
+// kMcEdgeOwner as a compile-time constant (5 bits per edge: d0 | d1 << 1 | d2 << 2 | axis << 3), so that the unrolled
+// per-edge look-ups of mc_tri_kernel have static offsets.
+constexpr unsigned long long kEdgeOwnerPacked =
+    16ull | (12ull << 5) | (18ull << 10) | (8ull << 15) | (17ull << 20) | (13ull << 25) | (19ull << 30) | (9ull << 35) |
+    (0ull << 40) | (4ull << 45) | (6ull << 50) | (2ull << 55);
+
+// Triangle `j` of the cube (x, y, zb) with tiling `variant`, written as face `ti`.
+__device__ __forceinline__ void emit_triangle(const McGrid& g, const McEmit& out, int x, int y, int zb, int variant, int j,
+                                              size_t ti, unsigned int centre_index) {
     if ((long long)ti >= out.cap_tris) return;
     const uint8_t* tri = kMcTris + 3 * ((size_t)kMcVarTriOff[variant] + (size_t)j);
+    int ox[3], oy[3], oz[3], axis[3];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const int e = tri[q];
+        ox[q] = oy[q] = oz[q] = 0;
+        axis[q] = 3;
+        if (e < 12) {
+            ox[q] = kMcEdgeOwner[4 * e], oy[q] = kMcEdgeOwner[4 * e + 1], oz[q] = kMcEdgeOwner[4 * e + 2];
+            axis[q] = kMcEdgeOwner[4 * e + 3];
+        }
+    }
     if (out.face_keys) {
 #pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            const int e = tri[q];
-            unsigned long long key;
-            if (e < 12)
-                key = vertex_key(g, x + kMcEdgeOwner[4 * e], y + kMcEdgeOwner[4 * e + 1], zb + kMcEdgeOwner[4 * e + 2],
-                                 kMcEdgeOwner[4 * e + 3]);
-            else
-                key = vertex_key(g, x, y, zb, 3);
-            out.face_keys[3 * ti + q] = key;
-        }
+        for (int q = 0; q < 3; ++q) out.face_keys[3 * ti + q] = vertex_key(g, x + ox[q], y + oy[q], zb + oz[q], axis[q]);
         if (out.face_cubes) out.face_cubes[ti] = vertex_key(g, x, y, zb, 0) >> 2;
         return;
     }
     unsigned int v[3];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
-        const int e = tri[q];
-        if (e < 12) {
-            const int ox = kMcEdgeOwner[4 * e], oy = kMcEdgeOwner[4 * e + 1], oz = kMcEdgeOwner[4 * e + 2];
-            const unsigned int* bp = T.bits[(s0 + ox) % 3];
-            const unsigned int* bq = T.bits[(s0 + ox + 1) % 3];
-            v[q] = edge_vertex_index(g, bp, bq, T.vpre[(x + ox) & 1], x + ox, y + oy, c + oy, zb + oz, kMcEdgeOwner[4 * e + 3]);
-        } else {
-            const int t = c * g.G + gq;
-            v[q] = centre_base + T.cpre[t] + __popc(T.mw[t] & ((1u << k) - 1u));
-        }
-    }
+    for (int q = 0; q < 3; ++q)
+        v[q] = axis[q] < 3 ? edge_vertex_index(g, x + ox[q], y + oy[q], zb + oz[q], axis[q]) : centre_index;
 #pragma unroll
     for (int q = 0; q < 3; ++q) out.faces[3 * ti + q] = (int32_t)v[q];
 }
 
-// Bits (i0 | i1 << 1 | ... ) -> Lewiner configuration index: corner i of the cube sits at cube-local (ia, ib, ic) along
-// (edge axis, lower other axis, upper other axis); kCornerPos[axis] holds ia * 4 + ib * 2 + ic for i = 0..7, 3 bits each.
-__device__ __forceinline__ unsigned int corner_positions(int axis) {
-    // corner offsets (axis0, axis1, axis2): 0:(0,0,0) 1:(0,0,1) 2:(0,1,1) 3:(0,1,0) 4:(1,0,0) 5:(1,0,1) 6:(1,1,1) 7:(1,1,0)
-    // axis 0: (ia, ib, ic) = (o0, o1, o2); axis 1: (o1, o0, o2); axis 2: (o2, o0, o1)   [tools/gen_mc_tables.py CORNERS]
-    return axis == 0 ? 0xdec4c8u : (axis == 1 ? 0xdda948u : 0x7f2360u);
+// Cube-local frame of an edge vertex: corner i of a cube sits at (ia, ib, ic) along (edge axis, lower other axis, upper
+// other axis); kCornerPos[axis] holds ia * 4 + ib * 2 + ic for i = 0..7, 3 bits each.
+// corner offsets (axis0, axis1, axis2): 0:(0,0,0) 1:(0,0,1) 2:(0,1,1) 3:(0,1,0) 4:(1,0,0) 5:(1,0,1) 6:(1,1,1) 7:(1,1,0)
+// axis 0: (ia, ib, ic) = (o0, o1, o2); axis 1: (o1, o0, o2); axis 2: (o2, o0, o1)   [tools/gen_mc_tables.py CORNERS]
+constexpr unsigned int kCornerPos[3] = {0xdec4c8u, 0xdda948u, 0x7f2360u};
+
+// sign bits at the eight cube-local positions (bit ia * 4 + ib * 2 + ic) -> Lewiner configuration index, per edge axis
+struct LocToIndex {
+    uint8_t t[3][256];
+};
+constexpr LocToIndex make_loc_to_index() {
+    LocToIndex r{};
+    for (int axis = 0; axis < 3; ++axis)
+        for (int loc = 0; loc < 256; ++loc) {
+            int idx = 0;
+            for (int i = 0; i < 8; ++i) idx |= ((loc >> ((kCornerPos[axis] >> (3 * i)) & 7u)) & 1) << i;
+            r.t[axis][loc] = (uint8_t)idx;
+        }
+    return r;
 }
+static __device__ const LocToIndex kLocToIndex = make_loc_to_index();
+
+// cube-local position -> corner id (the inverse of kCornerPos), 3 bits each
+constexpr unsigned int inverse_corner_pos(unsigned int cpos) {
+    unsigned int inv = 0;
+    for (unsigned int i = 0; i < 8; ++i) inv |= i << (3 * ((cpos >> (3 * i)) & 7u));
+    return inv;
+}
+constexpr unsigned int kPosCorner0 = inverse_corner_pos(kCornerPos[0]), kPosCorner1 = inverse_corner_pos(kCornerPos[1]),
+                       kPosCorner2 = inverse_corner_pos(kCornerPos[2]);
+
+// out of line: the decision tree indexes its eight values dynamically (they live on the stack either way)
+__device__ __noinline__ int cube_variant_values(int idx, const double* v) { return cube_variant(idx, v); }
 
 // One edge vertex (fusion.py:338-348 for one vertex): position on the edge, normal accumulated over the (up to four) cubes
 // around the edge in scan order, colour of the nearest voxel, world transform.  The edge's 2 x 3 x 3 neighbourhood lives in
-// registers in an edge-relative frame (a = along the edge, b < c the other two axes), so nothing is indexed dynamically.
+// registers in an edge-relative frame (a = along the edge, b < c the other two axes): one base pointer and three strides,
+// nothing is indexed dynamically, and the tilings of the surrounding cubes -- face and interior tests included -- are decided
+// from those registers.  (r02: fetching the corners of every ambiguous cube again was 25 % of this kernel's instructions on
+// the room scene, the per-value coordinate permutation another 25 %.)
 __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& out, int x, int y, int zb, int axis, size_t vi) {
-    const int bax = axis == 0 ? 1 : 0, cax = axis == 2 ? 1 : 2;
-    const int pb = bax == 0 ? x : y, pc = cax == 1 ? y : zb;
-    const int db_dim = bax == 0 ? g.X : g.Y, dc_dim = cax == 1 ? g.Y : g.Zb;
+    const int pb = axis == 0 ? y : x, pc = axis == 2 ? y : zb;
+    const int db_dim = axis == 0 ? g.Y : g.X, dc_dim = axis == 2 ? g.Y : g.Zb;
+    bool okb[3], okc[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        okb[i] = pb + i - 1 >= 0 && pb + i - 1 < db_dim;
+        okc[i] = pc + i - 1 >= 0 && pc + i - 1 < dc_dim;
+    }
     float n[2][3][3];
+    if (g.halo_lo == nullptr && g.halo_hi == nullptr) {  // whole volume: zb == z, every neighbour is in the plane array
+        const ptrdiff_t sx = (ptrdiff_t)g.Y * g.pitch, sy = g.pitch;
+        const ptrdiff_t sa = axis == 0 ? sx : (axis == 1 ? sy : 1), sb = axis == 0 ? sy : sx, sc = axis == 2 ? sy : 1;
+        const float* p0 = g.tsdf + ((size_t)x * g.Y + y) * (size_t)g.pitch + zb;
+#pragma unroll
+        for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+            for (int ib = 0; ib < 3; ++ib)
+#pragma unroll
+                for (int ic = 0; ic < 3; ++ic)
+                    n[ia][ib][ic] = (okb[ib] && okc[ic]) ? __ldg(p0 + ia * sa + (ib - 1) * sb + (ic - 1) * sc) : 0.0f;
+    } else {
+#pragma unroll
+        for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+            for (int ib = 0; ib < 3; ++ib)
+#pragma unroll
+                for (int ic = 0; ic < 3; ++ic) {
+                    const int qb = pb + ib - 1, qc = pc + ic - 1;
+                    float f = 0.0f;
+                    if (okb[ib] && okc[ic]) {
+                        // (x, y, zb) of the neighbour: the three coordinates are (a, b, c) permuted by `axis`
+                        const int qx = axis == 0 ? x + ia : qb;
+                        const int qy = axis == 1 ? y + ia : (axis == 0 ? qb : qc);
+                        const int qz = axis == 2 ? zb + ia : qc;
+                        f = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, qx, qy, qz);
+                    }
+                    n[ia][ib][ic] = f;
+                }
+    }
+    const double level = g.level;
+    // sign bit of every neighbour, position ia * 9 + ib * 3 + ic
+    unsigned int sgn = 0u;
 #pragma unroll
     for (int ia = 0; ia < 2; ++ia)
 #pragma unroll
         for (int ib = 0; ib < 3; ++ib)
 #pragma unroll
-            for (int ic = 0; ic < 3; ++ic) {
-                const int qb = pb + ib - 1, qc = pc + ic - 1;
-                float f = 0.0f;
-                if (qb >= 0 && qb < db_dim && qc >= 0 && qc < dc_dim) {
-                    // (x, y, zb) of the neighbour: the three coordinates are (a, b, c) permuted by `axis`
-                    const int qx = axis == 0 ? x + ia : qb;                      // bax == 0 whenever axis != 0
-                    const int qy = axis == 1 ? y + ia : (axis == 0 ? qb : qc);    // axis 0: b = y; axis 2: c = y
-                    const int qz = axis == 2 ? zb + ia : qc;                     // cax == 2 whenever axis != 2
-                    f = mc_fetch(g, g.tsdf, g.halo_lo, g.halo_hi, qx, qy, qz);
-                }
-                n[ia][ib][ic] = f;
-            }
-    const double level = g.level;
+            for (int ic = 0; ic < 3; ++ic)
+                sgn |= (((double)n[ia][ib][ic] - level) > 0.0 ? 1u : 0u) << (ia * 9 + ib * 3 + ic);
     const double v_lo = (double)n[0][1][1] - level, v_hi = (double)n[1][1][1] - level;
     const double w_lo = 1.0 / ((double)FLT_EPSILON + fabs(v_lo)), w_hi = 1.0 / ((double)FLT_EPSILON + fabs(v_hi));
     const double frac = w_hi / __dadd_rn(w_lo, w_hi);
-    const unsigned int cpos = corner_positions(axis);
+    const unsigned int pos_corner = axis == 0 ? kPosCorner0 : (axis == 1 ? kPosCorner1 : kPosCorner2);
     float acc_a = 0.0f, acc_b = 0.0f, acc_c = 0.0f;
     // the cubes around the edge in scan order (axis0 outermost): larger offsets first; b is the lower axis
 #pragma unroll
     for (int db = 1; db >= 0; --db) {
 #pragma unroll
         for (int dc = 1; dc >= 0; --dc) {
-            const int bb = pb - db, bc = pc - dc;  // base of the cube along b, c
-            if (bb < 0 || bc < 0 || bb + 1 >= db_dim || bc + 1 >= dc_dim) continue;
+            if (!okb[1 - db] || !okc[1 - dc] || !okb[2 - db] || !okc[2 - dc]) continue;  // the cube does not exist
             // sign bits of the cube's corners at cube-local (ia, ib, ic)
             unsigned int loc = 0;
 #pragma unroll
@@ -689,18 +736,19 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
                 for (int ib = 0; ib < 2; ++ib)
 #pragma unroll
                     for (int ic = 0; ic < 2; ++ic)
-                        loc |= (((double)n[ia][ib + 1 - db][ic + 1 - dc] - level) > 0.0 ? 1u : 0u) << (ia * 4 + ib * 2 + ic);
-            int idx = 0;
+                        loc |= ((sgn >> (ia * 9 + (ib + 1 - db) * 3 + (ic + 1 - dc))) & 1u) << (ia * 4 + ib * 2 + ic);
+            const int idx = kLocToIndex.t[axis][loc];
+            int variant = kMcVariantBase[idx];
+            if (kMcAmbCount[idx] != 0 || kMcInteriorBase[idx] != 255) {
+                double v[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) idx |= (int)((loc >> ((cpos >> (3 * i)) & 7u)) & 1u) << i;
-            int variant;
-            if (kMcAmbCount[idx] == 0 && kMcInteriorBase[idx] == 255) {
-                variant = kMcVariantBase[idx];
-            } else {
-                const int cx = axis == 0 ? x : bb;
-                const int cy = axis == 1 ? y : (axis == 0 ? bb : bc);
-                const int cz = axis == 2 ? zb : bc;
-                variant = cube_variant_ambiguous(g.tsdf, g.halo_lo, g.halo_hi, g.Y, g.pitch, g.Z, g.hl, g.level, idx, cx, cy, cz);
+                for (int ia = 0; ia < 2; ++ia)
+#pragma unroll
+                    for (int ib = 0; ib < 2; ++ib)
+#pragma unroll
+                        for (int ic = 0; ic < 2; ++ic)
+                            v[(pos_corner >> (3 * (ia * 4 + ib * 2 + ic))) & 7u] = (double)n[ia][ib + 1 - db][ic + 1 - dc] - level;
+                variant = cube_variant_values(idx, v);
             }
             // the edge inside this cube: lower corner at cube-local (0, db, dc)
             const int d0 = axis == 0 ? 0 : db, d1 = axis == 1 ? 0 : (axis == 0 ? db : dc), d2 = axis == 2 ? 0 : dc;
@@ -803,123 +851,68 @@ __device__ __noinline__ void emit_centre_vertex(const McGrid& g, const McEmit& o
     if (out.vert_keys) out.vert_keys[vi] = vertex_key(g, x, y, zb, 3);
 }
 
-__global__ void __launch_bounds__(kSweepThreads, 2) mc_emit_kernel(const McGrid g, const McEmit out) {
-    extern __shared__ unsigned int s_mem[];
-    EmitTables T;
-    {
-        const int tabw = (g.TY + 2) * g.GP, vw = (g.TY + 1) * g.G, ow = g.TY * g.G;
-        unsigned int* p = s_mem;
-        for (int i = 0; i < 3; ++i, p += tabw) T.bits[i] = p;
-        for (int i = 0; i < 2; ++i, p += vw) T.vpre[i] = p;
-        T.tpre = p; p += ow;
-        T.cpre = p; p += ow;
-        T.cnt = p; p += ow;
-        T.mw = p; p += ow;
-        T.s_warp = p; p += 8;
-        T.s_misc = p; p += 8;
-        T.rec = reinterpret_cast<uint2*>(p + ((reinterpret_cast<uintptr_t>(p) & 4) ? 1 : 0));
-    }
-    const int strip = blockIdx.x % g.S, chunk = blockIdx.x / g.S;
-    const int y0 = strip * g.TY, ny = min(g.TY, g.Y - y0);
-    const int xa = chunk * out.CX, xb = min(g.X, xa + out.CX);
-    const int n_own = ny * g.G;
-    const unsigned int n_edge_total = (unsigned int)g.totals[4];
-    int held_bits[3] = {-1, -1, -1}, held_v[2] = {-1, -1};
-    for (int x = xa; x < xb; ++x) {
-        const uint4 rt = g.run_tot[(size_t)x * g.S + strip];
-        if ((rt.x | rt.y | rt.z) == 0u) continue;  // nothing owned by this run (uniform over the block)
-        __syncthreads();                           // the previous plane's readers are done with the tables
-        for (int d = 0; d < 3; ++d)
-            if (held_bits[(x + d) % 3] != x + d) {
-                emit_load_bits(g, T.bits[(x + d) % 3], x + d, y0);
-                held_bits[(x + d) % 3] = x + d;
-            }
-        for (int d = 0; d < 2; ++d)
-            if (held_v[(x + d) & 1] != x + d) {
-                emit_build_vpre(g, T, T.vpre[(x + d) & 1], x + d, strip, y0, ny);
-                held_v[(x + d) & 1] = x + d;
-            }
-        emit_build_own(g, T, x, y0, ny);
-        __syncthreads();
-        const uint4 rb = g.run_base[(size_t)x * g.S + strip];
-        const unsigned int run_nv = T.s_misc[2], run_nt = T.s_misc[3], run_nc = T.s_misc[4];
-        const int s0 = x % 3;
-        const unsigned int* B0 = T.bits[s0];
-        const unsigned int* B1 = T.bits[(s0 + 1) % 3];
-        // ---- triangles: one record per triangle, then one thread per record
-        for (unsigned int lo = 0; lo < run_nt; lo += kRecCap) {
-            const unsigned int hi = lo + kRecCap;
-            for (int t = threadIdx.x; t < n_own; t += kSweepThreads) {
-                const unsigned int nt = T.cnt[t] >> 16;
-                unsigned int o = T.tpre[t];
-                if (nt == 0u || o + nt <= lo || o >= hi) continue;
-                const int c = t / g.G, gq = t - c * g.G;
-                const CubeWords w = cube_words(g, B0, B1, x, y0 + c, c, gq);
-                unsigned int mw = 0u;
-                for (unsigned int rest = w.active; rest; rest &= rest - 1) {
-                    const int k = __ffs(rest) - 1;
-                    const int variant = cube_variant_at(g, cube_index(w, k), x, y0 + c, gq * 32 + k);
-                    const unsigned int ntri = kMcVarNtri[variant];
-                    if ((kMcVarMult[variant] >> 48) & 15ull) mw |= 1u << k;
-                    const unsigned int head = (unsigned int)c | ((unsigned int)gq << 5) | ((unsigned int)k << 13) |
-                                              ((unsigned int)variant << 18);
-                    for (unsigned int j = 0; j < ntri; ++j)
-                        if (o + j >= lo && o + j < hi) T.rec[o + j - lo] = make_uint2(head | (j << 28), o + j);
-                    o += ntri;
-                }
-                T.mw[t] = mw;
-            }
-            __syncthreads();
-            const unsigned int n = min(run_nt - lo, (unsigned int)kRecCap);
-            for (unsigned int i = threadIdx.x; i < n; i += kSweepThreads)
-                emit_triangle(g, out, T, s0, x, y0, T.rec[i], rb.y, n_edge_total + rb.z);
-            __syncthreads();
-        }
-        // ---- edge vertices
-        for (unsigned int lo = 0; lo < run_nv; lo += kRecCap) {
-            const unsigned int hi = lo + kRecCap;
-            for (int t = threadIdx.x; t < n_own; t += kSweepThreads) {
-                const unsigned int nv = T.cnt[t] & 255u;
-                unsigned int o = T.vpre[x & 1][t] - rb.x;  // run-local
-                if (nv == 0u || o + nv <= lo || o >= hi) continue;
-                const int c = t / g.G, gq = t - c * g.G;
-                const CubeWords w = cube_words(g, B0, B1, x, y0 + c, c, gq);
-                const unsigned int head = (unsigned int)c | ((unsigned int)gq << 5);
-                for (unsigned int rest = w.mx | w.my | w.mz; rest; rest &= rest - 1) {
-                    const int k = __ffs(rest) - 1;
+constexpr int kEmitThreads = 256;
+
+// ---- 3. triangles (+ cube-centre vertices): one thread per cube record ---------------------------------------------------------
+// The vertex indices of the cube's (up to 12) edges are looked up first, all loads independent; its triangles then pick
+// from that array.  (One thread walking its triangles with three dependent look-ups each was measured at 66 us.)
+__global__ void __launch_bounds__(kEmitThreads, 4) mc_tri_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out) {
+    __shared__ unsigned int s_vidx[13][kEmitThreads];  // [edge][thread]: dynamic indexing without local memory
+    if (g.totals[6]) return;  // the records are incomplete: the host re-runs the count with a larger work buffer
+    const unsigned int n_cubes = (unsigned int)g.totals[5], n_edge = (unsigned int)g.totals[4];
+    for (unsigned int i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_cubes; i += gridDim.x * kEmitThreads) {
+        const uint4 rec = __ldg(g.cube_rec + i);
+        int x, y, gq;
+        decode_group(g, rec.x, x, y, gq);
+        const uint4 tb = __ldg(g.tile_base + rec.x / (32 * kTileBatches)), bb = __ldg(g.batch_base + rec.x / 32);
+        const uint4 base = make_uint4(tb.x + bb.x, tb.y + bb.y, tb.z + bb.z, 0u);
+        const int k = (int)(rec.y & 31u), variant = (int)(rec.y >> 5), zb = gq * 32 + k;
+        const int ntri = kMcVarNtri[variant];
+        const unsigned long long mult = kMcVarMult[variant];
+        const unsigned int centre_index = n_edge + base.z + rec.w;
+        const size_t t0 = (size_t)base.y + rec.z;
+        if (out.face_keys) {
+            for (int j = 0; j < ntri; ++j) emit_triangle(g, out, x, y, zb, variant, j, t0 + j, centre_index);
+        } else {
+            unsigned int vidx[12];
 #pragma unroll
-                    for (int axis = 0; axis < 3; ++axis) {
-                        const unsigned int m = axis == 0 ? w.mx : (axis == 1 ? w.my : w.mz);
-                        if ((m >> k) & 1u) {
-                            if (o >= lo && o < hi) T.rec[o - lo] = make_uint2(head | ((unsigned int)k << 13) | ((unsigned int)axis << 18), o);
-                            ++o;
-                        }
-                    }
-                }
+            for (int e = 0; e < 12; ++e) {
+                constexpr unsigned long long P = kEdgeOwnerPacked;
+                const int code = (int)((P >> (5 * e)) & 31ull);
+                vidx[e] = 0u;
+                if ((mult >> (4 * e)) & 15ull)
+                    vidx[e] = edge_vertex_index(g, x + (code & 1), y + ((code >> 1) & 1), zb + ((code >> 2) & 1), code >> 3);
             }
-            __syncthreads();
-            const unsigned int n = min(run_nv - lo, (unsigned int)kRecCap);
-            for (unsigned int i = threadIdx.x; i < n; i += kSweepThreads) {
-                const uint2 r = T.rec[i];
-                const size_t vi = (size_t)rb.x + r.y;
-                if ((long long)vi < out.cap_verts)
-                    emit_edge_vertex(g, out, x, y0 + (int)(r.x & 31u), (int)((r.x >> 5) & 255u) * 32 + (int)((r.x >> 13) & 31u),
-                                     (int)((r.x >> 18) & 3u), vi);
-            }
-            __syncthreads();
-        }
-        // ---- cube-centre vertices (tilings 6.1.2, 7.3, 10.2, 12.2, 13.3, 13.4): after all edge vertices
-        if (run_nc) {
-            for (int t = threadIdx.x; t < n_own; t += kSweepThreads) {
-                unsigned int m = ((T.cnt[t] >> 8) & 255u) ? T.mw[t] : 0u;
-                unsigned int o = T.cpre[t];
-                const int c = t / g.G, gq = t - c * g.G;
-                for (; m; m &= m - 1, ++o) {
-                    const size_t vi = (size_t)n_edge_total + rb.z + o;
-                    if ((long long)vi < out.cap_verts) emit_centre_vertex(g, out, x, y0 + c, gq * 32 + (__ffs(m) - 1), vi);
-                }
+#pragma unroll
+            for (int e = 0; e < 12; ++e) s_vidx[e][threadIdx.x] = vidx[e];
+            s_vidx[12][threadIdx.x] = centre_index;
+            const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
+            for (int j = 0; j < ntri; ++j) {
+                const size_t ti = t0 + j;
+                if ((long long)ti >= out.cap_tris) break;
+                const unsigned int a = s_vidx[tri[3 * j]][threadIdx.x], b = s_vidx[tri[3 * j + 1]][threadIdx.x],
+                                   c = s_vidx[tri[3 * j + 2]][threadIdx.x];
+                out.faces[3 * ti] = (int32_t)a;
+                out.faces[3 * ti + 1] = (int32_t)b;
+                out.faces[3 * ti + 2] = (int32_t)c;
             }
         }
+        if (((mult >> 48) & 15ull) && (long long)centre_index < out.cap_verts) emit_centre_vertex(g, out, x, y, zb, centre_index);
+    }
+}
+
+// ---- 4. edge vertices: one thread per vertex record ----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kEmitThreads, 2) mc_vert_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out) {
+    if (g.totals[6]) return;
+    const unsigned int n_edge = (unsigned int)g.totals[4];
+    for (unsigned int i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_edge; i += gridDim.x * kEmitThreads) {
+        const unsigned long long rec = __ldg(g.vert_rec + i);
+        const unsigned int gid = (unsigned int)(rec & 0x7fffffffull);
+        const int k = (int)((rec >> 31) & 31ull), axis = (int)((rec >> 36) & 3ull);
+        int x, y, gq;
+        decode_group(g, gid, x, y, gq);
+        const size_t vi = (size_t)__ldg(&g.tile_base[gid / (32 * kTileBatches)].x) + __ldg(&g.batch_base[gid / 32].x) + (unsigned int)(rec >> 38);
+        if ((long long)vi < out.cap_verts) emit_edge_vertex(g, out, x, y, gq * 32 + k, axis, vi);
     }
 }
 
@@ -929,9 +922,9 @@ __global__ void __launch_bounds__(kSweepThreads, 2) mc_emit_kernel(const McGrid 
 namespace {
 
 struct McLayout {
-    long long n_groups, n_runs;
-    int G, Zb, TY, S, GP;
-    size_t off_bits, off_gcnt, off_run_tot, off_run_base, total;
+    long long n_groups, n_batches, n_tiles;
+    int G, Zb;
+    size_t off_bits, off_gtab, off_batch_base, off_tile_tot, off_tile_base, off_ctrl, total;
 };
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -943,37 +936,42 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
                "marching cubes: bad dims %lld x %lld x %lld", (long long)X, (long long)Y, (long long)Z);
     L->Zb = (int)Z + (lo ? 1 : 0) + (hi ? 1 : 0);
     L->G = (L->Zb + 31) / 32;
-    HV_REQUIRE(L->G <= 256, "marching cubes: more than 8192 voxels along axis 2 per shard (%d): cut the volume into z-slabs", L->Zb);
     L->n_groups = (long long)X * Y * L->G;
-    HV_REQUIRE(L->n_groups < (1ll << 32), "marching cubes: volume too large");
-    int ty = 512 / L->G;  // about two rounds of the 256 threads per plane of a strip
-    ty = ty < 1 ? 1 : (ty > 30 ? 30 : ty);
-    if (ty > Y) ty = (int)Y;
-    L->TY = ty;
-    L->S = (int)((Y + ty - 1) / ty);
-    L->GP = L->G + 2;
-    L->n_runs = (long long)X * L->S;
-    HV_REQUIRE(L->n_runs < (1ll << 31), "marching cubes: too many runs");
+    HV_REQUIRE(L->n_groups < (1ll << 31) && L->Zb < (1 << 22), "marching cubes: volume too large");
+    L->n_batches = (L->n_groups + 31) / 32;
+    L->n_tiles = (L->n_batches + hv::kTileBatches - 1) / hv::kTileBatches;
     size_t o = 0;
-    L->off_run_tot = o;
-    o = align_up(o + (size_t)L->n_runs * sizeof(uint4));
-    L->off_run_base = o;
-    o = align_up(o + (size_t)L->n_runs * sizeof(uint4));
+    L->off_gtab = o;  // 16-byte elements first
+    o = align_up(o + (size_t)L->n_groups * sizeof(uint4));
+    L->off_batch_base = o;
+    o = align_up(o + (size_t)L->n_batches * sizeof(uint4));
+    L->off_tile_tot = o;
+    o = align_up(o + (size_t)L->n_tiles * sizeof(uint4));
+    L->off_tile_base = o;
+    o = align_up(o + (size_t)L->n_tiles * sizeof(uint4));
     L->off_bits = o;
     o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
-    L->off_gcnt = o;
-    o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
+    L->off_ctrl = o;
+    o = align_up(o + 8 * sizeof(unsigned int));
     L->total = o;
     return HV_OK;
 }
 
+size_t work_bytes(int64_t rec_verts, int64_t rec_cubes) {
+    return align_up((size_t)rec_cubes * sizeof(uint4)) + align_up((size_t)rec_verts * sizeof(unsigned long long));
+}
+
 int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims,
-            int64_t pitch, double level, void* scratch, int64_t scratch_bytes, McLayout* L) {
+            int64_t pitch, double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+            int64_t rec_cubes, McLayout* L) {
     int rc = mc_layout(h_dims, halo_lo != nullptr, halo_hi != nullptr, L);
     if (rc != HV_OK) return rc;
     HV_REQUIRE(tsdf && scratch, "marching cubes: null pointer");
     HV_REQUIRE(pitch >= h_dims[2], "marching cubes: pitch %lld < Z", (long long)pitch);
     HV_REQUIRE(((uintptr_t)scratch & 255) == 0, "marching cubes: scratch must be 256-byte aligned");
+    HV_REQUIRE(rec_verts >= 0 && rec_cubes >= 0 && rec_verts < (1ll << 31) && rec_cubes < (1ll << 31) &&
+                   (work != nullptr || (rec_verts == 0 && rec_cubes == 0)) && ((uintptr_t)work & 255) == 0,
+               "marching cubes: bad work buffer");
     if ((size_t)scratch_bytes < L->total) {
         hv::set_error("marching cubes: scratch of %lld bytes, need %lld", (long long)scratch_bytes, (long long)L->total);
         return HV_E_CAPACITY;
@@ -995,24 +993,21 @@ int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float*
     g->zoff = -(long long)g->hl;
     g->Zg = g->Z;
     g->level = level;
-    g->TY = L->TY;
-    g->S = L->S;
-    g->GP = L->GP;
     g->bits = reinterpret_cast<unsigned int*>(s + L->off_bits);
-    g->gcnt = reinterpret_cast<unsigned int*>(s + L->off_gcnt);
-    g->run_tot = reinterpret_cast<uint4*>(s + L->off_run_tot);
-    g->run_base = reinterpret_cast<uint4*>(s + L->off_run_base);
+    g->gtab = reinterpret_cast<uint4*>(s + L->off_gtab);
+    g->batch_base = reinterpret_cast<uint4*>(s + L->off_batch_base);
+    g->tile_tot = reinterpret_cast<uint4*>(s + L->off_tile_tot);
+    g->tile_base = reinterpret_cast<uint4*>(s + L->off_tile_base);
+    g->ctrl = reinterpret_cast<unsigned int*>(s + L->off_ctrl);
+    g->cube_rec = reinterpret_cast<uint4*>(work);
+    g->vert_rec = reinterpret_cast<unsigned long long*>(static_cast<char*>(work) + align_up((size_t)rec_cubes * sizeof(uint4)));
+    g->cap_cubes = rec_cubes;
+    g->cap_vrec = rec_verts;
     g->totals = nullptr;
     g->n_groups = L->n_groups;
+    g->n_batches = L->n_batches;
+    g->n_tiles = (int)L->n_tiles;
     return HV_OK;
-}
-
-// planes per chunk so that about `target` CTAs exist
-int planes_per_chunk(int X, int S, long long target) {
-    long long chunks = (target + S - 1) / S;
-    if (chunks < 1) chunks = 1;
-    if (chunks > X) chunks = X;
-    return (int)((X + chunks - 1) / chunks);
 }
 
 }  // namespace
@@ -1026,38 +1021,49 @@ extern "C" int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int h
     return HV_OK;
 }
 
+extern "C" int hv_mc_work_bytes(int64_t rec_verts, int64_t rec_cubes, int64_t* h_bytes) {
+    HV_REQUIRE(h_bytes && rec_verts >= 0 && rec_cubes >= 0 && rec_verts < (1ll << 31) && rec_cubes < (1ll << 31),
+               "hv_mc_work_bytes: bad arguments");
+    *h_bytes = (int64_t)work_bytes(rec_verts, rec_cubes);
+    return HV_OK;
+}
+
 extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims,
-                           int64_t pitch, double level, void* scratch, int64_t scratch_bytes,
-                           unsigned long long* totals, void* stream) {
+                           int64_t pitch, double level, void* scratch, int64_t scratch_bytes, void* work,
+                           int64_t rec_verts, int64_t rec_cubes, unsigned long long* totals, void* stream) {
     hv::McGrid g;
     McLayout L;
-    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, &L);
+    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, work, rec_verts, rec_cubes, &L);
     if (rc != HV_OK) return rc;
     HV_REQUIRE(totals, "hv_mc_count: null totals");
     g.totals = totals;
     cudaStream_t st = hv::as_stream(stream);
-    hv::mc_init_kernel<<<1, 32, 0, st>>>(totals);  // (a pageable H2D of the counters would block the host)
+    hv::mc_init_kernel<<<1, 32, 0, st>>>(totals, g.ctrl);  // (a pageable H2D of the counters would block the host)
     const int sms = hv::device_info().sm_count;
-    const int vec = (!halo_lo && (pitch & 3) == 0 && ((uintptr_t)tsdf & 15) == 0) ? 1 : 0;
-    const int CX = planes_per_chunk(g.X, g.S, (long long)sms * 4);
-    const int chunks = (g.X + CX - 1) / CX;
-    const size_t smem = (size_t)2 * (g.TY + 2) * g.GP * sizeof(unsigned int);
-    hv::mc_classify_kernel<<<(unsigned int)(g.S * chunks), hv::kSweepThreads, smem, st>>>(g, CX, vec);
-    hv::mc_run_scan_kernel<<<1, hv::kRunScanThreads, 0, st>>>(g.run_tot, g.run_base, (int)L.n_runs, totals);
+    static int sign_res = 0;  // resident CTAs per SM of the sign kernel: the grid is exactly one wave
+    if (sign_res == 0 &&
+        (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sign_res, hv::mc_sign_kernel, 256, 0) != cudaSuccess || sign_res < 1))
+        sign_res = 4;
+    const long long want = ((long long)g.X * g.Y + 7) / 8;  // 8 warps per block, a warp per column (grid-stride)
+    const long long cap = (long long)sms * sign_res;
+    const int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
+    hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g);
+    hv::mc_count_kernel<<<(unsigned int)L.n_tiles, hv::kCountThreads, 0, st>>>(g);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }
 
 extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
                           const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
-                          double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
-                          float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
-                          float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces,
-                          unsigned long long* face_keys, unsigned long long* face_cubes, unsigned long long* vert_keys,
-                          unsigned long long* totals, void* stream) {
+                          double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+                          int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
+                          const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world, float* verts_voxel,
+                          float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
+                          unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals,
+                          void* stream) {
     hv::McGrid g;
     McLayout L;
-    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, &L);
+    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, work, rec_verts, rec_cubes, &L);
     if (rc != HV_OK) return rc;
     HV_REQUIRE(n_verts >= 0 && n_tris >= 0 && n_verts < (1ll << 31) && n_tris < (1ll << 31), "hv_mc_emit: bad counts");
     if (n_verts == 0 && n_tris == 0) return HV_OK;  // a shard the surface does not cross / no capacity at all
@@ -1088,33 +1094,39 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     em.voxel_size = voxel_size;
     for (int k = 0; k < 3; ++k) em.origin[k] = h_origin[k];
     const int sms = hv::device_info().sm_count;
-    em.CX = planes_per_chunk(g.X, g.S, (long long)sms * 16);
-    if (em.CX < 4 && g.X >= 4) em.CX = 4;
-    const int chunks = (g.X + em.CX - 1) / em.CX;
-    const size_t words = (size_t)3 * (g.TY + 2) * g.GP + (size_t)2 * (g.TY + 1) * g.G + (size_t)4 * g.TY * g.G + 16 + 2;
-    const size_t smem = words * sizeof(unsigned int) + (size_t)hv::kRecCap * sizeof(uint2);
-    HV_REQUIRE(smem <= 48 * 1024, "hv_mc_emit: %lld bytes of shared memory", (long long)smem);
-    hv::mc_emit_kernel<<<(unsigned int)(g.S * chunks), hv::kSweepThreads, smem, st>>>(g, em);
+    // one thread per record that can exist: a surface cube has a triangle, an edge vertex is a vertex
+    const long long max_cubes = rec_cubes < n_tris ? rec_cubes : n_tris, max_verts = rec_verts < n_verts ? rec_verts : n_verts;
+    // (grid-stride: a capacity far above the surface would otherwise launch tens of thousands of CTAs that only read the totals)
+    const long long grid_cap = (long long)sms * 32;
+    if (max_cubes > 0) {
+        const long long blocks = (max_cubes + hv::kEmitThreads - 1) / hv::kEmitThreads;
+        hv::mc_tri_kernel<<<(unsigned int)(blocks < grid_cap ? blocks : grid_cap), hv::kEmitThreads, 0, st>>>(g, em);
+    }
+    if (max_verts > 0) {
+        const long long blocks = (max_verts + hv::kEmitThreads - 1) / hv::kEmitThreads;
+        hv::mc_vert_kernel<<<(unsigned int)(blocks < grid_cap ? blocks : grid_cap), hv::kEmitThreads, 0, st>>>(g, em);
+    }
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }
 
 // Count + emit in one call: the only host round trip (the output sizes are data dependent) is a stream synchronise on
 // the counters copied into the caller's pinned `h_totals`; the caller provides output buffers with a capacity and gets
-// HV_E_CAPACITY (with h_totals filled, scratch still valid for a plain hv_mc_emit) if the surface is larger.
+// HV_E_CAPACITY (with h_totals filled, scratch still valid) if the surface -- or its work records -- is larger.
 extern "C" int hv_mc_extract(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
                              const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
-                             double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset,
-                             int64_t z_global_dim, float voxel_size, const float* h_origin, int64_t cap_verts,
-                             int64_t cap_tris, float* verts_world, float* verts_voxel, float* normals, uint8_t* colors,
-                             int32_t* faces, unsigned long long* face_keys, unsigned long long* face_cubes,
-                             unsigned long long* vert_keys, unsigned long long* totals, unsigned long long* h_totals,
-                             void* stream) {
+                             double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+                             int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
+                             const float* h_origin, int64_t cap_verts, int64_t cap_tris, float* verts_world,
+                             float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces,
+                             unsigned long long* face_keys, unsigned long long* face_cubes, unsigned long long* vert_keys,
+                             unsigned long long* totals, unsigned long long* h_totals, void* stream) {
     HV_REQUIRE(h_totals, "hv_mc_extract: null h_totals");
-    int rc = hv_mc_count(tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, totals, stream);
+    int rc = hv_mc_count(tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, work, rec_verts, rec_cubes,
+                         totals, stream);
     if (rc != HV_OK) return rc;
     cudaStream_t st = hv::as_stream(stream);
-    HV_CUDA(cudaMemcpyAsync(h_totals, totals, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    HV_CUDA(cudaMemcpyAsync(h_totals, totals, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     HV_CUDA(cudaStreamSynchronize(st));
     const int64_t n_verts = (int64_t)h_totals[0], n_tris = (int64_t)h_totals[1];
     auto key_to_float = [](unsigned long long k) {
@@ -1133,12 +1145,13 @@ extern "C" int hv_mc_extract(const float* tsdf, const float* halo_lo, const floa
         hv::set_error("No surface found at the given iso value.");
         return HV_E_NOSURFACE;
     }
-    if (n_verts > cap_verts || n_tris > cap_tris) {
-        hv::set_error("hv_mc_extract: %lld vertices / %lld triangles exceed the capacity %lld / %lld", (long long)n_verts,
-                      (long long)n_tris, (long long)cap_verts, (long long)cap_tris);
+    if (n_verts > cap_verts || n_tris > cap_tris || h_totals[6]) {
+        hv::set_error("hv_mc_extract: %lld vertices / %lld triangles (%lld edge vertices / %lld cubes to record) exceed the "
+                      "capacity %lld / %lld (%lld / %lld)", (long long)n_verts, (long long)n_tris, (long long)h_totals[4],
+                      (long long)h_totals[5], (long long)cap_verts, (long long)cap_tris, (long long)rec_verts, (long long)rec_cubes);
         return HV_E_CAPACITY;
     }
     return hv_mc_emit(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch,
-                      scratch_bytes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris, verts_world,
-                      verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys, totals, stream);
+                      scratch_bytes, work, rec_verts, rec_cubes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts,
+                      n_tris, verts_world, verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys, totals, stream);
 }

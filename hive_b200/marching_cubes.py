@@ -18,8 +18,8 @@ from . import _lib
 from . import _xfer
 
 
-#: kernels launched by one extraction (init, classify, run scan, emit); bench.py reports it
-LAUNCHES_PER_EXTRACTION = 4
+#: kernels launched by one extraction (init, sign, count+scan, triangles, vertices); bench.py reports it
+LAUNCHES_PER_EXTRACTION = 5
 
 
 def _ptr(t):
@@ -89,16 +89,44 @@ class McPlan:
             pad = (-self.scratch.data_ptr()) % 256
             self.scratch_ptr = ctypes.c_void_p(self.scratch.data_ptr() + pad)
             self.totals = torch.zeros(8, dtype=torch.int64, device=self.device)
+        self.work = None
+        self.work_ptr = None
+        self.rec_verts = self.rec_cubes = 0
+        self._records_incomplete = False
 
-    def count(self):
-        """Launch the classification; returns the device tensor of totals (no sync)."""
+    def _ensure_work(self, rec_verts, rec_cubes):
+        """Work records of the emit kernels (one per edge vertex, one per surface cube): a surface cube has at least one
+        triangle, so (vertex capacity, triangle capacity) always suffices."""
+        rec_verts, rec_cubes = int(rec_verts), int(rec_cubes)
+        if self.work is not None and rec_verts <= self.rec_verts and rec_cubes <= self.rec_cubes:
+            return
         torch = self._torch
+        nbytes = ctypes.c_int64(0)
+        _lib.check(self._lib.hv_mc_work_bytes(rec_verts, rec_cubes, ctypes.byref(nbytes)))
+        with torch.cuda.device(self.device):
+            self.work = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=self.device)
+        self.work_ptr = ctypes.c_void_p(self.work.data_ptr() + (-self.work.data_ptr()) % 256)
+        self.rec_verts, self.rec_cubes = rec_verts, rec_cubes
+
+    def default_capacity(self):
+        """A few voxel layers' worth of surface (an extraction that needs more counts twice)."""
+        X, Y, Z = (int(d) for d in self.dims)
+        area = X * Y + Y * Z + X * Z
+        return min(6 * area, 3 * X * Y * Z), min(12 * area, 5 * X * Y * Z)
+
+    def count(self, cap_verts=None, cap_tris=None):
+        """Launch the classification (sign bits, per-group counts, work records for a surface of at most ``cap_verts``
+        vertices / ``cap_tris`` triangles); returns the device tensor of totals (no sync)."""
+        torch = self._torch
+        if cap_verts is None or cap_tris is None:
+            cap_verts, cap_tris = self.default_capacity()
+        self._ensure_work(cap_verts, cap_tris)
         with torch.cuda.device(self.device):
             stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
             _lib.check(self._lib.hv_mc_count(
                 _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")),
                 ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
-                _ptr(self.totals), stream))
+                self.work_ptr, self.rec_verts, self.rec_cubes, _ptr(self.totals), stream))
         return self.totals
 
     def read_totals(self):
@@ -109,13 +137,18 @@ class McPlan:
         with torch.cuda.device(self.device):
             host.copy_(self.totals, non_blocking=True)
             torch.cuda.current_stream().synchronize()
-        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist()[:4])
+        vals = [int(v) for v in host.tolist()]
+        n_verts, n_tris, kmin, kmax = vals[:4]
+        self._records_incomplete = bool(vals[6])
         return n_verts, n_tris, _key_to_float(kmin), _key_to_float(kmax)
 
     def emit(self, n_verts, n_tris, voxel_size, origin, want_voxel=False, keys=False) -> DeviceMesh:
         torch = self._torch
         dev = self.device
         origin = np.ascontiguousarray(origin, dtype=np.float32)
+        if self._records_incomplete:  # the surface outgrew the work buffer of the count: count again, exactly sized
+            self.count(n_verts, n_tris)
+            self._records_incomplete = False
         with torch.cuda.device(dev):
             verts = torch.empty((n_verts, 3), dtype=torch.float32, device=dev)
             verts_voxel = torch.empty((n_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
@@ -130,6 +163,7 @@ class McPlan:
                 _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
                 _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
                 ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.work_ptr, self.rec_verts, self.rec_cubes,
                 self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
                 origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
                 _ptr(colors), _ptr(faces), _ptr(face_keys), _ptr(face_cubes), _ptr(vert_keys), _ptr(self.totals), stream))
@@ -144,6 +178,7 @@ class McPlan:
         dev = self.device
         origin = np.ascontiguousarray(origin, dtype=np.float32)
         host = _pinned_totals(torch, dev)
+        self._ensure_work(cap_verts, cap_tris)
         with torch.cuda.device(dev):
             verts = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
             verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
@@ -155,11 +190,13 @@ class McPlan:
                 _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
                 _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
                 ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
-                self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
+                self.work_ptr, self.rec_verts, self.rec_cubes, self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
                 origin.ctypes.data_as(ctypes.c_void_p), cap_verts, cap_tris, _ptr(verts), _ptr(verts_voxel),
                 _ptr(normals), _ptr(colors), _ptr(faces), None, None, None, _ptr(self.totals),
                 ctypes.c_void_p(host.data_ptr()), stream)
-        n_verts, n_tris, kmin, kmax = (int(v) for v in host.tolist()[:4])
+        vals = [int(v) for v in host.tolist()]
+        n_verts, n_tris, kmin, kmax = vals[:4]
+        self._records_incomplete = bool(vals[6])
         vmin, vmax = _key_to_float(kmin), _key_to_float(kmax)
         if rc == _lib.HV_E_CAPACITY:
             mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
@@ -177,7 +214,7 @@ class McPlan:
         into exactly sized buffers."""
         torch = self._torch
         dev = self.device
-        self.count()
+        self.count(cap_verts, cap_tris)
         with torch.cuda.device(dev):
             verts = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev)
             verts_voxel = torch.empty((cap_verts, 3), dtype=torch.float32, device=dev) if want_voxel else None
@@ -193,6 +230,7 @@ class McPlan:
                     _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
                     _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
                     ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                    self.work_ptr, self.rec_verts, self.rec_cubes,
                     self.z_global_offset, self.z_global_dim, ctypes.c_float(np.float32(voxel_size)),
                     origin.ctypes.data_as(ctypes.c_void_p), cap_verts, cap_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
                     _ptr(colors), _ptr(faces), None, None, None, _ptr(self.totals), stream))
@@ -201,7 +239,7 @@ class McPlan:
             launch()
         n_verts, n_tris, vmin, vmax = self.read_totals()
         check_surface(self.level, vmin, vmax, n_verts)
-        if n_verts > cap_verts or n_tris > cap_tris:
+        if n_verts > cap_verts or n_tris > cap_tris or self._records_incomplete:
             mesh = self.emit(n_verts, n_tris, voxel_size, origin, want_voxel=want_voxel)
         else:
             if not speculative:

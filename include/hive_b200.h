@@ -94,14 +94,19 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * get_point_cloud (fusion.py:317,338 -- scikit-image's Lewiner implementation, a third-party dependency) and the
  * in-tree post-processing fusion.py:339-348 (nearest-voxel colour gather, b/g/r unpack, voxel -> world transform).
  *
- * Two calls with a host read of two counters in between (the output size is data dependent):
- *   hv_mc_count  classifies the volume into `scratch` and writes totals (DEVICE, 8 x uint64): [0] = #vertices,
- *                [1] = #triangles, [2] / [3] = min / max of the volume as order-preserving int32 keys of the floats
- *                (key = bits >= 0 ? bits : bits ^ 0x7fffffff) for skimage's "level within data range" check
- *                (ValueError, relied on by scripts/experiments.py:167), [4] = #vertices that lie on lattice edges.
+ * Two calls with a host read of the counters in between (the output size is data dependent):
+ *   hv_mc_count  classifies the volume into `scratch`, writes one work record per surface cube and per edge vertex
+ *                into `work`, and writes totals (DEVICE, 8 x uint64): [0] = #vertices, [1] = #triangles, [2] / [3] =
+ *                min / max of the volume as order-preserving int32 keys of the floats (key = bits >= 0 ? bits :
+ *                bits ^ 0x7fffffff) for skimage's "level within data range" check (ValueError, relied on by
+ *                scripts/experiments.py:167), [4] = #vertices that lie on lattice edges, [5] = #surface cubes,
+ *                [6] = 1 if the records did not fit (rec_verts < [4] or rec_cubes < [5]: call hv_mc_count again with a
+ *                larger work buffer before hv_mc_emit; [5] <= [1] and [4] <= [0], so rec_cubes = triangle capacity and
+ *                rec_verts = vertex capacity is always enough).
  *   hv_mc_emit   writes the mesh: at most n_verts vertices / n_tris triangles (the capacity of the output buffers;
  *                `totals` as left by hv_mc_count says how many there are -- a caller that reuses a capacity from an
- *                earlier extraction can launch both calls back to back and read the totals afterwards).  Vertices on
+ *                earlier extraction can launch both calls back to back and read the totals afterwards; nothing is
+ *                written when [6] is set).  Vertices on
  *                lattice edges come first, sorted by (owner voxel in C scan order, edge axis), then the vertices
  *                inside cubes (Lewiner's c-vertex) by cube; triangles by cube scan order; right-hand normals of the
  *                faces point towards increasing values (what skimage returns for gradient_direction='descent').
@@ -110,6 +115,8 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * halo_lo / halo_hi (and the colour pair): optional [X][Y] planes just below z = 0 / above z = Z-1 of a z-slab
  *                shard (NULL for a whole volume).  A shard owns the cubes whose base voxel lies in its slab.
  * scratch      : device buffer of hv_mc_scratch_bytes() bytes, 256-byte aligned; must be kept between the two calls.
+ * work         : device buffer of hv_mc_work_bytes(rec_verts, rec_cubes) bytes, 256-byte aligned; kept likewise, and
+ *                passed with the same rec_verts / rec_cubes to both calls.
  * z_global_offset / z_global_dim : position of the slab in the global volume (0 / Z for a whole volume); vertex keys
  *                are ((x*Y + y)*z_global_dim + z_global)*4 + axis, axis 3 = the extra vertex inside a cube.
  * faces / face_keys : exactly one is non-NULL: int32 [T][3] indices into this call's vertices (whole volume only), or
@@ -120,23 +127,27 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * vert_keys    : optional uint64 [V] key of every vertex (shards: what face_keys refer to); NULL to skip.
  * ---------------------------------------------------------------------------------------------------------- */
 int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, int64_t* h_bytes);
+int hv_mc_work_bytes(int64_t rec_verts, int64_t rec_cubes, int64_t* h_bytes);
 int hv_mc_count(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims, int64_t pitch,
-                double level, void* scratch, int64_t scratch_bytes, unsigned long long* totals, void* stream);
+                double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,
+                unsigned long long* totals, void* stream);
 int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
                const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
-               double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
+               double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,
+               int64_t z_global_offset, int64_t z_global_dim,
                float voxel_size, const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world,
                float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
                unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals, void* stream);
 
 /* hv_mc_count + hv_mc_emit in one call with caller-provided capacity (cap_verts vertices, cap_tris triangles in every
- * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 4 x uint64, pinned memory
+ * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 8 x uint64, pinned memory
  * recommended; same meaning as `totals`).  Returns HV_E_LEVEL_RANGE / HV_E_NOSURFACE like skimage would raise
- * (fusion.py:338), or HV_E_CAPACITY when the surface exceeds the capacity: h_totals is filled and the scratch is still
- * valid, so the caller can allocate exactly and finish with hv_mc_emit. */
+ * (fusion.py:338), or HV_E_CAPACITY when the surface (or its work records) exceeds the capacity: h_totals is filled, so
+ * the caller can allocate exactly and finish with hv_mc_count (if [6] is set) + hv_mc_emit. */
 int hv_mc_extract(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
                   const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
-                  double level, void* scratch, int64_t scratch_bytes, int64_t z_global_offset, int64_t z_global_dim,
+                  double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,
+                  int64_t z_global_offset, int64_t z_global_dim,
                   float voxel_size, const float* h_origin, int64_t cap_verts, int64_t cap_tris, float* verts_world,
                   float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
                   unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals,
