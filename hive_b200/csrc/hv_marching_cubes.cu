@@ -52,13 +52,17 @@ struct McGrid {
     double level;
     // scratch
     unsigned int* bits;          // [n_groups] sign words
-    uint4* gtab;                 // [n_groups], written only where the group owns a vertex: {batch-local first vertex, mx, my, mz}
-    uint4* batch_base;           // [n_batches] {edge vertices, triangles, centre vertices} of the tile before this batch of 32 groups
+    uint4* gtab;                 // [n_groups], written only where the group owns a vertex: {batch-local first vertex | batch of the tile << 12, mx, my, mz}
+    unsigned int* glist;         // [n_tiles][1024] ids of the groups near the surface, per tile, ascending
+    unsigned int* tile_cnt;      // [n_tiles] entries of glist used
+    unsigned int* work;          // [n_batches] work items of the count kernel: tile * 32 + batch of the tile, any order
+    uint4* batch_tot;            // [n_batches] {edge vertices, triangles, centre vertices, cubes} of a batch
+    uint4* batch_base;           // [n_batches] {edge vertices, triangles, centre vertices} of the tile before this batch of 32 listed groups
     uint4* tile_tot;             // [n_tiles] {edge vertices, triangles, centre vertices, cubes} of every tile of 32 batches
     uint4* tile_base;            // [n_tiles] exclusive prefix of tile_tot (x, y, z)
-    unsigned int* ctrl;          // [0] tiles done, [1] / [2] cursors of the record arrays
+    unsigned int* ctrl;          // [0] scan blocks done, [3] work items, [4..5] cursors of the record arrays (vertices | cubes << 32)
     // work records (caller-sized: hv_mc_work_bytes)
-    uint4* cube_rec;             // {group, voxel | tiling << 5, batch-local first triangle, batch-local centre vertex}
+    uint4* cube_rec;             // {group, voxel | tiling << 5 | batch of the tile << 16, batch-local first triangle, batch-local centre vertex}
     unsigned long long* vert_rec;  // pack_vertex_record()
     long long cap_cubes, cap_vrec;
     unsigned long long* totals;  // [0] vertices [1] triangles [2] min key [3] max key (ordered-int float) [4] edge vertices
@@ -367,21 +371,118 @@ __device__ __forceinline__ int select_bit(unsigned int mask, int r) {
     return pos;
 }
 
-// ---- 2. count: per-group masks, work records, scan -------------------------------------------------------------------------
-// The unit of work is a batch of 32 consecutive groups (the global group order is the vertex / triangle order), one per
-// lane: sign words of the four columns around the group, owner masks, surface-cube mask.  Nearly all batches are empty
-// and end there.  The cubes of a batch are then spread over the lanes with a warp scan -- 32 cubes at a time whatever the
+// ---- 2a. detect: which groups does the surface come near? ---------------------------------------------------------------------
+// A tile = 1024 consecutive groups (the global group order is the vertex / triangle order).  One thread looks at four
+// consecutive groups (one 16-byte load per neighbouring column when the column length allows it) and the block compacts the
+// ids of the groups with a sign change in reach -- in order -- into the tile's slice of `glist`.  With a floor in the scene
+// every column has one such group and 30 that have none: the kernels after this one only ever see the former, 32 to a warp.
+constexpr int kTileGroups = 1024;
+constexpr int kTileBatches = kTileGroups / 32;
+constexpr int kDetectThreads = kTileGroups / 4;
+
+__device__ __forceinline__ bool group_near_surface(const unsigned int (&b)[4], const unsigned int (&n)[4]) {
+    unsigned int all8 = 0xffffffffu, any8 = 0u;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const unsigned int u = (b[i] >> 1) | (n[i] << 31);
+        all8 &= b[i] & u;
+        any8 |= b[i] | u;
+    }
+    return (any8 & ~all8) != 0u;  // (columns / words beyond the volume read as zero: conservative)
+}
+
+__global__ void __launch_bounds__(kDetectThreads) mc_detect_kernel(const __grid_constant__ McGrid g) {
+    __shared__ unsigned int s_warp[kDetectThreads / 32];
+    const unsigned int tile = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long gid0 = (long long)tile * kTileGroups + 4 * (long long)threadIdx.x;
+    unsigned int flags = 0u;
+    if (gid0 < g.n_groups) {
+        const int G = g.G;
+        if ((G & 3) == 0) {  // the four groups share a column and a 16-byte word
+            const unsigned int col = (unsigned int)gid0 / (unsigned int)G;
+            const int gq = (int)((unsigned int)gid0 - col * (unsigned int)G);
+            const unsigned int x = col / (unsigned int)g.Y, y = col - x * (unsigned int)g.Y;
+            const bool x1 = (int)x + 1 < g.X, y1 = (int)y + 1 < g.Y;
+            const unsigned int* p[4];
+            p[0] = g.bits + gid0;
+            p[1] = y1 ? p[0] + G : nullptr;
+            p[2] = x1 ? p[0] + (size_t)g.Y * G : nullptr;
+            p[3] = (x1 && y1) ? p[2] + G : nullptr;
+            unsigned int w[4][5];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                uint4 q = make_uint4(0u, 0u, 0u, 0u);
+                unsigned int nx = 0u;
+                if (p[i]) {
+                    q = __ldg(reinterpret_cast<const uint4*>(p[i]));
+                    if (gq + 4 < G) nx = __ldg(p[i] + 4);
+                }
+                w[i][0] = q.x; w[i][1] = q.y; w[i][2] = q.z; w[i][3] = q.w; w[i][4] = nx;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned int b[4] = {w[0][k], w[1][k], w[2][k], w[3][k]};
+                const unsigned int n[4] = {w[0][k + 1], w[1][k + 1], w[2][k + 1], w[3][k + 1]};
+                if (group_near_surface(b, n)) flags |= 1u << k;
+            }
+        } else {
+            for (int k = 0; k < 4 && gid0 + k < g.n_groups; ++k) {
+                int x, y, gq;
+                decode_group(g, (unsigned int)(gid0 + k), x, y, gq);
+                const CubeWords c = load_cube_words(g, x, y, gq);
+                unsigned int all8 = 0xffffffffu, any8 = 0u;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    all8 &= c.w[i];
+                    any8 |= c.w[i];
+                }
+                if (any8 & ~all8) flags |= 1u << k;
+            }
+        }
+    }
+    const unsigned int cnt = __popc(flags);
+    unsigned int total;
+    const unsigned int ex = warp_excl_scan(cnt, total);
+    if (lane == 31) s_warp[warp] = ex + cnt;
+    __syncthreads();
+    unsigned int carry = 0, sum = 0;
+#pragma unroll
+    for (int w = 0; w < kDetectThreads / 32; ++w) {
+        const unsigned int v = s_warp[w];
+        if (w < warp) carry += v;
+        sum += v;
+    }
+    unsigned int* dst = g.glist + (size_t)tile * kTileGroups + carry + ex;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if ((flags >> k) & 1u) *dst++ = (unsigned int)(gid0 + k);
+    if (threadIdx.x == 0) g.tile_cnt[tile] = sum;
+    // one work item per batch of 32 listed groups (their order in `work` does not matter)
+    if (warp == 0 && sum) {
+        const unsigned int nb = (sum + 31u) / 32u;
+        unsigned int base = 0;
+        if (lane == 0) base = atomicAdd(g.ctrl + 3, nb);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if ((unsigned int)lane < nb) g.work[base + lane] = tile * kTileBatches + (unsigned int)lane;
+    }
+}
+
+// ---- 2b. count: per-group masks, work records, scan ------------------------------------------------------------------------
+// The unit of work is a batch of 32 consecutive entries of a tile's group list, one per lane: sign words of the four
+// columns around the group, owner masks, surface-cube mask.  (Batches of 32 consecutive groups -- two columns -- cost
+// 167 us at 512^3: with a floor in the scene every one of the 131 k batches had one or two lanes with work.)  The cubes
+// of a batch are then spread over the lanes with a warp scan -- 32 cubes at a time whatever the
 // shape of the surface (one thread per group walked up to 32 cubes serially, one thread per column up to Z: 315 us and
 // 370 us at 512^3 with a wall parallel to z in the scene) -- so every tiling decision (face and interior tests included)
 // is made ONCE, lane-parallel, and lands in the cube's work record together with the cube's batch-local triangle offset.
-// A tile = 32 batches (16 warps x 2); the batch totals are scanned in the tile, the last tile to finish scans the tile
+// A tile has at most 32 batches (16 warps x 2); the batch totals are scanned in the tile, the last tile to finish scans the tile
 // totals: a consumer adds two hot small-table entries per look-up.  (A decoupled look-back over tiles of 256 groups was
 // measured at 520 us: with ~600 tiles in flight every tile walks back ~20 windows.)  Records go to a bump-allocated range
 // per batch: their order in the record arrays is arbitrary, the indices they carry are not.
-constexpr int kCountThreads = 512;
-constexpr int kBatchesPerWarp = 2;
-constexpr int kTileBatches = (kCountThreads / 32) * kBatchesPerWarp;
-static_assert(kTileBatches == 32, "the batch totals of a tile are scanned by one warp");
+constexpr int kCountThreads = 128;
+constexpr int kCubeChunk = 256;
+static_assert(HV_MC_NUM_VARIANTS <= 1024, "cube words keep the tiling in 10 bits");
 
 __global__ void mc_init_kernel(unsigned long long* totals, unsigned int* ctrl) {
     if (threadIdx.x == 0) {
@@ -396,30 +497,36 @@ __global__ void mc_init_kernel(unsigned long long* totals, unsigned int* ctrl) {
     if (threadIdx.x < 8) ctrl[threadIdx.x] = 0u;
 }
 
-// vertex record: group (31 bits) | voxel << 31 (5) | axis << 36 (2) | batch-local vertex index << 38 (<= 32 * 96)
-__device__ __forceinline__ unsigned long long pack_vertex_record(unsigned int gid, int k, int axis, unsigned int local) {
-    return (unsigned long long)gid | ((unsigned long long)k << 31) | ((unsigned long long)axis << 36) | ((unsigned long long)local << 38);
+// vertex record: group (31 bits) | voxel << 31 (5) | axis << 36 (2) | batch-local vertex index << 38 (12: <= 32 * 96) |
+// batch of the tile << 50 (5)
+__device__ __forceinline__ unsigned long long pack_vertex_record(unsigned int gid, int k, int axis, unsigned int local, int slot) {
+    return (unsigned long long)gid | ((unsigned long long)k << 31) | ((unsigned long long)axis << 36) |
+           ((unsigned long long)local << 38) | ((unsigned long long)slot << 50);
 }
 
 __global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_constant__ McGrid g) {
-    __shared__ uint4 s_batch[kTileBatches];
-    __shared__ unsigned long long s_wa[kCountThreads / 32], s_wb[kCountThreads / 32];
-    __shared__ unsigned int s_last;
-    const unsigned int tile = blockIdx.x;
+    __shared__ unsigned int s_cube[kCountThreads / 32][kCubeChunk];
+    __shared__ unsigned short s_queue[kCountThreads / 32][kCubeChunk];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned int lt = (1u << lane) - 1u;
+    const unsigned int n_work = g.ctrl[3];
+    const unsigned int n_warps = gridDim.x * (kCountThreads / 32);
 #pragma unroll 1
-    for (int b = 0; b < kBatchesPerWarp; ++b) {
-        const int slot = warp * kBatchesPerWarp + b;
-        const long long gid64 = ((long long)tile * kTileBatches + slot) * 32 + lane;
-        const unsigned int gid = (unsigned int)gid64;
+    for (unsigned int wi = blockIdx.x * (kCountThreads / 32) + warp; wi < n_work; wi += n_warps) {
+        const unsigned int item = __ldg(g.work + wi);
+        const unsigned int tile = item / kTileBatches;
+        const int slot = (int)(item % kTileBatches);
+        const unsigned int n_listed = __ldg(g.tile_cnt + tile);
+        const unsigned int li = (unsigned int)slot * 32u + (unsigned int)lane;
         uint4 tot = make_uint4(0u, 0u, 0u, 0u);
+        unsigned int gid = 0u;
         int x = 0, y = 0, gq = 0;
         CubeWords c;
 #pragma unroll
         for (int i = 0; i < 8; ++i) c.w[i] = 0u;
         c.active = c.mx = c.my = c.mz = 0u;
-        if (gid64 < g.n_groups) {
+        if (li < n_listed) {
+            gid = __ldg(g.glist + (size_t)tile * kTileGroups + li);
             decode_group(g, gid, x, y, gq);
             c = load_cube_words(g, x, y, gq);
         }
@@ -428,77 +535,126 @@ __global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_co
             const unsigned int nv = __popc(c.mx) + __popc(c.my) + __popc(c.mz);
             unsigned int NV;
             const unsigned int vpre = warp_excl_scan(nv, NV);
-            if (nv) g.gtab[gid] = make_uint4(vpre, c.mx, c.my, c.mz);
+            if (nv) g.gtab[gid] = make_uint4(vpre | ((unsigned int)slot << 12), c.mx, c.my, c.mz);
+            unsigned int C;
+            const unsigned int coff = warp_excl_scan(__popc(c.active), C);
+            // space in both record arrays with one atomic: (vertex cursor | cube cursor << 32)
+            unsigned long long cursors = 0ull;
+            if (lane == 0)
+                cursors = atomicAdd(reinterpret_cast<unsigned long long*>(g.ctrl + 4), (unsigned long long)NV | ((unsigned long long)C << 32));
+            cursors = __shfl_sync(0xffffffffu, cursors, 0);
+            const unsigned int vbase = (unsigned int)cursors, cbase = (unsigned int)(cursors >> 32);
             if (NV) {
-                unsigned int vbase = 0;
-                if (lane == 0) vbase = atomicAdd(g.ctrl + 2, NV);
-                vbase = __shfl_sync(0xffffffffu, vbase, 0);
                 if ((long long)vbase + NV <= g.cap_vrec) {
                     unsigned long long* dst = g.vert_rec + vbase;
                     unsigned int o = vpre;
                     for (unsigned int rest = c.mx | c.my | c.mz; rest; rest &= rest - 1) {
                         const int k = __ffs(rest) - 1;
-                        if ((c.mx >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 0, o); ++o; }
-                        if ((c.my >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 1, o); ++o; }
-                        if ((c.mz >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 2, o); ++o; }
+                        if ((c.mx >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 0, o, slot); ++o; }
+                        if ((c.my >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 1, o, slot); ++o; }
+                        if ((c.mz >> k) & 1u) { dst[o] = pack_vertex_record(gid, k, 2, o, slot); ++o; }
                     }
                 }
             }
             // ---- surface cubes, one lane per cube
-            unsigned int C;
-            const unsigned int coff = warp_excl_scan(__popc(c.active), C);
-            unsigned int cbase = 0;
-            if (C && lane == 0) cbase = atomicAdd(g.ctrl + 1, C);
-            cbase = __shfl_sync(0xffffffffu, cbase, 0);
             const bool write_ok = (long long)cbase + C <= g.cap_cubes;
             unsigned int tri_run = 0, cen_run = 0;
-            for (unsigned int c0 = 0; c0 < C; c0 += 32u) {
-                const unsigned int q = c0 + (unsigned int)lane;
-                const bool cv = q < C;
-                const int s = warp_owner(coff, cv ? q : C - 1u);
-                const unsigned int r = q - __shfl_sync(0xffffffffu, coff, s);
-                const unsigned int am = __shfl_sync(0xffffffffu, c.active, s);
-                unsigned int w[8];
+            // 256 cubes at a time, three sweeps: (A) configuration index of every cube, tiling where the tables alone
+            // decide, the others queued; (B) the queued cubes, one per lane -- the only step that waits on TSDF values, and
+            // it waits once per 32 ambiguous cubes instead of once per 32 cubes (r02: a dense batch in a noisy region had an
+            // ambiguous cube in every one of its 32 rounds: 64 us, with the other 15 warps of the tile at the barrier);
+            // (C) scans + records.
+            unsigned int* s_var = s_cube[warp];
+            unsigned short* s_q = s_queue[warp];
+            for (unsigned int ch0 = 0; ch0 < C; ch0 += kCubeChunk) {
+                const unsigned int ch1 = min(C, ch0 + kCubeChunk);
+                unsigned int n_queued = 0;
+                for (unsigned int c0 = ch0; c0 < ch1; c0 += 32u) {  // (A)
+                    const unsigned int q = c0 + (unsigned int)lane;
+                    const bool cv = q < ch1;
+                    const int s = warp_owner(coff, cv ? q : ch1 - 1u);
+                    const unsigned int r = q - __shfl_sync(0xffffffffu, coff, s);
+                    const unsigned int am = __shfl_sync(0xffffffffu, c.active, s);
+                    unsigned int w[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) w[i] = __shfl_sync(0xffffffffu, c.w[i], s);
-                const int cx = __shfl_sync(0xffffffffu, x, s), cy = __shfl_sync(0xffffffffu, y, s);
-                const int cgq = __shfl_sync(0xffffffffu, gq, s);
-                int variant = 0, k = 0;
-                unsigned int ntri = 0;
-                bool hasc = false;
-                if (cv) {
-                    k = select_bit(am, (int)r);
-                    int idx = 0;
+                    for (int i = 0; i < 8; ++i) w[i] = __shfl_sync(0xffffffffu, c.w[i], s);
+                    bool amb = false;
+                    if (cv) {
+                        const int k = select_bit(am, (int)r);
+                        int idx = 0;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) idx |= (int)((w[i] >> k) & 1u) << i;
-                    variant = cube_variant_at_ool(g, idx, cx, cy, cgq * 32 + k);
-                    ntri = kMcVarNtri[variant];
-                    hasc = ((kMcVarMult[variant] >> 48) & 15ull) != 0ull;
+                        for (int i = 0; i < 8; ++i) idx |= (int)((w[i] >> k) & 1u) << i;
+                        amb = kMcAmbCount[idx] != 0 || kMcInteriorBase[idx] != 255;
+                        // tiling (10 bits; the configuration index for now if it is still open) | voxel << 10 | lane of the group << 15
+                        s_var[q - ch0] = (amb ? (unsigned int)idx : (unsigned int)kMcVariantBase[idx]) | ((unsigned int)k << 10) | ((unsigned int)s << 15);
+                    }
+                    const unsigned int ab = __ballot_sync(0xffffffffu, amb);
+                    if (amb) s_q[n_queued + __popc(ab & lt)] = (unsigned short)(q - ch0);
+                    n_queued += __popc(ab);
                 }
-                unsigned int T;
-                const unsigned int toff = warp_excl_scan(ntri, T);
-                const unsigned int cb = __ballot_sync(0xffffffffu, hasc);
-                if (cv && write_ok)
-                    g.cube_rec[cbase + q] = make_uint4(gid - (unsigned int)lane + (unsigned int)s, (unsigned int)k | ((unsigned int)variant << 5),
-                                                       tri_run + toff, cen_run + __popc(cb & lt));
-                tri_run += T;
-                cen_run += __popc(cb);
+                __syncwarp();
+                for (unsigned int i0 = 0; i0 < n_queued; i0 += 32u) {  // (B)
+                    const bool qv = i0 + (unsigned int)lane < n_queued;
+                    const unsigned int e = qv ? s_q[i0 + lane] : 0u;
+                    const unsigned int word = s_var[e];
+                    const int s = (int)(word >> 15), k = (int)((word >> 10) & 31u);
+                    const int cx = __shfl_sync(0xffffffffu, x, s), cy = __shfl_sync(0xffffffffu, y, s);
+                    const int cgq = __shfl_sync(0xffffffffu, gq, s);
+                    if (qv) {
+                        const int variant = cube_variant_ambiguous(g.tsdf, g.halo_lo, g.halo_hi, g.Y, g.pitch, g.Z, g.hl, g.level,
+                                                                   (int)(word & 1023u), cx, cy, cgq * 32 + k);
+                        s_var[e] = (word & ~1023u) | (unsigned int)variant;
+                    }
+                }
+                __syncwarp();
+                for (unsigned int c0 = ch0; c0 < ch1; c0 += 32u) {  // (C)
+                    const unsigned int q = c0 + (unsigned int)lane;
+                    const bool cv = q < ch1;
+                    const unsigned int word = cv ? s_var[q - ch0] : 0u;
+                    const int variant = (int)(word & 1023u);
+                    const unsigned int cgid = __shfl_sync(0xffffffffu, gid, (int)(word >> 15));
+                    const unsigned int ntri = cv ? kMcVarNtri[variant] : 0u;
+                    const bool hasc = cv && ((kMcVarMult[variant] >> 48) & 15ull) != 0ull;
+                    unsigned int T;
+                    const unsigned int toff = warp_excl_scan(ntri, T);
+                    const unsigned int cb = __ballot_sync(0xffffffffu, hasc);
+                    if (cv && write_ok)
+                        g.cube_rec[cbase + q] = make_uint4(cgid, ((word >> 10) & 31u) | ((unsigned int)variant << 5) | ((unsigned int)slot << 16),
+                                                           tri_run + toff, cen_run + __popc(cb & lt));
+                    tri_run += T;
+                    cen_run += __popc(cb);
+                }
+                __syncwarp();
             }
             tot = make_uint4(NV, tri_run, cen_run, C);
         }
-        if (lane == 0) s_batch[slot] = tot;
+        if (lane == 0) g.batch_tot[item] = tot;
     }
-    __syncthreads();
-    if (warp == 0) {  // scan of the tile's batch totals
-        const uint4 v = s_batch[lane];
+}
+
+// ---- 2c. scan: batch totals within their tile, tile totals over the volume ----------------------------------------------------
+// One warp per tile (its <= 32 batch totals); the last block to finish scans the tile totals: a consumer adds two hot
+// small-table entries per look-up.  (A decoupled look-back over tiles of 256 groups inside the count kernel was measured at
+// 520 us -- with ~600 tiles in flight every tile walks back ~20 windows -- and a tile-wide barrier in the count kernel at
+// 135 us: most warps of a tile have no batch, all of them wait for the one that has a dense one.)
+constexpr int kScanThreads2 = 256;
+
+__global__ void __launch_bounds__(kScanThreads2) mc_scan_kernel(const __grid_constant__ McGrid g) {
+    __shared__ unsigned long long s_wa[kScanThreads2 / 32], s_wb[kScanThreads2 / 32];
+    __shared__ unsigned int s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long tile = (long long)blockIdx.x * (kScanThreads2 / 32) + warp;
+    if (tile < g.n_tiles) {
+        const unsigned int nb = (__ldg(g.tile_cnt + tile) + 31u) / 32u;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if ((unsigned int)lane < nb) v = __ldg(g.batch_tot + tile * kTileBatches + lane);
         unsigned int sx, sy, sz, sw;
         const unsigned int ex = warp_excl_scan(v.x, sx), ey = warp_excl_scan(v.y, sy), ez = warp_excl_scan(v.z, sz);
         warp_excl_scan(v.w, sw);
-        const long long batch = (long long)tile * kTileBatches + lane;
-        if (batch < g.n_batches) g.batch_base[batch] = make_uint4(ex, ey, ez, 0u);
+        if ((unsigned int)lane < nb) g.batch_base[tile * kTileBatches + lane] = make_uint4(ex, ey, ez, 0u);
         if (lane == 0) g.tile_tot[tile] = make_uint4(sx, sy, sz, sw);
     }
-    // the last tile to get here turns the tile totals into bases
+    // the last block to get here turns the tile totals into bases
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) s_last = (atomicAdd(g.ctrl, 1u) == gridDim.x - 1u) ? 1u : 0u;
@@ -509,10 +665,10 @@ __global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_co
     unsigned long long carry_a = 0, carry_b = 0;  // (edge vertices | triangles << 32), (centre vertices | cubes << 32): all < 2^31
     uint4 v = make_uint4(0u, 0u, 0u, 0u);
     if ((int)threadIdx.x < n_tiles) v = __ldcg(g.tile_tot + threadIdx.x);
-    for (int i0 = 0; i0 < n_tiles; i0 += kCountThreads) {
+    for (int i0 = 0; i0 < n_tiles; i0 += kScanThreads2) {
         const int i = i0 + (int)threadIdx.x;
         uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-        if (i + kCountThreads < n_tiles) nxt = __ldcg(g.tile_tot + i + kCountThreads);  // next round's entry, requested early
+        if (i + kScanThreads2 < n_tiles) nxt = __ldcg(g.tile_tot + i + kScanThreads2);  // next round's entry, requested early
         const unsigned long long a = (unsigned long long)v.x | ((unsigned long long)v.y << 32);
         const unsigned long long bb = (unsigned long long)v.z | ((unsigned long long)v.w << 32);
         unsigned long long ia = a, ib = bb;
@@ -531,7 +687,7 @@ __global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_co
         __syncthreads();
         unsigned long long ca = 0, cb = 0, ta = 0, tb = 0;
 #pragma unroll
-        for (int w = 0; w < kCountThreads / 32; ++w) {
+        for (int w = 0; w < kScanThreads2 / 32; ++w) {
             const unsigned long long xa = s_wa[w], xb = s_wb[w];
             if (w < warp) {
                 ca += xa;
@@ -583,9 +739,10 @@ __device__ __forceinline__ unsigned int edge_vertex_index(const McGrid& g, int x
     const size_t og = ((size_t)xo * g.Y + yo) * g.G + (zo >> 5);
     const int bit = zo & 31;
     const uint4 m = __ldg(g.gtab + og);
-    const unsigned int base = __ldg(&g.tile_base[og / (32 * kTileBatches)].x) + __ldg(&g.batch_base[og / 32].x);
+    const size_t ot = og / kTileGroups;
+    const unsigned int base = __ldg(&g.tile_base[ot].x) + __ldg(&g.batch_base[ot * kTileBatches + (m.x >> 12)].x);
     const unsigned int low = (1u << bit) - 1u;
-    unsigned int r = base + m.x + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
+    unsigned int r = base + (m.x & 4095u) + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
     if (axis > 0) r += (m.y >> bit) & 1u;
     if (axis > 1) r += (m.z >> bit) & 1u;
     return r;
@@ -864,9 +1021,10 @@ __global__ void __launch_bounds__(kEmitThreads, 4) mc_tri_kernel(const __grid_co
         const uint4 rec = __ldg(g.cube_rec + i);
         int x, y, gq;
         decode_group(g, rec.x, x, y, gq);
-        const uint4 tb = __ldg(g.tile_base + rec.x / (32 * kTileBatches)), bb = __ldg(g.batch_base + rec.x / 32);
+        const size_t tile = rec.x / kTileGroups;
+        const uint4 tb = __ldg(g.tile_base + tile), bb = __ldg(g.batch_base + tile * kTileBatches + (rec.y >> 16));
         const uint4 base = make_uint4(tb.x + bb.x, tb.y + bb.y, tb.z + bb.z, 0u);
-        const int k = (int)(rec.y & 31u), variant = (int)(rec.y >> 5), zb = gq * 32 + k;
+        const int k = (int)(rec.y & 31u), variant = (int)((rec.y >> 5) & 2047u), zb = gq * 32 + k;
         const int ntri = kMcVarNtri[variant];
         const unsigned long long mult = kMcVarMult[variant];
         const unsigned int centre_index = n_edge + base.z + rec.w;
@@ -902,7 +1060,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) mc_tri_kernel(const __grid_co
 }
 
 // ---- 4. edge vertices: one thread per vertex record ----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kEmitThreads, 2) mc_vert_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out) {
+__global__ void __launch_bounds__(kEmitThreads, 3) mc_vert_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out) {
     if (g.totals[6]) return;
     const unsigned int n_edge = (unsigned int)g.totals[4];
     for (unsigned int i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_edge; i += gridDim.x * kEmitThreads) {
@@ -911,7 +1069,9 @@ __global__ void __launch_bounds__(kEmitThreads, 2) mc_vert_kernel(const __grid_c
         const int k = (int)((rec >> 31) & 31ull), axis = (int)((rec >> 36) & 3ull);
         int x, y, gq;
         decode_group(g, gid, x, y, gq);
-        const size_t vi = (size_t)__ldg(&g.tile_base[gid / (32 * kTileBatches)].x) + __ldg(&g.batch_base[gid / 32].x) + (unsigned int)(rec >> 38);
+        const size_t tile = gid / kTileGroups;
+        const size_t vi = (size_t)__ldg(&g.tile_base[tile].x) + __ldg(&g.batch_base[tile * kTileBatches + (unsigned int)((rec >> 50) & 31ull)].x) +
+                          (unsigned int)((rec >> 38) & 4095ull);
         if ((long long)vi < out.cap_verts) emit_edge_vertex(g, out, x, y, gq * 32 + k, axis, vi);
     }
 }
@@ -924,7 +1084,7 @@ namespace {
 struct McLayout {
     long long n_groups, n_batches, n_tiles;
     int G, Zb;
-    size_t off_bits, off_gtab, off_batch_base, off_tile_tot, off_tile_base, off_ctrl, total;
+    size_t off_bits, off_gtab, off_glist, off_tile_cnt, off_work, off_batch_tot, off_batch_base, off_tile_tot, off_tile_base, off_ctrl, total;
 };
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -938,12 +1098,14 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     L->G = (L->Zb + 31) / 32;
     L->n_groups = (long long)X * Y * L->G;
     HV_REQUIRE(L->n_groups < (1ll << 31) && L->Zb < (1 << 22), "marching cubes: volume too large");
-    L->n_batches = (L->n_groups + 31) / 32;
-    L->n_tiles = (L->n_batches + hv::kTileBatches - 1) / hv::kTileBatches;
+    L->n_tiles = (L->n_groups + hv::kTileGroups - 1) / hv::kTileGroups;
+    L->n_batches = L->n_tiles * hv::kTileBatches;
     size_t o = 0;
     L->off_gtab = o;  // 16-byte elements first
     o = align_up(o + (size_t)L->n_groups * sizeof(uint4));
     L->off_batch_base = o;
+    o = align_up(o + (size_t)L->n_batches * sizeof(uint4));
+    L->off_batch_tot = o;
     o = align_up(o + (size_t)L->n_batches * sizeof(uint4));
     L->off_tile_tot = o;
     o = align_up(o + (size_t)L->n_tiles * sizeof(uint4));
@@ -951,6 +1113,12 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     o = align_up(o + (size_t)L->n_tiles * sizeof(uint4));
     L->off_bits = o;
     o = align_up(o + (size_t)L->n_groups * sizeof(unsigned int));
+    L->off_glist = o;
+    o = align_up(o + (size_t)L->n_tiles * hv::kTileGroups * sizeof(unsigned int));
+    L->off_tile_cnt = o;
+    o = align_up(o + (size_t)L->n_tiles * sizeof(unsigned int));
+    L->off_work = o;
+    o = align_up(o + (size_t)L->n_batches * sizeof(unsigned int));
     L->off_ctrl = o;
     o = align_up(o + 8 * sizeof(unsigned int));
     L->total = o;
@@ -995,6 +1163,10 @@ int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float*
     g->level = level;
     g->bits = reinterpret_cast<unsigned int*>(s + L->off_bits);
     g->gtab = reinterpret_cast<uint4*>(s + L->off_gtab);
+    g->glist = reinterpret_cast<unsigned int*>(s + L->off_glist);
+    g->tile_cnt = reinterpret_cast<unsigned int*>(s + L->off_tile_cnt);
+    g->work = reinterpret_cast<unsigned int*>(s + L->off_work);
+    g->batch_tot = reinterpret_cast<uint4*>(s + L->off_batch_tot);
     g->batch_base = reinterpret_cast<uint4*>(s + L->off_batch_base);
     g->tile_tot = reinterpret_cast<uint4*>(s + L->off_tile_tot);
     g->tile_base = reinterpret_cast<uint4*>(s + L->off_tile_base);
@@ -1048,7 +1220,18 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     const long long cap = (long long)sms * sign_res;
     const int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
     hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g);
-    hv::mc_count_kernel<<<(unsigned int)L.n_tiles, hv::kCountThreads, 0, st>>>(g);
+    hv::mc_detect_kernel<<<(unsigned int)L.n_tiles, hv::kDetectThreads, 0, st>>>(g);
+    {
+        // one warp per batch of 32 listed groups; how many there are is only known on the device
+        static int count_res = 0;
+        if (count_res == 0 && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&count_res, hv::mc_count_kernel, hv::kCountThreads, 0) !=
+                                   cudaSuccess || count_res < 1))
+            count_res = 4;
+        const long long want = (L.n_batches + hv::kCountThreads / 32 - 1) / (hv::kCountThreads / 32);
+        const long long cap = (long long)sms * count_res;
+        hv::mc_count_kernel<<<(unsigned int)(want < cap ? want : cap), hv::kCountThreads, 0, st>>>(g);
+    }
+    hv::mc_scan_kernel<<<(unsigned int)((L.n_tiles + hv::kScanThreads2 / 32 - 1) / (hv::kScanThreads2 / 32)), hv::kScanThreads2, 0, st>>>(g);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

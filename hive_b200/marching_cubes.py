@@ -18,8 +18,8 @@ from . import _lib
 from . import _xfer
 
 
-#: kernels launched by one extraction (init, sign, count+scan, triangles, vertices); bench.py reports it
-LAUNCHES_PER_EXTRACTION = 5
+#: kernels launched by one extraction (init, sign, detect, count, scan, triangles, vertices); bench.py reports it
+LAUNCHES_PER_EXTRACTION = 7
 
 
 def _ptr(t):
