@@ -35,6 +35,7 @@ SIGNATURES = {
     "hv_integrate": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                      c_void_p, c_int, c_int, c_double, c_double, c_int, c_void_p, c_void_p],
     "hv_mc_scratch_bytes": [c_void_p, c_int, c_int, c_void_p],
+    "hv_mc_scratch_init": [c_void_p, c_int, c_int, c_void_p, c_int64, c_void_p],
     "hv_mc_work_bytes": [c_int64, c_int64, c_void_p],
     "hv_mc_count": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p, c_int64, c_void_p, c_int64,
                     c_int64, c_void_p, c_void_p],

@@ -5,21 +5,29 @@
 // nearest-voxel colour gather, b/g/r unpack, voxel -> world transform).  The arithmetic contract is the one restated in
 // oracle/mc_oracle.c (scikit-image itself is not available anywhere on the box: parity unpinned).
 //
-// Pipeline (HBM-bound streaming + sparse compaction, no tensor cores), DESIGN.md 4.2:
-//   1. mc_sign_kernel   the one pass over the TSDF plane (4 B/voxel): one sign bit per voxel (N/8 bytes, L2 resident)
-//                       + min / max for the skimage level-range check.
-//   2. mc_count_kernel  one thread per 32-voxel z-group over the bit volume: masks of the voxels owning a vertex on
-//                       their +axis0 / +axis1 / +axis2 edge, triangles of the group's surface cubes (TSDF values are
-//                       fetched only for cubes with an ambiguous face or an interior test).  A tile of 256 groups is
-//                       scanned in the block; written: a 16-byte record {first vertex, mx, my, mz} in place for every
-//                       group that owns a vertex (`gtab`, sparse: the index look-up of a triangle corner is ONE load
-//                       plus a hot small-table entry), one work record per surface cube and per edge vertex, the
-//                       tile totals.  The last tile to finish scans the tile totals (no extra launch, no look-back).
-//   3. mc_tri_kernel    one thread per cube record: its triangles (three `gtab` look-ups each) and its centre vertex.
-//   4. mc_vert_kernel   one thread per vertex record: position, normal accumulated over the <= 4 cubes around the
-//                       edge in scan order, colour, world transform -- the edge's 2x3x3 neighbourhood in registers.
-// The emit kernels read the totals on the device, so all launches can be queued back to back; the host reads the totals
-// once, afterwards.
+// Pipeline (HBM-bound streaming + sparse compaction, no tensor cores), DESIGN.md 4.2.  The global order of the 32-voxel
+// z-groups (column-major, z fastest) is the order of vertices and triangles; a tile = 1024 consecutive groups.
+//   1. mc_sign_kernel    the one pass over the TSDF plane (4 B/voxel): one sign bit per voxel (N/8 bytes, L2 resident),
+//                        a warp vote per word; per-block min / max for the skimage level-range check.
+//   2. mc_detect_kernel  a thread per four groups: does any sign change come near?  Ordered compaction of those groups
+//                        into the tile's list; one work item per 32 listed groups.
+//   3. mc_count_kernel   a warp per work item, no barriers: lane = listed group (masks of the voxels owning a vertex on
+//                        their +axis0 / +axis1 / +axis2 edge, surface-cube mask), then lane = surface cube (warp scans
+//                        spread the cubes, 32 at a time whatever the shape of the surface).  Every tiling decision is made
+//                        once: cubes that need the face / interior tests are queued and evaluated 32 at a time (the only
+//                        step that waits on TSDF values).  Written: a 16-byte record {first vertex, mx, my, mz} in place
+//                        for every group that owns a vertex (`gtab`, sparse: the index look-up of a triangle corner is
+//                        ONE load plus two hot small-table entries), one work record per surface cube (with its tiling
+//                        and batch-local triangle offset) and per edge vertex, the batch totals.
+//   4. mc_scan_kernel    batch totals -> batch bases within the tile (a warp per tile), tile totals -> tile bases (last
+//                        block), grand totals, min / max; resets the counters for the next extraction.
+//   5. mc_emit_kernel    one thread per cube record (its triangles: the vertex indices of the cube's edges are looked up
+//                        first, all loads independent; its centre vertex) and one thread per vertex record (position,
+//                        normal accumulated over the <= 4 cubes around the edge in scan order, colour, world transform
+//                        -- the edge's 2x3x3 neighbourhood in registers, nothing indexed dynamically), the two kinds of
+//                        block interleaved in one grid.
+// Launches 2-5 are programmatic dependents (their set-up overlaps the predecessor's tail) and read the totals on the
+// device, so all five can be queued back to back; the host reads the totals once, afterwards.
 // Vertex order: edge vertices sorted by (owner voxel in scan order, axis), then the cube-centre vertices by cube;
 // triangles in cube scan order.  Deterministic; no dedup pass because each lattice edge has exactly one owner.
 //
@@ -28,6 +36,7 @@
 #include "hv_common.cuh"
 
 #include <float.h>
+#include <stdlib.h>
 #include <string.h>
 
 #define HV_MC_TABLE static __device__ const
@@ -55,12 +64,15 @@ struct McGrid {
     uint4* gtab;                 // [n_groups], written only where the group owns a vertex: {batch-local first vertex | batch of the tile << 12, mx, my, mz}
     unsigned int* glist;         // [n_tiles][1024] ids of the groups near the surface, per tile, ascending
     unsigned int* tile_cnt;      // [n_tiles] entries of glist used
+    unsigned short* cvar;        // [n_groups][32] tiling of a cube, written only for cubes whose tiling needs the face / interior tests
+    int2* sign_minmax;           // [sign_blocks] min / max key (ordered-int float) of the voxels a block of the sign kernel saw
+    int sign_blocks;
     unsigned int* work;          // [n_batches] work items of the count kernel: tile * 32 + batch of the tile, any order
     uint4* batch_tot;            // [n_batches] {edge vertices, triangles, centre vertices, cubes} of a batch
     uint4* batch_base;           // [n_batches] {edge vertices, triangles, centre vertices} of the tile before this batch of 32 listed groups
     uint4* tile_tot;             // [n_tiles] {edge vertices, triangles, centre vertices, cubes} of every tile of 32 batches
     uint4* tile_base;            // [n_tiles] exclusive prefix of tile_tot (x, y, z)
-    unsigned int* ctrl;          // [0] scan blocks done, [3] work items, [4..5] cursors of the record arrays (vertices | cubes << 32)
+    unsigned int* ctrl;          // [0] scan blocks done, [3] work items, [4..5] cursors of the record arrays (vertices | cubes << 32), [6] work ticket
     // work records (caller-sized: hv_mc_work_bytes)
     uint4* cube_rec;             // {group, voxel | tiling << 5 | batch of the tile << 16, batch-local first triangle, batch-local centre vertex}
     unsigned long long* vert_rec;  // pack_vertex_record()
@@ -284,9 +296,19 @@ __global__ void __launch_bounds__(256) mc_sign_kernel(const __grid_constant__ Mc
         vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o));
         vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
     }
-    if (lane == 0 && vmin <= vmax) {  // at least one real value seen
-        atomicMin(reinterpret_cast<int*>(g.totals + 2), float_order_key(vmin));
-        atomicMax(reinterpret_cast<int*>(g.totals + 3), float_order_key(vmax));
+    __shared__ float s_min[8], s_max[8];
+    if (lane == 0) {
+        s_min[threadIdx.x >> 5] = vmin;
+        s_max[threadIdx.x >> 5] = vmax;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) {
+            vmin = fminf(vmin, s_min[w]);
+            vmax = fmaxf(vmax, s_max[w]);
+        }
+        // (no voxel seen: min > max, keys stay at their neutral values)
+        g.sign_minmax[blockIdx.x] = vmin <= vmax ? make_int2(float_order_key(vmin), float_order_key(vmax)) : make_int2(0x7fffffff, (int)0x80000000);
     }
 }
 
@@ -393,6 +415,7 @@ __device__ __forceinline__ bool group_near_surface(const unsigned int (&b)[4], c
 
 __global__ void __launch_bounds__(kDetectThreads) mc_detect_kernel(const __grid_constant__ McGrid g) {
     __shared__ unsigned int s_warp[kDetectThreads / 32];
+    cudaGridDependencySynchronize();  // launched as a programmatic dependent of the sign kernel (launch latency hidden)
     const unsigned int tile = blockIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long gid0 = (long long)tile * kTileGroups + 4 * (long long)threadIdx.x;
@@ -484,19 +507,6 @@ constexpr int kCountThreads = 128;
 constexpr int kCubeChunk = 256;
 static_assert(HV_MC_NUM_VARIANTS <= 1024, "cube words keep the tiling in 10 bits");
 
-__global__ void mc_init_kernel(unsigned long long* totals, unsigned int* ctrl) {
-    if (threadIdx.x == 0) {
-        totals[0] = 0ull;
-        totals[1] = 0ull;
-        totals[2] = 0x7fffffffull;  // min key
-        totals[3] = 0x80000000ull;  // max key
-        totals[4] = 0ull;
-        totals[5] = 0ull;
-        totals[6] = 0ull;
-    }
-    if (threadIdx.x < 8) ctrl[threadIdx.x] = 0u;
-}
-
 // vertex record: group (31 bits) | voxel << 31 (5) | axis << 36 (2) | batch-local vertex index << 38 (12: <= 32 * 96) |
 // batch of the tile << 50 (5)
 __device__ __forceinline__ unsigned long long pack_vertex_record(unsigned int gid, int k, int axis, unsigned int local, int slot) {
@@ -504,15 +514,21 @@ __device__ __forceinline__ unsigned long long pack_vertex_record(unsigned int gi
            ((unsigned long long)local << 38) | ((unsigned long long)slot << 50);
 }
 
-__global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_constant__ McGrid g) {
+__global__ void __launch_bounds__(kCountThreads, 8) mc_count_kernel(const __grid_constant__ McGrid g) {
     __shared__ unsigned int s_cube[kCountThreads / 32][kCubeChunk];
     __shared__ unsigned short s_queue[kCountThreads / 32][kCubeChunk];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned int lt = (1u << lane) - 1u;
+    cudaGridDependencySynchronize();
     const unsigned int n_work = g.ctrl[3];
     const unsigned int n_warps = gridDim.x * (kCountThreads / 32);
+    // the first item of a warp is its own index, the following ones come from a ticket counter -- requested before the
+    // current item is processed, so the round trip is never waited for
+    unsigned int wi = blockIdx.x * (kCountThreads / 32) + warp;
 #pragma unroll 1
-    for (unsigned int wi = blockIdx.x * (kCountThreads / 32) + warp; wi < n_work; wi += n_warps) {
+    while (wi < n_work) {
+        unsigned int ticket = 0;
+        if (lane == 0) ticket = atomicAdd(g.ctrl + 6, 1u);
         const unsigned int item = __ldg(g.work + wi);
         const unsigned int tile = item / kTileBatches;
         const int slot = (int)(item % kTileBatches);
@@ -600,10 +616,12 @@ __global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_co
                     const int s = (int)(word >> 15), k = (int)((word >> 10) & 31u);
                     const int cx = __shfl_sync(0xffffffffu, x, s), cy = __shfl_sync(0xffffffffu, y, s);
                     const int cgq = __shfl_sync(0xffffffffu, gq, s);
+                    const unsigned int qgid = __shfl_sync(0xffffffffu, gid, s);
                     if (qv) {
                         const int variant = cube_variant_ambiguous(g.tsdf, g.halo_lo, g.halo_hi, g.Y, g.pitch, g.Z, g.hl, g.level,
                                                                    (int)(word & 1023u), cx, cy, cgq * 32 + k);
                         s_var[e] = (word & ~1023u) | (unsigned int)variant;
+                        g.cvar[(size_t)qgid * 32 + k] = (unsigned short)variant;  // the vertex kernel looks it up
                     }
                 }
                 __syncwarp();
@@ -629,6 +647,7 @@ __global__ void __launch_bounds__(kCountThreads) mc_count_kernel(const __grid_co
             tot = make_uint4(NV, tri_run, cen_run, C);
         }
         if (lane == 0) g.batch_tot[item] = tot;
+        wi = n_warps + __shfl_sync(0xffffffffu, ticket, 0);
     }
 }
 
@@ -644,6 +663,7 @@ __global__ void __launch_bounds__(kScanThreads2) mc_scan_kernel(const __grid_con
     __shared__ unsigned int s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long tile = (long long)blockIdx.x * (kScanThreads2 / 32) + warp;
+    cudaGridDependencySynchronize();
     if (tile < g.n_tiles) {
         const unsigned int nb = (__ldg(g.tile_cnt + tile) + 31u) / 32u;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
@@ -661,47 +681,57 @@ __global__ void __launch_bounds__(kScanThreads2) mc_scan_kernel(const __grid_con
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    // every thread takes a run of consecutive tiles, 16 at a time with all loads in flight together (a block-wide scan per
+    // 256 tiles cost a load round trip per round: 12.5 us at 4096 tiles)
     const int n_tiles = g.n_tiles;
-    unsigned long long carry_a = 0, carry_b = 0;  // (edge vertices | triangles << 32), (centre vertices | cubes << 32): all < 2^31
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if ((int)threadIdx.x < n_tiles) v = __ldcg(g.tile_tot + threadIdx.x);
-    for (int i0 = 0; i0 < n_tiles; i0 += kScanThreads2) {
-        const int i = i0 + (int)threadIdx.x;
-        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-        if (i + kScanThreads2 < n_tiles) nxt = __ldcg(g.tile_tot + i + kScanThreads2);  // next round's entry, requested early
-        const unsigned long long a = (unsigned long long)v.x | ((unsigned long long)v.y << 32);
-        const unsigned long long bb = (unsigned long long)v.z | ((unsigned long long)v.w << 32);
-        unsigned long long ia = a, ib = bb;
+    const int per = (n_tiles + kScanThreads2 - 1) / kScanThreads2;
+    const int i0 = min(n_tiles, (int)threadIdx.x * per), i1 = min(n_tiles, i0 + per);
+    unsigned long long a = 0, bsum = 0;  // (edge vertices | triangles << 32), (centre vertices | cubes << 32): all < 2^31
+    for (int j0 = i0; j0 < i1; j0 += 16) {
+        uint4 v[16];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned long long ua = __shfl_up_sync(0xffffffffu, ia, o), ub = __shfl_up_sync(0xffffffffu, ib, o);
-            if (lane >= o) {
-                ia += ua;
-                ib += ub;
-            }
-        }
-        if (lane == 31) {
-            s_wa[warp] = ia;
-            s_wb[warp] = ib;
-        }
-        __syncthreads();
-        unsigned long long ca = 0, cb = 0, ta = 0, tb = 0;
+        for (int j = 0; j < 16; ++j) v[j] = (j0 + j < i1) ? __ldcg(g.tile_tot + j0 + j) : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-        for (int w = 0; w < kScanThreads2 / 32; ++w) {
-            const unsigned long long xa = s_wa[w], xb = s_wb[w];
-            if (w < warp) {
-                ca += xa;
-                cb += xb;
-            }
-            ta += xa;
-            tb += xb;
+        for (int j = 0; j < 16; ++j) {
+            a += (unsigned long long)v[j].x | ((unsigned long long)v[j].y << 32);
+            bsum += (unsigned long long)v[j].z | ((unsigned long long)v[j].w << 32);
         }
-        __syncthreads();
-        const unsigned long long ea = carry_a + ca + ia - a, eb = carry_b + cb + ib - bb;
-        if (i < n_tiles) g.tile_base[i] = make_uint4((unsigned int)ea, (unsigned int)(ea >> 32), (unsigned int)eb, 0u);
-        carry_a += ta;
-        carry_b += tb;
-        v = nxt;
+    }
+    unsigned long long ia = a, ib = bsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long ua = __shfl_up_sync(0xffffffffu, ia, o), ub = __shfl_up_sync(0xffffffffu, ib, o);
+        if (lane >= o) {
+            ia += ua;
+            ib += ub;
+        }
+    }
+    if (lane == 31) {
+        s_wa[warp] = ia;
+        s_wb[warp] = ib;
+    }
+    __syncthreads();
+    unsigned long long ea = ia - a, eb = ib - bsum, carry_a = 0, carry_b = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads2 / 32; ++w) {
+        const unsigned long long xa = s_wa[w], xb = s_wb[w];
+        if (w < warp) {
+            ea += xa;
+            eb += xb;
+        }
+        carry_a += xa;
+        carry_b += xb;
+    }
+    for (int j0 = i0; j0 < i1; j0 += 16) {
+        uint4 v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = (j0 + j < i1) ? __ldcg(g.tile_tot + j0 + j) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j0 + j < i1) g.tile_base[j0 + j] = make_uint4((unsigned int)ea, (unsigned int)(ea >> 32), (unsigned int)eb, 0u);
+            ea += (unsigned long long)v[j].x | ((unsigned long long)v[j].y << 32);
+            eb += (unsigned long long)v[j].z | ((unsigned long long)v[j].w << 32);
+        }
     }
     if (threadIdx.x == 0) {
         const unsigned long long n_edge = carry_a & 0xffffffffull, n_tri = carry_a >> 32, n_centre = carry_b & 0xffffffffull, n_cube = carry_b >> 32;
@@ -710,6 +740,34 @@ __global__ void __launch_bounds__(kScanThreads2) mc_scan_kernel(const __grid_con
         g.totals[4] = n_edge;
         g.totals[5] = n_cube;
         g.totals[6] = ((long long)n_cube > g.cap_cubes || (long long)n_edge > g.cap_vrec) ? 1ull : 0ull;  // records incomplete
+    }
+    // min / max of the volume (skimage's level-range check) from the sign kernel's per-block values
+    int kmin = 0x7fffffff, kmax = (int)0x80000000;
+    for (int i = threadIdx.x; i < g.sign_blocks; i += kScanThreads2) {
+        const int2 v = __ldcg(g.sign_minmax + i);
+        kmin = min(kmin, v.x);
+        kmax = max(kmax, v.y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+        kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+    }
+    __shared__ int s_kmin[kScanThreads2 / 32], s_kmax[kScanThreads2 / 32];
+    if (lane == 0) {
+        s_kmin[warp] = kmin;
+        s_kmax[warp] = kmax;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kScanThreads2 / 32; ++w) {
+            kmin = min(kmin, s_kmin[w]);
+            kmax = max(kmax, s_kmax[w]);
+        }
+        g.totals[2] = (unsigned long long)(unsigned int)kmin;
+        g.totals[3] = (unsigned long long)(unsigned int)kmax;
+        // every counter back to zero for the next extraction (hv_mc_scratch_init zeroed them for the first)
+        for (int i = 0; i < 8; ++i) g.ctrl[i] = 0u;
     }
 }
 
@@ -824,6 +882,9 @@ __device__ __noinline__ int cube_variant_values(int idx, const double* v) { retu
 // nothing is indexed dynamically, and the tilings of the surrounding cubes -- face and interior tests included -- are decided
 // from those registers.  (r02: fetching the corners of every ambiguous cube again was 25 % of this kernel's instructions on
 // the room scene, the per-value coordinate permutation another 25 %.)
+// WHOLE: a whole volume (no halo planes): direct loads, and the tiling of an ambiguous cube is read from `cvar` (the count
+// kernel decided it) instead of being derived again.  LEVEL0: level == 0, the value every caller in HIVE uses: x - 0.0 == x.
+template <bool WHOLE, bool LEVEL0>
 __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& out, int x, int y, int zb, int axis, size_t vi) {
     const int pb = axis == 0 ? y : x, pc = axis == 2 ? y : zb;
     const int db_dim = axis == 0 ? g.Y : g.X, dc_dim = axis == 2 ? g.Y : g.Zb;
@@ -834,7 +895,7 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
         okc[i] = pc + i - 1 >= 0 && pc + i - 1 < dc_dim;
     }
     float n[2][3][3];
-    if (g.halo_lo == nullptr && g.halo_hi == nullptr) {  // whole volume: zb == z, every neighbour is in the plane array
+    if (WHOLE) {  // zb == z, every neighbour is in the plane array
         const ptrdiff_t sx = (ptrdiff_t)g.Y * g.pitch, sy = g.pitch;
         const ptrdiff_t sa = axis == 0 ? sx : (axis == 1 ? sy : 1), sb = axis == 0 ? sy : sx, sc = axis == 2 ? sy : 1;
         const float* p0 = g.tsdf + ((size_t)x * g.Y + y) * (size_t)g.pitch + zb;
@@ -864,7 +925,8 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
                     n[ia][ib][ic] = f;
                 }
     }
-    const double level = g.level;
+    const double level = LEVEL0 ? 0.0 : g.level;
+#define HV_DV(f) (LEVEL0 ? (double)(f) : ((double)(f) - level))
     // sign bit of every neighbour, position ia * 9 + ib * 3 + ic
     unsigned int sgn = 0u;
 #pragma unroll
@@ -873,8 +935,8 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
         for (int ib = 0; ib < 3; ++ib)
 #pragma unroll
             for (int ic = 0; ic < 3; ++ic)
-                sgn |= (((double)n[ia][ib][ic] - level) > 0.0 ? 1u : 0u) << (ia * 9 + ib * 3 + ic);
-    const double v_lo = (double)n[0][1][1] - level, v_hi = (double)n[1][1][1] - level;
+                sgn |= ((LEVEL0 ? (n[ia][ib][ic] > 0.0f) : (HV_DV(n[ia][ib][ic]) > 0.0)) ? 1u : 0u) << (ia * 9 + ib * 3 + ic);
+    const double v_lo = HV_DV(n[0][1][1]), v_hi = HV_DV(n[1][1][1]);
     const double w_lo = 1.0 / ((double)FLT_EPSILON + fabs(v_lo)), w_hi = 1.0 / ((double)FLT_EPSILON + fabs(v_hi));
     const double frac = w_hi / __dadd_rn(w_lo, w_hi);
     const unsigned int pos_corner = axis == 0 ? kPosCorner0 : (axis == 1 ? kPosCorner1 : kPosCorner2);
@@ -897,6 +959,12 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
             const int idx = kLocToIndex.t[axis][loc];
             int variant = kMcVariantBase[idx];
             if (kMcAmbCount[idx] != 0 || kMcInteriorBase[idx] != 255) {
+              if (WHOLE) {
+                // base voxel of the cube: (a, b, c) = (edge position, pb - db, pc - dc) permuted back by `axis`
+                const int bb = pb - db, bc = pc - dc;
+                const int cx = axis == 0 ? x : bb, cy = axis == 1 ? y : (axis == 0 ? bb : bc), cz = axis == 2 ? zb : bc;
+                variant = __ldg(g.cvar + (((size_t)cx * g.Y + cy) * g.G + (cz >> 5)) * 32 + (cz & 31));
+              } else {
                 double v[8];
 #pragma unroll
                 for (int ia = 0; ia < 2; ++ia)
@@ -904,8 +972,9 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
                     for (int ib = 0; ib < 2; ++ib)
 #pragma unroll
                         for (int ic = 0; ic < 2; ++ic)
-                            v[(pos_corner >> (3 * (ia * 4 + ib * 2 + ic))) & 7u] = (double)n[ia][ib + 1 - db][ic + 1 - dc] - level;
+                            v[(pos_corner >> (3 * (ia * 4 + ib * 2 + ic))) & 7u] = HV_DV(n[ia][ib + 1 - db][ic + 1 - dc]);
                 variant = cube_variant_values(idx, v);
+              }
             }
             // the edge inside this cube: lower corner at cube-local (0, db, dc)
             const int d0 = axis == 0 ? 0 : db, d1 = axis == 1 ? 0 : (axis == 0 ? db : dc), d2 = axis == 2 ? 0 : dc;
@@ -914,10 +983,10 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
             if (mult == 0) continue;
             // down-hill in-cube finite differences at the edge's two end corners, weighted like the position
             const double ga = v_lo - v_hi;
-            const double gb_lo = ((double)n[0][1 - db][1] - level) - ((double)n[0][2 - db][1] - level);
-            const double gb_hi = ((double)n[1][1 - db][1] - level) - ((double)n[1][2 - db][1] - level);
-            const double gc_lo = ((double)n[0][1][1 - dc] - level) - ((double)n[0][1][2 - dc] - level);
-            const double gc_hi = ((double)n[1][1][1 - dc] - level) - ((double)n[1][1][2 - dc] - level);
+            const double gb_lo = HV_DV(n[0][1 - db][1]) - HV_DV(n[0][2 - db][1]);
+            const double gb_hi = HV_DV(n[1][1 - db][1]) - HV_DV(n[1][2 - db][1]);
+            const double gc_lo = HV_DV(n[0][1][1 - dc]) - HV_DV(n[0][1][2 - dc]);
+            const double gc_hi = HV_DV(n[1][1][1 - dc]) - HV_DV(n[1][1][2 - dc]);
             const float fa = (float)__dadd_rn(__dmul_rn(ga, w_lo), __dmul_rn(ga, w_hi));
             const float fb = (float)__dadd_rn(__dmul_rn(gb_lo, w_lo), __dmul_rn(gb_hi, w_hi));
             const float fc = (float)__dadd_rn(__dmul_rn(gc_lo, w_lo), __dmul_rn(gc_hi, w_hi));
@@ -947,7 +1016,9 @@ __device__ __forceinline__ void emit_edge_vertex(const McGrid& g, const McEmit& 
     // colour of the nearest voxel (fusion.py:339,343-348), half-to-even like np.round
     const int i0 = (int)rintf(pv[0]), i1 = (int)rintf(pv[1]);
     const int i2 = (int)((long long)rintf(pv[2]) - g.zoff);
-    const unsigned int packed = (unsigned int)mc_fetch(g, g.color, g.chalo_lo, g.chalo_hi, i0, i1, i2);
+    const unsigned int packed = WHOLE ? (unsigned int)__ldg(g.color + ((size_t)i0 * g.Y + i1) * (size_t)g.pitch + i2)
+                                      : (unsigned int)mc_fetch(g, g.color, g.chalo_lo, g.chalo_hi, i0, i1, i2);
+#undef HV_DV
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         out.verts_world[3 * vi + k] = __fadd_rn(__fmul_rn(pv[k], out.voxel_size), out.origin[k]);  // fusion.py:340
@@ -1013,11 +1084,10 @@ constexpr int kEmitThreads = 256;
 // ---- 3. triangles (+ cube-centre vertices): one thread per cube record ---------------------------------------------------------
 // The vertex indices of the cube's (up to 12) edges are looked up first, all loads independent; its triangles then pick
 // from that array.  (One thread walking its triangles with three dependent look-ups each was measured at 66 us.)
-__global__ void __launch_bounds__(kEmitThreads, 4) mc_tri_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out) {
+__device__ __forceinline__ void emit_cubes(const McGrid& g, const McEmit& out, unsigned int block, unsigned int n_blocks) {
     __shared__ unsigned int s_vidx[13][kEmitThreads];  // [edge][thread]: dynamic indexing without local memory
-    if (g.totals[6]) return;  // the records are incomplete: the host re-runs the count with a larger work buffer
     const unsigned int n_cubes = (unsigned int)g.totals[5], n_edge = (unsigned int)g.totals[4];
-    for (unsigned int i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_cubes; i += gridDim.x * kEmitThreads) {
+    for (unsigned int i = block * kEmitThreads + threadIdx.x; i < n_cubes; i += n_blocks * kEmitThreads) {
         const uint4 rec = __ldg(g.cube_rec + i);
         int x, y, gq;
         decode_group(g, rec.x, x, y, gq);
@@ -1060,10 +1130,10 @@ __global__ void __launch_bounds__(kEmitThreads, 4) mc_tri_kernel(const __grid_co
 }
 
 // ---- 4. edge vertices: one thread per vertex record ----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kEmitThreads, 3) mc_vert_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out) {
-    if (g.totals[6]) return;
+template <bool WHOLE, bool LEVEL0>
+__device__ __forceinline__ void emit_vertices(const McGrid& g, const McEmit& out, unsigned int block, unsigned int n_blocks) {
     const unsigned int n_edge = (unsigned int)g.totals[4];
-    for (unsigned int i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_edge; i += gridDim.x * kEmitThreads) {
+    for (unsigned int i = block * kEmitThreads + threadIdx.x; i < n_edge; i += n_blocks * kEmitThreads) {
         const unsigned long long rec = __ldg(g.vert_rec + i);
         const unsigned int gid = (unsigned int)(rec & 0x7fffffffull);
         const int k = (int)((rec >> 31) & 31ull), axis = (int)((rec >> 36) & 3ull);
@@ -1072,8 +1142,23 @@ __global__ void __launch_bounds__(kEmitThreads, 3) mc_vert_kernel(const __grid_c
         const size_t tile = gid / kTileGroups;
         const size_t vi = (size_t)__ldg(&g.tile_base[tile].x) + __ldg(&g.batch_base[tile * kTileBatches + (unsigned int)((rec >> 50) & 31ull)].x) +
                           (unsigned int)((rec >> 38) & 4095ull);
-        if ((long long)vi < out.cap_verts) emit_edge_vertex(g, out, x, y, gq * 32 + k, axis, vi);
+        if ((long long)vi < out.cap_verts) emit_edge_vertex<WHOLE, LEVEL0>(g, out, x, y, gq * 32 + k, axis, vi);
     }
+}
+
+// One launch for both: triangles and vertices do not depend on each other and stall on different things (index look-ups in
+// L2 / arithmetic), so their blocks are interleaved in the grid in the ratio n_tri_blocks : n_vert_blocks.  (Two launches:
+// 33 + 40 us; the triangle kernel on a forked side stream gained 6 us of that -- the event hand-over costs what it hides.)
+template <bool WHOLE, bool LEVEL0>
+__global__ void __launch_bounds__(kEmitThreads, (WHOLE && LEVEL0) ? 4 : 3)
+    mc_emit_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out, const unsigned int n_tri_blocks,
+                   const unsigned int n_vert_blocks) {
+    cudaGridDependencySynchronize();
+    if (g.totals[6]) return;  // the records are incomplete: the host re-runs the count with a larger work buffer
+    const unsigned long long b = blockIdx.x, n = (unsigned long long)n_tri_blocks + n_vert_blocks;
+    const unsigned int t_before = (unsigned int)(b * n_tri_blocks / n), t_after = (unsigned int)((b + 1) * n_tri_blocks / n);
+    if (t_after > t_before) emit_cubes(g, out, t_before, n_tri_blocks);
+    else emit_vertices<WHOLE, LEVEL0>(g, out, (unsigned int)b - t_before, n_vert_blocks);
 }
 
 }  // namespace hv
@@ -1084,10 +1169,29 @@ namespace {
 struct McLayout {
     long long n_groups, n_batches, n_tiles;
     int G, Zb;
-    size_t off_bits, off_gtab, off_glist, off_tile_cnt, off_work, off_batch_tot, off_batch_base, off_tile_tot, off_tile_base, off_ctrl, total;
+    size_t off_bits, off_gtab, off_glist, off_tile_cnt, off_work, off_cvar, off_minmax, off_batch_tot, off_batch_base, off_tile_tot, off_tile_base, off_ctrl, total;
 };
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+constexpr int kMaxSignBlocks = 8192;
+
+// Launch as a programmatic dependent of the kernel before it in the stream: the grid may be set up while its predecessor
+// drains; the kernel itself waits (cudaGridDependencySynchronize, its first statement) before it reads anything.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_dependent(void (*kernel)(KArgs...), unsigned int grid, unsigned int block, cudaStream_t st, Args... args) {
+    static const bool plain = getenv("HV_MC_NO_PDL") != nullptr;  // A/B switch
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = plain ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     HV_REQUIRE(h_dims, "marching cubes: null dims");
@@ -1119,6 +1223,10 @@ int mc_layout(const int64_t* h_dims, bool lo, bool hi, McLayout* L) {
     o = align_up(o + (size_t)L->n_tiles * sizeof(unsigned int));
     L->off_work = o;
     o = align_up(o + (size_t)L->n_batches * sizeof(unsigned int));
+    L->off_cvar = o;
+    o = align_up(o + (size_t)L->n_groups * 32 * sizeof(unsigned short));
+    L->off_minmax = o;
+    o = align_up(o + (size_t)kMaxSignBlocks * sizeof(int2));
     L->off_ctrl = o;
     o = align_up(o + 8 * sizeof(unsigned int));
     L->total = o;
@@ -1166,6 +1274,9 @@ int mc_grid(hv::McGrid* g, const float* tsdf, const float* halo_lo, const float*
     g->glist = reinterpret_cast<unsigned int*>(s + L->off_glist);
     g->tile_cnt = reinterpret_cast<unsigned int*>(s + L->off_tile_cnt);
     g->work = reinterpret_cast<unsigned int*>(s + L->off_work);
+    g->cvar = reinterpret_cast<unsigned short*>(s + L->off_cvar);
+    g->sign_minmax = reinterpret_cast<int2*>(s + L->off_minmax);
+    g->sign_blocks = 0;
     g->batch_tot = reinterpret_cast<uint4*>(s + L->off_batch_tot);
     g->batch_base = reinterpret_cast<uint4*>(s + L->off_batch_base);
     g->tile_tot = reinterpret_cast<uint4*>(s + L->off_tile_tot);
@@ -1193,6 +1304,16 @@ extern "C" int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int h
     return HV_OK;
 }
 
+extern "C" int hv_mc_scratch_init(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, void* scratch, int64_t scratch_bytes,
+                                   void* stream) {
+    McLayout L;
+    int rc = mc_layout(h_dims, has_halo_lo != 0, has_halo_hi != 0, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(scratch && ((uintptr_t)scratch & 255) == 0 && (size_t)scratch_bytes >= L.total, "hv_mc_scratch_init: bad scratch");
+    HV_CUDA(cudaMemsetAsync(static_cast<char*>(scratch) + L.off_ctrl, 0, 8 * sizeof(unsigned int), hv::as_stream(stream)));
+    return HV_OK;
+}
+
 extern "C" int hv_mc_work_bytes(int64_t rec_verts, int64_t rec_cubes, int64_t* h_bytes) {
     HV_REQUIRE(h_bytes && rec_verts >= 0 && rec_cubes >= 0 && rec_verts < (1ll << 31) && rec_cubes < (1ll << 31),
                "hv_mc_work_bytes: bad arguments");
@@ -1210,7 +1331,6 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     HV_REQUIRE(totals, "hv_mc_count: null totals");
     g.totals = totals;
     cudaStream_t st = hv::as_stream(stream);
-    hv::mc_init_kernel<<<1, 32, 0, st>>>(totals, g.ctrl);  // (a pageable H2D of the counters would block the host)
     const int sms = hv::device_info().sm_count;
     static int sign_res = 0;  // resident CTAs per SM of the sign kernel: the grid is exactly one wave
     if (sign_res == 0 &&
@@ -1218,9 +1338,11 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
         sign_res = 4;
     const long long want = ((long long)g.X * g.Y + 7) / 8;  // 8 warps per block, a warp per column (grid-stride)
     const long long cap = (long long)sms * sign_res;
-    const int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
+    int sign_blocks = (int)(want < cap ? (want > 0 ? want : 1) : cap);
+    if (sign_blocks > kMaxSignBlocks) sign_blocks = kMaxSignBlocks;
+    g.sign_blocks = sign_blocks;
     hv::mc_sign_kernel<<<sign_blocks, 256, 0, st>>>(g);
-    hv::mc_detect_kernel<<<(unsigned int)L.n_tiles, hv::kDetectThreads, 0, st>>>(g);
+    HV_CUDA(launch_dependent(hv::mc_detect_kernel, (unsigned int)L.n_tiles, hv::kDetectThreads, st, g));
     {
         // one warp per batch of 32 listed groups; how many there are is only known on the device
         static int count_res = 0;
@@ -1229,9 +1351,10 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
             count_res = 4;
         const long long want = (L.n_batches + hv::kCountThreads / 32 - 1) / (hv::kCountThreads / 32);
         const long long cap = (long long)sms * count_res;
-        hv::mc_count_kernel<<<(unsigned int)(want < cap ? want : cap), hv::kCountThreads, 0, st>>>(g);
+        HV_CUDA(launch_dependent(hv::mc_count_kernel, (unsigned int)(want < cap ? want : cap), hv::kCountThreads, st, g));
     }
-    hv::mc_scan_kernel<<<(unsigned int)((L.n_tiles + hv::kScanThreads2 / 32 - 1) / (hv::kScanThreads2 / 32)), hv::kScanThreads2, 0, st>>>(g);
+    HV_CUDA(launch_dependent(hv::mc_scan_kernel, (unsigned int)((L.n_tiles + hv::kScanThreads2 / 32 - 1) / (hv::kScanThreads2 / 32)),
+                             hv::kScanThreads2, st, g));
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }
@@ -1280,14 +1403,26 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     // one thread per record that can exist: a surface cube has a triangle, an edge vertex is a vertex
     const long long max_cubes = rec_cubes < n_tris ? rec_cubes : n_tris, max_verts = rec_verts < n_verts ? rec_verts : n_verts;
     // (grid-stride: a capacity far above the surface would otherwise launch tens of thousands of CTAs that only read the totals)
-    const long long grid_cap = (long long)sms * 32;
-    if (max_cubes > 0) {
-        const long long blocks = (max_cubes + hv::kEmitThreads - 1) / hv::kEmitThreads;
-        hv::mc_tri_kernel<<<(unsigned int)(blocks < grid_cap ? blocks : grid_cap), hv::kEmitThreads, 0, st>>>(g, em);
+    const long long grid_cap = (long long)sms * 48;
+    const long long tb = max_cubes > 0 ? (max_cubes + hv::kEmitThreads - 1) / hv::kEmitThreads : 0;
+    const long long vb = max_verts > 0 ? (max_verts + hv::kEmitThreads - 1) / hv::kEmitThreads : 0;
+    // (both roles grid-stride, so the block counts can be scaled down together when the capacity is far above the surface)
+    long long nt = tb, nv = vb;
+    if (nt + nv > grid_cap) {
+        nt = tb * grid_cap / (tb + vb);
+        nv = vb * grid_cap / (tb + vb);
+        if (tb > 0 && nt == 0) nt = 1;
+        if (vb > 0 && nv == 0) nv = 1;
     }
-    if (max_verts > 0) {
-        const long long blocks = (max_verts + hv::kEmitThreads - 1) / hv::kEmitThreads;
-        hv::mc_vert_kernel<<<(unsigned int)(blocks < grid_cap ? blocks : grid_cap), hv::kEmitThreads, 0, st>>>(g, em);
+    if (nt + nv > 0) {
+        const unsigned int grid = (unsigned int)(nt + nv);
+        const bool whole = !halo_lo && !halo_hi, level0 = level == 0.0;
+        // (a dependent launch is harmless when something else precedes it in the stream: it then just waits for that)
+        const unsigned int unt = (unsigned int)nt, unv = (unsigned int)nv;
+        if (whole && level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<true, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else if (whole) HV_CUDA(launch_dependent(hv::mc_emit_kernel<true, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else if (level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
     }
     HV_CUDA(cudaGetLastError());
     return HV_OK;

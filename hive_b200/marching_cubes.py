@@ -18,8 +18,8 @@ from . import _lib
 from . import _xfer
 
 
-#: kernels launched by one extraction (init, sign, detect, count, scan, triangles, vertices); bench.py reports it
-LAUNCHES_PER_EXTRACTION = 7
+#: kernels launched by one extraction (sign, detect, count, scan, emit); bench.py reports it
+LAUNCHES_PER_EXTRACTION = 5
 
 
 def _ptr(t):
@@ -89,6 +89,11 @@ class McPlan:
             pad = (-self.scratch.data_ptr()) % 256
             self.scratch_ptr = ctypes.c_void_p(self.scratch.data_ptr() + pad)
             self.totals = torch.zeros(8, dtype=torch.int64, device=self.device)
+            _lib.check(self._lib.hv_mc_scratch_init(ctypes.cast(self.dims, ctypes.c_void_p),
+                                                    int(self.halo.get("tsdf_lo") is not None),
+                                                    int(self.halo.get("tsdf_hi") is not None), self.scratch_ptr,
+                                                    self.scratch_bytes,
+                                                    ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
         self.work = None
         self.work_ptr = None
         self.rec_verts = self.rec_cubes = 0
@@ -207,7 +212,11 @@ class McPlan:
         mesh.vmin, mesh.vmax = vmin, vmax
         return mesh
 
-    def extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False, speculative=False) -> DeviceMesh:
+    #: set by extract_overlapped(timing_event=True) when the emit was launched behind the count without a host round trip
+    done_event = None
+
+    def extract_overlapped(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False, speculative=False,
+                           timing_event=False) -> DeviceMesh:
         """count -> (allocate the outputs while the classification runs) -> emit.  ``speculative``: the capacity comes from
         an earlier extraction of the same volume, so emit is launched right behind the classification and the totals are
         read afterwards -- no host round trip between the kernels; a surface that outgrew the capacity is emitted again
@@ -235,8 +244,13 @@ class McPlan:
                     origin.ctypes.data_as(ctypes.c_void_p), cap_verts, cap_tris, _ptr(verts), _ptr(verts_voxel), _ptr(normals),
                     _ptr(colors), _ptr(faces), None, None, None, _ptr(self.totals), stream))
 
+        done = None
         if speculative:
             launch()
+            if timing_event:  # end of the device work of this extraction (what follows is the host reading the totals)
+                with torch.cuda.device(dev):
+                    done = torch.cuda.Event(enable_timing=True)
+                    done.record()
         n_verts, n_tris, vmin, vmax = self.read_totals()
         check_surface(self.level, vmin, vmax, n_verts)
         if n_verts > cap_verts or n_tris > cap_tris or self._records_incomplete:
@@ -247,6 +261,7 @@ class McPlan:
             mesh = DeviceMesh(verts[:n_verts], verts_voxel[:n_verts] if want_voxel else None, normals[:n_verts],
                               colors[:n_verts], faces[:n_tris], None, None, None, 0.0, 0.0)
         mesh.vmin, mesh.vmax = vmin, vmax
+        self.done_event = done
         return mesh
 
 
@@ -262,8 +277,9 @@ def check_surface(level, vmin, vmax, n_verts):
 _LAST_SIZES = {}
 
 
-def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
-    """Mesh of a (single-GPU, whole) ``TSDFVolume`` as device tensors."""
+def extract_device_mesh(vol, level=0.0, want_voxel=False, timing_event=False) -> DeviceMesh:
+    """Mesh of a (single-GPU, whole) ``TSDFVolume`` as device tensors.  ``timing_event``: leave a CUDA event recorded
+    right behind the last kernel in ``vol._mc_plan.done_event`` (bench.py times the device work with it)."""
     X, Y, Z = (int(d) for d in vol._local_dim)
     assert min(X, Y, Z) >= 2, "Input array must be at least 2x2x2."
     # scratch (1.1 B/voxel) is kept with the volume: repeated extractions (HIVE meshes once, a live preview meshes often)
@@ -279,7 +295,7 @@ def extract_device_mesh(vol, level=0.0, want_voxel=False) -> DeviceMesh:
     cap_v = min(guess[0], 3 * X * Y * Z)
     cap_t = min(guess[1], 5 * X * Y * Z)
     mesh = plan.extract_overlapped(vol._voxel_size, vol._vol_origin, cap_v, cap_t, want_voxel=want_voxel,
-                                   speculative=(X, Y, Z) in _LAST_SIZES)
+                                   speculative=(X, Y, Z) in _LAST_SIZES, timing_event=timing_event)
     n_v, n_t = int(mesh.verts.shape[0]), int(mesh.faces.shape[0])
     _LAST_SIZES[(X, Y, Z)] = (n_v + n_v // 2 + 1024, n_t + n_t // 2 + 1024)
     return mesh

@@ -114,7 +114,8 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * tsdf / color : float32 planes [X][Y][pitch] (z fastest), h_dims = {X, Y, Z}.
  * halo_lo / halo_hi (and the colour pair): optional [X][Y] planes just below z = 0 / above z = Z-1 of a z-slab
  *                shard (NULL for a whole volume).  A shard owns the cubes whose base voxel lies in its slab.
- * scratch      : device buffer of hv_mc_scratch_bytes() bytes, 256-byte aligned; must be kept between the two calls.
+ * scratch      : device buffer of hv_mc_scratch_bytes() bytes, 256-byte aligned, passed to hv_mc_scratch_init once;
+ *                must be kept between the two calls.
  * work         : device buffer of hv_mc_work_bytes(rec_verts, rec_cubes) bytes, 256-byte aligned; kept likewise, and
  *                passed with the same rec_verts / rec_cubes to both calls.
  * z_global_offset / z_global_dim : position of the slab in the global volume (0 / Z for a whole volume); vertex keys
@@ -127,6 +128,8 @@ int hv_integrate(float* tsdf, float* weight, float* color, const int64_t* h_dims
  * vert_keys    : optional uint64 [V] key of every vertex (shards: what face_keys refer to); NULL to skip.
  * ---------------------------------------------------------------------------------------------------------- */
 int hv_mc_scratch_bytes(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, int64_t* h_bytes);
+/* once per scratch buffer, before its first hv_mc_count: zeroes the counters the kernels keep (and reset themselves) */
+int hv_mc_scratch_init(const int64_t* h_dims, int has_halo_lo, int has_halo_hi, void* scratch, int64_t scratch_bytes, void* stream);
 int hv_mc_work_bytes(int64_t rec_verts, int64_t rec_cubes, int64_t* h_bytes);
 int hv_mc_count(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims, int64_t pitch,
                 double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,

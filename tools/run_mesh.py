@@ -40,11 +40,13 @@ def main():
         for r in range(args.reps):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            mesh = mc.extract_device_mesh(vol)
+            mesh = mc.extract_device_mesh(vol, timing_event=True)
             e1.record()
             torch.cuda.synchronize()
-            print(f"mc rep {r}: {e0.elapsed_time(e1):.3f} ms, {mesh.verts.shape[0]} vertices, {mesh.faces.shape[0]} triangles",
-                  flush=True)
+            done = vol._mc_plan.done_event
+            dev_ms = f"{e0.elapsed_time(done):.3f}" if done is not None else "n/a"
+            print(f"mc rep {r}: {e0.elapsed_time(e1):.3f} ms (kernels only {dev_ms} ms), {mesh.verts.shape[0]} vertices, "
+                  f"{mesh.faces.shape[0]} triangles", flush=True)
         # phase split: classification (sign + count + scans) | host read of the totals | emit + vertices
         plan = mc.McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, tuple(int(d) for d in vol._local_dim), vol._pitch)
         for r in range(args.reps):
