@@ -72,6 +72,8 @@ def parse_args():
     ap.add_argument("--no-d2m", action="store_true")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = one base volume per GPU along z (default); strong = the base volume cut in N slabs")
+    ap.add_argument("--no-c5", action="store_true", help="skip the 2048^3 strong-scaling block (c5_strong)")
+    ap.add_argument("--c5-frames", type=int, default=6, help="timed frames of the c5_strong block")
     ap.add_argument("--no-driver", action="store_true", help="skip the hive.fusion.tsdf_fusion driver measurement")
     ap.add_argument("--driver-frames", type=int, default=60)
     return ap.parse_args()
@@ -609,6 +611,70 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
 
 
 # ----------------------------------------------------------------------------------------------------------------------
+def measure_c5_strong(args, frames, world, rank, torch, dist, Vol, peak):
+    """BASELINE config C5 at its named size: ONE 2048^3 volume (103 GB of voxel state), 1920x1080 frames, cut into
+    `world` z-slabs (strong scaling).  With more than one GPU the same frames are afterwards integrated into the whole
+    volume on rank 0 alone, so that the line carries its own single-GPU baseline (`speedup_vs_n1`)."""
+    from hive_b200 import synthetic
+    dim = tuple(synthetic.CONFIGS["C5"]["dim"])
+    sc = _scene("C5", "dense", dim)
+    n_vox = int(np.prod(dim))
+    warm, timed = 2, max(2, args.c5_frames)
+
+    sequence = []
+
+    def run(vol, w, r):
+        dev_frames = vol.upload_frames(frames if r == 0 else None, sc.K)
+        n_f = dev_frames.num_frames
+        del sequence[:]
+        sequence.extend([i % n_f for i in range(warm)] + [(warm + i) % n_f for i in range(timed)])
+        vol.count_updates(False)
+        vol.integrate_batch_device(dev_frames, [i % n_f for i in range(warm)])
+        vol.count_updates(True)
+        vol.reset_update_counter()
+        _barrier(w, dist, torch)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(0, timed, 2):
+            vol.integrate_batch_device(dev_frames, [(warm + i + j) % n_f for j in range(min(2, timed - i))])
+        e1.record()
+        torch.cuda.synchronize()
+        _barrier(w, dist, torch)
+        ms = _max_over_ranks(e0.elapsed_time(e1), w, dist, torch)
+        updates = _sum_over_ranks(vol.num_updated_local(), w, dist, torch)
+        return ms, updates
+
+    vol = Vol(sc.vol_bnds.copy(), sc.voxel_size, world_size=world, rank=rank)
+    ms, updates = run(vol, world, rank)
+    value = n_vox * timed / (ms / 1e3)
+    per_gpu_gbs = (24.0 * updates / world + 8.0 * sc.H * sc.W * timed) / (ms / 1e3) / 1e9
+    res = {"workload": f"C5: {'x'.join(map(str, dim))} TSDF @ {sc.voxel_size * 100:g} cm ({12 * n_vox / 1e9:.0f} GB of voxel state), "
+                       f"{sc.W}x{sc.H} frames, scene=dense, {world} z-slab(s)",
+           "scaling": "strong", "n_gpus": world, "frames_timed": timed, "value": value, "unit": UNIT,
+           "frames_per_s": timed / (ms / 1e3), "ms_per_frame": ms / timed,
+           "updated_fraction": updates / float(n_vox * timed), "achieved_gbs_per_gpu": per_gpu_gbs,
+           "roofline_frac_per_gpu": per_gpu_gbs / peak}
+    if world == 1:
+        res["parity"] = parity_check(vol.local, sc, frames, sequence)  # block-sampled against the oracle, incl. z > 1024
+    del vol
+    torch.cuda.empty_cache()
+    if world > 1:
+        _barrier(world, dist, torch)
+        if rank == 0:
+            from hive_b200.sharded import SlabShardedTSDFVolume
+            one = SlabShardedTSDFVolume(sc.vol_bnds.copy(), sc.voxel_size, world_size=1, rank=0)
+            ms1, _ = run(one, 1, 0)
+            res["n1"] = {"value": n_vox * timed / (ms1 / 1e3), "ms_per_frame": ms1 / timed,
+                         "what": "the same frames into the whole 2048^3 volume on rank 0 alone, same run"}
+            res["speedup_vs_n1"] = res["value"] / res["n1"]["value"]
+            res["parity"] = parity_check(one.local, sc, frames, sequence)
+            del one
+            torch.cuda.empty_cache()
+        _barrier(world, dist, torch)
+    return res
+
+
+# ----------------------------------------------------------------------------------------------------------------------
 def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -622,6 +688,9 @@ def run_ours(args):
     # Host-side synthetic data first (fork pool), CUDA afterwards.  Only rank 0 owns frames; others receive broadcasts.
     scenes = [args.scene] + ([] if args.no_room or args.scene == "room" else ["room"])
     frames = {v: make_frames(base_cfg, v, n_distinct, dim if n_gpus > 1 else None) if rank == 0 else None for v in scenes}
+    do_c5 = not args.no_c5 and base_cfg == "C2" and args.scaling == "weak"  # the default (driver) invocation only
+    from hive_b200 import synthetic as _syn
+    c5_frames = make_frames("C5", "dense", 4, tuple(_syn.CONFIGS["C5"]["dim"])) if do_c5 and rank == 0 else None
 
     import torch
     torch.cuda.set_device(local_rank)
@@ -649,6 +718,11 @@ def run_ours(args):
     d2m_res = None
     if not args.no_d2m:
         d2m_res = measure_d2m(args, base_cfg, world, rank, torch, dist, peak)
+
+    c5_res = None
+    if do_c5:
+        torch.cuda.empty_cache()
+        c5_res = measure_c5_strong(args, c5_frames, world, rank, torch, dist, SlabShardedTSDFVolume, peak)
 
     driver_res = None
     if not args.no_driver and world == 1 and "room" in frames:
@@ -700,6 +774,8 @@ def run_ours(args):
             out["mesh"] = r["mesh"]
     if d2m_res is not None:
         out["depth_to_mesh"] = d2m_res
+    if c5_res is not None:
+        out["c5_strong"] = c5_res
     if driver_res is not None:
         out["driver"] = driver_res
     if not args.no_cpu_baseline and n_gpus == 1:

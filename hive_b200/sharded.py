@@ -122,19 +122,38 @@ class SlabShardedTSDFVolume:
                 self.local.integrate_device(sf.dev, i, obs_weight)
             return
         torch = self._torch
+        dev = self.local.device
         slot = self._step & 1
         self._step += 1
-        buf = self._batch_buffer(slot, len(idx), sf.H, sf.W)
-        if self.rank == 0:
-            torch.index_select(sf.dev.texels, 0, torch.as_tensor(idx, device=buf.device), out=buf)
-        self._dist.broadcast(buf, src=0)  # NCCL over NVLink; stream-ordered after the producers/consumers of `buf`
-        frames = DeviceFrames(buf, [sf.world2cam[i] for i in idx], sf.intr, sf.H, sf.W)
-        for j in range(len(idx)):
-            self.local.integrate_device(frames, j, obs_weight)
-        with torch.cuda.device(self.local.device):
+        idx = [int(i) for i in idx]
+        contiguous = all(b == a + 1 for a, b in zip(idx[:-1], idx[1:]))
+        with torch.cuda.device(dev):
+            compute = torch.cuda.current_stream()
+            copy = self._copy_stream
+            # The broadcast of this batch runs on the side stream, behind the integration that last used the slot (two
+            # batches ago) and therefore next to the integration of the previous batch, which is still on the compute stream.
+            if self._consumed[slot] is not None:
+                copy.wait_event(self._consumed[slot])
+            else:
+                copy.wait_stream(compute)
+            with torch.cuda.stream(copy):
+                if self.rank == 0 and contiguous:
+                    # rank 0 sends straight out of its resident frames and integrates from them: no staging copy
+                    buf = sf.dev.texels[idx[0]:idx[0] + len(idx)]
+                else:
+                    buf = self._batch_buffer(slot, len(idx), sf.H, sf.W)
+                    if self.rank == 0:
+                        torch.index_select(sf.dev.texels, 0, torch.as_tensor(idx, device=buf.device), out=buf)
+                self._dist.broadcast(buf, src=0)  # NCCL over NVLink
+                ready = torch.cuda.Event()
+                ready.record(copy)
+            compute.wait_event(ready)
+            frames = DeviceFrames(buf, [sf.world2cam[i] for i in idx], sf.intr, sf.H, sf.W)
+            for j in range(len(idx)):
+                self.local.integrate_device(frames, j, obs_weight)
             done = torch.cuda.Event()
-            done.record(torch.cuda.current_stream())
-            self._consumed[slot] = done  # the host path's side stream must not refill the slot before this
+            done.record(compute)
+            self._consumed[slot] = done  # the side stream must not refill the slot before this
 
     def integrate_batch_host(self, frames, idx, cam_intr, obs_weight=1.0):
         """End-to-end path: host numpy frames (rank 0) -> H2D -> (broadcast) -> integrate."""
