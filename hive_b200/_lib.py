@@ -45,6 +45,14 @@ SIGNATURES = {
     "hv_mc_extract": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
                       c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "hv_mc_column_counts": [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p, c_int64, c_void_p, c_int64,
+                            c_int64, c_void_p, c_void_p, c_void_p],
+    "hv_mc_shift_scratch_bytes": [c_int64, c_void_p],
+    "hv_mc_column_shifts": [c_void_p, c_int64, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p],
+    "hv_mc_emit_placed": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
+                          c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p,
+                          c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p],
+    "hv_scatter_rows": [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p],
     "hv_d2m_scratch_bytes": [c_int, c_int, c_int, c_void_p],
     "hv_d2m_count": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_int64, c_void_p,
                      c_void_p],

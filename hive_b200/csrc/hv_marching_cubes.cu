@@ -784,6 +784,16 @@ struct McEmit {
     long long cap_verts, cap_tris;   // capacity of the buffers above: anything beyond is counted, not written
     float voxel_size;
     float origin[3];
+    // placement of a z-slab's mesh in the mesh of the whole volume (hv_mc_column_shifts), or null: per column, what to add
+    // to the slab's own vertex / triangle / centre-vertex numbering, and the global index of the first vertex the slab
+    // above owns in that column (the seam vertices a slab's top cubes refer to)
+    const int32_t* vshift;
+    const int32_t* tshift;
+    const int32_t* cshift;
+    const int32_t* vnext;
+    unsigned int n_edge_global;      // edge vertices of the whole volume (centre vertices come after them)
+    int32_t* vert_dst;               // [V] index of every vertex of this slab in the whole mesh
+    int32_t* tri_dst;                // [T] ... of every triangle
 };
 
 __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x, int y, int zb, int axis) {
@@ -1099,6 +1109,9 @@ __device__ __forceinline__ void emit_cubes(const McGrid& g, const McEmit& out, u
         const unsigned long long mult = kMcVarMult[variant];
         const unsigned int centre_index = n_edge + base.z + rec.w;
         const size_t t0 = (size_t)base.y + rec.z;
+        const size_t col = (size_t)x * g.Y + y;
+        unsigned int centre_global = centre_index;
+        if (out.vshift) centre_global = out.n_edge_global + (base.z + rec.w) + (unsigned int)__ldg(out.cshift + col);
         if (out.face_keys) {
             for (int j = 0; j < ntri; ++j) emit_triangle(g, out, x, y, zb, variant, j, t0 + j, centre_index);
         } else {
@@ -1108,12 +1121,31 @@ __device__ __forceinline__ void emit_cubes(const McGrid& g, const McEmit& out, u
                 constexpr unsigned long long P = kEdgeOwnerPacked;
                 const int code = (int)((P >> (5 * e)) & 31ull);
                 vidx[e] = 0u;
-                if ((mult >> (4 * e)) & 15ull)
-                    vidx[e] = edge_vertex_index(g, x + (code & 1), y + ((code >> 1) & 1), zb + ((code >> 2) & 1), code >> 3);
+                if ((mult >> (4 * e)) & 15ull) {
+                    const int xo = x + (code & 1), yo = y + ((code >> 1) & 1), zo = zb + ((code >> 2) & 1), axis = code >> 3;
+                    if (!out.vshift) {
+                        vidx[e] = edge_vertex_index(g, xo, yo, zo, axis);
+                    } else {
+                        const size_t ocol = (size_t)xo * g.Y + yo;
+                        if (zo < g.own_hi) {
+                            vidx[e] = edge_vertex_index(g, xo, yo, zo, axis) + (unsigned int)__ldg(out.vshift + ocol);
+                        } else {
+                            // a seam vertex: on an axis-0 / axis-1 edge of the first voxel the slab above owns in this
+                            // column, i.e. that slab's first (axis 0) or first / second (axis 1) vertex of the column
+                            unsigned int r = (unsigned int)__ldg(out.vnext + ocol);
+                            if (axis == 1 && xo + 1 < g.X) {
+                                const unsigned int b0 = __ldg(g.bits + ocol * g.G + (zo >> 5)) >> (zo & 31);
+                                const unsigned int b1 = __ldg(g.bits + (ocol + g.Y) * g.G + (zo >> 5)) >> (zo & 31);
+                                r += (b0 ^ b1) & 1u;
+                            }
+                            vidx[e] = r;
+                        }
+                    }
+                }
             }
 #pragma unroll
             for (int e = 0; e < 12; ++e) s_vidx[e][threadIdx.x] = vidx[e];
-            s_vidx[12][threadIdx.x] = centre_index;
+            s_vidx[12][threadIdx.x] = centre_global;
             const uint8_t* tri = kMcTris + 3 * (size_t)kMcVarTriOff[variant];
             for (int j = 0; j < ntri; ++j) {
                 const size_t ti = t0 + j;
@@ -1123,9 +1155,13 @@ __device__ __forceinline__ void emit_cubes(const McGrid& g, const McEmit& out, u
                 out.faces[3 * ti] = (int32_t)a;
                 out.faces[3 * ti + 1] = (int32_t)b;
                 out.faces[3 * ti + 2] = (int32_t)c;
+                if (out.tri_dst) out.tri_dst[ti] = (int32_t)(ti + (size_t)__ldg(out.tshift + col));
             }
         }
-        if (((mult >> 48) & 15ull) && (long long)centre_index < out.cap_verts) emit_centre_vertex(g, out, x, y, zb, centre_index);
+        if (((mult >> 48) & 15ull) && (long long)centre_index < out.cap_verts) {
+            emit_centre_vertex(g, out, x, y, zb, centre_index);
+            if (out.vert_dst) out.vert_dst[centre_index] = (int32_t)centre_global;
+        }
     }
 }
 
@@ -1142,7 +1178,10 @@ __device__ __forceinline__ void emit_vertices(const McGrid& g, const McEmit& out
         const size_t tile = gid / kTileGroups;
         const size_t vi = (size_t)__ldg(&g.tile_base[tile].x) + __ldg(&g.batch_base[tile * kTileBatches + (unsigned int)((rec >> 50) & 31ull)].x) +
                           (unsigned int)((rec >> 38) & 4095ull);
-        if ((long long)vi < out.cap_verts) emit_edge_vertex<WHOLE, LEVEL0>(g, out, x, y, gq * 32 + k, axis, vi);
+        if ((long long)vi < out.cap_verts) {
+            emit_edge_vertex<WHOLE, LEVEL0>(g, out, x, y, gq * 32 + k, axis, vi);
+            if (out.vert_dst) out.vert_dst[vi] = (int32_t)(vi + (size_t)__ldg(out.vshift + (size_t)x * g.Y + y));
+        }
     }
 }
 
@@ -1159,6 +1198,86 @@ __global__ void __launch_bounds__(kEmitThreads, (WHOLE && LEVEL0) ? 4 : 3)
     const unsigned int t_before = (unsigned int)(b * n_tri_blocks / n), t_after = (unsigned int)((b + 1) * n_tri_blocks / n);
     if (t_after > t_before) emit_cubes(g, out, t_before, n_tri_blocks);
     else emit_vertices<WHOLE, LEVEL0>(g, out, (unsigned int)b - t_before, n_vert_blocks);
+}
+
+// ---- z-slab placement (hive_b200/sharded.py): where does a slab's mesh go in the mesh of the whole volume? --------------------
+// The whole-volume order is column-major, so the slabs interleave column by column: every slab counts its edge vertices,
+// triangles and centre vertices per column (from its work records), the counts of all slabs are all-gathered, and every
+// slab derives its per-column shifts itself.  Nothing is sorted and nothing is searched.
+__global__ void __launch_bounds__(256) mc_column_counts_kernel(const __grid_constant__ McGrid g, int32_t* __restrict__ counts,
+                                                                const long long XY) {
+    if (g.totals[6]) return;
+    const unsigned int n_edge = (unsigned int)g.totals[4], n_cubes = (unsigned int)g.totals[5];
+    const unsigned int n = n_edge > n_cubes ? n_edge : n_cubes;
+    for (unsigned int i = blockIdx.x * 256u + threadIdx.x; i < n; i += gridDim.x * 256u) {
+        if (i < n_edge) {
+            const unsigned int gid = (unsigned int)(__ldg(g.vert_rec + i) & 0x7fffffffull);
+            atomicAdd(counts + gid / (unsigned int)g.G, 1);
+        }
+        if (i < n_cubes) {
+            const uint4 rec = __ldg(g.cube_rec + i);
+            const int variant = (int)((rec.y >> 5) & 2047u);
+            const unsigned int col = rec.x / (unsigned int)g.G;
+            atomicAdd(counts + XY + col, (int)kMcVarNtri[variant]);
+            if ((kMcVarMult[variant] >> 48) & 15ull) atomicAdd(counts + 2 * XY + col, 1);
+        }
+    }
+}
+
+// all[w * slab_stride + k * XY + c]: count k (0 edge vertices, 1 triangles, 2 centre vertices) of slab w in column c
+__global__ void __launch_bounds__(256) mc_shift_prepare_kernel(const int32_t* __restrict__ all, const long long slab_stride,
+                                                                const int W, const int rank,
+                                                                const long long XY, uint2* __restrict__ pa, uint2* __restrict__ pb,
+                                                                uint2* __restrict__ pc, int32_t* __restrict__ below) {
+    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (c >= XY) return;
+    unsigned int tot[3] = {0u, 0u, 0u}, low[3] = {0u, 0u, 0u}, own[3] = {0u, 0u, 0u};
+    for (int w = 0; w < W; ++w)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const unsigned int v = (unsigned int)__ldg(all + (long long)w * slab_stride + k * XY + c);
+            tot[k] += v;
+            if (w < rank) low[k] += v;
+            if (w == rank) own[k] = v;
+        }
+    pa[c] = make_uint2(tot[0], tot[1]);
+    pb[c] = make_uint2(tot[2], own[0]);
+    pc[c] = make_uint2(own[1], own[2]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) below[k * XY + c] = (int32_t)low[k];
+    below[3 * XY + c] = (int32_t)own[0];
+}
+
+// sa / sb / sc: exclusive scans of pa / pb / pc.  shifts[0..3][c] = vshift, tshift, cshift, vnext (holds `below` on entry).
+__global__ void __launch_bounds__(256) mc_shift_finish_kernel(const uint2* __restrict__ sa, const uint2* __restrict__ sb,
+                                                               const uint2* __restrict__ sc, const long long XY,
+                                                               int32_t* __restrict__ shifts) {
+    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (c >= XY) return;
+    const uint2 a = sa[c], b = sb[c], cc = sc[c];
+    const unsigned int low_v = (unsigned int)shifts[c], low_t = (unsigned int)shifts[XY + c], low_c = (unsigned int)shifts[2 * XY + c];
+    const unsigned int own_v = (unsigned int)shifts[3 * XY + c];
+    shifts[c] = (int32_t)(a.x + low_v - b.y);            // global start of my vertices in the column - my own start
+    shifts[XY + c] = (int32_t)(a.y + low_t - cc.x);
+    shifts[2 * XY + c] = (int32_t)(b.x + low_c - cc.y);
+    shifts[3 * XY + c] = (int32_t)(a.x + low_v + own_v);  // first vertex of the slab above in this column
+}
+
+// dst[index[i]] = src[i] for rows of `words` 32-bit words (or of 3 bytes when words == 0)
+__global__ void __launch_bounds__(256) scatter_rows_kernel(const void* __restrict__ src, const int32_t* __restrict__ index,
+                                                            const long long n, const int words, void* __restrict__ dst) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (words > 0) {
+        const long long row = i / words;
+        const int k = (int)(i - row * words);
+        if (row < n) static_cast<unsigned int*>(dst)[(long long)index[row] * words + k] = static_cast<const unsigned int*>(src)[i];
+    } else if (i < n) {
+        const unsigned char* s3 = static_cast<const unsigned char*>(src) + 3 * i;
+        unsigned char* d3 = static_cast<unsigned char*>(dst) + 3 * (long long)index[i];
+        d3[0] = s3[0];
+        d3[1] = s3[1];
+        d3[2] = s3[2];
+    }
 }
 
 }  // namespace hv
@@ -1359,14 +1478,23 @@ extern "C" int hv_mc_count(const float* tsdf, const float* halo_lo, const float*
     return HV_OK;
 }
 
-extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
-                          const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
-                          double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
-                          int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
-                          const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world, float* verts_voxel,
-                          float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
-                          unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals,
-                          void* stream) {
+namespace {
+struct Placement {
+    const int32_t* col_shifts;  // [4][X*Y] from hv_mc_column_shifts
+    int64_t n_edge_global;
+    int32_t* vert_dst;
+    int32_t* tri_dst;
+};
+}  // namespace
+
+static int mc_emit_impl(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                        const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                        double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+                        int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
+                        const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world, float* verts_voxel,
+                        float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
+                        unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals,
+                        const Placement* place, void* stream) {
     hv::McGrid g;
     McLayout L;
     int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, work, rec_verts, rec_cubes, &L);
@@ -1377,7 +1505,10 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     HV_REQUIRE((faces != nullptr) != (face_keys != nullptr), "hv_mc_emit: pass exactly one of faces / face_keys");
     HV_REQUIRE((halo_lo != nullptr) == (color_halo_lo != nullptr) && (halo_hi != nullptr) == (color_halo_hi != nullptr),
                "hv_mc_emit: tsdf and colour halos must come in pairs");
-    HV_REQUIRE(faces == nullptr || (!halo_lo && !halo_hi), "hv_mc_emit: a shard with halos must emit face_keys");
+    HV_REQUIRE(faces == nullptr || place != nullptr || (!halo_lo && !halo_hi),
+               "hv_mc_emit: a shard with halos must emit face_keys (or be placed: hv_mc_emit_placed)");
+    HV_REQUIRE(place == nullptr || (faces && place->col_shifts && place->vert_dst && place->tri_dst && place->n_edge_global >= 0 &&
+                                    place->n_edge_global < (1ll << 31)), "hv_mc_emit_placed: bad placement");
     HV_REQUIRE(z_global_dim >= z_global_offset + g.Z, "hv_mc_emit: slab exceeds the global z extent");
     g.color = color;
     g.chalo_lo = color_halo_lo;
@@ -1399,6 +1530,19 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
     em.cap_tris = n_tris;
     em.voxel_size = voxel_size;
     for (int k = 0; k < 3; ++k) em.origin[k] = h_origin[k];
+    em.vshift = em.tshift = em.cshift = em.vnext = nullptr;
+    em.n_edge_global = 0u;
+    em.vert_dst = em.tri_dst = nullptr;
+    if (place) {
+        const long long XY = (long long)g.X * g.Y;
+        em.vshift = place->col_shifts;
+        em.tshift = place->col_shifts + XY;
+        em.cshift = place->col_shifts + 2 * XY;
+        em.vnext = place->col_shifts + 3 * XY;
+        em.n_edge_global = (unsigned int)place->n_edge_global;
+        em.vert_dst = place->vert_dst;
+        em.tri_dst = place->tri_dst;
+    }
     const int sms = hv::device_info().sm_count;
     // one thread per record that can exist: a surface cube has a triangle, an edge vertex is a vertex
     const long long max_cubes = rec_cubes < n_tris ? rec_cubes : n_tris, max_verts = rec_verts < n_verts ? rec_verts : n_verts;
@@ -1424,6 +1568,114 @@ extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* 
         else if (level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
         else HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
     }
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                          const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                          double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+                          int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
+                          const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world, float* verts_voxel,
+                          float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
+                          unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals,
+                          void* stream) {
+    return mc_emit_impl(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch, scratch_bytes,
+                        work, rec_verts, rec_cubes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris,
+                        verts_world, verts_voxel, normals, colors, faces, face_keys, face_cubes, vert_keys, totals, nullptr, stream);
+}
+
+extern "C" int hv_mc_emit_placed(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                                 const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                                 double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+                                 int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
+                                 const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world, float* normals,
+                                 uint8_t* colors, int32_t* faces, const int32_t* col_shifts, int64_t n_edge_global,
+                                 int32_t* vert_dst, int32_t* tri_dst, unsigned long long* totals, void* stream) {
+    Placement pl = {col_shifts, n_edge_global, vert_dst, tri_dst};
+    return mc_emit_impl(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch, scratch_bytes,
+                        work, rec_verts, rec_cubes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris,
+                        verts_world, nullptr, normals, colors, faces, nullptr, nullptr, nullptr, totals, &pl, stream);
+}
+
+extern "C" int hv_mc_column_counts(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims,
+                                   int64_t pitch, double level, void* scratch, int64_t scratch_bytes, void* work,
+                                   int64_t rec_verts, int64_t rec_cubes, unsigned long long* totals, int32_t* counts,
+                                   void* stream) {
+    hv::McGrid g;
+    McLayout L;
+    int rc = mc_grid(&g, tsdf, halo_lo, halo_hi, h_dims, pitch, level, scratch, scratch_bytes, work, rec_verts, rec_cubes, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE(totals && counts, "hv_mc_column_counts: null pointer");
+    g.totals = totals;
+    cudaStream_t st = hv::as_stream(stream);
+    const long long XY = (long long)g.X * g.Y;
+    HV_CUDA(cudaMemsetAsync(counts, 0, (size_t)3 * XY * sizeof(int32_t), st));
+    const long long n = rec_verts > rec_cubes ? rec_verts : rec_cubes;
+    if (n > 0) {
+        const long long want = (n + 255) / 256, cap = (long long)hv::device_info().sm_count * 16;
+        hv::mc_column_counts_kernel<<<(unsigned int)(want < cap ? want : cap), 256, 0, st>>>(g, counts, XY);
+    }
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+namespace {
+struct ShiftLayout {
+    size_t off_pairs[6], off_bsum, total;
+};
+void shift_layout(int64_t XY, ShiftLayout* L) {
+    size_t o = 0;
+    for (int i = 0; i < 6; ++i) {
+        L->off_pairs[i] = o;
+        o = align_up(o + (size_t)XY * sizeof(uint2));
+    }
+    L->off_bsum = o;
+    o = align_up(o + (size_t)hv::scan_scratch_pairs(XY) * sizeof(uint2));
+    L->total = o;
+}
+}  // namespace
+
+extern "C" int hv_mc_shift_scratch_bytes(int64_t n_columns, int64_t* h_bytes) {
+    HV_REQUIRE(h_bytes && n_columns > 0 && n_columns < (1ll << 31), "hv_mc_shift_scratch_bytes: bad arguments");
+    ShiftLayout L;
+    shift_layout(n_columns, &L);
+    *h_bytes = (int64_t)L.total;
+    return HV_OK;
+}
+
+extern "C" int hv_mc_column_shifts(const int32_t* all_counts, int64_t slab_stride, int world_size, int rank, int64_t n_columns, int32_t* shifts,
+                                   unsigned long long* g_totals, void* scratch, int64_t scratch_bytes, void* stream) {
+    HV_REQUIRE(all_counts && shifts && g_totals && scratch && world_size >= 1 && rank >= 0 && rank < world_size &&
+                   n_columns > 0 && n_columns < (1ll << 31) && slab_stride >= 3 * n_columns && ((uintptr_t)scratch & 255) == 0,
+               "hv_mc_column_shifts: bad arguments");
+    ShiftLayout L;
+    shift_layout(n_columns, &L);
+    HV_REQUIRE((size_t)scratch_bytes >= L.total, "hv_mc_column_shifts: scratch of %lld bytes, need %lld", (long long)scratch_bytes,
+               (long long)L.total);
+    char* s = static_cast<char*>(scratch);
+    uint2* p[6];
+    for (int i = 0; i < 6; ++i) p[i] = reinterpret_cast<uint2*>(s + L.off_pairs[i]);
+    uint2* bsum = reinterpret_cast<uint2*>(s + L.off_bsum);
+    cudaStream_t st = hv::as_stream(stream);
+    const unsigned int blocks = (unsigned int)((n_columns + 255) / 256);
+    hv::mc_shift_prepare_kernel<<<blocks, 256, 0, st>>>(all_counts, slab_stride, world_size, rank, n_columns, p[0], p[1], p[2], shifts);
+    // g_totals: [0] edge vertices, [1] triangles, [2] centre vertices of the whole volume ([3] scratch)
+    hv::exclusive_scan_u2(p[0], p[3], bsum, n_columns, g_totals, st);
+    hv::exclusive_scan_u2(p[1], p[4], bsum, n_columns, g_totals + 2, st);
+    hv::exclusive_scan_u2(p[2], p[5], bsum, n_columns, nullptr, st);
+    hv::mc_shift_finish_kernel<<<blocks, 256, 0, st>>>(p[3], p[4], p[5], n_columns, shifts);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+extern "C" int hv_scatter_rows(const void* src, const int32_t* index, int64_t n, int row_bytes, void* dst, void* stream) {
+    HV_REQUIRE(n >= 0 && (row_bytes == 3 || (row_bytes > 0 && row_bytes % 4 == 0)), "hv_scatter_rows: rows of 3 or 4k bytes");
+    if (n == 0) return HV_OK;
+    HV_REQUIRE(src && index && dst, "hv_scatter_rows: null pointer");
+    const int words = row_bytes == 3 ? 0 : row_bytes / 4;
+    const long long threads = words ? n * words : n;
+    hv::scatter_rows_kernel<<<(unsigned int)((threads + 255) / 256), 256, 0, hv::as_stream(stream)>>>(src, index, n, words, dst);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

@@ -176,6 +176,84 @@ class McPlan:
                           vert_keys[:n_verts] if keys else None, 0.0, 0.0)
 
 
+    # ------------------------------------------------------------------ z-slab placement (hive_b200/sharded.py)
+    def ensure_records(self, n_verts, n_tris):
+        """Make the work records of the last count complete (count again, exactly sized, if they did not fit)."""
+        if self._records_incomplete:
+            self.count(n_verts, n_tris)
+            self._records_incomplete = False
+
+    #: words appended to a slab's column counts in the all-gather: min key, max key, vertices, triangles, edge vertices
+    SLAB_TAIL = 5
+
+    def column_counts(self):
+        """int32 (3 * X*Y + SLAB_TAIL,) device tensor: edge vertices / triangles / centre vertices this slab owns per
+        column, then the slab's totals (everything the other slabs and rank 0 need to know about it -- one all-gather)."""
+        torch = self._torch
+        X, Y = int(self.dims[0]), int(self.dims[1])
+        with torch.cuda.device(self.device):
+            counts = torch.empty((3 * X * Y + self.SLAB_TAIL,), dtype=torch.int32, device=self.device)
+            counts[3 * X * Y:] = self.totals.view(torch.int32)[self._tail_words(torch)]  # low words of totals[2, 3, 0, 1, 4]
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_column_counts(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.work_ptr, self.rec_verts, self.rec_cubes, _ptr(self.totals), _ptr(counts), stream))
+        return counts
+
+    def _tail_words(self, torch):
+        idx = getattr(self, "_tail_idx", None)
+        if idx is None:
+            idx = self._tail_idx = torch.tensor([4, 6, 0, 2, 8], dtype=torch.int64, device=self.device)
+        return idx
+
+    def column_shifts(self, all_counts, rank):
+        """``all_counts``: int32 (world, 3 * X*Y + SLAB_TAIL), ``column_counts()`` of every slab.  Returns (shifts int32
+        (4, X*Y), totals of the whole volume int64 (4,): edge vertices, triangles, centre vertices) -- device tensors, no
+        sync."""
+        torch = self._torch
+        world, stride = (int(v) for v in all_counts.shape)
+        n_cols = (stride - self.SLAB_TAIL) // 3
+        nbytes = ctypes.c_int64(0)
+        _lib.check(self._lib.hv_mc_shift_scratch_bytes(n_cols, ctypes.byref(nbytes)))
+        with torch.cuda.device(self.device):
+            scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=self.device)
+            sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
+            shifts = torch.empty((4, n_cols), dtype=torch.int32, device=self.device)
+            g_totals = torch.zeros(4, dtype=torch.int64, device=self.device)
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_column_shifts(_ptr(all_counts.contiguous()), stride, world, int(rank), n_cols, _ptr(shifts),
+                                                     _ptr(g_totals), sptr, int(nbytes.value), stream))
+            scratch.record_stream(torch.cuda.current_stream())
+        return shifts, g_totals
+
+    def emit_placed(self, n_verts, n_tris, voxel_size, origin, shifts, n_edge_global):
+        """The slab's mesh with faces as indices into the mesh of the WHOLE volume; returns a dict of device tensors:
+        verts, normals, colors, faces, vert_dst (where each vertex goes in the whole mesh), tri_dst."""
+        torch = self._torch
+        dev = self.device
+        origin = np.ascontiguousarray(origin, dtype=np.float32)
+        self.ensure_records(n_verts, n_tris)
+        with torch.cuda.device(dev):
+            out = {"verts": torch.empty((n_verts, 3), dtype=torch.float32, device=dev),
+                   "normals": torch.empty((n_verts, 3), dtype=torch.float32, device=dev),
+                   "colors": torch.empty((n_verts, 3), dtype=torch.uint8, device=dev),
+                   "faces": torch.empty((n_tris, 3), dtype=torch.int32, device=dev),
+                   "vert_dst": torch.empty((n_verts,), dtype=torch.int32, device=dev),
+                   "tri_dst": torch.empty((n_tris,), dtype=torch.int32, device=dev)}
+            if n_verts == 0 and n_tris == 0:
+                return out
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_emit_placed(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
+                _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.work_ptr, self.rec_verts, self.rec_cubes, self.z_global_offset, self.z_global_dim,
+                ctypes.c_float(np.float32(voxel_size)), origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris,
+                _ptr(out["verts"]), _ptr(out["normals"]), _ptr(out["colors"]), _ptr(out["faces"]), _ptr(shifts),
+                int(n_edge_global), _ptr(out["vert_dst"]), _ptr(out["tri_dst"]), _ptr(self.totals), stream))
+        return out
+
     def extract(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
         """count + emit in one library call (``hv_mc_extract``) into buffers of the given capacity; falls back to an
         exactly sized ``emit`` when the surface turns out larger.  Whole volumes only (faces as indices)."""
@@ -263,6 +341,21 @@ class McPlan:
         mesh.vmin, mesh.vmax = vmin, vmax
         self.done_event = done
         return mesh
+
+
+def scatter_rows(src, index, dst):
+    """``dst[index[i]] = src[i]`` on the device (rows of 3 bytes or a multiple of 4): assembles a whole-volume mesh from slab
+    meshes whose rows know where they go (``McPlan.emit_placed``)."""
+    torch = _lib.require_cuda()
+    n = int(src.shape[0])
+    if n == 0:
+        return
+    row_bytes = src.element_size() * (int(src.numel()) // n)
+    src = src.contiguous()
+    assert dst.is_contiguous() and index.dtype == torch.int32 and index.is_contiguous()
+    with torch.cuda.device(src.device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _lib.check(_lib.load().hv_scatter_rows(_ptr(src), _ptr(index), n, row_bytes, _ptr(dst), stream))
 
 
 def check_surface(level, vmin, vmax, n_verts):

@@ -240,14 +240,17 @@ class SlabShardedTSDFVolume:
         """``TSDFVolume.get_mesh`` of the global volume on rank 0 (``None`` x4 elsewhere).
 
         Each slab owns the cubes whose base voxel it holds; the planes either side of a seam are exchanged once
-        (one tsdf + one colour plane per direction), every rank emits its vertices with global edge keys and its faces
-        as key triples, and rank 0 resolves keys to indices.  The result is identical -- vertex and face order
-        included -- to the mesh of the unsharded volume.
+        (one tsdf + one colour plane per direction).  The whole-volume mesh is ordered column by column, so the slabs
+        interleave: every slab counts what it owns per column, the counts are all-gathered, and every slab works out by
+        itself where its vertices and triangles go in the whole mesh and writes its faces with whole-mesh indices (seam
+        vertices, owned by the slab above, included).  Rank 0 receives the slab meshes in one grouped exchange and drops
+        every row into place.  The result is identical -- vertex and face order included -- to the mesh of the
+        unsharded volume; nothing is sorted or searched.
         """
         from . import marching_cubes as mc
         if self.world_size == 1:
             return self.local.get_mesh()
-        dist, loc = self._dist, self.local
+        dist, loc, torch = self._dist, self.local, self._torch
         z0, z1 = self.ranges[self.rank]
         Zg = self.global_dim[2]
         first_t, last_t, first_c, last_c = self._boundary_planes()
@@ -257,19 +260,21 @@ class SlabShardedTSDFVolume:
         plan = mc.McPlan(loc._tsdf_vol_gpu, loc._color_vol_gpu, (X, Y, Z), loc._pitch, halo=halo, z_global_offset=z0,
                          z_global_dim=Zg)
         plan.count()
-        n_verts, n_tris, vmin, vmax = plan.read_totals()
-        stats = self._torch.tensor([float(n_verts), -vmin, vmax], dtype=self._torch.float64, device=loc.device)
-        counts = stats[:1].clone()
-        dist.all_reduce(counts, op=dist.ReduceOp.SUM)
-        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
-        mc.check_surface(0.0, -float(stats[1].item()), float(stats[2].item()), int(counts[0].item()))
-        mesh = plan.emit(n_verts, n_tris, loc._voxel_size, loc._vol_origin, keys=True)
-        part = {"verts": mesh.verts, "normals": mesh.normals, "colors": mesh.colors, "vert_keys": mesh.vert_keys,
-                "face_keys": mesh.face_keys, "face_cubes": mesh.face_cubes}
-        parts = gather_mesh_parts(dist, self.rank, self.world_size, part, loc.device)
+        n_verts, n_tris, _, _ = plan.read_totals()
+        plan.ensure_records(n_verts, n_tris)
+        # ONE collective tells every slab everything about every other: per-column counts + (min, max, sizes)
+        all_counts = exchange_column_counts(dist, self.world_size, plan.column_counts())
+        shifts, _ = plan.column_shifts(all_counts, self.rank)
+        tails = all_counts[:, -plan.SLAB_TAIL:].cpu().numpy()  # (world, 5): min key, max key, vertices, triangles, edge vertices
+        vmin = min(mc._key_to_float(int(k)) for k in tails[:, 0])
+        vmax = max(mc._key_to_float(int(k)) for k in tails[:, 1])
+        n_verts_g, n_tris_g, n_edge_g = (int(v) for v in tails[:, 2:5].sum(axis=0))
+        mc.check_surface(0.0, vmin, vmax, n_verts_g)
+        part = plan.emit_placed(n_verts, n_tris, loc._voxel_size, loc._vol_origin, shifts, n_edge_g)
+        parts = gather_placed_parts(dist, self.rank, self.world_size, part, loc.device, tails[:, 2:4])
         if self.rank != 0:
             return None, None, None, None
-        verts, faces, normals, colors = stitch_mesh_parts(parts)
+        verts, faces, normals, colors = place_mesh_parts(parts, n_verts_g, n_tris_g, mc.scatter_rows)
         return _xfer.to_host(verts, faces, normals, colors)
 
 
@@ -293,54 +298,59 @@ def exchange_halo_planes(dist, rank, world_size, planes):
     return out
 
 
-_PART_FIELDS = (("verts", 3, "float32"), ("normals", 3, "float32"), ("colors", 3, "uint8"), ("vert_keys", 0, "int64"),
-                ("face_keys", 3, "int64"), ("face_cubes", 0, "int64"))
+_PART_FIELDS = (("verts", 3, "float32"), ("normals", 3, "float32"), ("colors", 3, "uint8"), ("vert_dst", 0, "int32"),
+                ("faces", 3, "int32"), ("tri_dst", 0, "int32"))
 
 
-def gather_mesh_parts(dist, rank, world_size, part, device):
-    """Variable-length gather of the per-slab mesh parts to rank 0 (sizes by all_gather, payload by send/recv)."""
+def exchange_column_counts(dist, world_size, counts):
+    """All-gather of ``McPlan.column_counts()`` (per-column counts + the slab's totals) -> (world_size, ...)."""
     import torch
-    sizes = torch.tensor([part["vert_keys"].shape[0], part["face_cubes"].shape[0]], dtype=torch.int64, device=device)
-    all_sizes = [torch.zeros_like(sizes) for _ in range(world_size)]
-    dist.all_gather(all_sizes, sizes)
+    out = torch.empty((world_size,) + tuple(counts.shape), dtype=counts.dtype, device=counts.device)
+    dist.all_gather(list(out.unbind(0)), counts.contiguous())  # (views of one buffer: NCCL gathers in place)
+    return out
+
+
+def gather_placed_parts(dist, rank, world_size, part, device, all_sizes):
+    """Variable-length gather of the per-slab meshes to rank 0 -- ``all_sizes[w]`` = (vertices, triangles) of slab w, known
+    to everyone from the column-count exchange -- every array of every slab in ONE grouped exchange (rank 0 posts all
+    receives at once; nothing waits for anything else)."""
+    import torch
+    ops, parts = [], None
     if rank != 0:
         for name, _, _ in _PART_FIELDS:
             if part[name].numel():
-                dist.send(part[name].contiguous(), dst=0)
-        return None
-    parts = [part]
-    for src in range(1, world_size):
-        nv, nf = (int(v) for v in all_sizes[src].tolist())
-        got = {}
-        for name, cols, dtype in _PART_FIELDS:
-            n = nf if name.startswith("face") else nv
-            shape = (n, cols) if cols else (n,)
-            got[name] = torch.empty(shape, dtype=getattr(torch, dtype), device=device)
-            if got[name].numel():
-                dist.recv(got[name], src=src)
-        parts.append(got)
+                ops.append(dist.P2POp(dist.isend, part[name].contiguous(), 0))
+    else:
+        parts = [part]
+        for src in range(1, world_size):
+            nv, nf = (int(v) for v in all_sizes[src])
+            got = {}
+            for name, cols, dtype in _PART_FIELDS:
+                n = nf if name in ("faces", "tri_dst") else nv
+                got[name] = torch.empty((n, cols) if cols else (n,), dtype=getattr(torch, dtype), device=device)
+                if got[name].numel():
+                    ops.append(dist.P2POp(dist.irecv, got[name], src))
+            parts.append(got)
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
     return parts
 
 
-def stitch_mesh_parts(parts):
-    """Resolve the per-slab meshes into one: vertices sorted by global edge key (the whole-volume vertex order), faces
-    sorted by the cube that produced them (stable: the in-cube triangle order is kept), face keys -> vertex indices."""
+def place_mesh_parts(parts, n_verts, n_tris, scatter_rows):
+    """Rank 0: every row of every slab mesh goes where its slab said it goes (``vert_dst`` / ``tri_dst``).
+    ``scatter_rows(src, index, dst)`` is ``hive_b200.marching_cubes.scatter_rows`` (the CPU tests pass a numpy stand-in)."""
     import torch
-    keys = torch.cat([p["vert_keys"] for p in parts])
-    # whole-volume vertex order: lattice-edge vertices by key, then the vertices inside cubes (axis 3) by cube
-    keys = keys + ((keys & 3) == 3).to(keys.dtype) * (1 << 62)
-    order = torch.argsort(keys, stable=True)
-    sorted_keys = keys[order]
-    assert bool((sorted_keys[1:] != sorted_keys[:-1]).all()), "a seam vertex was emitted by two slabs"
-    verts = torch.cat([p["verts"] for p in parts])[order]
-    normals = torch.cat([p["normals"] for p in parts])[order]
-    colors = torch.cat([p["colors"] for p in parts])[order]
-    face_keys = torch.cat([p["face_keys"] for p in parts])
-    face_cubes = torch.cat([p["face_cubes"] for p in parts])
-    forder = torch.argsort(face_cubes, stable=True)
-    face_keys = face_keys[forder]
-    face_keys = face_keys + ((face_keys & 3) == 3).to(face_keys.dtype) * (1 << 62)
-    idx = torch.searchsorted(sorted_keys, face_keys.reshape(-1))
-    assert bool((sorted_keys[idx.clamp(max=sorted_keys.numel() - 1)] == face_keys.reshape(-1)).all()), \
-        "a face references a vertex no slab emitted"
-    return verts, idx.reshape(-1, 3).to(torch.int32), normals, colors
+    dev = parts[0]["verts"].device
+    verts = torch.empty((n_verts, 3), dtype=torch.float32, device=dev)
+    normals = torch.empty((n_verts, 3), dtype=torch.float32, device=dev)
+    colors = torch.empty((n_verts, 3), dtype=torch.uint8, device=dev)
+    faces = torch.empty((n_tris, 3), dtype=torch.int32, device=dev)
+    assert sum(int(p["vert_dst"].shape[0]) for p in parts) == n_verts, "the slabs' vertices do not add up to the whole mesh"
+    assert sum(int(p["tri_dst"].shape[0]) for p in parts) == n_tris, "the slabs' triangles do not add up to the whole mesh"
+    for p in parts:
+        scatter_rows(p["verts"], p["vert_dst"], verts)
+        scatter_rows(p["normals"], p["vert_dst"], normals)
+        scatter_rows(p["colors"], p["vert_dst"], colors)
+        scatter_rows(p["faces"], p["tri_dst"], faces)
+    return verts, faces, normals, colors

@@ -142,6 +142,33 @@ int hv_mc_emit(const float* tsdf, const float* halo_lo, const float* halo_hi, co
                float* verts_voxel, float* normals, uint8_t* colors, int32_t* faces, unsigned long long* face_keys,
                unsigned long long* face_cubes, unsigned long long* vert_keys, unsigned long long* totals, void* stream);
 
+/* ---- z-slab shards: placing a slab's mesh in the mesh of the whole volume (hive_b200/sharded.py; nothing in the reference:
+ * SURVEY.md 8(e)).  The whole-volume order is column-major, so the slabs interleave column by column.
+ *   hv_mc_column_counts  after hv_mc_count: counts[k][c] (DEVICE int32 [3][X*Y]) = edge vertices (k = 0), triangles (1), centre
+ *                        vertices (2) this slab owns in column c = x*Y + y.
+ *   hv_mc_column_shifts  all_counts (DEVICE int32, slab w's [3][X*Y] counts at w * slab_stride: the all-gathered counts, a
+ *                        few words of other per-slab data may follow each) -> shifts (DEVICE int32
+ *                        [4][X*Y]: what to add per column to the slab's own vertex / triangle / centre-vertex numbering, and
+ *                        the global index of the first vertex of the slab above in the column) and g_totals (DEVICE
+ *                        4 x uint64: [0] edge vertices, [1] triangles, [2] centre vertices of the whole volume).
+ *   hv_mc_emit_placed    hv_mc_emit for a slab (halo planes allowed) with faces as indices into the WHOLE mesh; vert_dst [V]
+ *                        / tri_dst [T] receive the index of every vertex / triangle of the slab in the whole mesh.
+ *   hv_scatter_rows      dst[index[i]] = src[i] for rows of row_bytes = 3 or a multiple of 4 (assembling the whole mesh). */
+int hv_mc_column_counts(const float* tsdf, const float* halo_lo, const float* halo_hi, const int64_t* h_dims, int64_t pitch,
+                        double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,
+                        unsigned long long* totals, int32_t* counts, void* stream);
+int hv_mc_shift_scratch_bytes(int64_t n_columns, int64_t* h_bytes);
+int hv_mc_column_shifts(const int32_t* all_counts, int64_t slab_stride, int world_size, int rank, int64_t n_columns, int32_t* shifts,
+                        unsigned long long* g_totals, void* scratch, int64_t scratch_bytes, void* stream);
+int hv_mc_emit_placed(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                      const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                      double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,
+                      int64_t z_global_offset, int64_t z_global_dim, float voxel_size, const float* h_origin, int64_t n_verts,
+                      int64_t n_tris, float* verts_world, float* normals, uint8_t* colors, int32_t* faces,
+                      const int32_t* col_shifts, int64_t n_edge_global, int32_t* vert_dst, int32_t* tri_dst,
+                      unsigned long long* totals, void* stream);
+int hv_scatter_rows(const void* src, const int32_t* index, int64_t n, int row_bytes, void* dst, void* stream);
+
 /* hv_mc_count + hv_mc_emit in one call with caller-provided capacity (cap_verts vertices, cap_tris triangles in every
  * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 8 x uint64, pinned memory
  * recommended; same meaning as `totals`).  Returns HV_E_LEVEL_RANGE / HV_E_NOSURFACE like skimage would raise

@@ -152,7 +152,8 @@ def test_get_mesh_on_untouched_volume_raises_value_error():
 
 @pytest.mark.parametrize("n_slabs", [2, 3])
 def test_slab_halo_stitch_equals_whole_volume(n_slabs):
-    """z-slab shards emulated on one GPU: per-slab extraction with halo planes + key stitch == whole-volume mesh."""
+    """z-slab shards emulated on one GPU: per-slab extraction with halo planes, placed by the per-column counts of all
+    slabs == whole-volume mesh, bit for bit."""
     from hive_b200 import marching_cubes as mc
     from hive_b200 import sharded
     from hive_b200.fusion import TSDFVolume
@@ -170,7 +171,8 @@ def test_slab_halo_stitch_equals_whole_volume(n_slabs):
     for s, (z0, z1) in zip(slabs, ranges):
         st, sc = s.get_volume()
         assert np.array_equal(st, tsdf[:, :, z0:z1]) and np.array_equal(sc, color[:, :, z0:z1])
-    parts = []
+    import torch
+    plans, sizes, counts = [], [], []
     for k, (s, (z0, z1)) in enumerate(zip(slabs, ranges)):
         Z = z1 - z0
         halo = {}
@@ -186,12 +188,23 @@ def test_slab_halo_stitch_equals_whole_volume(n_slabs):
         X, Y = int(s._local_dim[0]), int(s._local_dim[1])
         plan = mc.McPlan(s._tsdf_vol_gpu, s._color_vol_gpu, (X, Y, Z), s._pitch, halo=halo, z_global_offset=z0,
                          z_global_dim=Zg)
-        plan.count()
+        plan.count(64, 64)  # far too small on purpose: the records do not fit and the count is repeated, exactly sized
         nv, nt, _, _ = plan.read_totals()
-        m = plan.emit(nv, nt, s._voxel_size, s._vol_origin, keys=True)
-        parts.append({"verts": m.verts, "normals": m.normals, "colors": m.colors, "vert_keys": m.vert_keys,
-                      "face_keys": m.face_keys, "face_cubes": m.face_cubes})
-    verts, faces, normals, colors = (t.cpu().numpy() for t in sharded.stitch_mesh_parts(parts))
+        plan.ensure_records(nv, nt)
+        plans.append(plan)
+        sizes.append((nv, nt))
+        counts.append(plan.column_counts())
+    all_counts = torch.stack(counts)  # what the all-gather of the NCCL path produces
+    parts = []
+    for k, (plan, (nv, nt), s) in enumerate(zip(plans, sizes, slabs)):
+        shifts, g_tot = plan.column_shifts(all_counts, k)
+        n_edge, n_tri, n_centre = (int(v) for v in g_tot[:3].tolist())
+        tails = all_counts[:, -plan.SLAB_TAIL:].cpu().numpy()  # every slab's (min key, max key, vertices, triangles, edge vertices)
+        assert [tuple(int(v) for v in t[2:4]) for t in tails] == sizes and int(tails[:, 4].sum()) == n_edge
+        parts.append(plan.emit_placed(nv, nt, s._voxel_size, s._vol_origin, shifts, n_edge))
+    assert sum(nv for nv, _ in sizes) == n_edge + n_centre and sum(nt for _, nt in sizes) == n_tri
+    verts, faces, normals, colors = (t.cpu().numpy() for t in
+                                     sharded.place_mesh_parts(parts, n_edge + n_centre, n_tri, mc.scatter_rows))
     wv, wf, wn, wc = whole.get_mesh()
     assert len(wv) > 1000
     assert np.array_equal(verts, wv) and np.array_equal(faces, wf)
