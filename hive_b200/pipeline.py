@@ -20,7 +20,7 @@ from . import _lib
 from . import _xfer
 from . import geometric
 
-__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh", "FrameMesh", "process_frame"]
+__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh", "FrameMesh", "process_frame", "process_clip", "frame_range"]
 
 
 def _ptr(t):
@@ -286,3 +286,48 @@ def process_frame(rgb, depth, mask_encoded, pose, camera_matrix, dilation_option
         return FrameMesh(frame_vertices, frame_faces)
     packed_textures, packed_uv = Pipeline._pack_textures(texture_atlas, uv_atlas, n_rows=1)
     return FrameMesh(frame_vertices, frame_faces, packed_textures, packed_uv, tuple(kept_ids))
+
+
+def frame_range(n_frames: int, world_size: int, rank: int):
+    """Contiguous, balanced frame range ``[start, stop)`` of ``rank``: the first ``n_frames % world_size`` ranks take one
+    frame more.  (Contiguous so that a rank reads one stretch of the dataset, like one worker of the reference's pool.)"""
+    assert world_size >= 1 and 0 <= rank < world_size and n_frames >= 0
+    base, extra = divmod(int(n_frames), int(world_size))
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
+def process_clip(n_frames, load_frame, camera_matrix, dilation_options=None, filtering_options=None,
+                 disable_coverage_constraint=False, world_size=1, rank=0, dist=None, gather=True, frame_fn=None):
+    """The foreground-mesh loop of a clip, ``Pipeline._create_scene`` of pipeline.py:486-497 (``tqdm_imap(process_frame,
+    range(num_frames))``: a ThreadPool over frames, hive/utils.py:93) partitioned over GPUs by frame: rank r processes
+    the contiguous range ``frame_range(n_frames, world_size, r)`` on its own GPU -- no collective while it computes, the
+    frames are independent -- and the variable-length results are either left where they are (``gather=False``: returns
+    ``(start, [FrameMesh, ...])`` of this rank) or gathered to rank 0 by ONE collective (``gather=True``: rank 0 returns the
+    ``n_frames`` meshes in frame order, the other ranks ``None``).
+
+    ``load_frame(i) -> (rgb, depth, mask_encoded, pose)`` reads frame i of the dataset (``dataset.rgb_dataset[i]`` ... of
+    pipeline.py:341-348); it is only called for this rank's frames.  ``frame_fn``: the per-frame step, ``process_frame``
+    of this module unless given (the CPU tests of the partition / gather logic pass a stand-in).
+    """
+    frame_fn = frame_fn or process_frame
+    start, stop = frame_range(n_frames, world_size, rank)
+    meshes = []
+    for i in range(start, stop):
+        rgb, depth, mask_encoded, pose = load_frame(i)
+        meshes.append(frame_fn(rgb, depth, mask_encoded, pose, camera_matrix, dilation_options, filtering_options,
+                               disable_coverage_constraint))
+    if world_size == 1:
+        return meshes if gather else (start, meshes)
+    if not gather:
+        return start, meshes
+    assert dist is not None, "process_clip: pass torch.distributed as `dist` when world_size > 1"
+    parts = [None] * world_size if rank == 0 else None
+    dist.gather_object((start, meshes), parts, dst=0)  # one variable-length gather
+    if rank != 0:
+        return None
+    out = [None] * n_frames
+    for part_start, part in parts:
+        out[part_start:part_start + len(part)] = part
+    assert all(m is not None for m in out), "process_clip: a frame is missing from the gather"
+    return out

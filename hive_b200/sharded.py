@@ -254,14 +254,19 @@ class SlabShardedTSDFVolume:
         z0, z1 = self.ranges[self.rank]
         Zg = self.global_dim[2]
         first_t, last_t, first_c, last_c = self._boundary_planes()
-        halo = exchange_halo_planes(dist, self.rank, self.world_size,
-                                    {"tsdf": (first_t, last_t), "color": (first_c, last_c)})
+        # the halo planes and the extraction plan (scratch, work records) live as long as the volume: a repeated get_mesh
+        # allocates nothing
+        self._halo = exchange_halo_planes(dist, self.rank, self.world_size,
+                                          {"tsdf": (first_t, last_t), "color": (first_c, last_c)}, out=getattr(self, "_halo", None))
         X, Y, Z = (int(d) for d in loc._local_dim)
-        plan = mc.McPlan(loc._tsdf_vol_gpu, loc._color_vol_gpu, (X, Y, Z), loc._pitch, halo=halo, z_global_offset=z0,
-                         z_global_dim=Zg)
-        plan.count()
+        plan = getattr(self, "_mc_plan", None)
+        if plan is None or plan.tsdf is not loc._tsdf_vol_gpu:
+            plan = self._mc_plan = mc.McPlan(loc._tsdf_vol_gpu, loc._color_vol_gpu, (X, Y, Z), loc._pitch, halo=self._halo,
+                                             z_global_offset=z0, z_global_dim=Zg)
+        plan.count(*getattr(self, "_mc_caps", (None, None)))
         n_verts, n_tris, _, _ = plan.read_totals()
         plan.ensure_records(n_verts, n_tris)
+        self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)  # next time: records sized by this surface
         # ONE collective tells every slab everything about every other: per-column counts + (min, max, sizes)
         all_counts = exchange_column_counts(dist, self.world_size, plan.column_counts())
         shifts, _ = plan.column_shifts(all_counts, self.rank)
@@ -278,18 +283,21 @@ class SlabShardedTSDFVolume:
         return _xfer.to_host(verts, faces, normals, colors)
 
 
-def exchange_halo_planes(dist, rank, world_size, planes):
+def exchange_halo_planes(dist, rank, world_size, planes, out=None):
     """Seam exchange: every rank sends its first plane down and its last plane up.  ``planes`` maps a name to
-    (first, last); returns {name_lo, name_hi} tensors (absent at the ends of the stack)."""
+    (first, last); returns {name_lo, name_hi} tensors (absent at the ends of the stack), received into the tensors of
+    ``out`` when given (an earlier result)."""
     import torch
-    ops, out = [], {}
+    ops, out = [], (out if out is not None else {})
     for name, (first, last) in planes.items():
         if rank > 0:
-            out[f"{name}_lo"] = torch.empty_like(first)
+            if f"{name}_lo" not in out:
+                out[f"{name}_lo"] = torch.empty_like(first)
             ops.append(dist.P2POp(dist.isend, first, rank - 1))
             ops.append(dist.P2POp(dist.irecv, out[f"{name}_lo"], rank - 1))
         if rank < world_size - 1:
-            out[f"{name}_hi"] = torch.empty_like(last)
+            if f"{name}_hi" not in out:
+                out[f"{name}_hi"] = torch.empty_like(last)
             ops.append(dist.P2POp(dist.isend, last, rank + 1))
             ops.append(dist.P2POp(dist.irecv, out[f"{name}_hi"], rank + 1))
     if ops:

@@ -330,3 +330,32 @@ def test_process_frame_without_objects_is_empty():
     pose[:3, :3], pose[:3, 3:] = R, t
     got = pipeline.process_frame(fr.rgb, fr.depth, np.zeros_like(fr.mask), pose, scene.K)
     assert got.is_empty and got.vertices.shape == (0, 3) and got.faces.shape == (0, 3)
+
+
+def test_process_clip_partitions_equal_the_frame_loop():
+    """process_clip over a short clip: the per-rank parts (ranks emulated one after the other on this GPU, gather=False)
+    put together equal the single-process loop, which equals process_frame frame by frame."""
+    from hive_b200 import image_processing, pipeline
+    scene = Scene("small", "room")
+    n = 5
+    frames = [scene.frame(i) for i in range(n)]
+
+    def load(i):
+        w2c = np.linalg.inv(frames[i].pose)
+        return frames[i].rgb, frames[i].depth, frames[i].mask, w2c
+
+    dil = image_processing.MaskDilationOptions(num_iterations=1)
+    whole = pipeline.process_clip(n, load, scene.K, dil)
+    assert len(whole) == n and any(not m.is_empty for m in whole)
+    for i, m in enumerate(whole):
+        one = pipeline.process_frame(*load(i), scene.K, dil)
+        assert np.array_equal(m.vertices, one.vertices) and np.array_equal(m.faces, one.faces) and m.object_ids == one.object_ids
+    for world in (2, 3):
+        got = [None] * n
+        for rank in range(world):
+            start, part = pipeline.process_clip(n, load, scene.K, dil, world_size=world, rank=rank, gather=False)
+            assert start == pipeline.frame_range(n, world, rank)[0]
+            got[start:start + len(part)] = part
+        for a, b in zip(got, whole):
+            assert np.array_equal(a.vertices, b.vertices) and np.array_equal(a.faces, b.faces)
+            assert a.is_empty == b.is_empty and (a.is_empty or (np.array_equal(a.texture, b.texture) and np.array_equal(a.uv, b.uv)))
