@@ -71,9 +71,11 @@ SIGNATURES = {
     "hv_byte_lut": [c_void_p, c_int64, c_void_p, c_void_p],
     "hv_atlas_pack": [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int64,
                       c_void_p, c_void_p],
-    "hv_cc_edge_keys": [c_void_p, c_int64, c_int64, c_void_p, c_void_p],
     "hv_cc_scratch_bytes": [c_int64, c_void_p],
-    "hv_cc_label": [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
+    "hv_cc_mask": [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
+    "hv_cc_compact_scratch_bytes": [c_int64, c_void_p],
+    "hv_cc_compact_vertices": [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+                               c_int64, c_void_p],
     "hv_meshwrite_ply": [ctypes.c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int],
     "hv_pcwrite_ply": [ctypes.c_char_p, c_void_p, c_void_p, c_int64, c_int],
     "hv_filter_faces": [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_double, c_double, c_void_p, c_int64, c_int,

@@ -190,15 +190,42 @@ class Pipeline:
     def _cleanup_with_connected_components(vertices, faces, is_object=True, min_components=5):
         """pipeline.py:741-779: drop floating fragments.  Faces adjacent across an edge that exactly two faces share form
         a graph; components with fewer than ``min_components`` faces go; for an object only the largest survives.
-        Returns (vertices, kept faces in their original order); the vertex array is returned as given (the reference's
-        ``mesh.vertices`` after ``update_faces`` also still holds the unreferenced vertices)."""
+
+        Returns (vertices, kept faces in their original order).  Like the reference's ``trimesh.Trimesh(vertices, faces)``
+        (built with ``process=True``) the returned vertex array holds only the vertices that the *input* faces refer to
+        -- a valid pixel whose faces were all filtered out does not reach the texture crop -- and the faces are
+        renumbered accordingly.  PARITY UNPINNED (trimesh is on neither box): trimesh additionally merges duplicate
+        vertices (there are none in a depth-to-mesh result) and orders the surviving vertices by a hash of their rows;
+        here they keep their original order.  A tie between equally large components goes to the one containing the
+        lowest face index (trimesh: the first in its own traversal order)."""
         vertices, faces = np.asarray(vertices), np.asarray(faces)
         geometric.validate_shape(vertices, 'vertices', (None, 3))
         geometric.validate_shape(faces, 'faces', (None, 3))
         if faces.shape[0] == 0:
             return vertices, faces
-        keep = face_component_mask(faces, vertices.shape[0], min_components, largest_only=is_object)
-        return vertices, faces[keep]
+        torch = _lib.require_cuda()
+        lib = _lib.load()
+        dev = torch.device("cuda", torch.cuda.current_device())
+        n_verts, n_faces = int(vertices.shape[0]), int(faces.shape[0])
+        keep = face_component_mask(faces, n_verts, min_components, largest_only=is_object)
+        kept_faces = np.ascontiguousarray(faces[keep])
+        with torch.cuda.device(dev):
+            f_all = _xfer.to_device(faces, dev, np.int32)
+            f_keep = _xfer.to_device(kept_faces, dev, np.int32) if len(kept_faces) else None
+            v_in = _xfer.to_device(vertices, dev, np.float64)
+            v_out = torch.empty((n_verts, 3), dtype=torch.float64, device=dev)
+            f_out = torch.empty((len(kept_faces), 3), dtype=torch.int32, device=dev)
+            count = torch.zeros(2, dtype=torch.int64, device=dev)
+            nbytes = ctypes.c_int64(0)
+            _lib.check(lib.hv_cc_compact_scratch_bytes(n_verts, ctypes.byref(nbytes)))
+            scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+            sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
+            _lib.check(lib.hv_cc_compact_vertices(_ptr(f_all), n_faces, _ptr(f_keep), len(kept_faces), _ptr(v_in), n_verts,
+                                                  _ptr(v_out), _ptr(f_out) if len(kept_faces) else None, _ptr(count), sptr,
+                                                  int(nbytes.value), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            n_kept = int(count[0].item())
+            out_v, out_f = _xfer.to_host(v_out[:n_kept], f_out)
+        return out_v.astype(vertices.dtype, copy=False), out_f.astype(faces.dtype, copy=False)
 
 
 def face_component_mask(faces, n_verts, min_len=5, largest_only=True, return_labels=False):
@@ -210,16 +237,14 @@ def face_component_mask(faces, n_verts, min_len=5, largest_only=True, return_lab
     f = _xfer.to_device(faces, dev, np.int32)
     with torch.cuda.device(dev):
         stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-        keys = torch.empty(3 * n_faces, dtype=torch.int64, device=dev)
-        _lib.check(lib.hv_cc_edge_keys(_ptr(f), n_faces, int(n_verts), _ptr(keys), stream))
-        sorted_keys, slot = torch.sort(keys, stable=True)  # radix sort of the 3F edge keys: library plumbing
         nbytes = ctypes.c_int64(0)
         _lib.check(lib.hv_cc_scratch_bytes(n_faces, ctypes.byref(nbytes)))
-        scratch = torch.empty(int(nbytes.value) // 8 + 1, dtype=torch.int64, device=dev)
+        scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+        sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
         keep = torch.empty(n_faces, dtype=torch.uint8, device=dev)
         labels = torch.empty(n_faces, dtype=torch.int32, device=dev) if return_labels else None
-        _lib.check(lib.hv_cc_label(_ptr(sorted_keys), _ptr(slot), n_faces, int(min_len), int(bool(largest_only)),
-                                   _ptr(scratch), int(nbytes.value), _ptr(keep), _ptr(labels), stream))
+        _lib.check(lib.hv_cc_mask(_ptr(f), n_faces, int(n_verts), int(min_len), int(bool(largest_only)), sptr,
+                                  int(nbytes.value), _ptr(keep), _ptr(labels), stream))
     if return_labels:
         k, lab = _xfer.to_host(keep, labels)
         return k.view(np.bool_), lab.view(np.uint32)

@@ -288,16 +288,22 @@ int hv_atlas_pack(const uint8_t* src, const int64_t* desc, int n_tex, const int6
 /* ------------------------------------------------------------------------------------------------------------
  * Connected components over the face-adjacency graph: the body of Pipeline._cleanup_with_connected_components
  * (hive/pipeline.py:741-779 -> trimesh.graph.connected_components(mesh.face_adjacency, min_len)).
- *   hv_cc_edge_keys: keys[3f + k] = min(v_a, v_b) * n_verts + max(v_a, v_b) for the three edges of face f.
- *   The caller sorts the 3F keys ascending (stable) and passes them with slot[i] = original index of sorted key i.
- *   hv_cc_label: keep[f] = 1 iff face f survives (faces adjacent across an edge that exactly two faces use form the
- *   graph; components below min_len faces are dropped; largest_only keeps the largest survivor, lowest face index on a
- *   tie); labels (optional, F uint32) = component root per face, 0xffffffff for faces without any neighbour.
+ *   hv_cc_mask: keep[f] = 1 iff face f (int32 [F][3], DEVICE) survives: faces adjacent across an edge that exactly two
+ *   faces use form the graph (edges found through a hash table in `scratch`: hv_cc_scratch_bytes, 256-byte aligned;
+ *   nothing is sorted); components below min_len faces are dropped; largest_only keeps the largest survivor, lowest
+ *   face index on a tie; labels (optional, F uint32) = component root per face, 0xffffffff for faces without any
+ *   neighbour.
  * ---------------------------------------------------------------------------------------------------------- */
-int hv_cc_edge_keys(const int32_t* faces, int64_t n_faces, int64_t n_verts, unsigned long long* keys, void* stream);
 int hv_cc_scratch_bytes(int64_t n_faces, int64_t* h_bytes);
-int hv_cc_label(const unsigned long long* sorted_keys, const int64_t* slot, int64_t n_faces, int min_len,
-                int largest_only, void* scratch, int64_t scratch_bytes, uint8_t* keep, uint32_t* labels, void* stream);
+int hv_cc_mask(const int32_t* faces, int64_t n_faces, int64_t n_verts, int min_len, int largest_only, void* scratch,
+               int64_t scratch_bytes, uint8_t* keep, uint32_t* labels, void* stream);
+/* The vertices `faces_all` refer to, in their original order, into verts_out (float64 [n_verts][3] capacity), `faces_keep`
+ * renumbered accordingly into faces_out; d_count[0..1] (DEVICE, 2 x uint64): [0] = vertices kept.  What building
+ * trimesh.Trimesh(vertices, faces) does to unreferenced vertices before the components are taken (pipeline.py:758). */
+int hv_cc_compact_scratch_bytes(int64_t n_verts, int64_t* h_bytes);
+int hv_cc_compact_vertices(const int32_t* faces_all, int64_t n_faces_all, const int32_t* faces_keep, int64_t n_faces_keep,
+                           const double* verts_in, int64_t n_verts, double* verts_out, int32_t* faces_out,
+                           unsigned long long* d_count, void* scratch, int64_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * PLY writers (host pointers, host threads; no CUDA).  Replace meshwrite / pcwrite, fusion.py:378-438: ASCII output

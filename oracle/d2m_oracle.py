@@ -179,7 +179,9 @@ def face_adjacency(faces):
 
 def cleanup_with_connected_components(vertices, faces, is_object=True, min_components=5):
     """hive/pipeline.py:741-779 with trimesh.graph.connected_components restated over scipy.sparse.csgraph (trimesh's
-    own default engine): nodes = faces with a neighbour, groups ordered by label, components below min_len dropped."""
+    own default engine): nodes = faces with a neighbour, groups ordered by label, components below min_len dropped.
+    Like trimesh.Trimesh(vertices, faces) (process=True) the vertices that no input face refers to are dropped and the
+    faces renumbered; the survivors keep their order here (trimesh orders them by a row hash: PARITY UNPINNED)."""
     from scipy.sparse import coo_matrix
     from scipy.sparse.csgraph import connected_components
     faces = np.asarray(faces)
@@ -199,7 +201,11 @@ def cleanup_with_connected_components(vertices, faces, is_object=True, min_compo
                 mask[components[int(np.argmax([len(c) for c in components]))]] = True
             else:
                 mask[np.concatenate(components)] = True
-    return vertices, faces[mask]
+    vertices = np.asarray(vertices)
+    referenced = np.zeros(len(vertices), dtype=bool)
+    referenced[faces.reshape(-1).astype(np.int64)] = True
+    new_index = np.cumsum(referenced) - 1
+    return vertices[referenced], new_index[faces[mask].astype(np.int64)].astype(faces.dtype)
 
 
 def process_frame(rgb, depth, mask_encoded, pose, camera_matrix, dilation_iterations=0, max_pixel_distance=2,

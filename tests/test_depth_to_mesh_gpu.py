@@ -185,11 +185,11 @@ def test_connected_components_cleanup_matches_oracle(is_object, min_components):
     faces = np.array(faces, dtype=np.int32)
     rng = np.random.default_rng(3)
     faces = faces[rng.permutation(len(faces))]
-    verts = rng.standard_normal((nv, 3))
+    verts = rng.standard_normal((nv + 4, 3))  # the last four vertices belong to no face: they do not come back
     gv, gf = Pipeline._cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_components)
     ov, of = d2m.cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_components)
-    assert gv is verts or np.array_equal(gv, verts)
-    assert np.array_equal(gf, of)
+    assert np.array_equal(gv, verts[:nv]) and np.array_equal(gv, ov) and gv.dtype == verts.dtype
+    assert np.array_equal(gf, of) and gf.dtype == faces.dtype
     if is_object and min_components <= 12:
         assert len(gf) == 12
 
@@ -206,9 +206,10 @@ def test_connected_components_on_a_depth_mesh():
     verts, faces, _, _ = pipeline.depth_to_mesh(depth, fr.mask > 0, sc.K, R, t)
     assert len(faces) > 2000
     for is_object, min_c in ((True, 5), (False, 5), (False, 40)):
-        _, gf = Pipeline._cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_c)
-        _, of = d2m.cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_c)
+        gv, gf = Pipeline._cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_c)
+        ov, of = d2m.cleanup_with_connected_components(verts, faces, is_object=is_object, min_components=min_c)
         assert np.array_equal(gf, of) and 0 < len(gf) <= len(faces)
+        assert np.array_equal(gv, ov) and len(gv) == len(np.unique(faces))  # the vertices the input faces refer to
     keep, labels = pipeline.face_component_mask(faces, len(verts), 5, largest_only=False, return_labels=True)
     assert len(np.unique(labels[keep])) >= 2  # both instances survive as separate components
 
