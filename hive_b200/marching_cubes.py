@@ -396,7 +396,8 @@ def extract_device_mesh(vol, level=0.0, want_voxel=False, timing_event=False) ->
 
 def extract_mesh(vol, srgb_colors=False):
     """``TSDFVolume.get_mesh`` (fusion.py:332-350): verts (V,3) f32 world, faces (F,3) i32, norms (V,3) f32,
-    colors (V,3) u8.  ``srgb_colors`` applies the vertex-colour conversion of hive/pipeline.py:281-282 on the device,
+    colors (V,3) u8.  The marching cubes inside is ``marching_cubes`` of this module: parity with skimage unpinned
+    (see there); everything after that call (fusion.py:339-348) is pinned against the reference's own lines.  ``srgb_colors`` applies the vertex-colour conversion of hive/pipeline.py:281-282 on the device,
     before the download."""
     mesh = extract_device_mesh(vol)
     if srgb_colors and mesh.colors.numel():
@@ -411,6 +412,13 @@ def marching_cubes(volume, level=None, *, spacing=(1., 1., 1.), gradient_directi
 
     Only the argument values the reference uses are supported (defaults, ``level`` given); returns
     ``(verts, faces, normals, values)`` with verts in voxel units, axis order (axis0, axis1, axis2).
+
+    PARITY WITH SKIMAGE UNPINNED: scikit-image is installed on neither box and its tables cannot be consulted.  The
+    surface is Lewiner's (face test, interior test, tunnel tilings: DESIGN.md 2.1), checked against an independently
+    written restatement and the triangle counts per sub-case of SURVEY.md App. C; known differences from the real
+    implementation: the triangulation inside a cube and the vertex numbering are this package's (vertices sorted by
+    lattice edge, then the cube-centre vertices), and ``values`` is the constant ``level`` (skimage returns a local
+    maximum of the data near each vertex; HIVE discards it, fusion.py:338).
     """
     torch = _lib.require_cuda()
     if (tuple(spacing) != (1., 1., 1.) or gradient_direction != 'descent' or step_size != 1 or not allow_degenerate
