@@ -13,6 +13,9 @@ One process per GPU (``torch.distributed``); ``world_size == 1`` degenerates to 
 """
 from __future__ import annotations
 
+import os
+import time
+
 import numpy as np
 
 from . import _xfer
@@ -253,11 +256,27 @@ class SlabShardedTSDFVolume:
         dist, loc, torch = self._dist, self.local, self._torch
         z0, z1 = self.ranges[self.rank]
         Zg = self.global_dim[2]
+        trace = [] if os.environ.get("HV_MESH_TRACE") else None  # (step, ms) with a device sync per step: tools/trace_sharded_mesh.py
+
+        def mark(step):
+            if trace is not None:
+                torch.cuda.synchronize()
+                trace.append((step, time.perf_counter()))
+
+        mark("start")
         first_t, last_t, first_c, last_c = self._boundary_planes()
         # the halo planes and the extraction plan (scratch, work records) live as long as the volume: a repeated get_mesh
-        # allocates nothing
-        self._halo = exchange_halo_planes(dist, self.rank, self.world_size,
-                                          {"tsdf": (first_t, last_t), "color": (first_c, last_c)}, out=getattr(self, "_halo", None))
+        # allocates nothing.  tsdf and colour plane travel as one message per neighbour.
+        packed = exchange_halo_planes(dist, self.rank, self.world_size,
+                                      {"tc": (torch.stack((first_t, first_c)), torch.stack((last_t, last_c)))},
+                                      out=getattr(self, "_halo_packed", None))
+        if getattr(self, "_halo_packed", None) is None:
+            self._halo_packed = packed
+            self._halo = {}
+            for side in ("lo", "hi"):
+                if f"tc_{side}" in packed:
+                    self._halo[f"tsdf_{side}"], self._halo[f"color_{side}"] = packed[f"tc_{side}"][0], packed[f"tc_{side}"][1]
+        mark("halo exchange")
         X, Y, Z = (int(d) for d in loc._local_dim)
         plan = getattr(self, "_mc_plan", None)
         if plan is None or plan.tsdf is not loc._tsdf_vol_gpu:
@@ -266,21 +285,30 @@ class SlabShardedTSDFVolume:
         plan.count(*getattr(self, "_mc_caps", (None, None)))
         n_verts, n_tris, _, _ = plan.read_totals()
         plan.ensure_records(n_verts, n_tris)
+        mark("count + totals")
         self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)  # next time: records sized by this surface
         # ONE collective tells every slab everything about every other: per-column counts + (min, max, sizes)
         all_counts = exchange_column_counts(dist, self.world_size, plan.column_counts())
+        mark("column counts + all-gather")
         shifts, _ = plan.column_shifts(all_counts, self.rank)
         tails = all_counts[:, -plan.SLAB_TAIL:].cpu().numpy()  # (world, 5): min key, max key, vertices, triangles, edge vertices
         vmin = min(mc._key_to_float(int(k)) for k in tails[:, 0])
         vmax = max(mc._key_to_float(int(k)) for k in tails[:, 1])
         n_verts_g, n_tris_g, n_edge_g = (int(v) for v in tails[:, 2:5].sum(axis=0))
         mc.check_surface(0.0, vmin, vmax, n_verts_g)
+        mark("shifts + tails read")
         part = plan.emit_placed(n_verts, n_tris, loc._voxel_size, loc._vol_origin, shifts, n_edge_g)
+        mark("emit")
         parts = gather_placed_parts(dist, self.rank, self.world_size, part, loc.device, tails[:, 2:4])
+        mark("gather")
+        self.last_mesh_trace = trace
         if self.rank != 0:
             return None, None, None, None
         verts, faces, normals, colors = place_mesh_parts(parts, n_verts_g, n_tris_g, mc.scatter_rows)
-        return _xfer.to_host(verts, faces, normals, colors)
+        mark("place")
+        out = _xfer.to_host(verts, faces, normals, colors)
+        mark("download")
+        return out
 
 
 def exchange_halo_planes(dist, rank, world_size, planes, out=None):
@@ -314,34 +342,58 @@ def exchange_column_counts(dist, world_size, counts):
     """All-gather of ``McPlan.column_counts()`` (per-column counts + the slab's totals) -> (world_size, ...)."""
     import torch
     out = torch.empty((world_size,) + tuple(counts.shape), dtype=counts.dtype, device=counts.device)
-    dist.all_gather(list(out.unbind(0)), counts.contiguous())  # (views of one buffer: NCCL gathers in place)
+    if counts.is_cuda:
+        dist.all_gather_into_tensor(out.view(-1), counts.contiguous().view(-1))  # NCCL: one flat gather, no staging
+    else:
+        dist.all_gather(list(out.unbind(0)), counts.contiguous())  # gloo (CPU tests)
     return out
+
+
+def _part_layout(nv, nf):
+    """Byte offsets of the arrays of one slab mesh inside its packed message (every array starts on a 16-byte boundary)."""
+    import torch
+    offs, o = {}, 0
+    for name, cols, dtype in _PART_FIELDS:
+        n = nf if name in ("faces", "tri_dst") else nv
+        nbytes = n * max(cols, 1) * torch.empty((), dtype=getattr(torch, dtype)).element_size()
+        offs[name] = (o, nbytes, n, cols, dtype)
+        o = (o + nbytes + 15) & ~15
+    return offs, o
 
 
 def gather_placed_parts(dist, rank, world_size, part, device, all_sizes):
     """Variable-length gather of the per-slab meshes to rank 0 -- ``all_sizes[w]`` = (vertices, triangles) of slab w, known
-    to everyone from the column-count exchange -- every array of every slab in ONE grouped exchange (rank 0 posts all
-    receives at once; nothing waits for anything else)."""
+    to everyone from the column-count exchange.  Every slab packs its six arrays into ONE message; rank 0 posts all
+    receives at once and unpacks by view (nothing waits for anything else, nothing is copied twice)."""
     import torch
-    ops, parts = [], None
     if rank != 0:
-        for name, _, _ in _PART_FIELDS:
-            if part[name].numel():
-                ops.append(dist.P2POp(dist.isend, part[name].contiguous(), 0))
-    else:
-        parts = [part]
-        for src in range(1, world_size):
-            nv, nf = (int(v) for v in all_sizes[src])
-            got = {}
-            for name, cols, dtype in _PART_FIELDS:
-                n = nf if name in ("faces", "tri_dst") else nv
-                got[name] = torch.empty((n, cols) if cols else (n,), dtype=getattr(torch, dtype), device=device)
-                if got[name].numel():
-                    ops.append(dist.P2POp(dist.irecv, got[name], src))
-            parts.append(got)
+        offs, total = _part_layout(int(part["vert_dst"].shape[0]), int(part["tri_dst"].shape[0]))
+        if total:
+            msg = torch.empty(total, dtype=torch.uint8, device=device)
+            for name, (o, nbytes, _, _, _) in offs.items():
+                if nbytes:
+                    msg[o:o + nbytes] = part[name].contiguous().view(-1).view(torch.uint8)
+            for req in dist.batch_isend_irecv([dist.P2POp(dist.isend, msg, 0)]):
+                req.wait()
+        return None
+    ops, msgs = [], []
+    for src in range(1, world_size):
+        nv, nf = (int(v) for v in all_sizes[src])
+        offs, total = _part_layout(nv, nf)
+        msg = torch.empty(total, dtype=torch.uint8, device=device)
+        if total:
+            ops.append(dist.P2POp(dist.irecv, msg, src))
+        msgs.append((offs, msg))
     if ops:
         for req in dist.batch_isend_irecv(ops):
             req.wait()
+    parts = [part]
+    for offs, msg in msgs:
+        got = {}
+        for name, (o, nbytes, n, cols, dtype) in offs.items():
+            t = msg[o:o + nbytes].view(getattr(torch, dtype))
+            got[name] = t.view(n, cols) if cols else t
+        parts.append(got)
     return parts
 
 
