@@ -41,15 +41,18 @@ struct D2mGrid {
 
 struct PixelFaces {
     int n;
-    // Corners of the (at most four) faces, winding with negative signed area in (u, v).  Every corner lies within one
-    // pixel of the owner, so a corner is 4 bits ((du + 1) | (dv + 1) << 2), a face 12, and the whole set one register
-    // pair -- as int2 p[4][3] indexed by the running face count it lived in local memory (104-byte stack frame, a
-    // store and a load per corner in the emit loop).
+    // Corners of the (at most four) faces, winding with negative signed area in (u, v).  Every corner is one of six
+    // pixels around the owner (corner_code), so a corner is 4 bits, a face 12, and the whole set one register pair -- as
+    // int2 p[4][3] indexed by the running face count it lived in local memory (104-byte stack frame, a store and a
+    // load per corner in the emit loop).
     unsigned long long codes;
 };
 
+// Which of the six pixels a face of (u, v) can touch: 0 = (u, v), 1 = (u+1, v), 2 = (u, v+1), 3 = (u+1, v+1), 4 = (u, v-1),
+// 5 = (u-1, v).  (Call sites pass constants relative to (u, v): this folds at compile time.)
 __device__ __forceinline__ unsigned int corner_code(int2 p, int u, int v) {
-    return (unsigned int)(p.x - u + 1) | ((unsigned int)(p.y - v + 1) << 2);
+    const int du = p.x - u, dv = p.y - v;
+    return dv == 0 ? (du == 0 ? 0u : (du == 1 ? 1u : 5u)) : (dv == 1 ? (du == 0 ? 2u : 3u) : 4u);
 }
 
 // Depth of pixel (u, v) if it is a vertex (inside the image, mask set, depth > 0: geometric.py:117), else 0.
@@ -216,6 +219,47 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_count_kernel(const D2mGrid g)
     const int b = (int)blockIdx.z;
     const int v0 = (int)blockIdx.y * kD2mRows, v1 = min(v0 + kD2mRows, g.H);
     const bool faces = !g.verts_only;
+    {
+        // Most 32 x 8 pixel blocks of a foreground frame hold no vertex at all: look at the block and its one-pixel rim
+        // first (mask bytes when there is a mask, depths otherwise; all ten rows requested together) and leave with
+        // zeros.  (r01: the row-by-row walk spent ~70 warp-instructions per empty word row, 80 % of the rows.)
+        bool any = false;
+        if (g.mask && (g.W & 3) == 0 && (reinterpret_cast<uintptr_t>(g.mask) & 3) == 0) {
+            // ten 4-byte words per row (pixels 32 cw - 4 .. 32 cw + 35: the word and, generously, its rim), ten rows:
+            // 100 words, one per lane in four rounds
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int k = i * 32 + lane, r = k / 10, c = k - r * 10;
+                const int v = v0 - 1 + r, uu = cw * 32 - 4 + 4 * c;
+                if (k < 100 && v >= 0 && v < g.H && v <= v1 && uu >= 0 && uu < g.W)
+                    any |= __ldg(reinterpret_cast<const unsigned int*>(g.mask + ((size_t)b * g.H + v) * g.W + uu)) != 0u;
+            }
+        } else {
+            const int u = cw * 32 + lane, hu = lane == 0 ? cw * 32 + 32 : cw * 32 - 1;
+            const bool hin = lane < 2 && hu >= 0 && hu < g.W;
+#pragma unroll
+            for (int r = -1; r <= kD2mRows; ++r) {
+                const int v = v0 + r;
+                if (v < 0 || v >= g.H || v > v1) continue;
+                const size_t row = ((size_t)b * g.H + v) * g.W;
+                if (g.mask) {
+                    if (u < g.W) any |= __ldg(g.mask + row + u) != 0;
+                    if (hin) any |= __ldg(g.mask + row + hu) != 0;
+                } else {
+                    if (u < g.W) any |= __ldg(g.depth + row + u) > 0.0f;
+                    if (hin) any |= __ldg(g.depth + row + hu) > 0.0f;
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, any)) {
+            if (lane < v1 - v0) {
+                const size_t w = (size_t)b * g.words_per_frame + (size_t)(v0 + lane) * g.wpr + cw;
+                g.wbits[w] = 0u;
+                g.wcount[w] = make_uint2(0u, 0u);
+            }
+            return;
+        }
+    }
     const RawRow q0 = load_raw(g, b, v0 - 1, cw, lane), q1 = load_raw(g, b, v0, cw, lane);
     RawRow raw_next = load_raw(g, b, v0 + 1, cw, lane);
     Row prev = finish_row(q0), cur = finish_row(q1);
@@ -253,17 +297,6 @@ struct D2mOut {
     long long* frame_off; // [B+1][2] (vertex, face) start of every frame in the concatenated outputs
     unsigned long long n_verts, n_faces;
 };
-
-// Frame-local vertex id (row-major rank among the frame's vertices, np.nonzero order, geometric.py:121) of a face corner
-// (pu, pv) in the 3x3 neighbourhood of the warp's word: from the vertex bits of the word in that row and the rank of the
-// word's first pixel -- all in registers.  A corner left of the word is the last vertex before it, a corner right of
-// it the first vertex after it (a face corner is always a vertex).
-__device__ __forceinline__ int corner_rank(int pu, int word_u0, unsigned int row_bits, unsigned int row_first_rank) {
-    const int du = pu - word_u0;
-    if (du < 0) return (int)row_first_rank - 1;
-    if (du >= 32) return (int)(row_first_rank + __popc(row_bits));
-    return (int)(row_first_rank + __popc(row_bits & ((1u << du) - 1u)));
-}
 
 __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, const D2mOut out) {
     const int lane = threadIdx.x & 31;
@@ -331,15 +364,22 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
                 }
                 size_t fi = (size_t)off.y + inc - (unsigned int)f.n;
                 unsigned long long codes = f.codes;
-                for (int k = 0; k < f.n; ++k, ++fi, codes >>= 12)
+                if (f.n) {
+                    // frame-local ranks of the six pixels the faces can touch, once per pixel (r01 derived the rank of
+                    // every corner of every face from its coordinates: ~25 instructions per corner, 28 % of this kernel).
+                    // A corner is always a vertex, so rank(u - 1) = rank(u) - 1 and rank(u + 1) = rank(u) + valid(u).
+                    const unsigned int lt = (1u << lane) - 1u;
+                    const unsigned int rc = first_cur + __popc(cur.bits & lt), rs = first_next + __popc(next.bits & lt);
+                    const unsigned int r0 = rc, r1 = rc + ((cur.bits >> lane) & 1u), r2 = rs, r3 = rs + ((next.bits >> lane) & 1u);
+                    const unsigned int r4 = first_prev + __popc(prev.bits & lt), r5 = rc - 1u;
+                    for (int k = 0; k < f.n; ++k, ++fi, codes >>= 12)
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const unsigned int nib = ((unsigned int)codes >> (4 * c)) & 15u;
-                        const int qx = u + (int)(nib & 3u) - 1, dv = (int)(nib >> 2) - 1;
-                        const unsigned int rb = dv < 0 ? prev.bits : (dv > 0 ? next.bits : cur.bits);
-                        const unsigned int rf = dv < 0 ? first_prev : (dv > 0 ? first_next : first_cur);
-                        out.faces[3 * fi + c] = corner_rank(qx, cw * 32, rb, rf);
-                    }
+                        for (int c = 0; c < 3; ++c) {
+                            const unsigned int id = ((unsigned int)codes >> (4 * c)) & 7u;
+                            const unsigned int lo3 = id == 0u ? r0 : (id == 1u ? r1 : r2), hi3 = id == 3u ? r3 : (id == 4u ? r4 : r5);
+                            out.faces[3 * fi + c] = (int32_t)(id < 3u ? lo3 : hi3);
+                        }
+                }
             }
             const unsigned int bits = has_f ? cur.bits : g.wbits[w];  // (the count kernel stored exactly cur.bits)
             if ((bits >> lane) & 1u) {  // image2world, hive/geometric.py:200-204 (float64)
