@@ -73,6 +73,10 @@ SIGNATURES = {
                       c_void_p, c_void_p],
     "hv_cc_scratch_bytes": [c_int64, c_void_p],
     "hv_cc_mask": [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
+    "hv_cc_cleanup_scratch_bytes": [c_int64, c_int64, c_void_p],
+    "hv_cc_cleanup": [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p],
+    "hv_count_nonzero": [c_void_p, c_int, c_int64, c_void_p, c_void_p],
+    "hv_uv_bbox": [c_void_p, c_int64, c_void_p, c_void_p],
     "hv_cc_compact_scratch_bytes": [c_int64, c_void_p],
     "hv_cc_compact_vertices": [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_int64, c_void_p],

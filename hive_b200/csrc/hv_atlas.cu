@@ -11,10 +11,13 @@
 // reference's operation order (add offset, divide, subtract from one).
 #include "hv_common.cuh"
 
+#include <limits.h>
+
 namespace hv {
 
-// desc[t] = {src byte offset, x0, y0, w, h, first uv row}
-constexpr int kAtlasDescWords = 6;
+// desc[t] = {src byte offset, x0, y0, w, h, first uv row, src row pitch in pixels (crop taken straight out of a larger image),
+//            u shift, v shift (subtracted from the uv before the crop's place is added: the crop's origin in that image)}
+constexpr int kAtlasDescWords = 9;
 
 __global__ void __launch_bounds__(256) atlas_pixels_kernel(const uint8_t* __restrict__ src,
                                                            const long long* __restrict__ desc,
@@ -37,7 +40,7 @@ __global__ void __launch_bounds__(256) atlas_pixels_kernel(const uint8_t* __rest
         const int dx = x - (int)d[1], dy = y - (int)d[2];
         uint8_t c0 = 0, c1 = 0, c2 = 0;
         if (dx >= 0 && dx < (int)d[3] && dy >= 0 && dy < (int)d[4]) {
-            const uint8_t* s = src + d[0] + ((long long)dy * d[3] + dx) * 3;
+            const uint8_t* s = src + d[0] + ((long long)dy * d[6] + dx) * 3;
             c0 = s[0];
             c1 = s[1];
             c2 = s[2];
@@ -61,13 +64,54 @@ __global__ void __launch_bounds__(256) atlas_uv_kernel(const double* __restrict_
         else hi = mid;
     }
     const long long* d = desc + (long long)lo * kAtlasDescWords;
-    const double u = __dadd_rn(uv[2 * i], (double)d[1]);      // uvs_atlas[k][:, 0] += moving_w   (pipeline.py:837)
-    const double v = __dadd_rn(uv[2 * i + 1], (double)d[2]);  // uvs_atlas[k][:, 1] += moving_h   (pipeline.py:857)
+    // uv -= crop origin (pipeline.py:806, integers: exact), then uvs_atlas[k] += (moving_w, moving_h) (pipeline.py:837, 857)
+    const double u = __dadd_rn(__dsub_rn(uv[2 * i], (double)d[7]), (double)d[1]);
+    const double v = __dadd_rn(__dsub_rn(uv[2 * i + 1], (double)d[8]), (double)d[2]);
     out[2 * i] = __ddiv_rn(u, (double)canvas_w);                              // pipeline.py:865
     out[2 * i + 1] = __dsub_rn(1.0, __ddiv_rn(v, (double)canvas_h));          // pipeline.py:866
 }
 
+// box = {min u, min v, max u, max v} of uv rows holding integers (world2image with rounding), pipeline.py:797-800
+__global__ void __launch_bounds__(256) uv_bbox_kernel(const double* __restrict__ uv, long long n, long long* box) {
+    long long lo_u = LLONG_MAX, lo_v = LLONG_MAX, hi_u = LLONG_MIN, hi_v = LLONG_MIN;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const long long u = (long long)rint(uv[2 * i]), v = (long long)rint(uv[2 * i + 1]);
+        lo_u = min(lo_u, u);
+        hi_u = max(hi_u, u);
+        lo_v = min(lo_v, v);
+        hi_v = max(hi_v, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo_u = min(lo_u, __shfl_xor_sync(0xffffffffu, lo_u, o));
+        lo_v = min(lo_v, __shfl_xor_sync(0xffffffffu, lo_v, o));
+        hi_u = max(hi_u, __shfl_xor_sync(0xffffffffu, hi_u, o));
+        hi_v = max(hi_v, __shfl_xor_sync(0xffffffffu, hi_v, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(box, lo_u);
+        atomicMin(box + 1, lo_v);
+        atomicMax(box + 2, hi_u);
+        atomicMax(box + 3, hi_v);
+    }
+}
+
+__global__ void uv_bbox_init_kernel(long long* box) {
+    box[0] = box[1] = LLONG_MAX;
+    box[2] = box[3] = LLONG_MIN;
+}
+
 }  // namespace hv
+
+extern "C" int hv_uv_bbox(const double* uv, int64_t n, int64_t* box, void* stream) {
+    HV_REQUIRE(uv && box && n > 0, "hv_uv_bbox: bad arguments");
+    cudaStream_t st = hv::as_stream(stream);
+    hv::uv_bbox_init_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(box));
+    const long long want = (n + 255) / 256;
+    hv::uv_bbox_kernel<<<(unsigned int)(want < 256 ? want : 256), 256, 0, st>>>(uv, n, reinterpret_cast<long long*>(box));
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
 
 extern "C" int hv_atlas_pack(const uint8_t* src, const int64_t* desc, int n_tex, const int64_t* row_first,
                              const int64_t* row_y0, int n_rows, int canvas_h, int canvas_w, uint8_t* atlas,

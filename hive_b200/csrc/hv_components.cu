@@ -163,6 +163,23 @@ __global__ void __launch_bounds__(256) cc_remap_kernel(const int32_t* __restrict
     if (i < n3) out[i] = (int32_t)offs[faces[i]].x;
 }
 
+__global__ void __launch_bounds__(256) cc_face_flags_kernel(const uint8_t* __restrict__ keep, long long n_faces,
+                                                            uint2* __restrict__ flags) {
+    const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < n_faces) flags[f] = make_uint2(keep[f] ? 1u : 0u, 0u);
+}
+
+// kept faces, in their original order, renumbered to the compacted vertices
+__global__ void __launch_bounds__(256) cc_face_gather_kernel(const int32_t* __restrict__ faces, const uint8_t* __restrict__ keep,
+                                                             long long n_faces, const uint2* __restrict__ foffs,
+                                                             const uint2* __restrict__ voffs, int32_t* __restrict__ out) {
+    const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= n_faces || !keep[f]) return;
+    const long long o = 3 * (long long)foffs[f].x;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) out[o + c] = (int32_t)voffs[faces[3 * f + c]].x;
+}
+
 }  // namespace hv
 
 namespace {
@@ -259,6 +276,81 @@ extern "C" int hv_cc_compact_vertices(const int32_t* faces_all, int64_t n_faces_
     hv::cc_gather_vertices_kernel<<<(unsigned int)((n_verts + 255) / 256), 256, 0, st>>>(flags, offs, n_verts, verts_in, verts_out);
     if (n_faces_keep > 0)
         hv::cc_remap_kernel<<<(unsigned int)((3 * n_faces_keep + 255) / 256), 256, 0, st>>>(faces_keep, 3 * n_faces_keep, offs, faces_out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
+// ---- the whole of Pipeline._cleanup_with_connected_components on device arrays (no host hop between its steps) ------------
+namespace {
+struct CleanupLayout {
+    size_t off_cc, off_keep, off_vflags, off_voffs, off_fflags, off_foffs, off_bsum, total;
+};
+size_t a256(size_t v) { return (v + 255) & ~(size_t)255; }
+int cleanup_layout(int64_t n_faces, int64_t n_verts, CleanupLayout* L) {
+    int64_t cc = 0;
+    int rc = hv_cc_scratch_bytes(n_faces, &cc);
+    if (rc != HV_OK) return rc;
+    const int64_t n_max = n_faces > n_verts ? n_faces : n_verts;
+    size_t o = 0;
+    L->off_cc = o;
+    o = a256(o + (size_t)cc);
+    L->off_keep = o;
+    o = a256(o + (size_t)n_faces);
+    L->off_vflags = o;
+    o = a256(o + (size_t)n_verts * sizeof(uint2));
+    L->off_voffs = o;
+    o = a256(o + (size_t)n_verts * sizeof(uint2));
+    L->off_fflags = o;
+    o = a256(o + (size_t)n_faces * sizeof(uint2));
+    L->off_foffs = o;
+    o = a256(o + (size_t)n_faces * sizeof(uint2));
+    L->off_bsum = o;
+    o = a256(o + (size_t)hv::scan_scratch_pairs(n_max) * sizeof(uint2));
+    L->total = o;
+    return HV_OK;
+}
+}  // namespace
+
+extern "C" int hv_cc_cleanup_scratch_bytes(int64_t n_faces, int64_t n_verts, int64_t* h_bytes) {
+    HV_REQUIRE(h_bytes && n_faces > 0 && n_verts > 0 && n_verts < (1ll << 31), "hv_cc_cleanup_scratch_bytes: bad arguments");
+    CleanupLayout L;
+    int rc = cleanup_layout(n_faces, n_verts, &L);
+    if (rc != HV_OK) return rc;
+    *h_bytes = (int64_t)L.total;
+    return HV_OK;
+}
+
+// verts_out (capacity n_verts rows) / faces_out (capacity n_faces rows); d_counts (DEVICE, 4 x uint64): [0] = vertices kept,
+// [2] = faces kept.
+extern "C" int hv_cc_cleanup(const int32_t* faces, int64_t n_faces, const double* verts_in, int64_t n_verts, int min_len,
+                             int largest_only, double* verts_out, int32_t* faces_out, unsigned long long* d_counts,
+                             void* scratch, int64_t scratch_bytes, void* stream) {
+    HV_REQUIRE(faces && verts_in && verts_out && faces_out && d_counts && scratch && n_faces > 0 && n_verts > 0,
+               "hv_cc_cleanup: bad arguments");
+    CleanupLayout L;
+    int rc = cleanup_layout(n_faces, n_verts, &L);
+    if (rc != HV_OK) return rc;
+    HV_REQUIRE((size_t)scratch_bytes >= L.total && ((uintptr_t)scratch & 255) == 0, "hv_cc_cleanup: scratch too small or unaligned");
+    char* s = static_cast<char*>(scratch);
+    uint8_t* keep = reinterpret_cast<uint8_t*>(s + L.off_keep);
+    uint2* vflags = reinterpret_cast<uint2*>(s + L.off_vflags);
+    uint2* voffs = reinterpret_cast<uint2*>(s + L.off_voffs);
+    uint2* fflags = reinterpret_cast<uint2*>(s + L.off_fflags);
+    uint2* foffs = reinterpret_cast<uint2*>(s + L.off_foffs);
+    uint2* bsum = reinterpret_cast<uint2*>(s + L.off_bsum);
+    int64_t cc_bytes = 0;
+    hv_cc_scratch_bytes(n_faces, &cc_bytes);
+    rc = hv_cc_mask(faces, n_faces, n_verts, min_len, largest_only, s + L.off_cc, cc_bytes, keep, nullptr, stream);
+    if (rc != HV_OK) return rc;
+    cudaStream_t st = hv::as_stream(stream);
+    const unsigned int fblk = (unsigned int)((n_faces + 255) / 256), vblk = (unsigned int)((n_verts + 255) / 256);
+    HV_CUDA(cudaMemsetAsync(vflags, 0, (size_t)n_verts * sizeof(uint2), st));
+    hv::cc_mark_kernel<<<(unsigned int)((3 * n_faces + 255) / 256), 256, 0, st>>>(faces, 3 * n_faces, vflags);
+    hv::exclusive_scan_u2(vflags, voffs, bsum, n_verts, d_counts, st);
+    hv::cc_gather_vertices_kernel<<<vblk, 256, 0, st>>>(vflags, voffs, n_verts, verts_in, verts_out);
+    hv::cc_face_flags_kernel<<<fblk, 256, 0, st>>>(keep, n_faces, fflags);
+    hv::exclusive_scan_u2(fflags, foffs, bsum, n_faces, d_counts + 2, st);
+    hv::cc_face_gather_kernel<<<fblk, 256, 0, st>>>(faces, keep, n_faces, foffs, voffs, faces_out);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

@@ -332,3 +332,26 @@ extern "C" int hv_byte_lut(uint8_t* bytes, int64_t n, const uint8_t* lut, void* 
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }
+
+// ---- coverage of (dilated) object masks: np.count_nonzero(mask) of hive/pipeline.py:377, per frame of a batch ---------------
+namespace hv {
+__global__ void __launch_bounds__(256) count_nonzero_kernel(const uint8_t* __restrict__ m, long long n, unsigned long long* out) {
+    const uint8_t* row = m + (size_t)blockIdx.y * n;
+    unsigned int c = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) c += row[i] != 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out + blockIdx.y, (unsigned long long)c);
+}
+}  // namespace hv
+
+extern "C" int hv_count_nonzero(const uint8_t* masks, int B, int64_t n, unsigned long long* counts, void* stream) {
+    HV_REQUIRE(masks && counts && B > 0 && n > 0, "hv_count_nonzero: bad arguments");
+    cudaStream_t st = hv::as_stream(stream);
+    HV_CUDA(cudaMemsetAsync(counts, 0, (size_t)B * sizeof(unsigned long long), st));
+    const long long want = (n + 255) / 256;
+    const dim3 grid((unsigned int)(want < 64 ? want : 64), (unsigned int)B);
+    hv::count_nonzero_kernel<<<grid, 256, 0, st>>>(masks, n, counts);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}

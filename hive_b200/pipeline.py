@@ -20,7 +20,8 @@ from . import _lib
 from . import _xfer
 from . import geometric
 
-__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh", "FrameMesh", "process_frame", "process_clip", "frame_range"]
+__all__ = ["MeshFilteringOptions", "Pipeline", "depth_to_mesh", "FrameMesh", "process_frame", "process_frame_stepwise",
+           "process_clip", "frame_range"]
 
 
 def _ptr(t):
@@ -149,7 +150,7 @@ class Pipeline:
         textures = [np.asarray(t) for t in textures_atlas]
         for t in textures:
             geometric.validate_shape(t, 'texture', (None, None, 3))
-        desc = np.zeros((max(n, 1), 6), dtype=np.int64)  # src byte offset, x0, y0, w, h, first uv row
+        desc = np.zeros((max(n, 1), 9), dtype=np.int64)  # src byte offset, x0, y0, w, h, first uv row, src pitch, uv shift
         row_first, row_y0 = np.zeros(n_rows + 1, dtype=np.int64), np.zeros(n_rows + 1, dtype=np.int64)
         src_off = uv_row = canvas_h = canvas_w = 0
         for i in range(n_rows):
@@ -159,7 +160,7 @@ class Pipeline:
             x0 = row_h = 0
             for k in range(first, end):
                 h, w = textures[k].shape[:2]
-                desc[k] = (src_off, x0, canvas_h, w, h, uv_row)
+                desc[k] = (src_off, x0, canvas_h, w, h, uv_row, w, 0, 0)
                 src_off += h * w * 3
                 uv_row += len(uvs_atlas[k])
                 x0 += w
@@ -266,9 +267,12 @@ class FrameMesh:
         return self.texture is None
 
 
-def process_frame(rgb, depth, mask_encoded, pose, camera_matrix, dilation_options=None, filtering_options=None,
-                  disable_coverage_constraint=False, diags=None) -> FrameMesh:
-    """The per-frame foreground mesh step, ``process_frame`` of pipeline.py:340-484, for the dynamic objects
+def process_frame_stepwise(rgb, depth, mask_encoded, pose, camera_matrix, dilation_options=None, filtering_options=None,
+                           disable_coverage_constraint=False, diags=None) -> FrameMesh:
+    """``process_frame`` composed from the reference-shaped static methods, every one of which takes and returns host arrays
+    (five host <-> device round trips per object).  Kept as the A/B partner of ``process_frame`` (same result, tests).
+
+    The per-frame foreground mesh step, ``process_frame`` of pipeline.py:340-484, for the dynamic objects
     (``include_background=False``): for every instance id in the mask -- dilate its mask, skip it below 1 % coverage,
     back-project + triangulate + filter (one fused CUDA call), skip below 9 vertices or without faces, drop floaters
     (largest face component), crop the texture and the UVs -- then pack the crops into the frame's atlas.
@@ -356,3 +360,122 @@ def process_clip(n_frames, load_frame, camera_matrix, dilation_options=None, fil
         out[part_start:part_start + len(part)] = part
     assert all(m is not None for m in out), "process_clip: a frame is missing from the gather"
     return out
+
+
+def process_frame(rgb, depth, mask_encoded, pose, camera_matrix, dilation_options=None, filtering_options=None,
+                  disable_coverage_constraint=False, diags=None) -> FrameMesh:
+    """The per-frame foreground mesh step, ``process_frame`` of pipeline.py:340-484, for the dynamic objects
+    (``include_background=False``), with the objects' data resident in HBM from the mask to the atlas: all object masks are
+    dilated in one batch, their coverage counted on the device, the surviving objects meshed in one batched depth-to-mesh
+    call, cleaned (components + vertex compaction) and projected on the device, and the atlas is cut straight out of the
+    frame.  The host sees four small read-backs per FRAME (coverage counts, mesh sizes, cleaned sizes, crop boxes: a few
+    integers per object -- every one decides what is launched next) and one download of the result; the step-wise
+    composition (``process_frame_stepwise``) moves every object's arrays across PCIe five times.  Same skip rules, same
+    result.  Not performed: mesh decimation (OpenMesh's sequential edge collapse) and the billboard flattening.
+    """
+    from . import image_processing
+    torch = _lib.require_cuda()
+    lib = _lib.load()
+    dilation_options = dilation_options or image_processing.MaskDilationOptions(num_iterations=0)
+    filtering_options = filtering_options or MeshFilteringOptions()
+    rgb = np.ascontiguousarray(np.asarray(rgb)[:, :, :3])
+    depth, mask_encoded = np.asarray(depth), np.asarray(mask_encoded)
+    H, W = depth.shape
+    rotation, translation = geometric.get_pose_components(np.asarray(pose))
+    empty = FrameMesh(np.zeros((0, 3)), np.zeros((0, 3)))
+    n_obj = int(mask_encoded.max())
+    if n_obj < 1:
+        return empty
+    n_iter = image_processing._check_filter(dilation_options)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    with torch.cuda.device(dev):
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        depth_d = _xfer.to_device(depth[None], dev, np.float32)
+        rgb_d = _xfer.to_device(rgb, dev, np.uint8)
+        # ---- masks of all objects: dilate (one batch), coverage (pipeline.py:370-381)
+        ids = np.arange(1, n_obj + 1)
+        masks_d = image_processing.dilate_masks_device(
+            _xfer.to_device(mask_encoded[None] == ids[:, None, None], dev, np.uint8), n_iter)
+        counts = torch.empty(n_obj, dtype=torch.int64, device=dev)
+        _lib.check(lib.hv_count_nonzero(_ptr(masks_d), n_obj, H * W, _ptr(counts), stream))
+        coverage = counts.cpu().numpy() / float(H * W)                                             # read-back 1
+        cand = [k for k in range(n_obj) if disable_coverage_constraint or not coverage[k] < 0.01]
+        if not cand:
+            return empty
+        # ---- back-projection + triangulation + face filter of the candidates, one batched call (pipeline.py:386-409)
+        B = len(cand)
+        sel = masks_d if B == n_obj else masks_d[torch.as_tensor(cand, device=dev)]
+        diag_d = None
+        if diags is not None:
+            diag_h = np.stack([np.asarray(diags[int(ids[k])], dtype=np.uint8).reshape(H, W) if int(ids[k]) in diags
+                               else np.zeros((H, W), np.uint8) for k in cand])
+            diag_d = _xfer.to_device(diag_h, dev, np.uint8)
+        cam = np.concatenate([np.asarray(rotation, dtype=np.float64).reshape(9), np.asarray(translation, dtype=np.float64).reshape(3)])
+        cams_d = _xfer.to_device(np.tile(cam, (B, 1)), dev, np.float64)
+        batch = geometric.depth_to_mesh_device(depth_d.expand(B, H, W).contiguous(), sel, geometric._kinv64(camera_matrix),
+                                               cams_d, filtering_options.max_depth_distance,
+                                               geometric.d2m_flags(filtering_options.max_pixel_distance), diag_d,
+                                               want_points=False)                                  # read-back 2
+        off = batch.frame_offsets
+        alive = [j for j in range(B) if off[j + 1, 0] - off[j, 0] >= 9 and off[j + 1, 1] - off[j, 1] >= 1]
+        if not alive:
+            return empty
+        # ---- floater removal + vertex compaction per object, on its slice of the batch (pipeline.py:741-779)
+        parts, counts4 = [], torch.zeros((len(alive), 4), dtype=torch.int64, device=dev)
+        for i, j in enumerate(alive):
+            v0, f0 = (int(v) for v in off[j])
+            nv, nf = int(off[j + 1, 0]) - v0, int(off[j + 1, 1]) - f0
+            nbytes = ctypes.c_int64(0)
+            _lib.check(lib.hv_cc_cleanup_scratch_bytes(nf, nv, ctypes.byref(nbytes)))
+            scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+            sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
+            v_out = torch.empty((nv, 3), dtype=torch.float64, device=dev)
+            f_out = torch.empty((nf, 3), dtype=torch.int32, device=dev)
+            _lib.check(lib.hv_cc_cleanup(_ptr(batch.faces[f0:f0 + nf]), nf, _ptr(batch.verts[v0:v0 + nv]), nv,
+                                         int(filtering_options.min_num_components), 1, _ptr(v_out), _ptr(f_out),
+                                         _ptr(counts4[i]), sptr, int(nbytes.value), stream))
+            parts.append((v_out, f_out, scratch))
+        sizes = counts4.cpu().numpy()                                                              # read-back 3
+        # ---- projection into the frame, crop box (pipeline.py:782-808)
+        cam21 = torch.from_numpy(geometric._cam21(np.asarray(camera_matrix, dtype=np.float64), rotation, translation)).to(dev)
+        boxes = torch.empty((len(alive), 4), dtype=torch.int64, device=dev)
+        uvs = []
+        for i, (v_out, f_out, _) in enumerate(parts):
+            nk = int(sizes[i, 0])
+            uv = torch.empty((nk, 2), dtype=torch.float64, device=dev)
+            zc = torch.empty((nk,), dtype=torch.float64, device=dev)
+            _lib.check(lib.hv_world2image(_ptr(v_out), nk, _ptr(cam21), 1.0, 1, _ptr(uv), _ptr(zc), stream))
+            _lib.check(lib.hv_uv_bbox(_ptr(uv), nk, _ptr(boxes[i]), stream))
+            uvs.append(uv)
+        box = boxes.cpu().numpy()                                                                  # read-back 4
+        # ---- atlas (pipeline.py:810-868 with n_rows = 1): layout on the host, pixels straight out of the frame
+        n = len(alive)
+        desc = np.zeros((n, 9), dtype=np.int64)
+        x0 = canvas_h = uv_row = 0
+        for i in range(n):
+            min_u, min_v, max_u, max_v = (int(v) for v in box[i])
+            assert min_u >= 0 and min_v >= 0, "a vertex projects left of / above the frame"
+            w, h = max(min(max_u + 1, W) - min_u, 0), max(min(max_v + 1, H) - min_v, 0)  # numpy slicing clips at the frame
+            desc[i] = ((min_v * W + min_u) * 3, x0, 0, w, h, uv_row, W, min_u, min_v)
+            x0 += w
+            canvas_h = max(canvas_h, h)
+            uv_row += int(sizes[i, 0])
+        canvas_w = x0
+        rows = np.array([0, n, 0, canvas_h], dtype=np.int64)  # row_first, row_y0 of the single row
+        d_desc, d_rows = _xfer.to_device(desc, dev, np.int64), _xfer.to_device(rows, dev, np.int64)
+        uv_all = torch.cat(uvs)
+        atlas = torch.empty((canvas_h, canvas_w, 3), dtype=torch.uint8, device=dev)
+        uv_out = torch.empty((uv_row, 2), dtype=torch.float64, device=dev)
+        _lib.check(lib.hv_atlas_pack(_ptr(rgb_d), _ptr(d_desc), n, _ptr(d_rows), ctypes.c_void_p(d_rows.data_ptr() + 16), 1,
+                                     canvas_h, canvas_w, _ptr(atlas) if atlas.numel() else None, _ptr(uv_all), uv_row,
+                                     _ptr(uv_out), stream))
+        verts_all = torch.cat([parts[i][0][:int(sizes[i, 0])] for i in range(n)])
+        faces_dev = [parts[i][1][:int(sizes[i, 2])] for i in range(n)]
+        host = _xfer.to_host(verts_all, atlas, uv_out, *faces_dev)                                 # the download
+    frame_vertices, packed_textures, packed_uv = host[0], host[1], host[2]
+    frame_faces, vertex_count = np.zeros((0, 3)), 0
+    for i in range(n):
+        frame_faces = np.vstack((frame_faces, host[3 + i] + vertex_count))  # float64 like the reference's stacking
+        vertex_count += int(sizes[i, 0])
+    kept_ids = tuple(int(ids[cand[j]]) for j in alive)
+    return FrameMesh(frame_vertices, frame_faces, packed_textures, packed_uv, kept_ids)

@@ -274,13 +274,18 @@ int hv_keyframe_overlap(const float* depth, const uint8_t* mask, int H, int W, c
  * lut: 256 device bytes. */
 int hv_byte_lut(uint8_t* bytes, int64_t n, const uint8_t* lut, void* stream);
 
+/* np.count_nonzero per mask of a batch (the 1 % coverage rule, hive/pipeline.py:377): counts = DEVICE uint64 [B]. */
+int hv_count_nonzero(const uint8_t* masks, int B, int64_t n, unsigned long long* counts, void* stream);
+/* box (DEVICE int64 [4]) = min u, min v, max u, max v over uv rows holding integers (hive/pipeline.py:797-800). */
+int hv_uv_bbox(const double* uv, int64_t n, int64_t* box, void* stream);
 /* Texture atlas of a frame's objects, the pixel and UV work of Pipeline._pack_textures (hive/pipeline.py:810-868); the
- * placement (a few integers per crop) is the host's.  src: the crops' (h, w, 3) uint8 pixels back to back; desc[t] =
- * {byte offset in src, x0, y0, w, h, first row of the crop's UVs in `uv`} (int64 x 6); rows r = 0..n_rows-1 hold crops
- * row_first[r] .. row_first[r+1]-1 (in x order) and start at canvas row row_y0[r] (both n_rows+1 entries).
- * atlas: (canvas_h, canvas_w, 3) uint8, every byte written (black where no crop lies).  uv: (n_uv, 2) float64 crop-local
- * pixel coordinates; uv_out[i] = ((u + x0) / canvas_w, 1 - (v + y0) / canvas_h) (pipeline.py:837, 857, 865-866).
- * All pointers device. */
+ * placement (a few integers per crop) is the host's.  src: uint8 pixels the crops are read from -- the crops back to back,
+ * or the frame itself; desc[t] = {byte offset of the crop's first pixel in src, x0, y0, w, h, first row of the crop's UVs
+ * in `uv`, row pitch of the crop in src in pixels (w, or the frame's width), u shift, v shift} (int64 x 9); rows
+ * r = 0..n_rows-1 hold crops row_first[r] .. row_first[r+1]-1 (in x order) and start at canvas row row_y0[r] (both
+ * n_rows+1 entries).  atlas: (canvas_h, canvas_w, 3) uint8, every byte written (black where no crop lies).  uv: (n_uv, 2)
+ * float64 pixel coordinates; uv_out[i] = (((u - u shift) + x0) / canvas_w, 1 - ((v - v shift) + y0) / canvas_h)
+ * (pipeline.py:806, 837, 857, 865-866).  All pointers device. */
 int hv_atlas_pack(const uint8_t* src, const int64_t* desc, int n_tex, const int64_t* row_first, const int64_t* row_y0,
                   int n_rows, int canvas_h, int canvas_w, uint8_t* atlas, const double* uv, int64_t n_uv, double* uv_out,
                   void* stream);
@@ -300,6 +305,12 @@ int hv_cc_mask(const int32_t* faces, int64_t n_faces, int64_t n_verts, int min_l
 /* The vertices `faces_all` refer to, in their original order, into verts_out (float64 [n_verts][3] capacity), `faces_keep`
  * renumbered accordingly into faces_out; d_count[0..1] (DEVICE, 2 x uint64): [0] = vertices kept.  What building
  * trimesh.Trimesh(vertices, faces) does to unreferenced vertices before the components are taken (pipeline.py:758). */
+/* hv_cc_mask + the compaction above in one call on device arrays (no host hop between the steps): verts_out / faces_out have
+ * the capacity of the inputs; d_counts (DEVICE, 4 x uint64): [0] = vertices kept, [2] = faces kept. */
+int hv_cc_cleanup_scratch_bytes(int64_t n_faces, int64_t n_verts, int64_t* h_bytes);
+int hv_cc_cleanup(const int32_t* faces, int64_t n_faces, const double* verts_in, int64_t n_verts, int min_len, int largest_only,
+                  double* verts_out, int32_t* faces_out, unsigned long long* d_counts, void* scratch, int64_t scratch_bytes,
+                  void* stream);
 int hv_cc_compact_scratch_bytes(int64_t n_verts, int64_t* h_bytes);
 int hv_cc_compact_vertices(const int32_t* faces_all, int64_t n_faces_all, const int32_t* faces_keep, int64_t n_faces_keep,
                            const double* verts_in, int64_t n_verts, double* verts_out, int32_t* faces_out,

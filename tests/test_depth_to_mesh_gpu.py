@@ -360,3 +360,24 @@ def test_process_clip_partitions_equal_the_frame_loop():
         for a, b in zip(got, whole):
             assert np.array_equal(a.vertices, b.vertices) and np.array_equal(a.faces, b.faces)
             assert a.is_empty == b.is_empty and (a.is_empty or (np.array_equal(a.texture, b.texture) and np.array_equal(a.uv, b.uv)))
+
+
+@pytest.mark.parametrize("config,index,dilation,disable_coverage", [("small", 1, 0, False), ("small", 2, 2, True),
+                                                                    ("tiny", 3, 1, True)])
+def test_process_frame_device_resident_equals_stepwise(config, index, dilation, disable_coverage):
+    """The device-resident per-frame step and the composition of the reference-shaped static methods (host arrays between
+    every step) give the same FrameMesh, bit for bit."""
+    from hive_b200 import image_processing, pipeline
+    scene, fr, R, t = _frame(config, index)
+    pose = np.eye(4)
+    pose[:3, :3], pose[:3, 3:] = R, t
+    mask = _with_small_blobs(fr.mask, fr.depth)
+    args = (fr.rgb, fr.depth, mask, pose, scene.K, image_processing.MaskDilationOptions(num_iterations=dilation),
+            pipeline.MeshFilteringOptions())
+    a = pipeline.process_frame(*args, disable_coverage_constraint=disable_coverage)
+    b = pipeline.process_frame_stepwise(*args, disable_coverage_constraint=disable_coverage)
+    assert a.object_ids == b.object_ids and a.is_empty == b.is_empty
+    assert a.vertices.dtype == b.vertices.dtype and np.array_equal(a.vertices, b.vertices)
+    assert a.faces.dtype == b.faces.dtype and np.array_equal(a.faces, b.faces)
+    if not a.is_empty:
+        assert np.array_equal(a.texture, b.texture) and np.array_equal(a.uv, b.uv)
