@@ -598,6 +598,21 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
                "kind": "port", "host": host_cpu(), "frames": [n1, B],
                "what": "oracle/d2m_oracle.py = hive.geometric.point_cloud_from_depth + scipy.spatial.Delaunay + "
                        "Pipeline._filter_faces (hive/pipeline.py:386-409), ThreadPool as hive/pipeline.py:491"}
+    pf = None
+    if rank == 0 and world == 1:
+        # the composed per-frame step (hive/pipeline.py:340-484): objects resident in HBM vs host arrays between the steps
+        from hive_b200 import image_processing, pipeline
+        dil = image_processing.MaskDilationOptions(num_iterations=2)
+        pf = {}
+        for name, fn in (("stepwise_ms_per_frame", pipeline.process_frame_stepwise), ("ms_per_frame", pipeline.process_frame)):
+            for rep in range(2):  # first pass warms the allocators
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for f in fr[:6]:
+                    mesh_f = fn(f.rgb, f.depth, f.mask, np.linalg.inv(f.pose), sc.K, dil)
+                pf[name] = 1e3 * (time.perf_counter() - t0) / len(fr[:6])
+        pf["vertices_last_frame"] = int(len(mesh_f.vertices))
+        pf["api"] = "hive_b200.pipeline.process_frame(rgb, depth, mask_encoded, pose, K, ...): host frame in, FrameMesh (vertices, faces, atlas, uv) out"
     algo_survey = 5.0 * H * W * B + 24.0 * V + 12.0 * F  # without the optional (u, v, depth) outputs
     return {"frames_per_s": world * B / (ms / 1e3), "ms_per_batch": ms, "frames_per_batch_per_gpu": B,
             "vertices": V, "faces": F, "achieved_gbs": algo_survey / (ms / 1e3) / 1e9,
@@ -605,7 +620,7 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
             "roofline_frac_with_points2d": algo / (ms / 1e3) / 1e9 / peak,
             "roofline_note": "roofline_frac uses SURVEY 8(d)'s 5*H*W + 24*V + 12*F; the kernel also writes 12 B/vertex of "
                              "(u, v, depth) for _filter_faces' callers, counted in roofline_frac_with_points2d",
-            "cpu_baseline": cpu, "e2e_frames_per_s": float(e2e_fps),
+            "cpu_baseline": cpu, "e2e_frames_per_s": float(e2e_fps), "process_frame": pf,
             "h2d_bytes": int(depths.nbytes + masks.nbytes), "d2h_bytes": int(hv.nbytes + hf.nbytes + hp.nbytes + hd.nbytes),
             "workload": f"{B} frames/GPU of {W}x{H}, instance masks of the room scene, frame-partitioned"}
 
