@@ -804,10 +804,10 @@ __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x,
 // Index of the edge vertex owned by voxel (xo, yo, zo) on `axis`: the tile's and the batch's base + the group's first vertex,
 // plus the vertices of lower voxels, plus lower axes of its own -- one 16-byte load and two hot small-table entries.
 __device__ __forceinline__ unsigned int edge_vertex_index(const McGrid& g, int xo, int yo, int zo, int axis) {
-    const size_t og = ((size_t)xo * g.Y + yo) * g.G + (zo >> 5);
+    const unsigned int og = ((unsigned int)xo * (unsigned int)g.Y + (unsigned int)yo) * (unsigned int)g.G + (unsigned int)(zo >> 5);  // < 2^31
     const int bit = zo & 31;
     const uint4 m = __ldg(g.gtab + og);
-    const size_t ot = og / kTileGroups;
+    const unsigned int ot = og / kTileGroups;
     const unsigned int base = __ldg(&g.tile_base[ot].x) + __ldg(&g.batch_base[ot * kTileBatches + (m.x >> 12)].x);
     const unsigned int low = (1u << bit) - 1u;
     unsigned int r = base + (m.x & 4095u) + __popc(m.y & low) + __popc(m.z & low) + __popc(m.w & low);
@@ -1194,10 +1194,12 @@ __global__ void __launch_bounds__(kEmitThreads, (WHOLE && LEVEL0) ? 4 : 3)
                    const unsigned int n_vert_blocks) {
     cudaGridDependencySynchronize();
     if (g.totals[6]) return;  // the records are incomplete: the host re-runs the count with a larger work buffer
-    const unsigned long long b = blockIdx.x, n = (unsigned long long)n_tri_blocks + n_vert_blocks;
-    const unsigned int t_before = (unsigned int)(b * n_tri_blocks / n), t_after = (unsigned int)((b + 1) * n_tri_blocks / n);
+    // (32-bit: the host keeps the grid below 2^16 blocks, so b * n_tri_blocks < 2^32; the 64-bit divisions were 7 % of the
+    //  kernel's instructions)
+    const unsigned int b = blockIdx.x, n = n_tri_blocks + n_vert_blocks;
+    const unsigned int t_before = b * n_tri_blocks / n, t_after = (b + 1u) * n_tri_blocks / n;
     if (t_after > t_before) emit_cubes(g, out, t_before, n_tri_blocks);
-    else emit_vertices<WHOLE, LEVEL0>(g, out, (unsigned int)b - t_before, n_vert_blocks);
+    else emit_vertices<WHOLE, LEVEL0>(g, out, b - t_before, n_vert_blocks);
 }
 
 // ---- z-slab placement (hive_b200/sharded.py): where does a slab's mesh go in the mesh of the whole volume? --------------------
