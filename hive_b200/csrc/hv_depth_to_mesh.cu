@@ -33,27 +33,30 @@ struct D2mGrid {
     float max_depth_distance;
     int bridges;
     int verts_only;        // skip triangulation (point_cloud_from_depth)
+    uint8_t* slots;        // [B][H][W] which of a pixel's eight candidate faces exist (count -> emit), written where a word row has faces
     unsigned int* wbits;   // [n_words] valid bits
     uint2* wcount;         // [n_words] (vertices, faces)
     uint2* woff;           // [n_words] exclusive prefix
     uint2* bsum;
 };
 
+// The faces a pixel (u, v) can own, in the order they are emitted, as corner triples over the six pixels 0 = (u, v),
+// 1 = (u+1, v), 2 = (u, v+1), 3 = (u+1, v+1), 4 = (u, v-1), 5 = (u-1, v); winding with negative signed area in (u, v):
+//   quad:  slot 0 (A, D, B)   1 (A, C, D)   [main diagonal]      2 (A, C, B)   3 (B, C, D)   [anti-diagonal]
+//   hole:  slot 4 (W, E, N)   5 (W, S, E)   [split W-E]          6 (N, S, E)   7 (N, W, S)   [split N-S]
+// A quad / hole with three of its four vertices gives the one triangle of these that avoids the missing one.  The count
+// kernel decides which slots exist (validity, diagonal, depth filter) and leaves the slot mask -- one byte -- for the emit
+// kernel, which therefore needs neither the neighbourhood depths nor the tests again.  (r01: both kernels enumerated the
+// faces; the emit kernel spent ~680 warp-instructions per word row.)
 struct PixelFaces {
     int n;
-    // Corners of the (at most four) faces, winding with negative signed area in (u, v).  Every corner is one of six
-    // pixels around the owner (corner_code), so a corner is 4 bits, a face 12, and the whole set one register pair -- as
-    // int2 p[4][3] indexed by the running face count it lived in local memory (104-byte stack frame, a store and a
-    // load per corner in the emit loop).
-    unsigned long long codes;
+    unsigned int slots;
 };
-
-// Which of the six pixels a face of (u, v) can touch: 0 = (u, v), 1 = (u+1, v), 2 = (u, v+1), 3 = (u+1, v+1), 4 = (u, v-1),
-// 5 = (u-1, v).  (Call sites pass constants relative to (u, v): this folds at compile time.)
-__device__ __forceinline__ unsigned int corner_code(int2 p, int u, int v) {
-    const int du = p.x - u, dv = p.y - v;
-    return dv == 0 ? (du == 0 ? 0u : (du == 1 ? 1u : 5u)) : (dv == 1 ? (du == 0 ? 2u : 3u) : 4u);
-}
+// corner ids of the quad slots 0..3 and the hole slots 4..7, 3 bits per corner, 9 per slot
+constexpr unsigned long long kQuadCorners = (0ull | 3ull << 3 | 1ull << 6) | (0ull | 2ull << 3 | 3ull << 6) << 9 |
+                                            (0ull | 2ull << 3 | 1ull << 6) << 18 | (1ull | 2ull << 3 | 3ull << 6) << 27;
+constexpr unsigned long long kHoleCorners = (5ull | 1ull << 3 | 4ull << 6) | (5ull | 2ull << 3 | 1ull << 6) << 9 |
+                                            (4ull | 2ull << 3 | 1ull << 6) << 18 | (4ull | 5ull << 3 | 2ull << 6) << 27;
 
 // Depth of pixel (u, v) if it is a vertex (inside the image, mask set, depth > 0: geometric.py:117), else 0.
 __device__ __forceinline__ float d2m_vdepth(const D2mGrid& g, int b, int u, int v) {
@@ -148,62 +151,55 @@ __device__ __forceinline__ bool depth_ok(const D2mGrid& g, float a, float b, flo
            fabsf(__fsub_rn(a, c)) <= g.max_depth_distance;
 }
 
-__device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, bool keep_coords, int u, int v, int2 a,
-                                          float da, int2 b, float db, int2 c, float dc) {
+__device__ __forceinline__ void push_face(const D2mGrid& g, PixelFaces& f, int slot, float da, float db, float dc) {
     if (!depth_ok(g, da, db, dc)) return;
-    if (keep_coords) {
-        const unsigned int face = corner_code(a, u, v) | (corner_code(b, u, v) << 4) | (corner_code(c, u, v) << 8);
-        f.codes |= (unsigned long long)face << (12 * f.n);
-    }
+    f.slots |= 1u << slot;
     ++f.n;
 }
 
 // Faces owned by pixel (u, v): the quad whose top-left corner it is, and -- if the pixel itself is absent -- the hole
 // around it.
-__device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int v, const Hood& h, bool keep_coords,
-                                            PixelFaces& f) {
+__device__ __forceinline__ void pixel_faces(const D2mGrid& g, int b, int u, int v, const Hood& h, PixelFaces& f) {
     f.n = 0;
-    f.codes = 0ull;
+    f.slots = 0u;
     if (u >= g.W) return;
     const unsigned int ov = g.diag ? g.diag[((size_t)b * g.H + v) * g.W + u] : 0u;
-    const float d_self = h.c, db = h.e, dc = h.s, dd = h.se;
-    const bool self_valid = d_self > 0.0f, vb = db > 0.0f, vc = dc > 0.0f, vd = dd > 0.0f;
-    const int2 A = make_int2(u, v), Bp = make_int2(u + 1, v), C = make_int2(u, v + 1), D = make_int2(u + 1, v + 1);
-    const int nq = (int)self_valid + (int)vb + (int)vc + (int)vd;
+    const float da = h.c, db = h.e, dc = h.s, dd = h.se;  // A = (u, v), B = (u+1, v), C = (u, v+1), D = (u+1, v+1)
+    const bool va = da > 0.0f, vb = db > 0.0f, vc = dc > 0.0f, vd = dd > 0.0f;
+    const int nq = (int)va + (int)vb + (int)vc + (int)vd;
     if (nq == 4) {
-        const bool anti = g.diag ? (ov & 1u) : !(fabsf(__fsub_rn(d_self, dd)) <= fabsf(__fsub_rn(db, dc)));
+        const bool anti = g.diag ? (ov & 1u) : !(fabsf(__fsub_rn(da, dd)) <= fabsf(__fsub_rn(db, dc)));
         if (!anti) {
-            push_face(g, f, keep_coords, u, v, A, d_self, D, dd, Bp, db);
-            push_face(g, f, keep_coords, u, v, A, d_self, C, dc, D, dd);
+            push_face(g, f, 0, da, dd, db);
+            push_face(g, f, 1, da, dc, dd);
         } else {
-            push_face(g, f, keep_coords, u, v, A, d_self, C, dc, Bp, db);
-            push_face(g, f, keep_coords, u, v, Bp, db, C, dc, D, dd);
+            push_face(g, f, 2, da, dc, db);
+            push_face(g, f, 3, db, dc, dd);
         }
     } else if (nq == 3) {
-        if (!vd) push_face(g, f, keep_coords, u, v, A, d_self, C, dc, Bp, db);
-        else if (!self_valid) push_face(g, f, keep_coords, u, v, Bp, db, C, dc, D, dd);
-        else if (!vb) push_face(g, f, keep_coords, u, v, A, d_self, C, dc, D, dd);
-        else push_face(g, f, keep_coords, u, v, A, d_self, D, dd, Bp, db);
+        if (!vd) push_face(g, f, 2, da, dc, db);
+        else if (!va) push_face(g, f, 3, db, dc, dd);
+        else if (!vb) push_face(g, f, 1, da, dc, dd);
+        else push_face(g, f, 0, da, dd, db);
     }
-    if (!self_valid && g.bridges) {
+    if (!va && g.bridges) {
         const float dn = h.n, de = h.e, ds = h.s, dw = h.w;
         const bool vn = dn > 0.0f, ve = de > 0.0f, vs = ds > 0.0f, vw = dw > 0.0f;
-        const int2 N = make_int2(u, v - 1), E = make_int2(u + 1, v), S = make_int2(u, v + 1), Wp = make_int2(u - 1, v);
         const int nh = (int)vn + (int)ve + (int)vs + (int)vw;
         if (nh == 4) {
             const bool vertical = g.diag ? ((ov >> 1) & 1u) : !(fabsf(__fsub_rn(dw, de)) <= fabsf(__fsub_rn(dn, ds)));
             if (!vertical) {
-                push_face(g, f, keep_coords, u, v, Wp, dw, E, de, N, dn);
-                push_face(g, f, keep_coords, u, v, Wp, dw, S, ds, E, de);
+                push_face(g, f, 4, dw, de, dn);
+                push_face(g, f, 5, dw, ds, de);
             } else {
-                push_face(g, f, keep_coords, u, v, N, dn, S, ds, E, de);
-                push_face(g, f, keep_coords, u, v, N, dn, Wp, dw, S, ds);
+                push_face(g, f, 6, dn, ds, de);
+                push_face(g, f, 7, dn, dw, ds);
             }
         } else if (nh == 3) {
-            if (!vn) push_face(g, f, keep_coords, u, v, Wp, dw, S, ds, E, de);
-            else if (!vs) push_face(g, f, keep_coords, u, v, Wp, dw, E, de, N, dn);
-            else if (!ve) push_face(g, f, keep_coords, u, v, N, dn, Wp, dw, S, ds);
-            else push_face(g, f, keep_coords, u, v, N, dn, S, ds, E, de);
+            if (!vn) push_face(g, f, 5, dw, ds, de);
+            else if (!vs) push_face(g, f, 4, dw, de, dn);
+            else if (!ve) push_face(g, f, 7, dn, dw, ds);
+            else push_face(g, f, 6, dn, ds, de);
         }
     }
 }
@@ -272,8 +268,9 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_count_kernel(const D2mGrid g)
         if (faces && !hood_empty(cur, next)) {
             const Hood h = make_hood(prev, cur, next, lane);
             PixelFaces f;
-            pixel_faces(g, b, cw * 32 + lane, v, h, false, f);
+            pixel_faces(g, b, cw * 32 + lane, v, h, f);
             nf = (unsigned int)f.n;
+            if (cw * 32 + lane < g.W) g.slots[((size_t)b * g.H + v) * g.W + cw * 32 + lane] = (uint8_t)f.slots;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) nf += __shfl_xor_sync(0xffffffffu, nf, o);
         }
@@ -299,6 +296,7 @@ struct D2mOut {
 };
 
 __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, const D2mOut out) {
+    __shared__ unsigned int s_rank[6][kD2mThreads];
     const int lane = threadIdx.x & 31;
     const int cw = (int)blockIdx.x * (kD2mThreads / 32) + (int)(threadIdx.x >> 5);
     if (cw >= g.wpr) return;
@@ -315,98 +313,96 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
             out.frame_off[2 * g.B + 1] = (long long)out.n_faces;
         }
     }
-    // counts of the warp's words (lane r holds row v0 + r): most word columns are empty and leave here
-    uint2 my_cnt = make_uint2(0u, 0u);
+    // counts (lane r holds row v0 + r), prefix offsets and vertex bits (lane l holds row v0 - 1 + l) of the warp's words and
+    // the frame's first offset: all requested together -- most word columns are empty and leave right after
+    uint2 my_cnt = make_uint2(0u, 0u), my_off = make_uint2(0u, 0u);
+    unsigned int my_bits = 0u;
     if (lane < v1 - v0) my_cnt = g.wcount[w0 + (size_t)lane * g.wpr];
-    const unsigned int has_v = __ballot_sync(0xffffffffu, my_cnt.x != 0u), has_f = __ballot_sync(0xffffffffu, my_cnt.y != 0u);
-    if ((has_v | has_f) == 0u) return;
-    const unsigned int vbase = g.woff[wframe].x;
-
-    Row prev, cur, next;
-    RawRow raw_next;
-    if (has_f) {
-        const RawRow q0 = load_raw(g, b, v0 - 1, cw, lane), q1 = load_raw(g, b, v0, cw, lane);
-        raw_next = load_raw(g, b, v0 + 1, cw, lane);
-        prev = finish_row(q0);
-        cur = finish_row(q1);
-    }
-    // prefix offsets of the word in rows v0 - 1 .. v1 (lane l holds row v0 - 1 + l): one load up front instead of three
-    // dependent loads per row inside the loop
-    uint2 my_off = make_uint2(0u, 0u);
     {
         const int row = v0 - 1 + lane;
-        if (lane < (v1 - v0) + 2 && row >= 0 && row < g.H) my_off = g.woff[wframe + (size_t)row * g.wpr + cw];
+        if (lane < (v1 - v0) + 2 && row >= 0 && row < g.H) {
+            my_off = g.woff[wframe + (size_t)row * g.wpr + cw];
+            my_bits = g.wbits[wframe + (size_t)row * g.wpr + cw];
+        }
     }
+    const unsigned int vbase = g.woff[wframe].x;
+    const unsigned int has_v = __ballot_sync(0xffffffffu, my_cnt.x != 0u), has_f = __ballot_sync(0xffffffffu, my_cnt.y != 0u);
+    if ((has_v | has_f) == 0u) return;
     const int u = cw * 32 + lane;
-    for (int r = 0; r < v1 - v0; ++r) {
+    const unsigned int lt = (1u << lane) - 1u;
+    // slot byte and depth of the lane's pixel in every row that has something, all requested before the first is used
+    // (r02 ncu: with one load per row inside the loop the kernel sat at 44 % issue utilisation, 12 stall cycles per
+    // instruction on those loads)
+    unsigned int sl_row[kD2mRows];
+    float d_row[kD2mRows];
+    double cam[12];  // R row-major, t of this frame: once per warp, not once per row
+#pragma unroll
+    for (int k = 0; k < 12; ++k) cam[k] = __ldg(out.cams + 12 * (size_t)b + k);
+#pragma unroll
+    for (int r = 0; r < kD2mRows; ++r) {
+        const size_t px = ((size_t)b * g.H + (v0 + r)) * g.W + u;
+        sl_row[r] = (((has_f >> r) & 1u) && u < g.W) ? g.slots[px] : 0u;
+        d_row[r] = (((has_v >> r) & 1u) && u < g.W) ? __ldg(g.depth + px) : 0.0f;
+    }
+#pragma unroll
+    for (int r = 0; r < kD2mRows; ++r) {
+        if (!(((has_v | has_f) >> r) & 1u)) continue;
         const int v = v0 + r;
-        const size_t w = w0 + (size_t)r * g.wpr;
-        if (has_f) {
-            const RawRow raw_next2 = load_raw(g, b, v + 2 <= v1 ? v + 2 : -1, cw, lane);  // prefetch, used next iteration
-            next = finish_row(raw_next);
-            raw_next = raw_next2;
-        }
-        if (((has_v | has_f) >> r) & 1u) {
-            const uint2 off = make_uint2(__shfl_sync(0xffffffffu, my_off.x, r + 1), __shfl_sync(0xffffffffu, my_off.y, r + 1));
-            // frame-local rank of the first pixel of the word in the rows above / of / below v
-            const unsigned int first_prev = v > 0 ? __shfl_sync(0xffffffffu, my_off.x, r) - vbase : 0u;
-            const unsigned int first_cur = off.x - vbase;
-            const unsigned int first_next = v + 1 < g.H ? __shfl_sync(0xffffffffu, my_off.x, r + 2) - vbase : 0u;
-            if ((has_f >> r) & 1u) {
-                const Hood h = make_hood(prev, cur, next, lane);
-                PixelFaces f;
-                pixel_faces(g, b, u, v, h, true, f);
-                unsigned int inc = (unsigned int)f.n;
+        const uint2 off = make_uint2(__shfl_sync(0xffffffffu, my_off.x, r + 1), __shfl_sync(0xffffffffu, my_off.y, r + 1));
+        const unsigned int bits = __shfl_sync(0xffffffffu, my_bits, r + 1);
+        if ((has_f >> r) & 1u) {
+            // the slot mask the count kernel left for this pixel: nothing is tested again
+            const unsigned int sl = sl_row[r];
+            const unsigned int nf = __popc(sl);
+            unsigned int inc = nf;
 #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += up;
-                }
-                size_t fi = (size_t)off.y + inc - (unsigned int)f.n;
-                unsigned long long codes = f.codes;
-                if (f.n) {
-                    // frame-local ranks of the six pixels the faces can touch, once per pixel (r01 derived the rank of
-                    // every corner of every face from its coordinates: ~25 instructions per corner, 28 % of this kernel).
-                    // A corner is always a vertex, so rank(u - 1) = rank(u) - 1 and rank(u + 1) = rank(u) + valid(u).
-                    const unsigned int lt = (1u << lane) - 1u;
-                    const unsigned int rc = first_cur + __popc(cur.bits & lt), rs = first_next + __popc(next.bits & lt);
-                    const unsigned int r0 = rc, r1 = rc + ((cur.bits >> lane) & 1u), r2 = rs, r3 = rs + ((next.bits >> lane) & 1u);
-                    const unsigned int r4 = first_prev + __popc(prev.bits & lt), r5 = rc - 1u;
-                    for (int k = 0; k < f.n; ++k, ++fi, codes >>= 12)
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int up = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += up;
+            }
+            // frame-local ranks (row-major rank among the frame's vertices, np.nonzero order, geometric.py:121) of the six
+            // pixels a face can touch, from the vertex bits of the word in the three rows and the ranks of their first
+            // pixels.  A corner is always a vertex, so rank(u - 1) = rank(u) - 1 and rank(u + 1) = rank(u) + valid(u).
+            const unsigned int bits_prev = __shfl_sync(0xffffffffu, my_bits, r), bits_next = __shfl_sync(0xffffffffu, my_bits, r + 2);
+            const unsigned int first_prev = __shfl_sync(0xffffffffu, my_off.x, r) - vbase, first_cur = off.x - vbase;
+            const unsigned int first_next = __shfl_sync(0xffffffffu, my_off.x, r + 2) - vbase;
+            if (sl) {
+                const unsigned int rc = first_cur + __popc(bits & lt), rs = first_next + __popc(bits_next & lt);
+                // the six ranks go through shared memory so that a corner is one indexed load (as a 6-way select chain
+                // they were 27 % of this kernel's instructions)
+                s_rank[0][threadIdx.x] = rc;
+                s_rank[1][threadIdx.x] = rc + ((bits >> lane) & 1u);
+                s_rank[2][threadIdx.x] = rs;
+                s_rank[3][threadIdx.x] = rs + ((bits_next >> lane) & 1u);
+                s_rank[4][threadIdx.x] = first_prev + __popc(bits_prev & lt);
+                s_rank[5][threadIdx.x] = rc - 1u;
+                size_t fi = (size_t)off.y + inc - nf;
+                for (unsigned int rest = sl; rest; rest &= rest - 1u, ++fi) {
+                    const int slot = __ffs(rest) - 1;
+                    const unsigned int code = (unsigned int)((slot < 4 ? kQuadCorners >> (9 * slot) : kHoleCorners >> (9 * (slot - 4))) & 511ull);
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            const unsigned int id = ((unsigned int)codes >> (4 * c)) & 7u;
-                            const unsigned int lo3 = id == 0u ? r0 : (id == 1u ? r1 : r2), hi3 = id == 3u ? r3 : (id == 4u ? r4 : r5);
-                            out.faces[3 * fi + c] = (int32_t)(id < 3u ? lo3 : hi3);
-                        }
+                    for (int c = 0; c < 3; ++c) out.faces[3 * fi + c] = (int32_t)s_rank[(code >> (3 * c)) & 7u][threadIdx.x];
                 }
             }
-            const unsigned int bits = has_f ? cur.bits : g.wbits[w];  // (the count kernel stored exactly cur.bits)
-            if ((bits >> lane) & 1u) {  // image2world, hive/geometric.py:200-204 (float64)
-                const float d = has_f ? cur.c : __ldg(g.depth + ((size_t)b * g.H + v) * g.W + u);
-                const size_t vi = off.x + __popc(bits & ((1u << lane) - 1u));
-                const double* R = out.cams + 12 * (size_t)b;
-                const double* t = R + 9;
-                const double du = (double)u, dv = (double)v, dd = (double)d;
-                double X[3];
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const double pc = fma(out.Kinv[3 * k + 2], 1.0, fma(out.Kinv[3 * k + 1], dv, __dmul_rn(out.Kinv[3 * k], du)));
-                    X[k] = __dsub_rn(__dmul_rn(dd, pc), t[k]);
-                }
-#pragma unroll
-                for (int k = 0; k < 3; ++k)  // R^T @ X
-                    out.verts[3 * vi + k] = fma(R[6 + k], X[2], fma(R[3 + k], X[1], __dmul_rn(R[k], X[0])));
-                if (out.points2d) {
-                    out.points2d[2 * vi] = u;
-                    out.points2d[2 * vi + 1] = v;
-                }
-                if (out.vdepth) out.vdepth[vi] = d;
-            }
         }
-        if (has_f) {
-            prev = cur;
-            cur = next;
+        if ((bits >> lane) & 1u) {  // image2world, hive/geometric.py:200-204 (float64)
+            const float d = d_row[r];
+            const size_t vi = off.x + __popc(bits & lt);
+            const double du = (double)u, dv = (double)v, dd = (double)d;
+            double X[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double pc = fma(out.Kinv[3 * k + 2], 1.0, fma(out.Kinv[3 * k + 1], dv, __dmul_rn(out.Kinv[3 * k], du)));
+                X[k] = __dsub_rn(__dmul_rn(dd, pc), cam[9 + k]);
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k)  // R^T @ X
+                out.verts[3 * vi + k] = fma(cam[6 + k], X[2], fma(cam[3 + k], X[1], __dmul_rn(cam[k], X[0])));
+            if (out.points2d) {
+                out.points2d[2 * vi] = u;
+                out.points2d[2 * vi + 1] = v;
+            }
+            if (out.vdepth) out.vdepth[vi] = d;
         }
     }
 }
@@ -508,7 +504,7 @@ namespace {
 struct D2mLayout {
     int wpr, words_per_frame;
     long long n_words;
-    size_t off_bits, off_count, off_off, off_bsum, total;
+    size_t off_bits, off_count, off_off, off_bsum, off_slots, total;
 };
 
 size_t d2m_align(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -528,6 +524,8 @@ int d2m_layout(int B, int H, int W, D2mLayout* L) {
     o = d2m_align(o + (size_t)L->n_words * sizeof(unsigned int));
     L->off_bsum = o;
     o = d2m_align(o + (size_t)hv::scan_scratch_pairs(L->n_words) * sizeof(uint2));
+    L->off_slots = o;
+    o = d2m_align(o + (size_t)B * H * W);
     L->total = o;
     return HV_OK;
 }
@@ -560,6 +558,7 @@ int d2m_grid(hv::D2mGrid* g, const float* depth, const uint8_t* mask, const uint
     g->wcount = reinterpret_cast<uint2*>(s + L->off_count);
     g->woff = reinterpret_cast<uint2*>(s + L->off_off);
     g->bsum = reinterpret_cast<uint2*>(s + L->off_bsum);
+    g->slots = reinterpret_cast<uint8_t*>(s + L->off_slots);
     return HV_OK;
 }
 
