@@ -209,3 +209,24 @@ def test_slab_halo_stitch_equals_whole_volume(n_slabs):
     assert len(wv) > 1000
     assert np.array_equal(verts, wv) and np.array_equal(faces, wf)
     assert np.array_equal(normals, wn) and np.array_equal(colors, wc)
+
+
+def test_one_call_extract_and_capacity_fallback():
+    """hv_mc_extract (count + emit in one library call): with room to spare it equals get_mesh; with a capacity far too
+    small it reports the sizes and the plan falls back to an exactly sized count + emit -- same mesh."""
+    from hive_b200 import marching_cubes as mc
+    from hive_b200.fusion import TSDFVolume
+    scene = Scene("small", "room")
+    vol = TSDFVolume(scene.vol_bnds.copy(), scene.voxel_size)
+    for i in range(4):
+        fr = scene.frame(i)
+        vol.integrate(fr.rgb, fr.depth, scene.K, fr.pose)
+    want = vol.get_mesh()
+    X, Y, Z = (int(d) for d in vol._local_dim)
+    for cap_v, cap_t in ((4 * len(want[0]), 4 * len(want[1])), (100, 100)):
+        plan = mc.McPlan(vol._tsdf_vol_gpu, vol._color_vol_gpu, (X, Y, Z), vol._pitch)
+        mesh = plan.extract(vol._voxel_size, vol._vol_origin, cap_v, cap_t)
+        got = mesh.to_host()
+        for a, b in zip(got, want):
+            assert a.shape == b.shape and np.array_equal(a, b)
+        assert mesh.vmin <= 0.0 <= mesh.vmax
