@@ -271,8 +271,7 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_count_kernel(const D2mGrid g)
             pixel_faces(g, b, cw * 32 + lane, v, h, f);
             nf = (unsigned int)f.n;
             if (cw * 32 + lane < g.W) g.slots[((size_t)b * g.H + v) * g.W + cw * 32 + lane] = (uint8_t)f.slots;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) nf += __shfl_xor_sync(0xffffffffu, nf, o);
+            nf = __reduce_add_sync(0xffffffffu, nf);
         }
         if (lane == 0) {
             g.wbits[w] = cur.bits;
