@@ -63,6 +63,8 @@ SIGNATURES = {
     "hv_filter_faces_scratch_bytes": [c_int64, c_void_p],
     "hv_dilate_scratch_bytes": [c_int, c_int, c_int, c_void_p],
     "hv_dilate_mask": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
+    "hv_dilate_static_max_bytes": [c_void_p],
+    "hv_dilate_mask_static": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p],
     "hv_pack_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p],
     "hv_upload_frame_masked": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_int64, c_void_p, c_void_p],

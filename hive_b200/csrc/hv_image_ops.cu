@@ -150,6 +150,65 @@ extern "C" int hv_dilate_mask(const uint8_t* mask, int B, int H, int W, int iter
     return HV_OK;
 }
 
+// ---- hv_dilate_mask without caller scratch ---------------------------------------------------------------------------------
+// The two bit-planes of hv_dilate_mask live in a fixed array in device memory, for callers that cannot allocate (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the 2 MiB until exit.
+namespace hv {
+
+constexpr long long kDilateStaticWords = 512 * 1024;  // 2 MiB: both planes of e.g. four 1920x1080 masks
+static __device__ __align__(256) uint32_t g_dilate_static[kDilateStaticWords];
+
+constexpr int kMaxDevices = 64;
+static uint32_t* g_dilate_static_ptr[kMaxDevices];  // device address of the array, per device (0: not asked yet)
+
+// In host code `g_dilate_static` is only a handle for the runtime, not a device address: the address the kernels get comes
+// from cudaGetSymbolAddress, asked once per device with that device current.  (Two threads racing here store the same value.)
+static int dilate_static_address(uint32_t** out) {
+    int dev = -1;
+    HV_CUDA(cudaGetDevice(&dev));
+    HV_REQUIRE(dev >= 0 && dev < kMaxDevices, "hv_dilate_mask_static: device ordinal %d out of range", dev);
+    uint32_t* p = g_dilate_static_ptr[dev];
+    if (!p) {
+        HV_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_dilate_static));
+        HV_REQUIRE(p && ((uintptr_t)p & 255) == 0, "hv_dilate_mask_static: bad symbol address");
+        g_dilate_static_ptr[dev] = p;
+    }
+    *out = p;
+    return HV_OK;
+}
+
+}  // namespace hv
+
+extern "C" int hv_dilate_static_max_bytes(int64_t* bytes) {
+    HV_REQUIRE(bytes, "hv_dilate_static_max_bytes: null pointer");
+    *bytes = hv::kDilateStaticWords * (int64_t)sizeof(uint32_t);
+    return HV_OK;
+}
+
+extern "C" int hv_dilate_mask_static(const uint8_t* mask, int B, int H, int W, int iterations, uint8_t* out, void* stream) {
+    HV_REQUIRE(mask && out, "hv_dilate_mask_static: null pointer");
+    HV_REQUIRE(B > 0 && H > 0 && W > 0 && iterations >= 0, "hv_dilate_mask_static: bad arguments");
+    const int Ww = hv::words_per_row(W);
+    const long long plane = (long long)B * H * Ww;
+    if (2 * plane > hv::kDilateStaticWords) {
+        hv::set_error("hv_dilate_mask_static: %d x %d x %d needs %lld bytes of scratch, the built-in array holds %lld; "
+                      "use hv_dilate_mask with caller scratch", B, H, W, 2 * plane * 4, hv::kDilateStaticWords * 4);
+        return HV_E_CAPACITY;
+    }
+    uint32_t* raw = nullptr;
+    const int ra = hv::dilate_static_address(&raw);
+    if (ra != HV_OK) return ra;
+    uint32_t* hb = raw + plane;
+    // nothing to clear: both planes are written in full (all B*H*Ww words) before the next kernel reads them
+    cudaStream_t st = hv::as_stream(stream);
+    const int rc = hv::launch_bits_and_hdilate(mask, (long long)B * H, W, iterations, raw, hb, st);
+    if (rc != HV_OK) return rc;
+    const long long total = (long long)B * H * W;
+    hv::mask_vdilate_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(hb, B, H, W, Ww, iterations, out);
+    HV_CUDA(cudaGetLastError());
+    return HV_OK;
+}
+
 extern "C" int hv_pack_frame_masked(const float* depth, const uint8_t* rgb, const uint8_t* mask, int H, int W,
                                     int iterations, void* scratch, int64_t scratch_bytes, void* texels, void* stream) {
     HV_REQUIRE(depth && rgb && mask && texels && scratch, "hv_pack_frame_masked: null pointer");

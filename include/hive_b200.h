@@ -253,6 +253,15 @@ int hv_filter_faces(const int32_t* points2d, const void* depth, int depth_is_f64
 int hv_dilate_scratch_bytes(int B, int H, int W, int64_t* h_bytes);
 int hv_dilate_mask(const uint8_t* mask, int B, int H, int W, int iterations, void* scratch, int64_t scratch_bytes,
                    uint8_t* out, void* stream);
+/* hv_dilate_mask_static: hv_dilate_mask for callers that cannot allocate device memory (CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.  The
+ * two bit-planes live in a 2 MiB array inside the library (hv_dilate_static_max_bytes; held by every GPU that loads the
+ * library until exit), so the call allocates nothing and takes no scratch argument.  2 * B * H * ceil(W/32) * 4 bytes must
+ * fit, e.g. four 1920x1080 masks; larger batches return HV_E_CAPACITY (use hv_dilate_mask).  All calls on a device share
+ * the array: calls that overlap on the GPU (different streams, no ordering between them) race; calls on one stream, or
+ * ordered by events, are safe.  Nothing in it has to start at zero -- each call overwrites what it reads. */
+int hv_dilate_static_max_bytes(int64_t* h_bytes);
+int hv_dilate_mask_static(const uint8_t* mask, int B, int H, int W, int iterations, uint8_t* out, void* stream);
 int hv_pack_frame_masked(const float* depth, const uint8_t* rgb, const uint8_t* mask, int H, int W, int iterations,
                          void* scratch, int64_t scratch_bytes, void* texels, void* stream);
 int hv_upload_frame_masked(const float* h_depth, const uint8_t* h_rgb, const uint8_t* h_mask, int H, int W,
