@@ -53,6 +53,14 @@ SIGNATURES = {
                           c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p,
                           c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_scatter_rows": [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p],
+    "hv_mc_emit_direct": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_double, c_void_p,
+                          c_int64, c_void_p, c_int64, c_int64, c_int64, c_int64, c_float, c_void_p, c_int64, c_int64, c_void_p,
+                          c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "hv_peer_alloc": [c_int64, c_void_p, c_void_p],
+    "hv_peer_free": [c_void_p],
+    "hv_peer_open": [c_void_p, c_void_p],
+    "hv_peer_close": [c_void_p],
+    "hv_copy_async": [c_void_p, c_void_p, c_int64, c_void_p],
     "hv_d2m_scratch_bytes": [c_int, c_int, c_int, c_void_p],
     "hv_d2m_count": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_int64, c_void_p,
                      c_void_p],

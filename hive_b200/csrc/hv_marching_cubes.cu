@@ -794,6 +794,9 @@ struct McEmit {
     unsigned int n_edge_global;      // edge vertices of the whole volume (centre vertices come after them)
     int32_t* vert_dst;               // [V] index of every vertex of this slab in the whole mesh
     int32_t* tri_dst;                // [T] ... of every triangle
+    // mc_emit_kernel<.., DIRECT>: rows are written AT their whole-mesh index -- verts / normals / colors / faces are the whole
+    // mesh's arrays (on this GPU or, mapped through NVLink, on a peer's), of this many rows
+    long long gcap_verts, gcap_tris;
 };
 
 __device__ __forceinline__ unsigned long long vertex_key(const McGrid& g, int x, int y, int zb, int axis) {
@@ -1094,6 +1097,7 @@ constexpr int kEmitThreads = 256;
 // ---- 3. triangles (+ cube-centre vertices): one thread per cube record ---------------------------------------------------------
 // The vertex indices of the cube's (up to 12) edges are looked up first, all loads independent; its triangles then pick
 // from that array.  (One thread walking its triangles with three dependent look-ups each was measured at 66 us.)
+template <bool DIRECT>
 __device__ __forceinline__ void emit_cubes(const McGrid& g, const McEmit& out, unsigned int block, unsigned int n_blocks) {
     __shared__ unsigned int s_vidx[13][kEmitThreads];  // [edge][thread]: dynamic indexing without local memory
     const unsigned int n_cubes = (unsigned int)g.totals[5], n_edge = (unsigned int)g.totals[4];
@@ -1152,21 +1156,30 @@ __device__ __forceinline__ void emit_cubes(const McGrid& g, const McEmit& out, u
                 if ((long long)ti >= out.cap_tris) break;
                 const unsigned int a = s_vidx[tri[3 * j]][threadIdx.x], b = s_vidx[tri[3 * j + 1]][threadIdx.x],
                                    c = s_vidx[tri[3 * j + 2]][threadIdx.x];
-                out.faces[3 * ti] = (int32_t)a;
-                out.faces[3 * ti + 1] = (int32_t)b;
-                out.faces[3 * ti + 2] = (int32_t)c;
-                if (out.tri_dst) out.tri_dst[ti] = (int32_t)(ti + (size_t)__ldg(out.tshift + col));
+                size_t row = ti;
+                if (DIRECT) {
+                    row = ti + (size_t)__ldg(out.tshift + col);
+                    if ((long long)row >= out.gcap_tris) break;
+                }
+                out.faces[3 * row] = (int32_t)a;
+                out.faces[3 * row + 1] = (int32_t)b;
+                out.faces[3 * row + 2] = (int32_t)c;
+                if (!DIRECT && out.tri_dst) out.tri_dst[ti] = (int32_t)(ti + (size_t)__ldg(out.tshift + col));
             }
         }
         if (((mult >> 48) & 15ull) && (long long)centre_index < out.cap_verts) {
-            emit_centre_vertex(g, out, x, y, zb, centre_index);
-            if (out.vert_dst) out.vert_dst[centre_index] = (int32_t)centre_global;
+            if (!DIRECT) {
+                emit_centre_vertex(g, out, x, y, zb, centre_index);
+                if (out.vert_dst) out.vert_dst[centre_index] = (int32_t)centre_global;
+            } else if ((long long)centre_global < out.gcap_verts) {
+                emit_centre_vertex(g, out, x, y, zb, centre_global);
+            }
         }
     }
 }
 
 // ---- 4. edge vertices: one thread per vertex record ----------------------------------------------------------------------------------
-template <bool WHOLE, bool LEVEL0>
+template <bool WHOLE, bool LEVEL0, bool DIRECT>
 __device__ __forceinline__ void emit_vertices(const McGrid& g, const McEmit& out, unsigned int block, unsigned int n_blocks) {
     const unsigned int n_edge = (unsigned int)g.totals[4];
     for (unsigned int i = block * kEmitThreads + threadIdx.x; i < n_edge; i += n_blocks * kEmitThreads) {
@@ -1179,8 +1192,13 @@ __device__ __forceinline__ void emit_vertices(const McGrid& g, const McEmit& out
         const size_t vi = (size_t)__ldg(&g.tile_base[tile].x) + __ldg(&g.batch_base[tile * kTileBatches + (unsigned int)((rec >> 50) & 31ull)].x) +
                           (unsigned int)((rec >> 38) & 4095ull);
         if ((long long)vi < out.cap_verts) {
-            emit_edge_vertex<WHOLE, LEVEL0>(g, out, x, y, gq * 32 + k, axis, vi);
-            if (out.vert_dst) out.vert_dst[vi] = (int32_t)(vi + (size_t)__ldg(out.vshift + (size_t)x * g.Y + y));
+            if (!DIRECT) {
+                emit_edge_vertex<WHOLE, LEVEL0>(g, out, x, y, gq * 32 + k, axis, vi);
+                if (out.vert_dst) out.vert_dst[vi] = (int32_t)(vi + (size_t)__ldg(out.vshift + (size_t)x * g.Y + y));
+            } else {
+                const size_t row = vi + (size_t)__ldg(out.vshift + (size_t)x * g.Y + y);
+                if ((long long)row < out.gcap_verts) emit_edge_vertex<WHOLE, LEVEL0>(g, out, x, y, gq * 32 + k, axis, row);
+            }
         }
     }
 }
@@ -1188,7 +1206,7 @@ __device__ __forceinline__ void emit_vertices(const McGrid& g, const McEmit& out
 // One launch for both: triangles and vertices do not depend on each other and stall on different things (index look-ups in
 // L2 / arithmetic), so their blocks are interleaved in the grid in the ratio n_tri_blocks : n_vert_blocks.  (Two launches:
 // 33 + 40 us; the triangle kernel on a forked side stream gained 6 us of that -- the event hand-over costs what it hides.)
-template <bool WHOLE, bool LEVEL0>
+template <bool WHOLE, bool LEVEL0, bool DIRECT>
 __global__ void __launch_bounds__(kEmitThreads, (WHOLE && LEVEL0) ? 4 : 3)
     mc_emit_kernel(const __grid_constant__ McGrid g, const __grid_constant__ McEmit out, const unsigned int n_tri_blocks,
                    const unsigned int n_vert_blocks) {
@@ -1198,8 +1216,8 @@ __global__ void __launch_bounds__(kEmitThreads, (WHOLE && LEVEL0) ? 4 : 3)
     //  kernel's instructions)
     const unsigned int b = blockIdx.x, n = n_tri_blocks + n_vert_blocks;
     const unsigned int t_before = b * n_tri_blocks / n, t_after = (b + 1u) * n_tri_blocks / n;
-    if (t_after > t_before) emit_cubes(g, out, t_before, n_tri_blocks);
-    else emit_vertices<WHOLE, LEVEL0>(g, out, b - t_before, n_vert_blocks);
+    if (t_after > t_before) emit_cubes<DIRECT>(g, out, t_before, n_tri_blocks);
+    else emit_vertices<WHOLE, LEVEL0, DIRECT>(g, out, b - t_before, n_vert_blocks);
 }
 
 // ---- z-slab placement (hive_b200/sharded.py): where does a slab's mesh go in the mesh of the whole volume? --------------------
@@ -1486,6 +1504,7 @@ struct Placement {
     int64_t n_edge_global;
     int32_t* vert_dst;
     int32_t* tri_dst;
+    int64_t whole_verts, whole_tris;  // > 0: direct placement, the output arrays are the whole mesh's, of this many rows
 };
 }  // namespace
 
@@ -1509,8 +1528,14 @@ static int mc_emit_impl(const float* tsdf, const float* halo_lo, const float* ha
                "hv_mc_emit: tsdf and colour halos must come in pairs");
     HV_REQUIRE(faces == nullptr || place != nullptr || (!halo_lo && !halo_hi),
                "hv_mc_emit: a shard with halos must emit face_keys (or be placed: hv_mc_emit_placed)");
-    HV_REQUIRE(place == nullptr || (faces && place->col_shifts && place->vert_dst && place->tri_dst && place->n_edge_global >= 0 &&
-                                    place->n_edge_global < (1ll << 31)), "hv_mc_emit_placed: bad placement");
+    const bool direct = place && place->whole_verts > 0;
+    HV_REQUIRE(place == nullptr || (faces && place->col_shifts && place->n_edge_global >= 0 && place->n_edge_global < (1ll << 31)),
+               "hv_mc_emit_placed: bad placement");
+    HV_REQUIRE(place == nullptr || (direct ? (!place->vert_dst && !place->tri_dst && place->whole_verts >= n_verts &&
+                                              place->whole_tris >= n_tris && place->whole_verts < (1ll << 31) &&
+                                              place->whole_tris < (1ll << 31))
+                                           : (place->vert_dst && place->tri_dst)),
+               "hv_mc_emit_placed: bad placement (row indices or whole-mesh sizes)");
     HV_REQUIRE(z_global_dim >= z_global_offset + g.Z, "hv_mc_emit: slab exceeds the global z extent");
     g.color = color;
     g.chalo_lo = color_halo_lo;
@@ -1535,6 +1560,7 @@ static int mc_emit_impl(const float* tsdf, const float* halo_lo, const float* ha
     em.vshift = em.tshift = em.cshift = em.vnext = nullptr;
     em.n_edge_global = 0u;
     em.vert_dst = em.tri_dst = nullptr;
+    em.gcap_verts = em.gcap_tris = 0;
     if (place) {
         const long long XY = (long long)g.X * g.Y;
         em.vshift = place->col_shifts;
@@ -1544,6 +1570,8 @@ static int mc_emit_impl(const float* tsdf, const float* halo_lo, const float* ha
         em.n_edge_global = (unsigned int)place->n_edge_global;
         em.vert_dst = place->vert_dst;
         em.tri_dst = place->tri_dst;
+        em.gcap_verts = place->whole_verts;
+        em.gcap_tris = place->whole_tris;
     }
     const int sms = hv::device_info().sm_count;
     // one thread per record that can exist: a surface cube has a triangle, an edge vertex is a vertex
@@ -1565,10 +1593,12 @@ static int mc_emit_impl(const float* tsdf, const float* halo_lo, const float* ha
         const bool whole = !halo_lo && !halo_hi, level0 = level == 0.0;
         // (a dependent launch is harmless when something else precedes it in the stream: it then just waits for that)
         const unsigned int unt = (unsigned int)nt, unv = (unsigned int)nv;
-        if (whole && level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<true, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
-        else if (whole) HV_CUDA(launch_dependent(hv::mc_emit_kernel<true, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
-        else if (level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
-        else HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        if (direct && level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, true, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else if (direct) HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, false, true>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else if (whole && level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<true, true, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else if (whole) HV_CUDA(launch_dependent(hv::mc_emit_kernel<true, false, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else if (level0) HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, true, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
+        else HV_CUDA(launch_dependent(hv::mc_emit_kernel<false, false, false>, grid, hv::kEmitThreads, st, g, em, unt, unv));
     }
     HV_CUDA(cudaGetLastError());
     return HV_OK;
@@ -1594,7 +1624,24 @@ extern "C" int hv_mc_emit_placed(const float* tsdf, const float* halo_lo, const 
                                  const float* h_origin, int64_t n_verts, int64_t n_tris, float* verts_world, float* normals,
                                  uint8_t* colors, int32_t* faces, const int32_t* col_shifts, int64_t n_edge_global,
                                  int32_t* vert_dst, int32_t* tri_dst, unsigned long long* totals, void* stream) {
-    Placement pl = {col_shifts, n_edge_global, vert_dst, tri_dst};
+    Placement pl = {col_shifts, n_edge_global, vert_dst, tri_dst, 0, 0};
+    return mc_emit_impl(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch, scratch_bytes,
+                        work, rec_verts, rec_cubes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris,
+                        verts_world, nullptr, normals, colors, faces, nullptr, nullptr, nullptr, totals, &pl, stream);
+}
+
+// The slab's rows written AT their whole-mesh positions: verts_world / normals / colors (whole_verts rows) and faces
+// (whole_tris rows) are the whole mesh's arrays -- on this GPU, or on another one whose memory is mapped into this
+// process (hv_peer_open): the stores then travel over NVLink and nothing is gathered or scattered afterwards.
+extern "C" int hv_mc_emit_direct(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                                 const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                                 double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts,
+                                 int64_t rec_cubes, int64_t z_global_offset, int64_t z_global_dim, float voxel_size,
+                                 const float* h_origin, int64_t n_verts, int64_t n_tris, const int32_t* col_shifts,
+                                 int64_t n_edge_global, int64_t whole_verts, int64_t whole_tris, float* verts_world,
+                                 float* normals, uint8_t* colors, int32_t* faces, unsigned long long* totals, void* stream) {
+    HV_REQUIRE(whole_verts > 0 && whole_tris >= 0, "hv_mc_emit_direct: bad whole-mesh sizes");
+    Placement pl = {col_shifts, n_edge_global, nullptr, nullptr, whole_verts, whole_tris};
     return mc_emit_impl(tsdf, halo_lo, halo_hi, color, color_halo_lo, color_halo_hi, h_dims, pitch, level, scratch, scratch_bytes,
                         work, rec_verts, rec_cubes, z_global_offset, z_global_dim, voxel_size, h_origin, n_verts, n_tris,
                         verts_world, nullptr, normals, colors, faces, nullptr, nullptr, nullptr, totals, &pl, stream);

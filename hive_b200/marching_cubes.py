@@ -254,6 +254,27 @@ class McPlan:
                 int(n_edge_global), _ptr(out["vert_dst"]), _ptr(out["tri_dst"]), _ptr(self.totals), stream))
         return out
 
+    def emit_direct(self, n_verts, n_tris, voxel_size, origin, shifts, n_edge_global, whole_verts, whole_tris, addr):
+        """The slab's rows written at their positions in the mesh of the WHOLE volume (``hv_mc_emit_direct``): ``addr`` maps
+        verts / normals / colors / faces to the device addresses (ints) of the whole mesh's arrays -- possibly another
+        GPU's memory mapped into this process (``hive_b200.peer``), in which case the stores travel over NVLink."""
+        torch = self._torch
+        origin = np.ascontiguousarray(origin, dtype=np.float32)
+        self.ensure_records(n_verts, n_tris)
+        if n_verts == 0 and n_tris == 0:
+            return
+        with torch.cuda.device(self.device):
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _lib.check(self._lib.hv_mc_emit_direct(
+                _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")), _ptr(self.color),
+                _ptr(self.halo.get("color_lo")), _ptr(self.halo.get("color_hi")),
+                ctypes.cast(self.dims, ctypes.c_void_p), self.pitch, self.level, self.scratch_ptr, self.scratch_bytes,
+                self.work_ptr, self.rec_verts, self.rec_cubes, self.z_global_offset, self.z_global_dim,
+                ctypes.c_float(np.float32(voxel_size)), origin.ctypes.data_as(ctypes.c_void_p), n_verts, n_tris,
+                _ptr(shifts), int(n_edge_global), int(whole_verts), int(whole_tris), ctypes.c_void_p(addr["verts"]),
+                ctypes.c_void_p(addr["normals"]), ctypes.c_void_p(addr["colors"]), ctypes.c_void_p(addr["faces"]),
+                _ptr(self.totals), stream))
+
     def extract(self, voxel_size, origin, cap_verts, cap_tris, want_voxel=False) -> DeviceMesh:
         """count + emit in one library call (``hv_mc_extract``) into buffers of the given capacity; falls back to an
         exactly sized ``emit`` when the surface turns out larger.  Whole volumes only (faces as indices)."""

@@ -1,0 +1,87 @@
+"""Device buffers shared between the ranks of one node (one process per GPU) through CUDA IPC -- the plumbing under the
+peer-to-peer mesh assembly of ``hive_b200.sharded``: rank 0 owns the whole-mesh arrays, every slab's emit kernel stores its
+rows into them over NVLink (``hv_mc_emit_direct``).  Nothing in the reference corresponds to this.
+
+The owner allocates with ``hv_peer_alloc`` (a plain ``cudaMalloc``: an IPC handle covers a whole allocation, so a block of
+torch's caching allocator will not do), broadcasts the 64-byte handle over the process group the ranks already have, and the
+others map it with ``hv_peer_open``.  Whether that worked is agreed on by all ranks (one all-reduce), so either every rank uses
+the shared buffer or none does.
+"""
+from __future__ import annotations
+
+import ctypes
+
+from . import _lib
+
+HANDLE_BYTES = 64
+_ALIGN = 256
+
+
+def mesh_layout(n_verts: int, n_tris: int):
+    """Byte offsets of the whole mesh's arrays inside the shared buffer -> ({name: offset}, total bytes).  Every rank
+    computes this from the all-gathered totals, so nothing about the layout is communicated."""
+    offs, o = {}, 0
+    for name, nbytes in (("verts", 12 * n_verts), ("normals", 12 * n_verts), ("colors", 3 * n_verts), ("faces", 12 * n_tris)):
+        offs[name] = o
+        o = (o + nbytes + _ALIGN - 1) & ~(_ALIGN - 1)
+    return offs, max(o, _ALIGN)
+
+
+class SharedBuffer:
+    """``nbytes`` of device memory on ``owner``'s GPU, addressable from every rank of ``dist``'s default group.
+
+    Collective: every rank constructs it at the same point.  ``self.ok`` is the same on every rank; ``self.base`` is this
+    process's address of the buffer (the owner's own pointer, a mapping elsewhere).
+    """
+
+    def __init__(self, dist, rank: int, device, nbytes: int, owner: int = 0):
+        torch = _lib.require_cuda()
+        lib = _lib.load()
+        self._lib, self._dist, self.rank, self.owner, self.device, self.nbytes = lib, dist, rank, owner, device, int(nbytes)
+        self.base, self.ok = None, False
+        good = 1
+        msg = torch.zeros(HANDLE_BYTES + 8, dtype=torch.uint8, device=device)
+        with torch.cuda.device(device):
+            if rank == owner:
+                ptr, handle = ctypes.c_void_p(0), (ctypes.c_uint8 * HANDLE_BYTES)()
+                if lib.hv_peer_alloc(self.nbytes, ctypes.byref(ptr), handle) == 0:
+                    self.base = int(ptr.value)
+                    msg[:HANDLE_BYTES] = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(device)
+                    msg[HANDLE_BYTES] = 1
+                else:
+                    good = 0
+            dist.broadcast(msg, src=owner)
+            if rank != owner:
+                host = msg.cpu().numpy()
+                if host[HANDLE_BYTES] == 1:
+                    ptr = ctypes.c_void_p(0)
+                    handle = (ctypes.c_uint8 * HANDLE_BYTES).from_buffer_copy(host[:HANDLE_BYTES].tobytes())
+                    if lib.hv_peer_open(handle, ctypes.byref(ptr)) == 0:
+                        self.base = int(ptr.value)
+                    else:
+                        good = 0
+                else:
+                    good = 0
+            flag = torch.tensor([good], dtype=torch.int32, device=device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            self.ok = bool(int(flag.item()) == 1)
+        if not self.ok:
+            self.error = _lib.last_error()
+            self.close()
+
+    def close(self):
+        """Collective: the mappings go first, then the owner frees."""
+        if self.base is not None and self.rank != self.owner:
+            self._lib.hv_peer_close(ctypes.c_void_p(self.base))
+            self.base = None
+        self._dist.barrier()
+        if self.base is not None:
+            self._lib.hv_peer_free(ctypes.c_void_p(self.base))
+            self.base = None
+
+    def copy_out(self, offset: int, host_tensor, stream):
+        """Owner: asynchronous copy of ``host_tensor.nbytes`` bytes at ``offset`` into a pinned host tensor."""
+        n = host_tensor.numel() * host_tensor.element_size()
+        assert self.base is not None and offset + n <= self.nbytes
+        _lib.check(self._lib.hv_copy_async(ctypes.c_void_p(host_tensor.data_ptr()), ctypes.c_void_p(self.base + offset), n,
+                                           ctypes.c_void_p(stream)))

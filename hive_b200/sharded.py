@@ -6,8 +6,9 @@ independent given the frame, so integration needs no reduction: the global ``[X]
 slab's slice of the global z world-coordinate table makes the result identical to the unsharded volume.  The only
 data-path collective of integration is the NCCL broadcast of each frame batch (packed texels) from rank 0,
 double-buffered so the broadcast of batch s+1 overlaps the integration of batch s; camera poses are tiny and broadcast
-once, up front.  Mesh extraction exchanges one boundary plane per seam and stitches the per-slab meshes on rank 0
-through global edge keys (``get_mesh``).
+once, up front.  Mesh extraction exchanges one boundary plane per seam and one table of per-column counts; every slab then
+stores its rows at their final positions in the whole mesh, which lives in rank 0's HBM and is mapped into every rank
+(CUDA IPC over NVLink, ``hive_b200/peer.py``) -- or, where the ranks cannot share memory, sends them to rank 0 (``get_mesh``).
 
 One process per GPU (``torch.distributed``); ``world_size == 1`` degenerates to a plain ``TSDFVolume``.
 """
@@ -18,7 +19,7 @@ import time
 
 import numpy as np
 
-from . import _xfer
+from . import _xfer, peer
 from .fusion import DeviceFrames, TSDFVolume
 
 
@@ -232,12 +233,11 @@ class SlabShardedTSDFVolume:
 
     # ------------------------------------------------------------------ mesh extraction (seam-stitched marching cubes)
     def _boundary_planes(self):
-        """(first, last) z-planes of this slab's tsdf and colour volumes as contiguous (X, Y) tensors."""
+        """(first, last) z-planes of this slab's tsdf and colour volumes as (X, Y) views."""
         loc = self.local
         Z = int(loc._local_dim[2])
         t, c = loc._tsdf_vol_gpu, loc._color_vol_gpu
-        return (t[:, :, 0].contiguous(), t[:, :, Z - 1].contiguous(), c[:, :, 0].contiguous(),
-                c[:, :, Z - 1].contiguous())
+        return t[:, :, 0], t[:, :, Z - 1], c[:, :, 0], c[:, :, Z - 1]  # strided views: torch.stack packs them in one pass each
 
     def get_mesh(self):
         """``TSDFVolume.get_mesh`` of the global volume on rank 0 (``None`` x4 elsewhere).
@@ -246,8 +246,10 @@ class SlabShardedTSDFVolume:
         (one tsdf + one colour plane per direction).  The whole-volume mesh is ordered column by column, so the slabs
         interleave: every slab counts what it owns per column, the counts are all-gathered, and every slab works out by
         itself where its vertices and triangles go in the whole mesh and writes its faces with whole-mesh indices (seam
-        vertices, owned by the slab above, included).  Rank 0 receives the slab meshes in one grouped exchange and drops
-        every row into place.  The result is identical -- vertex and face order included -- to the mesh of the
+        vertices, owned by the slab above, included).  The emit kernels then store every row at its final position in
+        rank 0's HBM over NVLink (``hv_mc_emit_direct``; one small all-reduce tells rank 0 that all rows have arrived);
+        where the ranks cannot share memory (gloo, HV_MESH_P2P=0), rank 0 receives the slab meshes in one grouped exchange
+        and drops every row into place.  The result is identical -- vertex and face order included -- to the mesh of the
         unsharded volume; nothing is sorted or searched.
         """
         from . import marching_cubes as mc
@@ -265,6 +267,7 @@ class SlabShardedTSDFVolume:
 
         mark("start")
         first_t, last_t, first_c, last_c = self._boundary_planes()
+        mark("boundary planes")
         # the halo planes and the extraction plan (scratch, work records) live as long as the volume: a repeated get_mesh
         # allocates nothing.  tsdf and colour plane travel as one message per neighbour.
         packed = exchange_halo_planes(dist, self.rank, self.world_size,
@@ -288,15 +291,37 @@ class SlabShardedTSDFVolume:
         mark("count + totals")
         self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)  # next time: records sized by this surface
         # ONE collective tells every slab everything about every other: per-column counts + (min, max, sizes)
-        all_counts = exchange_column_counts(dist, self.world_size, plan.column_counts())
-        mark("column counts + all-gather")
+        counts = plan.column_counts()
+        mark("column counts")
+        all_counts = exchange_column_counts(dist, self.world_size, counts)
+        mark("all-gather")
         shifts, _ = plan.column_shifts(all_counts, self.rank)
-        tails = all_counts[:, -plan.SLAB_TAIL:].cpu().numpy()  # (world, 5): min key, max key, vertices, triangles, edge vertices
+        mark("shifts")
+        # (world, 5): min key, max key, vertices, triangles, edge vertices of every slab -- the one host read of the exchange
+        tails = self._read_tails(all_counts[:, -plan.SLAB_TAIL:])
         vmin = min(mc._key_to_float(int(k)) for k in tails[:, 0])
         vmax = max(mc._key_to_float(int(k)) for k in tails[:, 1])
         n_verts_g, n_tris_g, n_edge_g = (int(v) for v in tails[:, 2:5].sum(axis=0))
         mc.check_surface(0.0, vmin, vmax, n_verts_g)
-        mark("shifts + tails read")
+        mark("tails read")
+        buf = self._shared_mesh_buffer(n_verts_g, n_tris_g)
+        if buf is not None:
+            # peer-to-peer assembly: every slab's emit kernel stores its rows at their final positions in rank 0's HBM
+            # (over NVLink from the other GPUs).  The all-reduce is the arrival signal: it is stream-ordered behind the emit
+            # kernel on every rank, so when rank 0's completes every slab's rows have landed.
+            offs, _ = peer.mesh_layout(n_verts_g, n_tris_g)
+            plan.emit_direct(n_verts, n_tris, loc._voxel_size, loc._vol_origin, shifts, n_edge_g, n_verts_g, n_tris_g,
+                             {name: buf.base + o for name, o in offs.items()})
+            mark("emit into rank 0")
+            dist.all_reduce(self._mesh_done)
+            mark("arrival")
+            self.last_mesh_trace, self.last_mesh_path = trace, "p2p"
+            if self.rank != 0:
+                return None, None, None, None
+            out = self._download_shared_mesh(buf, offs, n_verts_g, n_tris_g)
+            mark("download")
+            return out
+        self.last_mesh_path = "gather"
         part = plan.emit_placed(n_verts, n_tris, loc._voxel_size, loc._vol_origin, shifts, n_edge_g)
         mark("emit")
         parts = gather_placed_parts(dist, self.rank, self.world_size, part, loc.device, tails[:, 2:4])
@@ -309,6 +334,64 @@ class SlabShardedTSDFVolume:
         out = _xfer.to_host(verts, faces, normals, colors)
         mark("download")
         return out
+
+
+    def _read_tails(self, tails_dev):
+        torch = self._torch
+        if not tails_dev.is_cuda:
+            return tails_dev.numpy()
+        host = getattr(self, "_tails_host", None)
+        if host is None or host.shape != tails_dev.shape:
+            host = self._tails_host = torch.empty(tails_dev.shape, dtype=tails_dev.dtype, pin_memory=True)
+        host.copy_(tails_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return host.numpy().copy()
+
+    # -- the whole mesh in rank 0's HBM, written by every slab (hive_b200/peer.py)
+    def _shared_mesh_buffer(self, n_verts_g, n_tris_g):
+        """The buffer all slabs emit into, or None when the ranks cannot share memory (CPU process groups, HV_MESH_P2P=0,
+        CUDA IPC unavailable): every rank takes the same decision -- the sizes come from the all-gathered totals and
+        ``SharedBuffer`` agrees on success collectively.  Grown (collectively) when the mesh outgrows it."""
+        dist, torch = self._dist, self._torch
+        if getattr(self, "_p2p_off", None) is None:
+            self._p2p_off = (os.environ.get("HV_MESH_P2P", "1") == "0" or self.local.device.type != "cuda"
+                             or dist.get_backend() != "nccl")
+        if self._p2p_off:
+            return None
+        _, need = peer.mesh_layout(n_verts_g, n_tris_g)
+        buf = getattr(self, "_mesh_buf", None)
+        if buf is not None and buf.nbytes >= need:
+            return buf
+        if buf is not None:
+            buf.close()
+        buf = peer.SharedBuffer(dist, self.rank, self.local.device, need + need // 2)
+        if not buf.ok:
+            self._p2p_off, self._mesh_buf = True, None
+            return None
+        self._mesh_buf = buf
+        self._mesh_done = torch.zeros(1, dtype=torch.int32, device=self.local.device)
+        return buf
+
+    def _download_shared_mesh(self, buf, offs, n_verts, n_tris):
+        torch = self._torch
+        host = {"verts": torch.empty((n_verts, 3), dtype=torch.float32, pin_memory=True),
+                "faces": torch.empty((n_tris, 3), dtype=torch.int32, pin_memory=True),
+                "normals": torch.empty((n_verts, 3), dtype=torch.float32, pin_memory=True),
+                "colors": torch.empty((n_verts, 3), dtype=torch.uint8, pin_memory=True)}
+        with torch.cuda.device(self.local.device):
+            stream = torch.cuda.current_stream()
+            for name, h in host.items():
+                if h.numel():
+                    buf.copy_out(offs[name], h, stream.cuda_stream)
+            stream.synchronize()
+        return tuple(host[k].numpy() for k in ("verts", "faces", "normals", "colors"))
+
+    def close(self):
+        """Collective: releases the shared mesh buffer (otherwise it lives until the processes exit)."""
+        buf = getattr(self, "_mesh_buf", None)
+        if buf is not None:
+            buf.close()
+            self._mesh_buf = None
 
 
 def exchange_halo_planes(dist, rank, world_size, planes, out=None):

@@ -169,6 +169,31 @@ int hv_mc_emit_placed(const float* tsdf, const float* halo_lo, const float* halo
                       unsigned long long* totals, void* stream);
 int hv_scatter_rows(const void* src, const int32_t* index, int64_t n, int row_bytes, void* dst, void* stream);
 
+/* hv_mc_emit_direct: hv_mc_emit_placed with every row written AT its whole-mesh index -- verts_world / normals / colors
+ * (whole_verts rows) and faces (whole_tris rows) are the whole mesh's arrays, on this GPU or on a peer GPU whose buffer
+ * is mapped into this process (hv_peer_open): the slab's stores then go over NVLink straight into the final mesh and
+ * nothing is gathered or scattered afterwards.  n_verts / n_tris are still this slab's own counts. */
+int hv_mc_emit_direct(const float* tsdf, const float* halo_lo, const float* halo_hi, const float* color,
+                      const float* color_halo_lo, const float* color_halo_hi, const int64_t* h_dims, int64_t pitch,
+                      double level, void* scratch, int64_t scratch_bytes, void* work, int64_t rec_verts, int64_t rec_cubes,
+                      int64_t z_global_offset, int64_t z_global_dim, float voxel_size, const float* h_origin, int64_t n_verts,
+                      int64_t n_tris, const int32_t* col_shifts, int64_t n_edge_global, int64_t whole_verts,
+                      int64_t whole_tris, float* verts_world, float* normals, uint8_t* colors, int32_t* faces,
+                      unsigned long long* totals, void* stream);
+
+/* Device buffers the other ranks of the node can store into (one process per GPU; nothing in the reference).
+ *   hv_peer_alloc  cudaMalloc of `bytes` + its CUDA IPC handle (HV_PEER_HANDLE_BYTES bytes, HOST) -- send the handle to the
+ *                  other ranks by any means; free with hv_peer_free once every rank has closed it.
+ *   hv_peer_open   maps the buffer behind a handle made by ANOTHER process into this one (enables peer access between the
+ *                  two GPUs); the pointer is usable by kernels and copies of this process.  hv_peer_close unmaps it.
+ *   hv_copy_async  cudaMemcpyAsync between any two of: device, mapped peer, pinned host addresses. */
+#define HV_PEER_HANDLE_BYTES 64
+int hv_peer_alloc(int64_t bytes, void** h_ptr, void* h_handle);
+int hv_peer_free(void* ptr);
+int hv_peer_open(const void* h_handle, void** h_ptr);
+int hv_peer_close(void* ptr);
+int hv_copy_async(void* dst, const void* src, int64_t bytes, void* stream);
+
 /* hv_mc_count + hv_mc_emit in one call with caller-provided capacity (cap_verts vertices, cap_tris triangles in every
  * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 8 x uint64, pinned memory
  * recommended; same meaning as `totals`).  Returns HV_E_LEVEL_RANGE / HV_E_NOSURFACE like skimage would raise

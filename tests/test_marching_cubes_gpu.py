@@ -209,6 +209,28 @@ def test_slab_halo_stitch_equals_whole_volume(n_slabs):
     assert len(wv) > 1000
     assert np.array_equal(verts, wv) and np.array_equal(faces, wf)
     assert np.array_equal(normals, wn) and np.array_equal(colors, wc)
+    # direct placement (hv_mc_emit_direct, the peer-to-peer path of sharded.get_mesh): every slab stores its rows at their
+    # final positions in ONE buffer laid out like the one rank 0 shares with the other ranks
+    from hive_b200 import peer
+    n_v, n_t = n_edge + n_centre, n_tri
+    offs, total = peer.mesh_layout(n_v, n_t)
+    buf = torch.full((total,), 0xCD, dtype=torch.uint8, device=whole.device)
+    assert buf.data_ptr() % 256 == 0
+    for k, (plan, (nv, nt), s) in enumerate(zip(plans, sizes, slabs)):
+        shifts, _ = plan.column_shifts(all_counts, k)
+        plan.emit_direct(nv, nt, s._voxel_size, s._vol_origin, shifts, n_edge, n_v, n_t,
+                         {name: buf.data_ptr() + o for name, o in offs.items()})
+    torch.cuda.synchronize()
+    host = buf.cpu().numpy()
+    assert np.array_equal(host[offs["verts"]:offs["verts"] + 12 * n_v].view(np.float32).reshape(-1, 3), wv)
+    assert np.array_equal(host[offs["normals"]:offs["normals"] + 12 * n_v].view(np.float32).reshape(-1, 3), wn)
+    assert np.array_equal(host[offs["colors"]:offs["colors"] + 3 * n_v].reshape(-1, 3), wc)
+    assert np.array_equal(host[offs["faces"]:offs["faces"] + 12 * n_t].view(np.int32).reshape(-1, 3), wf)
+    # nothing outside the arrays was touched
+    used = np.zeros(total, dtype=bool)
+    for name, nbytes in (("verts", 12 * n_v), ("normals", 12 * n_v), ("colors", 3 * n_v), ("faces", 12 * n_t)):
+        used[offs[name]:offs[name] + nbytes] = True
+    assert np.all(host[~used] == 0xCD)
 
 
 def test_one_call_extract_and_capacity_fallback():

@@ -34,6 +34,22 @@ def main():
             tr = tr + [("place+download (wall)", None)]
             steps = [(b[0], 1e3 * (b[1] - a[1])) for a, b in zip(vol.last_mesh_trace[:-1], vol.last_mesh_trace[1:])]
             print(f"rep {rep}: " + ", ".join(f"{n} {ms:.3f}" for n, ms in steps) + f" | vertices {len(out[0])}", flush=True)
+    # and untraced (no per-step syncs): wall clock of the whole call on rank 0, both assembly paths
+    import time
+    os.environ.pop("HV_MESH_TRACE")
+    for label, off in (("p2p", False), ("gather", True)):
+        if off:
+            vol._p2p_off = True
+        ts = []
+        for rep in range(7):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            vol.get_mesh()
+            ts.append(1e3 * (time.perf_counter() - t0))
+        if rank == 0:
+            print(f"untraced get_mesh [{vol.last_mesh_path}]: median {sorted(ts[2:])[len(ts[2:]) // 2]:.3f} ms  {['%.3f' % t for t in ts]}", flush=True)
+    vol.close()
     dist.destroy_process_group()
 
 
