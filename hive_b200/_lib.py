@@ -66,6 +66,8 @@ SIGNATURES = {
                      c_void_p],
     "hv_d2m_emit": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p,
                     c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "hv_d2m_emit_capped": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p,
+                           c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "hv_image2world": [c_void_p, c_void_p, c_int64, c_void_p, c_double, c_void_p, c_void_p],
     "hv_world2image": [c_void_p, c_int64, c_void_p, c_double, c_int, c_void_p, c_void_p, c_void_p],
     "hv_filter_faces_scratch_bytes": [c_int64, c_void_p],

@@ -291,9 +291,13 @@ struct D2mOut {
     int32_t* points2d;    // [V][2] (u, v) or null
     float* vdepth;        // [V] or null
     long long* frame_off; // [B+1][2] (vertex, face) start of every frame in the concatenated outputs
-    unsigned long long n_verts, n_faces;
+    unsigned long long n_verts, n_faces;  // the totals, or (d2m_emit_kernel<true>) the capacity of the output arrays
+    const unsigned long long* d_totals;   // d2m_emit_kernel<true>: where hv_d2m_count left the totals (DEVICE)
 };
 
+// CAPPED: the host has not read the totals yet -- the outputs hold out.n_verts / out.n_faces rows (a guess from earlier
+// batches), rows past that are dropped (the host sees totals > capacity afterwards and repeats the call exactly sized).
+template <bool CAPPED>
 __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, const D2mOut out) {
     __shared__ unsigned int s_rank[6][kD2mThreads];
     const int lane = threadIdx.x & 31;
@@ -308,8 +312,8 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
         out.frame_off[2 * b] = off.x;
         out.frame_off[2 * b + 1] = off.y;
         if (b == g.B - 1) {
-            out.frame_off[2 * g.B] = (long long)out.n_verts;
-            out.frame_off[2 * g.B + 1] = (long long)out.n_faces;
+            out.frame_off[2 * g.B] = (long long)(CAPPED ? out.d_totals[0] : out.n_verts);
+            out.frame_off[2 * g.B + 1] = (long long)(CAPPED ? out.d_totals[1] : out.n_faces);
         }
     }
     // counts (lane r holds row v0 + r), prefix offsets and vertex bits (lane l holds row v0 - 1 + l) of the warp's words and
@@ -377,6 +381,7 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
                 s_rank[5][threadIdx.x] = rc - 1u;
                 size_t fi = (size_t)off.y + inc - nf;
                 for (unsigned int rest = sl; rest; rest &= rest - 1u, ++fi) {
+                    if (CAPPED && fi >= out.n_faces) break;
                     const int slot = __ffs(rest) - 1;
                     const unsigned int code = (unsigned int)((slot < 4 ? kQuadCorners >> (9 * slot) : kHoleCorners >> (9 * (slot - 4))) & 511ull);
 #pragma unroll
@@ -387,6 +392,7 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
         if ((bits >> lane) & 1u) {  // image2world, hive/geometric.py:200-204 (float64)
             const float d = d_row[r];
             const size_t vi = off.x + __popc(bits & lt);
+            if (CAPPED && vi >= out.n_verts) continue;
             const double du = (double)u, dv = (double)v, dd = (double)d;
             double X[3];
 #pragma unroll
@@ -588,10 +594,11 @@ extern "C" int hv_d2m_count(const float* depth, const uint8_t* mask, const uint8
     return HV_OK;
 }
 
-extern "C" int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
-                           float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
-                           int64_t scratch_bytes, int64_t n_verts, int64_t n_faces, double* verts, int32_t* faces,
-                           int32_t* points2d, float* vdepth, long long* frame_offsets, void* stream) {
+static int d2m_emit_impl(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                         float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
+                         int64_t scratch_bytes, int64_t n_verts, int64_t n_faces, double* verts, int32_t* faces,
+                         int32_t* points2d, float* vdepth, long long* frame_offsets, const unsigned long long* d_totals,
+                         void* stream) {
     hv::D2mGrid g;
     D2mLayout L;
     int rc = d2m_grid(&g, depth, mask, diag, B, H, W, max_depth_distance, flags, scratch, scratch_bytes, &L);
@@ -608,10 +615,33 @@ extern "C" int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_
     out.frame_off = frame_offsets;
     out.n_verts = (unsigned long long)n_verts;
     out.n_faces = (unsigned long long)n_faces;
+    out.d_totals = d_totals;
     const dim3 grid((unsigned int)((g.wpr + hv::kD2mThreads / 32 - 1) / (hv::kD2mThreads / 32)), (unsigned int)((H + hv::kD2mRows - 1) / hv::kD2mRows), (unsigned int)B);
-    hv::d2m_emit_kernel<<<grid, hv::kD2mThreads, 0, hv::as_stream(stream)>>>(g, out);
+    if (d_totals) hv::d2m_emit_kernel<true><<<grid, hv::kD2mThreads, 0, hv::as_stream(stream)>>>(g, out);
+    else hv::d2m_emit_kernel<false><<<grid, hv::kD2mThreads, 0, hv::as_stream(stream)>>>(g, out);
     HV_CUDA(cudaGetLastError());
     return HV_OK;
+}
+
+extern "C" int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                           float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
+                           int64_t scratch_bytes, int64_t n_verts, int64_t n_faces, double* verts, int32_t* faces,
+                           int32_t* points2d, float* vdepth, long long* frame_offsets, void* stream) {
+    return d2m_emit_impl(depth, mask, diag, B, H, W, max_depth_distance, flags, h_kinv, cams, scratch, scratch_bytes, n_verts,
+                         n_faces, verts, faces, points2d, vdepth, frame_offsets, nullptr, stream);
+}
+
+// hv_d2m_emit without the host having read the totals: the outputs hold cap_verts / cap_faces rows, `totals` is the DEVICE
+// pair hv_d2m_count wrote on the same stream.  Rows beyond the capacity are dropped; frame_offsets still end in the true
+// totals, so the caller sees the overflow when it reads them (and repeats with hv_d2m_emit, exactly sized).
+extern "C" int hv_d2m_emit_capped(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                                  float max_depth_distance, int flags, const double* h_kinv, const double* cams,
+                                  void* scratch, int64_t scratch_bytes, int64_t cap_verts, int64_t cap_faces, double* verts,
+                                  int32_t* faces, int32_t* points2d, float* vdepth, long long* frame_offsets,
+                                  const unsigned long long* totals, void* stream) {
+    HV_REQUIRE(totals, "hv_d2m_emit_capped: null totals");
+    return d2m_emit_impl(depth, mask, diag, B, H, W, max_depth_distance, flags, h_kinv, cams, scratch, scratch_bytes, cap_verts,
+                         cap_faces, verts, faces, points2d, vdepth, frame_offsets, totals, stream);
 }
 
 extern "C" int hv_image2world(const double* points2d, const double* depth, int64_t n, const double* cam, double scale,

@@ -77,33 +77,90 @@ class DepthMeshBatch:
         return _xfer.to_host(self.verts, self.faces, self.points2d, self.vdepth)
 
 
+_TRACE = None   # tools/time_d2m_phases.py sets a list: (label, perf_counter) after every host-side step of the batched call
+_D2M_SCRATCH = {}  # (device index, B, H, W, want_points, stream) -> (scratch, aligned pointer, size, totals pair)
+_D2M_CAPS = {}  # (device index, B, H, W, want_points) -> (vertices, faces) of the last batch of that shape
+
+
 def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, diag=None, want_points=True):
-    """Core batched call on device tensors.  depth (B,H,W) f32, mask (B,H,W) u8 or None, cams (B,12) f64."""
+    """Core batched call on device tensors.  depth (B,H,W) f32, mask (B,H,W) u8 or None, cams (B,12) f64.
+
+    The output sizes are data dependent.  The first batch of a shape reads the totals between the count and the emit
+    launch; later batches of that shape emit straight away into buffers sized 1.25 x the previous batch (consecutive batches
+    of a clip are alike), so count, scan and emit run back to back and the host reads the totals and the frame offsets in
+    one go afterwards -- if the guess was too small, the emit is repeated exactly sized.
+    """
     torch = _lib.require_cuda()
     lib = _lib.load()
     B, H, W = (int(s) for s in depth.shape)
     dev = depth.device
+    key = (dev.index, B, H, W, bool(want_points))
+    kinv = np.ascontiguousarray(kinv, dtype=np.float64)
+
+    def mark(label):
+        if _TRACE is not None:
+            import time
+            _TRACE.append((label, time.perf_counter()))
+
+    mark("start")
     with torch.cuda.device(dev):
-        nbytes = ctypes.c_int64(0)
-        _lib.check(lib.hv_d2m_scratch_bytes(B, H, W, ctypes.byref(nbytes)))
-        scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
-        sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
-        totals = torch.zeros(2, dtype=torch.int64, device=dev)
-        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        stream_id = torch.cuda.current_stream().cuda_stream
+        stream = ctypes.c_void_p(stream_id)
+        # scratch and the totals pair are kept per (shape, stream): calls on one stream are ordered, so the next call may
+        # overwrite them (everything a call hands out lives in its own tensors)
+        kept = _D2M_SCRATCH.get(key + (stream_id,))
+        if kept is None:
+            nbytes = ctypes.c_int64(0)
+            _lib.check(lib.hv_d2m_scratch_bytes(B, H, W, ctypes.byref(nbytes)))
+            scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=dev)
+            kept = (scratch, ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256), nbytes,
+                    torch.empty(2, dtype=torch.int64, device=dev))
+            if len(_D2M_SCRATCH) >= 8:
+                _D2M_SCRATCH.clear()
+            _D2M_SCRATCH[key + (stream_id,)] = kept
+        scratch, sptr, nbytes, totals = kept
         mdd = ctypes.c_float(np.float32(max_depth_distance))
         _lib.check(lib.hv_d2m_count(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags, sptr, int(nbytes.value),
                                     _ptr(totals), stream))
-        n_verts, n_faces = (int(v) for v in totals.cpu().tolist())
-        verts = torch.empty((n_verts, 3), dtype=torch.float64, device=dev)
-        faces = torch.empty((n_faces, 3), dtype=torch.int32, device=dev)
-        points2d = torch.empty((n_verts, 2), dtype=torch.int32, device=dev) if want_points else None
-        vdepth = torch.empty((n_verts,), dtype=torch.float32, device=dev) if want_points else None
-        frame_off = torch.zeros((B + 1, 2), dtype=torch.int64, device=dev)
-        kinv = np.ascontiguousarray(kinv, dtype=np.float64)
-        _lib.check(lib.hv_d2m_emit(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags,
-                                   kinv.ctypes.data_as(ctypes.c_void_p), _ptr(cams), sptr, int(nbytes.value), n_verts,
-                                   n_faces, _ptr(verts), _ptr(faces), _ptr(points2d), _ptr(vdepth), _ptr(frame_off), stream))
-        return DepthMeshBatch(verts, faces, points2d, vdepth, frame_off.cpu().numpy())
+        mark("scratch + count launched")
+
+        def outputs(n_verts, n_faces):
+            return (torch.empty((n_verts, 3), dtype=torch.float64, device=dev),
+                    torch.empty((n_faces, 3), dtype=torch.int32, device=dev),
+                    torch.empty((n_verts, 2), dtype=torch.int32, device=dev) if want_points else None,
+                    torch.empty((n_verts,), dtype=torch.float32, device=dev) if want_points else None,
+                    torch.empty((B + 1, 2), dtype=torch.int64, device=dev))
+
+        guess = _D2M_CAPS.get(key)
+        frame_off_host = None
+        if guess is not None:
+            cap_v, cap_f = (min(int(1.25 * g) + 4096, lim) for g, lim in zip(guess, (B * H * W, 8 * B * H * W)))
+            verts, faces, points2d, vdepth, frame_off = outputs(cap_v, cap_f)
+            _lib.check(lib.hv_d2m_emit_capped(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags,
+                                              kinv.ctypes.data_as(ctypes.c_void_p), _ptr(cams), sptr, int(nbytes.value), cap_v,
+                                              cap_f, _ptr(verts), _ptr(faces), _ptr(points2d), _ptr(vdepth), _ptr(frame_off),
+                                              _ptr(totals), stream))
+            mark("outputs + emit launched")
+            frame_off_host = _xfer.to_host(frame_off)  # the one host read: frame offsets, the last row = the totals
+            n_verts, n_faces = (int(v) for v in frame_off_host[B])
+            mark("offsets read")
+            if n_verts <= cap_v and n_faces <= cap_f:
+                verts, faces = verts[:n_verts], faces[:n_faces]
+                if want_points:
+                    points2d, vdepth = points2d[:n_verts], vdepth[:n_verts]
+            else:
+                frame_off_host = None  # too small a guess: again below, exactly sized
+        else:
+            n_verts, n_faces = (int(v) for v in _xfer.to_host(totals))
+        if frame_off_host is None:
+            verts, faces, points2d, vdepth, frame_off = outputs(n_verts, n_faces)
+            _lib.check(lib.hv_d2m_emit(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags,
+                                       kinv.ctypes.data_as(ctypes.c_void_p), _ptr(cams), sptr, int(nbytes.value), n_verts,
+                                       n_faces, _ptr(verts), _ptr(faces), _ptr(points2d), _ptr(vdepth), _ptr(frame_off), stream))
+            frame_off_host = _xfer.to_host(frame_off)
+        _D2M_CAPS[key] = (n_verts, n_faces)
+        mark("done")
+        return DepthMeshBatch(verts, faces, points2d, vdepth, frame_off_host)
 
 
 def d2m_flags(max_pixel_distance) -> int:

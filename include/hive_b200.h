@@ -239,6 +239,15 @@ int hv_d2m_emit(const float* depth, const uint8_t* mask, const uint8_t* diag, in
                 float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
                 int64_t scratch_bytes, int64_t n_verts, int64_t n_faces, double* verts, int32_t* faces, int32_t* points2d,
                 float* vdepth, long long* frame_offsets, void* stream);
+/* hv_d2m_emit before the host has read the totals (no round trip between count and emit): the outputs hold cap_verts /
+ * cap_faces rows -- a guess, e.g. from the previous batch -- and `totals` is the DEVICE pair hv_d2m_count wrote on the same
+ * stream.  Rows past the capacity are dropped; frame_offsets[B] still carries the true totals, so the caller sees an
+ * overflow when it reads them and repeats with hv_d2m_emit, exactly sized (the scratch stays valid). */
+int hv_d2m_emit_capped(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
+                       float max_depth_distance, int flags, const double* h_kinv, const double* cams, void* scratch,
+                       int64_t scratch_bytes, int64_t cap_verts, int64_t cap_faces, double* verts, int32_t* faces,
+                       int32_t* points2d, float* vdepth, long long* frame_offsets, const unsigned long long* totals,
+                       void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Elementwise projections, float64 like the reference.  `cam` is a DEVICE array of 21 doubles: a 3x3 matrix

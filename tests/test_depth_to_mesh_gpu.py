@@ -140,6 +140,32 @@ def test_batch_equals_single_frames_and_handles_empty_frames():
     assert v.shape == (0, 3) and f.shape == (0, 3)
 
 
+def test_batches_without_the_mid_call_read_equal_the_exactly_sized_call():
+    """Second and later batches of a shape emit into buffers sized from the previous batch before the host has seen the
+    totals (hv_d2m_emit_capped): same result when the guess is generous, and when it is far too small (repeated exactly)."""
+    from hive_b200 import geometric
+    scene = Scene("small", "room")
+    frames = [scene.frame(i) for i in range(3)]
+    depths = np.stack([f.depth for f in frames])
+    poses = np.stack([np.linalg.inv(f.pose) for f in frames])
+    sparse = np.stack([f.mask > 0 for f in frames])
+    dense = np.ones_like(sparse)  # every pixel with a depth: many times the vertices of the instance masks
+
+    def run(masks, fresh):
+        if fresh:
+            geometric._D2M_CAPS.clear()  # the exactly sized path (totals read between count and emit)
+        b = geometric.depth_to_mesh_batch(depths, masks, scene.K, poses)
+        return b.to_host() + (b.frame_offsets.copy(),)
+
+    want_sparse, want_dense = run(sparse, True), run(dense, True)
+    assert len(want_dense[0]) > 3 * len(want_sparse[0]) > 0
+    geometric._D2M_CAPS.clear()
+    for masks, want in ((sparse, want_sparse), (sparse, want_sparse), (dense, want_dense), (dense, want_dense), (sparse, want_sparse)):
+        got = run(masks, False)  # 1st: exact; 2nd: guess fits; 3rd: guess far too small; 4th: fits; 5th: far too large
+        for a, b in zip(got, want):
+            assert a.shape == b.shape and np.array_equal(a, b)
+
+
 def test_texture_crop_and_uv_match_oracle():
     """Pipeline._get_mesh_texture_and_uv (hive/pipeline.py:782-810): crop + UVs bit-exact."""
     from hive_b200.pipeline import Pipeline
