@@ -570,7 +570,17 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
         e2e.append(time.perf_counter() - t0)
         del batch
     e2e_s = float(np.median(e2e[1:]))
-    e2e_fps = _sum_over_ranks(int(B / e2e_s), world, dist, torch)
+    e2e_batch_fps = _sum_over_ranks(int(B / e2e_s), world, dist, torch)
+    # the same through the pipelined host call: chunks of frames, upload / kernels / download overlapped on three streams
+    e2e = []
+    for r in range(4):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        meshes = geometric.depth_to_mesh_host(depths, masks, sc.K, poses)
+        e2e.append(time.perf_counter() - t0)
+        assert meshes.n_vertices == V and meshes.n_faces == F
+        del meshes
+    e2e_fps = _sum_over_ranks(int(B / float(np.median(e2e[1:]))), world, dist, torch)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # the reference's per-frame code (point_cloud_from_depth + scipy Delaunay + _filter_faces,
@@ -620,7 +630,10 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
             "roofline_frac_with_points2d": algo / (ms / 1e3) / 1e9 / peak,
             "roofline_note": "roofline_frac uses SURVEY 8(d)'s 5*H*W + 24*V + 12*F; the kernel also writes 12 B/vertex of "
                              "(u, v, depth) for _filter_faces' callers, counted in roofline_frac_with_points2d",
-            "cpu_baseline": cpu, "e2e_frames_per_s": float(e2e_fps), "process_frame": pf,
+            "cpu_baseline": cpu, "e2e_frames_per_s": float(e2e_fps), "e2e_one_batch_frames_per_s": float(e2e_batch_fps),
+            "e2e_api": "hive_b200.geometric.depth_to_mesh_host (host arrays in, per-frame host arrays out, chunk pipeline); "
+                       "e2e_one_batch = depth_to_mesh_batch + to_host (upload, kernels, download in sequence)",
+            "process_frame": pf,
             "h2d_bytes": int(depths.nbytes + masks.nbytes), "d2h_bytes": int(hv.nbytes + hf.nbytes + hp.nbytes + hd.nbytes),
             "workload": f"{B} frames/GPU of {W}x{H}, instance masks of the room scene, frame-partitioned"}
 

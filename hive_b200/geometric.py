@@ -193,6 +193,130 @@ def depth_to_mesh_batch(depths, masks, K, poses, max_pixel_distance=2, max_depth
     return depth_to_mesh_device(d, m, _kinv64(K), c, max_depth_distance, d2m_flags(max_pixel_distance), g)
 
 
+class HostDepthMeshes:
+    """Per-frame meshes as HOST arrays, chunk by chunk (what ``depth_to_mesh_host`` returns): ``frame(i)`` is
+    (vertices (N,3) f64, faces (F,3) i32 frame-local, points2d (N,2) i32, depth (N,) f32), views of pinned blocks."""
+
+    def __init__(self, chunks, n_frames):
+        self._chunks, self._n = chunks, n_frames  # chunks: (first frame, verts, faces, points2d, vdepth, frame_offsets)
+
+    def __len__(self):
+        return self._n
+
+    def frame(self, i):
+        for first, verts, faces, points2d, vdepth, off in self._chunks:
+            k = i - first
+            if 0 <= k < off.shape[0] - 1:
+                (v0, f0), (v1, f1) = off[k], off[k + 1]
+                return verts[v0:v1], faces[f0:f1], points2d[v0:v1], vdepth[v0:v1]
+        raise IndexError(i)
+
+    @property
+    def n_vertices(self):
+        return sum(int(c[5][-1, 0]) for c in self._chunks)
+
+    @property
+    def n_faces(self):
+        return sum(int(c[5][-1, 1]) for c in self._chunks)
+
+
+def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_distance=0.1, chunk_frames=20,
+                       copy_threads=4):
+    """``depth_to_mesh_batch`` for host arrays in and host arrays out, as a pipeline over chunks of frames: while chunk c
+    is triangulated, chunk c + 1 is on its way up (pinned staging filled by ``copy_threads`` host threads, then H2D on its
+    own stream) and chunk c - 1 on its way down (D2H on a third stream) -- PCIe carries 1.5 MB per frame up and ~2.8 MB
+    down (float64 vertices), the kernels are 1 % of that.  Same per-frame results as ``depth_to_mesh_batch(...).frame(i)``.
+    """
+    from concurrent.futures import ThreadPoolExecutor
+    torch = _lib.require_cuda()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    depths = np.asarray(depths)
+    masks = None if masks is None else np.asarray(masks)
+    poses = np.asarray(poses, dtype=np.float64)
+    B, H, W = depths.shape
+    flags, kinv = d2m_flags(max_pixel_distance), _kinv64(K)
+    cams_host = np.concatenate([poses[:, :3, :3].reshape(B, 9), poses[:, :3, 3].reshape(B, 3)], axis=1)
+    n = max(1, min(int(chunk_frames), B))
+    bounds = [(a, min(a + n, B)) for a in range(0, B, n)]
+    slots = 3
+    pin_d = [torch.empty((n, H, W), dtype=torch.float32, pin_memory=True) for _ in range(slots)]
+    pin_m = [torch.empty((n, H, W), dtype=torch.uint8, pin_memory=True) for _ in range(slots)] if masks is not None else None
+    dev_d = [torch.empty((n, H, W), dtype=torch.float32, device=dev) for _ in range(slots)]
+    dev_m = [torch.empty((n, H, W), dtype=torch.uint8, device=dev) for _ in range(slots)] if masks is not None else None
+    with torch.cuda.device(dev):
+        cams = _xfer.to_device(cams_host, dev)
+        main = torch.cuda.current_stream()
+        s_in, s_run, s_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+        for s_ in (s_in, s_run):
+            s_.wait_stream(main)
+        slot_free = [None] * slots  # event: the kernels that read device slot k have run
+        up_done = [None] * slots    # event: the H2D out of pinned slot k has run
+
+        def stage(c):
+            a, b = bounds[c]
+            k = c % slots
+            if up_done[k] is not None:
+                up_done[k].synchronize()
+            rows = np.array_split(np.arange(a, b), copy_threads)
+
+            def copy(idx):
+                if len(idx):
+                    lo, hi = int(idx[0]), int(idx[-1]) + 1
+                    np.copyto(pin_d[k].numpy()[lo - a:hi - a], depths[lo:hi], casting="unsafe")
+                    if masks is not None:
+                        np.copyto(pin_m[k].numpy()[lo - a:hi - a], masks[lo:hi], casting="unsafe")
+            return [pool.submit(copy, idx) for idx in rows]
+
+        def upload(c, futures):
+            for f in futures:
+                f.result()
+            a, b = bounds[c]
+            k = c % slots
+            with torch.cuda.stream(s_in):
+                if slot_free[k] is not None:
+                    s_in.wait_event(slot_free[k])
+                dev_d[k][:b - a].copy_(pin_d[k][:b - a], non_blocking=True)
+                if masks is not None:
+                    dev_m[k][:b - a].copy_(pin_m[k][:b - a], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(s_in)
+            up_done[k] = ev
+            return ev
+
+        chunks, downloads = [], []
+        with ThreadPoolExecutor(max_workers=max(1, int(copy_threads))) as pool:
+            staged = {0: stage(0)}
+            if len(bounds) > 1:
+                staged[1] = stage(1)
+            uploaded = {0: upload(0, staged.pop(0))}
+            for c, (a, b) in enumerate(bounds):
+                if c + 1 < len(bounds):
+                    uploaded[c + 1] = upload(c + 1, staged.pop(c + 1))  # on its way up while chunk c is worked on
+                if c + 2 < len(bounds):
+                    staged[c + 2] = stage(c + 2)
+                k = c % slots
+                with torch.cuda.stream(s_run):
+                    s_run.wait_event(uploaded.pop(c))
+                    out = depth_to_mesh_device(dev_d[k][:b - a], None if masks is None else dev_m[k][:b - a], kinv,
+                                               cams[a:b], max_depth_distance, flags)
+                    done = torch.cuda.Event()
+                    done.record(s_run)
+                slot_free[k] = done
+                with torch.cuda.stream(s_out):  # (depth_to_mesh_device has synchronised s_run: the results exist)
+                    host = []
+                    for t in (out.verts, out.faces, out.points2d, out.vdepth):
+                        h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                        if t.numel():
+                            h.copy_(t, non_blocking=True)
+                            t.record_stream(s_out)
+                        host.append(h)
+                downloads.append(host)
+                chunks.append((a, out.frame_offsets))
+            s_out.synchronize()
+        main.wait_stream(s_run)
+    return HostDepthMeshes([(a,) + tuple(h.numpy() for h in host) + (off,) for (a, off), host in zip(chunks, downloads)], B)
+
+
 def point_cloud_from_depth(depth, mask, K, R=_EYE, t=_ZERO_T):
     """hive/geometric.py:107-126: (N, 3) float64 world points of ``mask & (depth > 0)``, row-major order."""
     torch = _lib.require_cuda()

@@ -166,6 +166,28 @@ def test_batches_without_the_mid_call_read_equal_the_exactly_sized_call():
             assert a.shape == b.shape and np.array_equal(a, b)
 
 
+@pytest.mark.parametrize("chunk_frames,with_masks", [(3, True), (7, True), (2, False)])
+def test_pipelined_host_call_equals_the_batch(chunk_frames, with_masks):
+    """depth_to_mesh_host (chunks of frames, upload / kernels / download overlapped on three streams) returns, frame by
+    frame, what the one-batch call returns -- chunks that do not divide the clip, an empty frame, bool masks."""
+    from hive_b200 import geometric
+    scene = Scene("small", "room")
+    frames = [scene.frame(i % 5) for i in range(7)]
+    depths = np.stack([f.depth for f in frames])
+    masks = np.stack([f.mask > 0 for f in frames])
+    masks[4] = False
+    poses = np.stack([np.linalg.inv(f.pose) for f in frames])
+    want = geometric.depth_to_mesh_batch(depths, masks if with_masks else None, scene.K, poses)
+    got = geometric.depth_to_mesh_host(depths, masks if with_masks else None, scene.K, poses, chunk_frames=chunk_frames,
+                                       copy_threads=3)
+    assert len(got) == 7 and got.n_vertices == want.frame_offsets[-1, 0] and got.n_faces == want.frame_offsets[-1, 1]
+    for i in range(7):
+        for a, b in zip(got.frame(i), want.frame(i)):
+            assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b)
+    if with_masks:
+        assert got.frame(4)[0].shape == (0, 3)
+
+
 def test_texture_crop_and_uv_match_oracle():
     """Pipeline._get_mesh_texture_and_uv (hive/pipeline.py:782-810): crop + UVs bit-exact."""
     from hive_b200.pipeline import Pipeline
