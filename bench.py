@@ -447,8 +447,8 @@ def measure_mesh(vol, torch, peak, repeats=5, cpu=True):
 
 
 def measure_mesh_sharded(vol, world, rank, dist, torch, repeats=3):
-    """Seam-stitched get_mesh of the z-slab sharded volume: halo exchange + per-slab marching cubes + gather to rank 0
-    + key resolution + D2H, wall clock between barriers, max over ranks (median of `repeats` after one warm-up)."""
+    """Seam-placed get_mesh of the z-slab sharded volume: halo exchange + per-slab marching cubes + column-count all-gather
+    + rows stored straight into rank 0's HBM (or gathered) + D2H, wall clock between barriers, max over ranks (median of `repeats` after one warm-up)."""
     times, out = [], None
     for r in range(repeats + 1):
         out = None
@@ -460,7 +460,10 @@ def measure_mesh_sharded(vol, world, rank, dist, torch, repeats=3):
         if r > 0:
             times.append(ms)
     res = {"get_mesh_e2e_ms": float(np.median(times)), "scene": "room", "slabs": world,
-           "voxels": int(np.prod(vol.global_dim)), "stitched": True}
+           "voxels": int(np.prod(vol.global_dim)), "stitched": True,
+           # "p2p": every slab's emit kernel stored its rows into rank 0's HBM over NVLink; "gather": grouped send/recv + scatter
+           "assembly": getattr(vol, "last_mesh_path", None)}
+    vol.close()  # collective: unmap / free the shared mesh buffer
     if rank == 0:
         res.update(vertices=int(out[0].shape[0]), triangles=int(out[1].shape[0]),
                    d2h_bytes=int(sum(a.nbytes for a in out)))
