@@ -584,6 +584,14 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
         assert meshes.n_vertices == V and meshes.n_faces == F
         del meshes
     e2e_fps = _sum_over_ranks(int(B / float(np.median(e2e[1:]))), world, dist, torch)
+    e2e = []
+    for r in range(4):  # and what a glTF export needs: float32 positions + faces only
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        meshes = geometric.depth_to_mesh_host(depths, masks, sc.K, poses, vertex_dtype=np.float32, want_points=False)
+        e2e.append(time.perf_counter() - t0)
+        del meshes
+    e2e_lean_fps = _sum_over_ranks(int(B / float(np.median(e2e[1:]))), world, dist, torch)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # the reference's per-frame code (point_cloud_from_depth + scipy Delaunay + _filter_faces,
@@ -634,6 +642,7 @@ def measure_d2m(args, base_cfg, world, rank, torch, dist, peak, repeats=5):
             "roofline_note": "roofline_frac uses SURVEY 8(d)'s 5*H*W + 24*V + 12*F; the kernel also writes 12 B/vertex of "
                              "(u, v, depth) for _filter_faces' callers, counted in roofline_frac_with_points2d",
             "cpu_baseline": cpu, "e2e_frames_per_s": float(e2e_fps), "e2e_one_batch_frames_per_s": float(e2e_batch_fps),
+            "e2e_f32_positions_only_frames_per_s": float(e2e_lean_fps), "d2h_bytes_f32_positions_only": int(12 * V + 12 * F),
             "e2e_api": "hive_b200.geometric.depth_to_mesh_host (host arrays in, per-frame host arrays out, chunk pipeline); "
                        "e2e_one_batch = depth_to_mesh_batch + to_host (upload, kernels, download in sequence)",
             "process_frame": pf,

@@ -287,6 +287,7 @@ struct D2mOut {
     const double* cams;  // [B][12]: R row-major (9), t (3) -- world-to-camera, as hive/geometric.py passes them
     double Kinv[9];
     double* verts;        // [V][3]
+    float* verts32;       // HV_D2M_VERTS_F32: the same rounded to float32 (what a glTF export keeps), verts is null then
     int32_t* faces;       // [F][3] frame-local vertex ids
     int32_t* points2d;    // [V][2] (u, v) or null
     float* vdepth;        // [V] or null
@@ -401,8 +402,11 @@ __global__ void __launch_bounds__(kD2mThreads) d2m_emit_kernel(const D2mGrid g, 
                 X[k] = __dsub_rn(__dmul_rn(dd, pc), cam[9 + k]);
             }
 #pragma unroll
-            for (int k = 0; k < 3; ++k)  // R^T @ X
-                out.verts[3 * vi + k] = fma(cam[6 + k], X[2], fma(cam[3 + k], X[1], __dmul_rn(cam[k], X[0])));
+            for (int k = 0; k < 3; ++k) {  // R^T @ X
+                const double w = fma(cam[6 + k], X[2], fma(cam[3 + k], X[1], __dmul_rn(cam[k], X[0])));
+                if (out.verts32) out.verts32[3 * vi + k] = __double2float_rn(w);
+                else out.verts[3 * vi + k] = w;
+            }
             if (out.points2d) {
                 out.points2d[2 * vi] = u;
                 out.points2d[2 * vi + 1] = v;
@@ -608,7 +612,8 @@ static int d2m_emit_impl(const float* depth, const uint8_t* mask, const uint8_t*
     hv::D2mOut out;
     out.cams = cams;
     for (int k = 0; k < 9; ++k) out.Kinv[k] = h_kinv[k];
-    out.verts = verts;
+    out.verts = (flags & HV_D2M_VERTS_F32) ? nullptr : verts;
+    out.verts32 = (flags & HV_D2M_VERTS_F32) ? reinterpret_cast<float*>(verts) : nullptr;
     out.faces = faces;
     out.points2d = points2d;
     out.vdepth = vdepth;

@@ -82,19 +82,27 @@ _D2M_SCRATCH = {}  # (device index, B, H, W, want_points, stream) -> (scratch, a
 _D2M_CAPS = {}  # (device index, B, H, W, want_points) -> (vertices, faces) of the last batch of that shape
 
 
-def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, diag=None, want_points=True):
+def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, diag=None, want_points=True,
+                         vertex_dtype=np.float64):
     """Core batched call on device tensors.  depth (B,H,W) f32, mask (B,H,W) u8 or None, cams (B,12) f64.
 
     The output sizes are data dependent.  The first batch of a shape reads the totals between the count and the emit
     launch; later batches of that shape emit straight away into buffers sized 1.25 x the previous batch (consecutive batches
     of a clip are alike), so count, scan and emit run back to back and the host reads the totals and the frame offsets in
     one go afterwards -- if the guess was too small, the emit is repeated exactly sized.
+
+    ``vertex_dtype=np.float32`` (HV_D2M_VERTS_F32) stores the float64 vertices rounded to float32 -- what a glTF export keeps
+    anyway -- for callers that pay for the bytes (host transfers); the reference's arrays are float64, the default.
     """
     torch = _lib.require_cuda()
     lib = _lib.load()
     B, H, W = (int(s) for s in depth.shape)
     dev = depth.device
-    key = (dev.index, B, H, W, bool(want_points))
+    f32 = np.dtype(vertex_dtype) == np.float32
+    assert f32 or np.dtype(vertex_dtype) == np.float64, "vertices are float64 (the reference) or float32"
+    if f32:
+        flags = int(flags) | 4  # HV_D2M_VERTS_F32
+    key = (dev.index, B, H, W, bool(want_points), f32)
     kinv = np.ascontiguousarray(kinv, dtype=np.float64)
 
     def mark(label):
@@ -125,11 +133,14 @@ def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, dia
         mark("scratch + count launched")
 
         def outputs(n_verts, n_faces):
-            return (torch.empty((n_verts, 3), dtype=torch.float64, device=dev),
+            return (torch.empty((n_verts, 3), dtype=torch.float32 if f32 else torch.float64, device=dev),
                     torch.empty((n_faces, 3), dtype=torch.int32, device=dev),
                     torch.empty((n_verts, 2), dtype=torch.int32, device=dev) if want_points else None,
                     torch.empty((n_verts,), dtype=torch.float32, device=dev) if want_points else None,
-                    torch.empty((B + 1, 2), dtype=torch.int64, device=dev))
+                    # the frame offsets are stored by the emit kernel straight into page-locked host memory (the address is
+                    # valid on the device: unified addressing) -- 16 bytes per frame over the bus as posted writes, no copy
+                    # to queue behind a bulk download on the D2H engine; visible to the host after the stream's sync
+                    torch.empty((B + 1, 2), dtype=torch.int64, pin_memory=True))
 
         guess = _D2M_CAPS.get(key)
         frame_off_host = None
@@ -141,7 +152,8 @@ def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, dia
                                               cap_f, _ptr(verts), _ptr(faces), _ptr(points2d), _ptr(vdepth), _ptr(frame_off),
                                               _ptr(totals), stream))
             mark("outputs + emit launched")
-            frame_off_host = _xfer.to_host(frame_off)  # the one host read: frame offsets, the last row = the totals
+            torch.cuda.current_stream().synchronize()  # the one wait of the call
+            frame_off_host = frame_off.numpy()             # frame offsets, the last row = the totals
             n_verts, n_faces = (int(v) for v in frame_off_host[B])
             mark("offsets read")
             if n_verts <= cap_v and n_faces <= cap_f:
@@ -157,7 +169,8 @@ def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, dia
             _lib.check(lib.hv_d2m_emit(_ptr(depth), _ptr(mask), _ptr(diag), B, H, W, mdd, flags,
                                        kinv.ctypes.data_as(ctypes.c_void_p), _ptr(cams), sptr, int(nbytes.value), n_verts,
                                        n_faces, _ptr(verts), _ptr(faces), _ptr(points2d), _ptr(vdepth), _ptr(frame_off), stream))
-            frame_off_host = _xfer.to_host(frame_off)
+            torch.cuda.current_stream().synchronize()
+            frame_off_host = frame_off.numpy()
         _D2M_CAPS[key] = (n_verts, n_faces)
         mark("done")
         return DepthMeshBatch(verts, faces, points2d, vdepth, frame_off_host)
@@ -193,6 +206,16 @@ def depth_to_mesh_batch(depths, masks, K, poses, max_pixel_distance=2, max_depth
     return depth_to_mesh_device(d, m, _kinv64(K), c, max_depth_distance, d2m_flags(max_pixel_distance), g)
 
 
+_HOST_STREAMS = {}  # device index -> (upload, kernel, download) streams of depth_to_mesh_host
+_HOST_TRACE = None  # tools/tune_d2m_host.py sets a list: (chunk, step, perf_counter) of depth_to_mesh_host's main thread
+
+
+def _host_mark(chunk, step):
+    if _HOST_TRACE is not None:
+        import time
+        _HOST_TRACE.append((chunk, step, time.perf_counter()))
+
+
 class HostDepthMeshes:
     """Per-frame meshes as HOST arrays, chunk by chunk (what ``depth_to_mesh_host`` returns): ``frame(i)`` is
     (vertices (N,3) f64, faces (F,3) i32 frame-local, points2d (N,2) i32, depth (N,) f32), views of pinned blocks."""
@@ -208,7 +231,8 @@ class HostDepthMeshes:
             k = i - first
             if 0 <= k < off.shape[0] - 1:
                 (v0, f0), (v1, f1) = off[k], off[k + 1]
-                return verts[v0:v1], faces[f0:f1], points2d[v0:v1], vdepth[v0:v1]
+                return (verts[v0:v1], faces[f0:f1], None if points2d is None else points2d[v0:v1],
+                        None if vdepth is None else vdepth[v0:v1])
         raise IndexError(i)
 
     @property
@@ -221,11 +245,13 @@ class HostDepthMeshes:
 
 
 def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_distance=0.1, chunk_frames=20,
-                       copy_threads=4):
+                       copy_threads=8, vertex_dtype=np.float64, want_points=True):
     """``depth_to_mesh_batch`` for host arrays in and host arrays out, as a pipeline over chunks of frames: while chunk c
     is triangulated, chunk c + 1 is on its way up (pinned staging filled by ``copy_threads`` host threads, then H2D on its
     own stream) and chunk c - 1 on its way down (D2H on a third stream) -- PCIe carries 1.5 MB per frame up and ~2.8 MB
     down (float64 vertices), the kernels are 1 % of that.  Same per-frame results as ``depth_to_mesh_batch(...).frame(i)``.
+    The bus is the limit, so the two options are about bytes: ``vertex_dtype=np.float32`` (12 instead of 24 bytes per vertex)
+    and ``want_points=False`` (no (u, v, depth) per vertex: 12 bytes less; ``frame(i)`` then returns None for them).
     """
     from concurrent.futures import ThreadPoolExecutor
     torch = _lib.require_cuda()
@@ -237,34 +263,44 @@ def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_
     flags, kinv = d2m_flags(max_pixel_distance), _kinv64(K)
     cams_host = np.concatenate([poses[:, :3, :3].reshape(B, 9), poses[:, :3, 3].reshape(B, 3)], axis=1)
     n = max(1, min(int(chunk_frames), B))
-    bounds = [(a, min(a + n, B)) for a in range(0, B, n)]
+    bounds, a, step = [], 0, max(1, n // 4)  # the first chunks are small: the pipeline starts after 1/4 of a chunk is staged
+    while a < B:
+        bounds.append((a, min(a + step, B)))
+        a += step
+        step = min(n, 2 * step)
     slots = 3
-    pin_d = [torch.empty((n, H, W), dtype=torch.float32, pin_memory=True) for _ in range(slots)]
-    pin_m = [torch.empty((n, H, W), dtype=torch.uint8, pin_memory=True) for _ in range(slots)] if masks is not None else None
+    # the whole clip is staged into pinned memory by the host threads, chunk by chunk in order, as fast as they can; the
+    # loop below only waits for the chunk it is about to send (staging chunk c + 2 while chunk c runs made the staging
+    # threads the bottleneck: next to the two DMA streams they copy at 4-6 GB/s each)
+    pin_d = torch.empty((B, H, W), dtype=torch.float32, pin_memory=True)
+    pin_m = torch.empty((B, H, W), dtype=torch.uint8, pin_memory=True) if masks is not None else None
     dev_d = [torch.empty((n, H, W), dtype=torch.float32, device=dev) for _ in range(slots)]
     dev_m = [torch.empty((n, H, W), dtype=torch.uint8, device=dev) for _ in range(slots)] if masks is not None else None
     with torch.cuda.device(dev):
         cams = _xfer.to_device(cams_host, dev)
         main = torch.cuda.current_stream()
-        s_in, s_run, s_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
-        for s_ in (s_in, s_run):
+        # the same three streams for every call: torch's caching allocator keeps its blocks per stream, so fresh streams
+        # would cudaMalloc the scratch and the outputs of the first chunks again on every call (measured: 5 ms)
+        streams = _HOST_STREAMS.get(dev.index)
+        if streams is None:
+            streams = _HOST_STREAMS[dev.index] = (torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream())
+        s_in, s_run, s_out = streams
+        for s_ in streams:
             s_.wait_stream(main)
         slot_free = [None] * slots  # event: the kernels that read device slot k have run
-        up_done = [None] * slots    # event: the H2D out of pinned slot k has run
 
         def stage(c):
             a, b = bounds[c]
-            k = c % slots
-            if up_done[k] is not None:
-                up_done[k].synchronize()
             rows = np.array_split(np.arange(a, b), copy_threads)
 
             def copy(idx):
+                _host_mark(c, "  worker: copy begins")
                 if len(idx):
                     lo, hi = int(idx[0]), int(idx[-1]) + 1
-                    np.copyto(pin_d[k].numpy()[lo - a:hi - a], depths[lo:hi], casting="unsafe")
+                    np.copyto(pin_d.numpy()[lo:hi], depths[lo:hi], casting="unsafe")
                     if masks is not None:
-                        np.copyto(pin_m[k].numpy()[lo - a:hi - a], masks[lo:hi], casting="unsafe")
+                        np.copyto(pin_m.numpy()[lo:hi], masks[lo:hi], casting="unsafe")
+                _host_mark(c, "  worker: copy ends")
             return [pool.submit(copy, idx) for idx in rows]
 
         def upload(c, futures):
@@ -275,36 +311,38 @@ def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_
             with torch.cuda.stream(s_in):
                 if slot_free[k] is not None:
                     s_in.wait_event(slot_free[k])
-                dev_d[k][:b - a].copy_(pin_d[k][:b - a], non_blocking=True)
+                dev_d[k][:b - a].copy_(pin_d[a:b], non_blocking=True)
                 if masks is not None:
-                    dev_m[k][:b - a].copy_(pin_m[k][:b - a], non_blocking=True)
+                    dev_m[k][:b - a].copy_(pin_m[a:b], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(s_in)
-            up_done[k] = ev
             return ev
 
         chunks, downloads = [], []
         with ThreadPoolExecutor(max_workers=max(1, int(copy_threads))) as pool:
-            staged = {0: stage(0)}
-            if len(bounds) > 1:
-                staged[1] = stage(1)
+            staged = {c: stage(c) for c in range(len(bounds))}
             uploaded = {0: upload(0, staged.pop(0))}
             for c, (a, b) in enumerate(bounds):
+                _host_mark(c, "begin")
                 if c + 1 < len(bounds):
                     uploaded[c + 1] = upload(c + 1, staged.pop(c + 1))  # on its way up while chunk c is worked on
-                if c + 2 < len(bounds):
-                    staged[c + 2] = stage(c + 2)
+                _host_mark(c, "next upload queued")
                 k = c % slots
                 with torch.cuda.stream(s_run):
                     s_run.wait_event(uploaded.pop(c))
                     out = depth_to_mesh_device(dev_d[k][:b - a], None if masks is None else dev_m[k][:b - a], kinv,
-                                               cams[a:b], max_depth_distance, flags)
+                                               cams[a:b], max_depth_distance, flags, want_points=want_points,
+                                               vertex_dtype=vertex_dtype)
                     done = torch.cuda.Event()
                     done.record(s_run)
                 slot_free[k] = done
+                _host_mark(c, "kernels done")
                 with torch.cuda.stream(s_out):  # (depth_to_mesh_device has synchronised s_run: the results exist)
                     host = []
                     for t in (out.verts, out.faces, out.points2d, out.vdepth):
+                        if t is None:
+                            host.append(None)
+                            continue
                         h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
                         if t.numel():
                             h.copy_(t, non_blocking=True)
@@ -312,9 +350,12 @@ def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_
                         host.append(h)
                 downloads.append(host)
                 chunks.append((a, out.frame_offsets))
+                _host_mark(c, "download queued")
             s_out.synchronize()
+            _host_mark(len(bounds), "downloads done")
         main.wait_stream(s_run)
-    return HostDepthMeshes([(a,) + tuple(h.numpy() for h in host) + (off,) for (a, off), host in zip(chunks, downloads)], B)
+    return HostDepthMeshes([(a,) + tuple(None if h is None else h.numpy() for h in host) + (off,)
+                            for (a, off), host in zip(chunks, downloads)], B)
 
 
 def point_cloud_from_depth(depth, mask, K, R=_EYE, t=_ZERO_T):

@@ -224,13 +224,16 @@ int hv_mc_extract(const float* tsdf, const float* halo_lo, const float* halo_hi,
  * Two calls (output sizes are data dependent): hv_d2m_count writes totals[0] = #vertices, totals[1] = #faces of the
  * whole batch; hv_d2m_emit writes the concatenated outputs.  Vertex ids in `faces` are frame-local ranks of the valid
  * pixels in row-major order (np.nonzero order); winding has negative signed area in (u, v), like the reference's
- * reversed Delaunay simplices.  frame_offsets: [B+1][2] int64 (vertex, face) start of each frame.
+ * reversed Delaunay simplices.  frame_offsets: [B+1][2] int64 (vertex, face) start of each frame (device memory, or
+ * page-locked host memory: 16 bytes per frame, written once).
  * h_kinv : HOST, 9 doubles, inv(K) computed in K's own dtype (geometric.py:202).  cams: DEVICE, [B][12] doubles, the
  * world-to-camera R (row-major) and t that geometric.py takes.  points2d ([V][2] int32 u,v) and vdepth ([V] float32)
  * are optional.
  * ---------------------------------------------------------------------------------------------------------- */
 #define HV_D2M_BRIDGES 1
 #define HV_D2M_VERTS_ONLY 2 /* point_cloud_from_depth: back-projection only, no faces */
+#define HV_D2M_VERTS_F32 4  /* hv_d2m_emit*: `verts` is float32 [V][3] -- the float64 result rounded to nearest (what a glTF
+                               export keeps; the reference's arrays are float64) -- for callers that pay for the bytes */
 int hv_d2m_scratch_bytes(int B, int H, int W, int64_t* h_bytes);
 int hv_d2m_count(const float* depth, const uint8_t* mask, const uint8_t* diag, int B, int H, int W,
                  float max_depth_distance, int flags, void* scratch, int64_t scratch_bytes, unsigned long long* totals,

@@ -186,6 +186,14 @@ def test_pipelined_host_call_equals_the_batch(chunk_frames, with_masks):
             assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b)
     if with_masks:
         assert got.frame(4)[0].shape == (0, 3)
+    # the byte-saving options: float32 vertices are the float64 ones rounded to nearest; no (u, v, depth) per vertex
+    lean = geometric.depth_to_mesh_host(depths, masks if with_masks else None, scene.K, poses, chunk_frames=chunk_frames,
+                                        vertex_dtype=np.float32, want_points=False)
+    for i in range(7):
+        v, f, p2, md = lean.frame(i)
+        wv, wf, _, _ = want.frame(i)
+        assert v.dtype == np.float32 and np.array_equal(v, wv.astype(np.float32)) and np.array_equal(f, wf)
+        assert p2 is None and md is None
 
 
 def test_texture_crop_and_uv_match_oracle():
