@@ -177,14 +177,17 @@ def depth_to_mesh_device(depth, mask, kinv, cams, max_depth_distance, flags, dia
 
 
 def d2m_flags(max_pixel_distance) -> int:
-    """The lattice rule is exact for max_pixel_distance in [sqrt2, sqrt5); HIVE's default is 2."""
+    """The lattice rule is exact for max_pixel_distance in [sqrt2, sqrt5); HIVE's default is 2.  Below
+    sqrt2 no triangle of lattice points survives the edge filter (the shortest one has a sqrt2 hypotenuse): vertices only."""
     mpd = float(max_pixel_distance)
-    if np.sqrt(2.0) <= mpd < 2.0:
+    if mpd < np.sqrt(2.0):
+        return 2  # HV_D2M_VERTS_ONLY
+    if mpd < 2.0:
         return 0
-    if 2.0 <= mpd < np.sqrt(5.0):
+    if mpd < np.sqrt(5.0):
         return 1  # HV_D2M_BRIDGES
     raise NotImplementedError(
-        f"max_pixel_distance={mpd}: the closed-form lattice triangulation covers [sqrt(2), sqrt(5)) only")
+        f"max_pixel_distance={mpd}: the closed-form lattice triangulation covers [0, sqrt(5)) only")
 
 
 def depth_to_mesh_batch(depths, masks, K, poses, max_pixel_distance=2, max_depth_distance=0.1, diag=None):

@@ -29,13 +29,16 @@ def _ptr(t):
 
 
 def _check_filter(options) -> int:
+    """The dilation radius: ``num_iterations`` applications of an all-ones k x k rectangle (k odd) are one dilation by a
+    square of radius ``num_iterations * (k // 2)`` -- OpenCV folds the iterations of a rectangular element into its size the
+    same way.  HIVE only ever builds the 3 x 3 rectangle (hive/options.py:248, ``from_args`` passes no filter)."""
     f = np.asarray(options.filter)
-    if f.shape != (3, 3) or not np.all(f != 0):
-        raise NotImplementedError("hive_b200.dilate_mask implements HIVE's default 3x3 rectangular filter only "
-                                  "(hive/options.py:248)")
+    if f.ndim != 2 or f.shape[0] != f.shape[1] or f.shape[0] % 2 != 1 or not np.all(f != 0):
+        raise NotImplementedError("hive_b200.dilate_mask implements all-ones square filters of odd size (HIVE's default is "
+                                  "the 3x3 rectangle, hive/options.py:248); other structuring elements are not supported")
     n = int(options.num_iterations)
     assert n >= 0, "num_iterations must be >= 0"
-    return n
+    return n * (int(f.shape[0]) // 2)
 
 
 def dilate_masks_device(masks, iterations: int):

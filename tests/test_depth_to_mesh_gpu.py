@@ -120,6 +120,25 @@ def test_triangulate_then_filter_composition_matches_oracle():
     assert np.array_equal(d2m.canonical_faces(perm[tri_s]), d2m.canonical_faces(tri))
 
 
+def test_max_pixel_distance_below_sqrt2_leaves_no_faces():
+    """Every triangle of lattice points has an edge >= sqrt2, so a smaller max_pixel_distance filters all faces -- the
+    reference (Delaunay + _filter_faces) agrees; the vertices are unaffected."""
+    from hive_b200 import pipeline
+    scene, fr, R, t = _frame("small", 1)
+    w2c = np.eye(4)
+    w2c[:3, :3], w2c[:3, 3:] = R, t
+    mask = fr.mask > 0
+    opts = pipeline.MeshFilteringOptions(max_pixel_distance=1.2)
+    v, f, p2, md = pipeline.depth_to_mesh(fr.depth, mask, scene.K, w2c[:3, :3], w2c[:3, 3:], opts)
+    ov, of = d2m.frame_mesh(fr.depth, mask, scene.K, w2c[:3, :3], w2c[:3, 3:], max_pixel_distance=1.2)[:2]
+    assert f.shape == (0, 3) and len(of) == 0
+    assert len(v) > 100 and _close(v, ov)
+    v2, f2, _, _ = pipeline.depth_to_mesh(fr.depth, mask, scene.K, w2c[:3, :3], w2c[:3, 3:])
+    assert np.array_equal(v, v2) and len(f2) > 0
+    with pytest.raises(NotImplementedError):
+        pipeline.depth_to_mesh(fr.depth, mask, scene.K, w2c[:3, :3], w2c[:3, 3:], pipeline.MeshFilteringOptions(max_pixel_distance=2.5))
+
+
 def test_batch_equals_single_frames_and_handles_empty_frames():
     from hive_b200 import geometric, pipeline
     scene = Scene("small", "room")

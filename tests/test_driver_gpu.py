@@ -27,6 +27,7 @@ def test_dilate_mask_matches_oracle(shape, n):
 
 def test_dilate_mask_edge_cases():
     from hive_b200.image_processing import MaskDilationOptions, dilate_mask
+    from oracle import driver_oracle as drv
     opts = MaskDilationOptions(num_iterations=3)
     assert not dilate_mask(np.zeros((20, 31), np.uint8), opts).any()
     assert dilate_mask(np.ones((20, 31), np.uint8), opts).all()
@@ -35,8 +36,16 @@ def test_dilate_mask_edge_cases():
     assert dilate_mask(corner, opts).sum() == 2 * 16
     with pytest.raises(AssertionError):
         dilate_mask(np.zeros((2, 3, 4), np.uint8), opts)
-    with pytest.raises(NotImplementedError):
-        dilate_mask(corner, MaskDilationOptions(1, np.ones((5, 5), np.uint8)))
+    # all-ones squares of odd size: n applications of k x k = one dilation by a square of radius n * (k // 2)
+    rng = np.random.default_rng(5)
+    sparse = (rng.random((37, 83)) < 0.01).astype(np.uint8)
+    for k, n in ((5, 1), (5, 2), (7, 1), (1, 3)):
+        got = dilate_mask(sparse, MaskDilationOptions(n, np.ones((k, k), np.uint8)))
+        assert np.array_equal(got, drv.dilate_mask_numpy(sparse, n * (k // 2)))
+    cross = np.array([[0, 1, 0], [1, 1, 1], [0, 1, 0]], np.uint8)  # cv2.MORPH_CROSS: not a rectangle
+    for bad in (cross, np.ones((4, 4), np.uint8), np.ones((3, 5), np.uint8)):
+        with pytest.raises(NotImplementedError):
+            dilate_mask(corner, MaskDilationOptions(1, bad))
 
 
 def test_dilate_masks_batched():
