@@ -61,6 +61,10 @@ SIGNATURES = {
     "hv_peer_open": [c_void_p, c_void_p],
     "hv_peer_close": [c_void_p],
     "hv_copy_async": [c_void_p, c_void_p, c_int64, c_void_p],
+    "hv_peer_signal": [c_void_p, c_int, ctypes.c_uint, c_void_p],
+    "hv_peer_wait": [c_void_p, c_int, ctypes.c_uint, c_void_p, c_void_p],
+    "hv_copy_planes": [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p],
+    "hv_mc_column_shifts_peers": [c_void_p, c_int, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p],
     "hv_d2m_scratch_bytes": [c_int, c_int, c_int, c_void_p],
     "hv_d2m_count": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_int64, c_void_p,
                      c_void_p],

@@ -1245,17 +1245,30 @@ __global__ void __launch_bounds__(256) mc_column_counts_kernel(const __grid_cons
 }
 
 // all[w * slab_stride + k * XY + c]: count k (0 edge vertices, 1 triangles, 2 centre vertices) of slab w in column c
+// (PEERS: slab w's counts are read where they are -- in the memory of the GPU that holds slab w, mapped into this process
+// (hv_peer_open); the loads travel over NVLink and nothing is gathered first.  The slabs' tail words are copied out for the host.)
+constexpr int kMaxSlabPtrs = 16;
+struct SlabCounts {
+    const int32_t* base[kMaxSlabPtrs];
+};
+
+template <bool PEERS>
 __global__ void __launch_bounds__(256) mc_shift_prepare_kernel(const int32_t* __restrict__ all, const long long slab_stride,
-                                                                const int W, const int rank,
+                                                                const SlabCounts peers, const int W, const int rank,
                                                                 const long long XY, uint2* __restrict__ pa, uint2* __restrict__ pb,
-                                                                uint2* __restrict__ pc, int32_t* __restrict__ below) {
+                                                                uint2* __restrict__ pc, int32_t* __restrict__ below,
+                                                                int32_t* __restrict__ tails, const int tail_words) {
     const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (PEERS && blockIdx.x == 0 && (int)threadIdx.x < W * tail_words) {
+        const int w = (int)threadIdx.x / tail_words, j = (int)threadIdx.x - w * tail_words;
+        tails[threadIdx.x] = peers.base[w][3 * XY + j];
+    }
     if (c >= XY) return;
     unsigned int tot[3] = {0u, 0u, 0u}, low[3] = {0u, 0u, 0u}, own[3] = {0u, 0u, 0u};
     for (int w = 0; w < W; ++w)
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            const unsigned int v = (unsigned int)__ldg(all + (long long)w * slab_stride + k * XY + c);
+            const unsigned int v = (unsigned int)(PEERS ? peers.base[w][k * XY + c] : __ldg(all + (long long)w * slab_stride + k * XY + c));
             tot[k] += v;
             if (w < rank) low[k] += v;
             if (w == rank) own[k] = v;
@@ -1693,10 +1706,35 @@ extern "C" int hv_mc_shift_scratch_bytes(int64_t n_columns, int64_t* h_bytes) {
     return HV_OK;
 }
 
+static int mc_column_shifts_impl(const int32_t* all_counts, int64_t slab_stride, const void* const* h_slab_ptrs, int32_t* tails,
+                                 int tail_words, int world_size, int rank, int64_t n_columns, int32_t* shifts,
+                                 unsigned long long* g_totals, void* scratch, int64_t scratch_bytes, void* stream);
+
 extern "C" int hv_mc_column_shifts(const int32_t* all_counts, int64_t slab_stride, int world_size, int rank, int64_t n_columns, int32_t* shifts,
                                    unsigned long long* g_totals, void* scratch, int64_t scratch_bytes, void* stream) {
-    HV_REQUIRE(all_counts && shifts && g_totals && scratch && world_size >= 1 && rank >= 0 && rank < world_size &&
-                   n_columns > 0 && n_columns < (1ll << 31) && slab_stride >= 3 * n_columns && ((uintptr_t)scratch & 255) == 0,
+    HV_REQUIRE(all_counts && slab_stride >= 3 * n_columns, "hv_mc_column_shifts: bad arguments");
+    return mc_column_shifts_impl(all_counts, slab_stride, nullptr, nullptr, 0, world_size, rank, n_columns, shifts, g_totals, scratch,
+                                 scratch_bytes, stream);
+}
+
+// hv_mc_column_shifts reading every slab's counts where they are: h_slab_ptrs (HOST array of world_size DEVICE addresses, at
+// most 16) -- slab w's [3][X*Y] counts followed by tail_words words of per-slab data -- typically the memory of the GPU holding
+// slab w, mapped with hv_peer_open.  `tails` (DEVICE, [world_size][tail_words]) receives the tail words of all slabs.
+extern "C" int hv_mc_column_shifts_peers(const void* const* h_slab_ptrs, int world_size, int rank, int64_t n_columns, int tail_words,
+                                         int32_t* shifts, unsigned long long* g_totals, int32_t* tails, void* scratch,
+                                         int64_t scratch_bytes, void* stream) {
+    HV_REQUIRE(h_slab_ptrs && tails && world_size >= 1 && world_size <= hv::kMaxSlabPtrs && tail_words >= 0 &&
+                   world_size * tail_words <= 256, "hv_mc_column_shifts_peers: bad arguments (at most 16 slabs)");
+    for (int w = 0; w < world_size; ++w) HV_REQUIRE(h_slab_ptrs[w], "hv_mc_column_shifts_peers: null slab pointer");
+    return mc_column_shifts_impl(nullptr, 0, h_slab_ptrs, tails, tail_words, world_size, rank, n_columns, shifts, g_totals, scratch,
+                                 scratch_bytes, stream);
+}
+
+static int mc_column_shifts_impl(const int32_t* all_counts, int64_t slab_stride, const void* const* h_slab_ptrs, int32_t* tails,
+                                 int tail_words, int world_size, int rank, int64_t n_columns, int32_t* shifts,
+                                 unsigned long long* g_totals, void* scratch, int64_t scratch_bytes, void* stream) {
+    HV_REQUIRE(shifts && g_totals && scratch && world_size >= 1 && rank >= 0 && rank < world_size &&
+                   n_columns > 0 && n_columns < (1ll << 31) && ((uintptr_t)scratch & 255) == 0,
                "hv_mc_column_shifts: bad arguments");
     ShiftLayout L;
     shift_layout(n_columns, &L);
@@ -1708,7 +1746,14 @@ extern "C" int hv_mc_column_shifts(const int32_t* all_counts, int64_t slab_strid
     uint2* bsum = reinterpret_cast<uint2*>(s + L.off_bsum);
     cudaStream_t st = hv::as_stream(stream);
     const unsigned int blocks = (unsigned int)((n_columns + 255) / 256);
-    hv::mc_shift_prepare_kernel<<<blocks, 256, 0, st>>>(all_counts, slab_stride, world_size, rank, n_columns, p[0], p[1], p[2], shifts);
+    hv::SlabCounts sc;
+    for (int w = 0; w < hv::kMaxSlabPtrs; ++w) sc.base[w] = (h_slab_ptrs && w < world_size) ? static_cast<const int32_t*>(h_slab_ptrs[w]) : nullptr;
+    if (h_slab_ptrs)
+        hv::mc_shift_prepare_kernel<true><<<blocks, 256, 0, st>>>(nullptr, 0, sc, world_size, rank, n_columns, p[0], p[1], p[2], shifts,
+                                                                   tails, tail_words);
+    else
+        hv::mc_shift_prepare_kernel<false><<<blocks, 256, 0, st>>>(all_counts, slab_stride, sc, world_size, rank, n_columns, p[0], p[1],
+                                                                    p[2], shifts, nullptr, 0);
     // g_totals: [0] edge vertices, [1] triangles, [2] centre vertices of the whole volume ([3] scratch)
     hv::exclusive_scan_u2(p[0], p[3], bsum, n_columns, g_totals, st);
     hv::exclusive_scan_u2(p[1], p[4], bsum, n_columns, g_totals + 2, st);

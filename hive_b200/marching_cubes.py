@@ -186,13 +186,14 @@ class McPlan:
     #: words appended to a slab's column counts in the all-gather: min key, max key, vertices, triangles, edge vertices
     SLAB_TAIL = 5
 
-    def column_counts(self):
+    def column_counts(self, out=None):
         """int32 (3 * X*Y + SLAB_TAIL,) device tensor: edge vertices / triangles / centre vertices this slab owns per
-        column, then the slab's totals (everything the other slabs and rank 0 need to know about it -- one all-gather)."""
+        column, then the slab's totals (everything the other slabs and rank 0 need to know about it -- one all-gather, or
+        read in place by the other slabs when ``out`` lies in memory they have mapped)."""
         torch = self._torch
         X, Y = int(self.dims[0]), int(self.dims[1])
         with torch.cuda.device(self.device):
-            counts = torch.empty((3 * X * Y + self.SLAB_TAIL,), dtype=torch.int32, device=self.device)
+            counts = out if out is not None else torch.empty((3 * X * Y + self.SLAB_TAIL,), dtype=torch.int32, device=self.device)
             counts[3 * X * Y:] = self.totals.view(torch.int32)[self._tail_words(torch)]  # low words of totals[2, 3, 0, 1, 4]
             stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
             _lib.check(self._lib.hv_mc_column_counts(
@@ -226,6 +227,27 @@ class McPlan:
                                                      _ptr(g_totals), sptr, int(nbytes.value), stream))
             scratch.record_stream(torch.cuda.current_stream())
         return shifts, g_totals
+
+    def column_shifts_peers(self, slab_addresses, rank, tails):
+        """``column_shifts`` reading every slab's ``column_counts(out=...)`` where it is: ``slab_addresses[w]`` is this
+        process's address of slab w's counts (mapped peer memory).  ``tails`` (int32 device tensor (world, SLAB_TAIL))
+        receives the slabs' tail words.  Returns the shifts; no sync."""
+        torch = self._torch
+        world = len(slab_addresses)
+        n_cols = int(self.dims[0]) * int(self.dims[1])
+        nbytes = ctypes.c_int64(0)
+        _lib.check(self._lib.hv_mc_shift_scratch_bytes(n_cols, ctypes.byref(nbytes)))
+        with torch.cuda.device(self.device):
+            scratch = torch.empty(int(nbytes.value) + 256, dtype=torch.uint8, device=self.device)
+            sptr = ctypes.c_void_p(scratch.data_ptr() + (-scratch.data_ptr()) % 256)
+            shifts = torch.empty((4, n_cols), dtype=torch.int32, device=self.device)
+            g_totals = torch.zeros(4, dtype=torch.int64, device=self.device)
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            ptrs = (ctypes.c_void_p * world)(*[ctypes.c_void_p(int(a)) for a in slab_addresses])
+            _lib.check(self._lib.hv_mc_column_shifts_peers(ptrs, world, int(rank), n_cols, self.SLAB_TAIL, _ptr(shifts),
+                                                           _ptr(g_totals), _ptr(tails), sptr, int(nbytes.value), stream))
+            scratch.record_stream(torch.cuda.current_stream())
+        return shifts
 
     def emit_placed(self, n_verts, n_tris, voxel_size, origin, shifts, n_edge_global):
         """The slab's mesh with faces as indices into the mesh of the WHOLE volume; returns a dict of device tensors:

@@ -266,6 +266,9 @@ class SlabShardedTSDFVolume:
                 trace.append((step, time.perf_counter()))
 
         mark("start")
+        X, Y, Z = (int(d) for d in loc._local_dim)
+        if self._peer_mailboxes(X * Y) is not None:
+            return self._get_mesh_peer(mark, trace)
         first_t, last_t, first_c, last_c = self._boundary_planes()
         mark("boundary planes")
         # the halo planes and the extraction plan (scratch, work records) live as long as the volume: a repeated get_mesh
@@ -347,6 +350,121 @@ class SlabShardedTSDFVolume:
         torch.cuda.current_stream().synchronize()
         return host.numpy().copy()
 
+    # -- the slabs talk through each other's memory: seam planes, per-column counts, flags (hive_b200/peer.py) ------------------
+    _FLAG_WORDS = 64  # per mailbox: [0] lo halo arrived, [1] hi halo arrived, [8 + w] counts of slab w ready, [24 + w] rows of slab w stored
+
+    def _peer_mailboxes(self, n_cols):
+        """Every rank's mailbox mapped into every rank, or None when that is not possible (decided collectively, once)."""
+        dist, torch = self._dist, self._torch
+        if getattr(self, "_mb_off", None) is None:
+            self._mb_off = (os.environ.get("HV_MESH_P2P", "1") == "0" or os.environ.get("HV_MESH_FLAGS", "1") == "0"
+                            or self.local.device.type != "cuda" or dist.get_backend() != "nccl" or self.world_size > 16)
+        if self._mb_off or getattr(self, "_p2p_off", False):
+            return None
+        if getattr(self, "_mb", None) is not None:
+            return self._mb
+        from . import marching_cubes as mc
+        tail = 8  # >= McPlan.SLAB_TAIL, keeps the next array 32-byte aligned
+        assert mc.McPlan.SLAB_TAIL <= tail
+        a = lambda v: (v + 255) & ~255  # noqa: E731
+        self._mb_halo = 0                                     # [parity 2][side 2][tsdf, colour][n_cols] float32
+        self._mb_counts = a(self._mb_halo + 8 * n_cols * 4)   # [parity 2][3 * n_cols + tail] int32
+        self._mb_count_words = 3 * n_cols + tail
+        self._mb_flags = a(self._mb_counts + 2 * self._mb_count_words * 4)
+        mb = peer.Mailboxes(dist, self.rank, self.world_size, self.local.device, self._mb_flags + 4 * self._FLAG_WORDS)
+        if not mb.ok:
+            self._mb_off = True
+            return None
+        dev, own = self.local.device, mb.base[self.rank]
+        self._mb_err = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._mb_tails = torch.zeros((self.world_size, mc.McPlan.SLAB_TAIL), dtype=torch.int32, device=dev)
+        self._mb_views = []
+        for par in range(2):
+            halo = {}
+            for side, name in ((0, "lo"), (1, "hi")):
+                if (side == 0 and self.rank == 0) or (side == 1 and self.rank == self.world_size - 1):
+                    continue
+                o = own + self._mb_halo + ((par * 2 + side) * 2) * n_cols * 4
+                shape = tuple(int(d) for d in self.local._local_dim[:2])
+                halo[f"tsdf_{name}"] = peer.view(o, shape, torch.float32, dev)
+                halo[f"color_{name}"] = peer.view(o + n_cols * 4, shape, torch.float32, dev)
+            counts = peer.view(own + self._mb_counts + par * self._mb_count_words * 4, (3 * n_cols + mc.McPlan.SLAB_TAIL,),
+                               torch.int32, dev)
+            self._mb_views.append((halo, counts))
+        self._mb, self._epoch = mb, 0
+        return mb
+
+    def _get_mesh_peer(self, mark, trace):
+        """``get_mesh`` without a collective: seam planes are stored into the neighbours' mailboxes, every slab reads the
+        others' per-column counts in place, the rows go straight into rank 0's HBM; flags (32-bit epochs stored into the
+        receiver's memory behind the data, ``hv_peer_signal`` / ``hv_peer_wait``) order it all.  Two parities of every inbox:
+        a slab can be at most one call ahead of its neighbours."""
+        from . import marching_cubes as mc
+        dist, loc, torch, mb = self._dist, self.local, self._torch, self._mb
+        lib, rank, world = _lib_handle(), self.rank, self.world_size
+        X, Y, Z = (int(d) for d in loc._local_dim)
+        n_cols, z0, Zg = X * Y, self.ranges[self.rank][0], self.global_dim[2]
+        self._epoch += 1
+        e, par = self._epoch, self._epoch & 1
+        halo, counts = self._mb_views[par]
+        stream = torch.cuda.current_stream().cuda_stream
+        flag = lambda w, i: mb.base[w] + self._mb_flags + 4 * i  # noqa: E731
+        with torch.cuda.device(loc.device):
+            # my first plane is the hi halo of the slab below, my last plane the lo halo of the slab above
+            to_signal = []
+            for nb, side, z in ((rank - 1, 1, 0), (rank + 1, 0, Z - 1)):
+                if 0 <= nb < world:
+                    dst = mb.base[nb] + self._mb_halo + ((par * 2 + side) * 2) * n_cols * 4
+                    _check(lib.hv_copy_planes(_p(loc._tsdf_vol_gpu), _p(loc._color_vol_gpu), int(loc._pitch), z, n_cols,
+                                              _c(dst), _c(dst + n_cols * 4), _c(stream)))
+                    to_signal.append(flag(nb, side))
+            mb.signal(to_signal, e, stream)
+            first = 0 if rank > 0 else 1
+            mb.wait(self._mb_flags + 4 * first, (1 if rank > 0 else 0) + (1 if rank < world - 1 else 0), e, self._mb_err, stream)
+            mark("seam planes stored + arrived")
+            plan = getattr(self, "_mc_plan_peer", None)
+            if plan is None or plan.tsdf is not loc._tsdf_vol_gpu:
+                plan = self._mc_plan_peer = mc.McPlan(loc._tsdf_vol_gpu, loc._color_vol_gpu, (X, Y, Z), loc._pitch, halo=halo,
+                                                      z_global_offset=z0, z_global_dim=Zg)
+            plan.halo = halo
+            plan.count(*getattr(self, "_mc_caps", (None, None)))
+            n_verts, n_tris, _, _ = plan.read_totals()
+            plan.ensure_records(n_verts, n_tris)
+            self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)
+            mark("count + totals")
+            plan.column_counts(out=counts)
+            mb.signal([flag(w, 8 + rank) for w in range(world)], e, stream)
+            mb.wait(self._mb_flags + 4 * 8, world, e, self._mb_err, stream)
+            mark("column counts ready everywhere")
+            shifts = plan.column_shifts_peers([mb.base[w] + self._mb_counts + par * self._mb_count_words * 4 for w in range(world)],
+                                              rank, self._mb_tails)
+            tails = self._read_tails(torch.cat((self._mb_tails.view(-1), self._mb_err)))
+            if int(tails[-1]):
+                raise RuntimeError(f"sharded get_mesh: rank {rank} waited ~2 s for flag {int(tails[-1]) - 1} of its mailbox")
+            tails = tails[:-1].reshape(world, plan.SLAB_TAIL)
+            mark("shifts + tails read")
+            vmin = min(mc._key_to_float(int(k)) for k in tails[:, 0])
+            vmax = max(mc._key_to_float(int(k)) for k in tails[:, 1])
+            n_verts_g, n_tris_g, n_edge_g = (int(v) for v in tails[:, 2:5].sum(axis=0))
+            mc.check_surface(0.0, vmin, vmax, n_verts_g)
+            buf = self._shared_mesh_buffer(n_verts_g, n_tris_g)
+            assert buf is not None, "the mesh buffer could not be shared although the mailboxes could"
+            offs, _ = peer.mesh_layout(n_verts_g, n_tris_g)
+            plan.emit_direct(n_verts, n_tris, loc._voxel_size, loc._vol_origin, shifts, n_edge_g, n_verts_g, n_tris_g,
+                             {name: buf.base + o for name, o in offs.items()})
+            mb.signal([flag(0, 24 + rank)], e, stream)
+            mark("emit into rank 0")
+            self.last_mesh_trace, self.last_mesh_path = trace, "peer"
+            if rank != 0:
+                return None, None, None, None
+            mb.wait(self._mb_flags + 4 * 24, world, e, self._mb_err, stream)
+            mark("arrival")
+            out = self._download_shared_mesh(buf, offs, n_verts_g, n_tris_g)
+            if int(self._mb_err.item()):
+                raise RuntimeError("sharded get_mesh: rank 0 waited ~2 s for the rows of a slab")
+            mark("download")
+            return out
+
     # -- the whole mesh in rank 0's HBM, written by every slab (hive_b200/peer.py)
     def _shared_mesh_buffer(self, n_verts_g, n_tris_g):
         """The buffer all slabs emit into, or None when the ranks cannot share memory (CPU process groups, HV_MESH_P2P=0,
@@ -392,6 +510,31 @@ class SlabShardedTSDFVolume:
         if buf is not None:
             buf.close()
             self._mesh_buf = None
+        mb = getattr(self, "_mb", None)
+        if mb is not None:
+            self._mb_views, self._mc_plan_peer = None, None  # (views into the mailbox)
+            mb.close()
+            self._mb = None
+
+
+def _lib_handle():
+    from . import _lib
+    return _lib.load()
+
+
+def _check(code):
+    from . import _lib
+    return _lib.check(code)
+
+
+def _p(t):
+    import ctypes
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _c(address):
+    import ctypes
+    return ctypes.c_void_p(int(address))
 
 
 def exchange_halo_planes(dist, rank, world_size, planes, out=None):

@@ -194,6 +194,26 @@ int hv_peer_open(const void* h_handle, void** h_ptr);
 int hv_peer_close(void* ptr);
 int hv_copy_async(void* dst, const void* src, int64_t bytes, void* stream);
 
+/* Signals and seam planes between the GPUs of a node (hive_b200/sharded.py, no counterpart in the reference): a flag is a 32-bit
+ * epoch in the receiver's (mapped) memory.
+ *   hv_peer_signal  stores `epoch` into n <= 16 flags (HOST array of DEVICE addresses, typically in peers' memory).  Stream
+ *                   order is the fence: everything earlier kernels of the stream wrote -- into peer memory too -- is visible
+ *                   to whoever sees the flag.
+ *   hv_peer_wait    a one-warp kernel that returns when each of the n <= 32 consecutive flags at `flags` (this GPU's memory)
+ *                   has reached `epoch`; after ~2 s it gives up and leaves 1 + the flag's index in *err (DEVICE uint32).
+ *   hv_copy_planes  dst_a[c] = a[c * pitch + z], dst_b[c] = b[c * pitch + z] for n_cols columns: one z-plane of the tsdf and
+ *                   colour volumes, e.g. into a neighbour's halo inbox.
+ *   hv_mc_column_shifts_peers  hv_mc_column_shifts reading every slab's counts where they are (h_slab_ptrs: HOST array of
+ *                   world_size <= 16 DEVICE addresses, slab w's [3][X*Y] counts + tail_words words) -- no all-gather;
+ *                   tails (DEVICE [world_size][tail_words]) receives every slab's tail words. */
+int hv_peer_signal(void* const* h_flags, int n, unsigned int epoch, void* stream);
+int hv_peer_wait(const void* flags, int n, unsigned int epoch, void* err, void* stream);
+int hv_copy_planes(const float* a, const float* b, int64_t pitch, int64_t z, int64_t n_cols, float* dst_a, float* dst_b,
+                   void* stream);
+int hv_mc_column_shifts_peers(const void* const* h_slab_ptrs, int world_size, int rank, int64_t n_columns, int tail_words,
+                              int32_t* shifts, unsigned long long* g_totals, int32_t* tails, void* scratch,
+                              int64_t scratch_bytes, void* stream);
+
 /* hv_mc_count + hv_mc_emit in one call with caller-provided capacity (cap_verts vertices, cap_tris triangles in every
  * output buffer).  The single host round trip -- the counters -- lands in `h_totals` (HOST, 8 x uint64, pinned memory
  * recommended; same meaning as `totals`).  Returns HV_E_LEVEL_RANGE / HV_E_NOSURFACE like skimage would raise

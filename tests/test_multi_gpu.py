@@ -38,18 +38,20 @@ def _worker(rank, world, port, out_path):
         vol.integrate_batch_device(sf, [0, 1, 2])                     # device-resident frames -> broadcast -> integrate
         tsdf, color = vol.get_volume()
         weight = vol.get_weight_volume()
-        verts, faces, norms, colors = vol.get_mesh()   # every slab stores its rows into rank 0's HBM (CUDA IPC, NVLink)
-        path = vol.last_mesh_path
-        again = vol.get_mesh()                          # the shared buffer is reused
-        vol._p2p_off = True                             # the same through the grouped send / receive + scatter
-        gathered = vol.get_mesh()
-        path2 = vol.last_mesh_path
+        verts, faces, norms, colors = vol.get_mesh()   # no collective: seam planes, counts and rows through peer memory + flags
+        paths = [vol.last_mesh_path]
+        again = [vol.get_mesh(), vol.get_mesh()]        # both parities of the mailboxes, the shared buffers reused
+        vol._mb_off = True                              # NCCL for planes / counts / arrival, rows still stored peer to peer
+        again.append(vol.get_mesh())
+        paths.append(vol.last_mesh_path)
+        vol._p2p_off = True                             # and through the grouped send / receive + scatter
+        again.append(vol.get_mesh())
+        paths.append(vol.last_mesh_path)
         vol.close()
         if rank == 0:
             np.savez(out_path, tsdf=tsdf, color=color, weight=weight, verts=verts, faces=faces, norms=norms, colors=colors,
-                     paths=np.array([path, path2]),
-                     same=np.array([all(np.array_equal(a, b) for a, b in zip((verts, faces, norms, colors), m))
-                                    for m in (again, gathered)]))
+                     paths=np.array(paths),
+                     same=np.array([all(np.array_equal(a, b) for a, b in zip((verts, faces, norms, colors), m)) for m in again]))
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -76,5 +78,5 @@ def test_sharded_volume_equals_single_gpu(world, tmp_path):
     verts, faces, norms, colors = ref.get_mesh()
     assert np.array_equal(got["verts"], verts) and np.array_equal(got["faces"], faces)
     assert np.array_equal(got["norms"], norms) and np.array_equal(got["colors"], colors)
-    assert list(got["paths"]) == ["p2p", "gather"], "the peer-to-peer mesh assembly did not run"
+    assert list(got["paths"]) == ["peer", "p2p", "gather"], "the peer-to-peer mesh assembly did not run"
     assert got["same"].all(), "the repeated / gathered mesh differs from the first"

@@ -37,8 +37,10 @@ def main():
     # and untraced (no per-step syncs): wall clock of the whole call on rank 0, both assembly paths
     import time
     os.environ.pop("HV_MESH_TRACE")
-    for label, off in (("p2p", False), ("gather", True)):
-        if off:
+    for label in ("peer", "p2p", "gather"):
+        if label == "p2p":
+            vol._mb_off = True
+        if label == "gather":
             vol._p2p_off = True
         ts = []
         for rep in range(7):
