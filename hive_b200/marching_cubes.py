@@ -183,8 +183,9 @@ class McPlan:
             self.count(n_verts, n_tris)
             self._records_incomplete = False
 
-    #: words appended to a slab's column counts in the all-gather: min key, max key, vertices, triangles, edge vertices
-    SLAB_TAIL = 5
+    #: words appended to a slab's column counts: min key, max key, vertices, triangles, edge vertices, 1 if the work records
+    #: of the count did not fit (the counts are then not valid: count again with the sizes given here)
+    SLAB_TAIL = 6
 
     def column_counts(self, out=None):
         """int32 (3 * X*Y + SLAB_TAIL,) device tensor: edge vertices / triangles / centre vertices this slab owns per
@@ -194,7 +195,7 @@ class McPlan:
         X, Y = int(self.dims[0]), int(self.dims[1])
         with torch.cuda.device(self.device):
             counts = out if out is not None else torch.empty((3 * X * Y + self.SLAB_TAIL,), dtype=torch.int32, device=self.device)
-            counts[3 * X * Y:] = self.totals.view(torch.int32)[self._tail_words(torch)]  # low words of totals[2, 3, 0, 1, 4]
+            counts[3 * X * Y:] = self.totals.view(torch.int32)[self._tail_words(torch)]  # low words of totals[2, 3, 0, 1, 4, 6]
             stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
             _lib.check(self._lib.hv_mc_column_counts(
                 _ptr(self.tsdf), _ptr(self.halo.get("tsdf_lo")), _ptr(self.halo.get("tsdf_hi")),
@@ -205,7 +206,7 @@ class McPlan:
     def _tail_words(self, torch):
         idx = getattr(self, "_tail_idx", None)
         if idx is None:
-            idx = self._tail_idx = torch.tensor([4, 6, 0, 2, 8], dtype=torch.int64, device=self.device)
+            idx = self._tail_idx = torch.tensor([4, 6, 0, 2, 8, 12], dtype=torch.int64, device=self.device)
         return idx
 
     def column_shifts(self, all_counts, rank):

@@ -394,7 +394,7 @@ class SlabShardedTSDFVolume:
         self._mb, self._epoch = mb, 0
         return mb
 
-    def _get_mesh_peer(self, mark, trace):
+    def _get_mesh_peer(self, mark, trace, redo=False):
         """``get_mesh`` without a collective: seam planes are stored into the neighbours' mailboxes, every slab reads the
         others' per-column counts in place, the rows go straight into rank 0's HBM; flags (32-bit epochs stored into the
         receiver's memory behind the data, ``hv_peer_signal`` / ``hv_peer_wait``) order it all.  Two parities of every inbox:
@@ -427,21 +427,25 @@ class SlabShardedTSDFVolume:
                 plan = self._mc_plan_peer = mc.McPlan(loc._tsdf_vol_gpu, loc._color_vol_gpu, (X, Y, Z), loc._pitch, halo=halo,
                                                       z_global_offset=z0, z_global_dim=Zg)
             plan.halo = halo
+            # the count is not waited for: its totals travel with the column counts, and the one host read below tells every
+            # slab the sizes of all slabs -- and whether some slab's work records did not fit (then all go round again)
             plan.count(*getattr(self, "_mc_caps", (None, None)))
-            n_verts, n_tris, _, _ = plan.read_totals()
-            plan.ensure_records(n_verts, n_tris)
-            self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)
-            mark("count + totals")
+            plan._records_incomplete = False
             plan.column_counts(out=counts)
             mb.signal([flag(w, 8 + rank) for w in range(world)], e, stream)
             mb.wait(self._mb_flags + 4 * 8, world, e, self._mb_err, stream)
-            mark("column counts ready everywhere")
+            mark("count + column counts ready everywhere")
             shifts = plan.column_shifts_peers([mb.base[w] + self._mb_counts + par * self._mb_count_words * 4 for w in range(world)],
                                               rank, self._mb_tails)
             tails = self._read_tails(torch.cat((self._mb_tails.view(-1), self._mb_err)))
             if int(tails[-1]):
                 raise RuntimeError(f"sharded get_mesh: rank {rank} waited ~2 s for flag {int(tails[-1]) - 1} of its mailbox")
             tails = tails[:-1].reshape(world, plan.SLAB_TAIL)
+            n_verts, n_tris = (int(v) for v in tails[rank, 2:4])
+            self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)  # next time: records sized by this surface
+            if tails[:, 5].any():
+                assert not redo, "the work records did not fit twice in a row"
+                return self._get_mesh_peer(mark, trace, redo=True)
             mark("shifts + tails read")
             vmin = min(mc._key_to_float(int(k)) for k in tails[:, 0])
             vmax = max(mc._key_to_float(int(k)) for k in tails[:, 1])

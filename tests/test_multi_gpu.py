@@ -41,6 +41,8 @@ def _worker(rank, world, port, out_path):
         verts, faces, norms, colors = vol.get_mesh()   # no collective: seam planes, counts and rows through peer memory + flags
         paths = [vol.last_mesh_path]
         again = [vol.get_mesh(), vol.get_mesh()]        # both parities of the mailboxes, the shared buffers reused
+        vol._mc_caps = (64, 64)                         # work records far too small: every slab sees it in the tails and all go round again
+        again.append(vol.get_mesh())
         vol._mb_off = True                              # NCCL for planes / counts / arrival, rows still stored peer to peer
         again.append(vol.get_mesh())
         paths.append(vol.last_mesh_path)
