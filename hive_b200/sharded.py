@@ -400,7 +400,7 @@ class SlabShardedTSDFVolume:
         receiver's memory behind the data, ``hv_peer_signal`` / ``hv_peer_wait``) order it all.  Two parities of every inbox:
         a slab can be at most one call ahead of its neighbours."""
         from . import marching_cubes as mc
-        dist, loc, torch, mb = self._dist, self.local, self._torch, self._mb
+        loc, torch, mb = self.local, self._torch, self._mb
         lib, rank, world = _lib_handle(), self.rank, self.world_size
         X, Y, Z = (int(d) for d in loc._local_dim)
         n_cols, z0, Zg = X * Y, self.ranges[self.rank][0], self.global_dim[2]
