@@ -782,6 +782,7 @@ def run_ours(args):
         "config": config_dict(args, sc, dim, n_gpus, n_distinct),
         "frames_per_s": main["frames_per_s"],
         "updated_fraction": main["updated_fraction"],
+        "per_rank": main.get("per_rank"),
         "e2e": main["e2e"],
         "gpu_launches": main["gpu_launches"],
         "clocks": main["clocks"],
@@ -857,9 +858,18 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
     torch.cuda.synchronize()
     _barrier(world, dist, torch)
     clocks = sampler.stop() if sampler is not None else None
-    ms = _max_over_ranks(e0.elapsed_time(e1), world, dist, torch)
+    ms_local = e0.elapsed_time(e1)
+    ms = _max_over_ranks(ms_local, world, dist, torch)
     local_updates = vol.num_updated_local()
     total_updates = _sum_over_ranks(local_updates, world, dist, torch)
+    per_rank = None
+    if world > 1:  # which slab sets the pace, and how much work each one had (the slabs of one scene are not alike)
+        mine = torch.tensor([ms_local, float(local_updates)], dtype=torch.float64, device="cuda")
+        every = torch.empty((world, 2), dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(every.view(-1), mine)
+        every = every.cpu().numpy()
+        per_rank = {"ms_per_step": [float(v) / K for v in every[:, 0]],
+                    "updated_fraction": [float(v) / (n_vox_global / world * K * B) for v in every[:, 1]]}
     n_frames = K * B
     value = n_vox_global * n_frames / (ms / 1000.0)
 
@@ -906,7 +916,7 @@ def _measure(args, sc, frames, variant, world, rank, local_rank, torch, dist, Vo
         "value": value, "ms_per_step": ms / K, "frames_per_s": n_frames / (ms / 1000.0),
         "updated_fraction": total_updates / float(n_vox_global * n_frames),
         "achieved_gbs": achieved_gbs, "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_launch_ms,
-        "gpu_launches": launches, "clocks": clocks, "H": H, "W": W, "mesh": mesh, "parity": parity,
+        "gpu_launches": launches, "clocks": clocks, "H": H, "W": W, "mesh": mesh, "parity": parity, "per_rank": per_rank,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * (H * W * 7 + 12 * 8 + 16),
                 "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e / K,
                 "api": "TSDFVolume.integrate(color_im, depth_im, cam_intr, cam_pose) with host numpy buffers"},
