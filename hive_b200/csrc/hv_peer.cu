@@ -56,7 +56,8 @@ extern "C" int hv_copy_async(void* dst, const void* src, int64_t bytes, void* st
 // Kernels of one stream run in order and a kernel's stores -- those into a peer's memory included -- are performed before the
 // next kernel starts, so "data, then flag" needs no fence inside a kernel: the data is written by the kernels before
 // hv_peer_signal, the flag by the one-warp kernel of hv_peer_signal itself.  The receiver's hv_peer_wait spins (system-scope
-// acquire loads) on flags in its OWN memory until every one has reached the epoch; it gives up after ~2 s (and reports which
+// acquire loads) on flags in its OWN memory until every one has reached the epoch -- a peer may still be busy with work queued
+// before its signal, so the wait is long -- and gives up after ~30 s (and reports which
 // flag through `err`) instead of hanging the GPU.
 namespace hv {
 
@@ -111,7 +112,7 @@ extern "C" int hv_peer_signal(void* const* h_flags, int n, unsigned int epoch, v
 extern "C" int hv_peer_wait(const void* flags, int n, unsigned int epoch, void* err, void* stream) {
     HV_REQUIRE(flags && err && n >= 1 && n <= 32, "hv_peer_wait: 1..32 flags");
     hv::peer_wait_kernel<<<1, 32, 0, hv::as_stream(stream)>>>(static_cast<const unsigned int*>(flags), n, epoch,
-                                                             4000000000ll /* ~2 s at 1.9 GHz */, static_cast<unsigned int*>(err));
+                                                             60000000000ll /* ~30 s at 1.9 GHz */, static_cast<unsigned int*>(err));
     HV_CUDA(cudaGetLastError());
     return HV_OK;
 }

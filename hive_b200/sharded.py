@@ -439,7 +439,7 @@ class SlabShardedTSDFVolume:
                                               rank, self._mb_tails)
             tails = self._read_tails(torch.cat((self._mb_tails.view(-1), self._mb_err)))
             if int(tails[-1]):
-                raise RuntimeError(f"sharded get_mesh: rank {rank} waited ~2 s for flag {int(tails[-1]) - 1} of its mailbox")
+                raise RuntimeError(f"sharded get_mesh: rank {rank} waited ~30 s for flag {int(tails[-1]) - 1} of its mailbox")
             tails = tails[:-1].reshape(world, plan.SLAB_TAIL)
             n_verts, n_tris = (int(v) for v in tails[rank, 2:4])
             self._mc_caps = (n_verts + n_verts // 2 + 1024, n_tris + n_tris // 2 + 1024)  # next time: records sized by this surface
@@ -465,7 +465,7 @@ class SlabShardedTSDFVolume:
             mark("arrival")
             out = self._download_shared_mesh(buf, offs, n_verts_g, n_tris_g)
             if int(self._mb_err.item()):
-                raise RuntimeError("sharded get_mesh: rank 0 waited ~2 s for the rows of a slab")
+                raise RuntimeError("sharded get_mesh: rank 0 waited ~30 s for the rows of a slab")
             mark("download")
             return out
 

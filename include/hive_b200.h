@@ -200,7 +200,7 @@ int hv_copy_async(void* dst, const void* src, int64_t bytes, void* stream);
  *                   order is the fence: everything earlier kernels of the stream wrote -- into peer memory too -- is visible
  *                   to whoever sees the flag.
  *   hv_peer_wait    a one-warp kernel that returns when each of the n <= 32 consecutive flags at `flags` (this GPU's memory)
- *                   has reached `epoch`; after ~2 s it gives up and leaves 1 + the flag's index in *err (DEVICE uint32).
+ *                   has reached `epoch`; after ~30 s it gives up and leaves 1 + the flag's index in *err (DEVICE uint32).
  *   hv_copy_planes  dst_a[c] = a[c * pitch + z], dst_b[c] = b[c * pitch + z] for n_cols columns: one z-plane of the tsdf and
  *                   colour volumes, e.g. into a neighbour's halo inbox.
  *   hv_mc_column_shifts_peers  hv_mc_column_shifts reading every slab's counts where they are (h_slab_ptrs: HOST array of
