@@ -248,13 +248,14 @@ class HostDepthMeshes:
 
 
 def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_distance=0.1, chunk_frames=20,
-                       copy_threads=8, vertex_dtype=np.float64, want_points=True):
+                       copy_threads=8, vertex_dtype=np.float64, want_points=True, max_pinned_bytes=1 << 30):
     """``depth_to_mesh_batch`` for host arrays in and host arrays out, as a pipeline over chunks of frames: while chunk c
     is triangulated, chunk c + 1 is on its way up (pinned staging filled by ``copy_threads`` host threads, then H2D on its
     own stream) and chunk c - 1 on its way down (D2H on a third stream) -- PCIe carries 1.5 MB per frame up and ~2.8 MB
     down (float64 vertices), the kernels are 1 % of that.  Same per-frame results as ``depth_to_mesh_batch(...).frame(i)``.
     The bus is the limit, so the two options are about bytes: ``vertex_dtype=np.float32`` (12 instead of 24 bytes per vertex)
     and ``want_points=False`` (no (u, v, depth) per vertex: 12 bytes less; ``frame(i)`` then returns None for them).
+    At most ``max_pinned_bytes`` of input are staged in page-locked memory at a time (longer clips run part after part).
     """
     from concurrent.futures import ThreadPoolExecutor
     torch = _lib.require_cuda()
@@ -263,6 +264,15 @@ def depth_to_mesh_host(depths, masks, K, poses, max_pixel_distance=2, max_depth_
     masks = None if masks is None else np.asarray(masks)
     poses = np.asarray(poses, dtype=np.float64)
     B, H, W = depths.shape
+    part = max(1, int(chunk_frames), int(max_pinned_bytes) // (5 * H * W))
+    if B > part:  # a long clip: part after part, each staged on its own
+        chunks = []
+        for a in range(0, B, part):
+            sub = depth_to_mesh_host(depths[a:a + part], None if masks is None else masks[a:a + part], K, poses[a:a + part],
+                                     max_pixel_distance, max_depth_distance, chunk_frames, copy_threads, vertex_dtype,
+                                     want_points, max_pinned_bytes)
+            chunks.extend((c[0] + a,) + tuple(c[1:]) for c in sub._chunks)
+        return HostDepthMeshes(chunks, B)
     flags, kinv = d2m_flags(max_pixel_distance), _kinv64(K)
     cams_host = np.concatenate([poses[:, :3, :3].reshape(B, 9), poses[:, :3, 3].reshape(B, 3)], axis=1)
     n = max(1, min(int(chunk_frames), B))

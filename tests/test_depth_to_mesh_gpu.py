@@ -205,6 +205,13 @@ def test_pipelined_host_call_equals_the_batch(chunk_frames, with_masks):
             assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b)
     if with_masks:
         assert got.frame(4)[0].shape == (0, 3)
+    # a clip longer than the pinned staging budget runs part after part
+    parts = geometric.depth_to_mesh_host(depths, masks if with_masks else None, scene.K, poses, chunk_frames=chunk_frames,
+                                         max_pinned_bytes=1)
+    assert len(parts) == 7 and parts.n_vertices == got.n_vertices
+    for i in range(7):
+        for a, b in zip(parts.frame(i), got.frame(i)):
+            assert np.array_equal(a, b)
     # the byte-saving options: float32 vertices are the float64 ones rounded to nearest; no (u, v, depth) per vertex
     lean = geometric.depth_to_mesh_host(depths, masks if with_masks else None, scene.K, poses, chunk_frames=chunk_frames,
                                         vertex_dtype=np.float32, want_points=False)
